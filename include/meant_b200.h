@@ -1,0 +1,119 @@
+/* meant_b200 -- C ABI of the B200 (sm_100a) kernels behind the MEANT encoder hot path.
+ *
+ * The reference (biirving/meant) is pure PyTorch: it has no FFI for this path.  What a
+ * maintainer would bind is therefore the *operator* boundary -- the bodies of the nn.Module
+ * forwards listed beside each entry point below (file:line relative to the reference tree).
+ * INTEGRATION.md shows the ctypes binding that replaces each reference forward.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into caller-owned memory; nothing is allocated here;
+ *   - `stream` is the CUDA stream to launch on (the caller's current stream);
+ *   - return value: 0 = ok, > 0 = cudaError_t of the failed launch, < 0 = argument error
+ *     (MEANT_EARG -1 bad argument, MEANT_EUNSUPPORTED -2 unsupported dtype/shape);
+ *     no exception crosses the boundary;
+ *   - re-entrant and thread-safe (no global state besides the launch counter and the
+ *     one-time cudaFuncSetAttribute calls);
+ *   - dtype: MEANT_F32 = 0, MEANT_BF16 = 1 -- the storage type of activations; math is fp32
+ *     (tensor-core products bf16 x bf16 -> fp32).  Norm gains/biases and every statistic /
+ *     LSE buffer are always fp32.
+ */
+#ifndef MEANT_B200_H_
+#define MEANT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* meant_stream_t; /* == cudaStream_t */
+
+enum { MEANT_F32 = 0, MEANT_BF16 = 1 };
+enum { MEANT_IMPL_AUTO = 0, MEANT_IMPL_EXACT = 1, MEANT_IMPL_TCGEN05 = 2 };
+
+/* ---- library ------------------------------------------------------------------------- */
+int meant_version(void);                 /* ABI version, bumped on any signature change   */
+int64_t meant_launch_count(void);        /* kernels launched by this library so far       */
+void meant_reset_launch_count(void);
+
+/* ---- RMSNorm: utils/rms_norm.py:40-57  y = gain * x / (||x||_2 d^-1/2 + eps) ----------
+ * Fused neighbours (all optional):
+ *   res/sum_out : s = x + res is normalised and also written to sum_out
+ *                 (meant/meant.py:116,120 residual adds feeding encode2[0] / the next block)
+ *   pre_gelu    : s = gelu(x), exact erf form (meant/meant.py:107 GELU -> RMSNorm)
+ *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107)
+ * rinv[rows] receives 1/(rms+eps) for the backward pass.                                  */
+int meant_rmsnorm_fwd(const void* x, const void* res, const float* gain, void* y, void* sum_out, float* rinv,
+                      int64_t rows, int d, float eps, int pre_gelu, float drop_p, uint64_t seed, int dtype,
+                      meant_stream_t stream);
+/* src = the forward's normalised-input source: x (plain), x (pre_gelu: pre-activation) or
+ * sum_out (residual form).  dsum_in (optional) is added to dx: the gradient that reaches the
+ * same tensor through the residual path.  dgain[d] (fp32) is ACCUMULATED atomically.       */
+int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv, const void* dsum_in,
+                      void* dx, float* dgain, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
+                      uint64_t seed, int dtype, meant_stream_t stream);
+
+/* ---- LayerNorm: nn.LayerNorm heads (meant/meant_tweet.py:143, meant/meant_vision.py:143) and
+ *      TimeSformer PreNorm (src/meant/timesformer_pytorch.py:17-25) ------------------------ */
+int meant_layernorm_fwd(const void* x, const float* gain, const float* bias, void* y, float* mean, float* rstd,
+                        int64_t rows, int d, float eps, int dtype, meant_stream_t stream);
+int meant_layernorm_bwd(const void* dy, const void* x, const float* gain, const float* mean, const float* rstd,
+                        void* dx, float* dgain, float* dbias, int64_t rows, int d, int dtype,
+                        meant_stream_t stream);
+
+/* ---- attention core --------------------------------------------------------------------
+ * Replaces the body of xPosAttention.forward between the projections and multi_mad
+ * (meant/xPosAttention.py:39-65), attention.forward (meant/attention.py:39-59), the flash
+ * variants (meant/xPosAttention_flash.py:40-43, meant/flash_attention.py:40-45: pos_is_head=1),
+ * temporal.forward (meant/temporal.py:43-58: Sq=1) and TimeSformer's grouped attn
+ * (src/meant/timesformer_pytorch.py:78-87,119-139).
+ *
+ * A head view addresses element (n, s, h, d) at  p + n1*sn1 + n2*sn2 + s*ss + h*sh + d  with
+ * n = n1*n2_count + n2 and strides in ELEMENTS, so `b s (h d)` projections, a fused
+ * [tokens, 3*dim] QKV buffer and the TimeSformer '(b n) f d' / '(b f) n d' groups are all
+ * read in place -- no rearranged copy is ever made.                                        */
+typedef struct {
+  void* p;
+  int64_t sn1, sn2, ss, sh;
+} meant_head_view;
+
+typedef struct {
+  meant_head_view q, k, v, o;   /* o: forward output; backward: dO                         */
+  meant_head_view dq, dk, dv;   /* backward outputs                                        */
+  meant_head_view out_saved;    /* backward: the forward output                            */
+  float* lse;                   /* [N, H, Sq] log-sum-exp of the scaled, masked scores     */
+  float* delta;                 /* [N, H, Sq] backward scratch: rowsum(dO * O)             */
+  const float* qcos;            /* [P, rot_dim] cos*xpos_scale; NULL = no rotation         */
+  const float* qsin;            /* [P, rot_dim] sin*xpos_scale                             */
+  const float* kcos;            /* [P, rot_dim] cos/xpos_scale                             */
+  const float* ksin;            /* [P, rot_dim] sin/xpos_scale                             */
+  const float* key_mask;        /* [N, Sk] 1 = keep, adds (1-m)*-1e9; NULL = none          */
+  int N, n2_count, H, Sq, Sk, Dh, rot_dim;
+  int pos_is_head;              /* rotary position = head index (reference flash variants) */
+  int causal;
+  float scale;                  /* softmax scale applied to q k^T                          */
+} meant_attn_args;
+
+int meant_attn_fwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);
+int meant_attn_bwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);
+/* 1 if the tcgen05 kernel takes this problem (bf16, Dh in {64, 96}, ...), else 0            */
+int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int backward);
+
+/* ---- mean over the token axis: meant/meant.py:231, meant/meant_tweet.py:157 ------------- */
+int meant_meanpool_fwd(const void* x, void* y, int64_t N, int S, int D, int dtype, meant_stream_t stream);
+int meant_meanpool_bwd(const void* dy, void* dx, int64_t N, int S, int D, int dtype, meant_stream_t stream);
+
+/* ---- GEGLU: src/meant/timesformer_pytorch.py:59-62   y = x[:, :F] * gelu(x[:, F:]) ------ */
+int meant_geglu_fwd(const void* x, void* y, int64_t rows, int F, int dtype, meant_stream_t stream);
+int meant_geglu_bwd(const void* dy, const void* x, void* dx, int64_t rows, int F, int dtype,
+                    meant_stream_t stream);
+
+/* ---- time token-shift: src/meant/timesformer_pytorch.py:29-55 on x[B, 1+f*n, d];
+ *      transpose != 0 applies the adjoint (backward) ---------------------------------------- */
+int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int transpose, int dtype,
+                      meant_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MEANT_B200_H_ */

@@ -1,0 +1,200 @@
+// Memory-bound helpers around the encoder blocks: mean-pool over the token axis
+// (meant/meant.py:231 `torch.mean(words, dim=2)`), GEGLU (src/meant/timesformer_pytorch.py:59-62)
+// and the TimeSformer time token-shift (:29-55).  128-bit vectorised, coalesced, fp32 math.
+#include "common.cuh"
+
+namespace meant {
+
+// y[n, :] = mean_s x[n, s, :]   — one thread per 16-byte column group, S split over blockIdx.y
+template <typename T>
+__global__ void __launch_bounds__(256) meanpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t N,
+                                                           int S, int D) {
+  constexpr int V = Vec16<T>::N;
+  const int vec_per_row = D / V;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= N * vec_per_row) return;
+  const int64_t n = gid / vec_per_row;
+  const int c = (int)(gid - n * vec_per_row) * V;
+  float acc[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[i] = 0.f;
+  const T* p = x + (n * S) * D + c;
+#pragma unroll 4
+  for (int s = 0; s < S; ++s) {
+    Vec16<T> t;
+    t.load(p + (int64_t)s * D);
+    float f[V];
+    t.unpack(f);
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[i] += f[i];
+  }
+  const float inv = 1.0f / (float)S;
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[i] *= inv;
+  Vec16<T> o;
+  o.pack(acc);
+  o.store(y + n * D + c);
+}
+
+// dx[n, s, :] = dy[n, :] / S
+template <typename T>
+__global__ void __launch_bounds__(256) meanpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int64_t N,
+                                                           int S, int D) {
+  constexpr int V = Vec16<T>::N;
+  const int vec_per_row = D / V;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= N * S * vec_per_row) return;
+  const int64_t row = gid / vec_per_row;  // n * S + s
+  const int c = (int)(gid - row * vec_per_row) * V;
+  const int64_t n = row / S;
+  Vec16<T> t;
+  t.load(dy + n * D + c);
+  float f[V];
+  t.unpack(f);
+  const float inv = 1.0f / (float)S;
+#pragma unroll
+  for (int i = 0; i < V; ++i) f[i] *= inv;
+  t.pack(f);
+  t.store(dx + row * D + c);
+}
+
+// y[t, :F] = x[t, :F] * gelu(x[t, F:2F])
+template <typename T>
+__global__ void __launch_bounds__(256) geglu_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t rows,
+                                                        int F) {
+  constexpr int V = Vec16<T>::N;
+  const int vpr = F / V;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= rows * vpr) return;
+  const int64_t r = gid / vpr;
+  const int c = (int)(gid - r * vpr) * V;
+  Vec16<T> a, g;
+  a.load(x + r * 2 * F + c);
+  g.load(x + r * 2 * F + F + c);
+  float fa[V], fg[V];
+  a.unpack(fa);
+  g.unpack(fg);
+#pragma unroll
+  for (int i = 0; i < V; ++i) fa[i] *= gelu_f(fg[i]);
+  a.pack(fa);
+  a.store(y + r * F + c);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) geglu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                                                        T* __restrict__ dx, int64_t rows, int F) {
+  constexpr int V = Vec16<T>::N;
+  const int vpr = F / V;
+  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= rows * vpr) return;
+  const int64_t r = gid / vpr;
+  const int c = (int)(gid - r * vpr) * V;
+  Vec16<T> a, g, d;
+  a.load(x + r * 2 * F + c);
+  g.load(x + r * 2 * F + F + c);
+  d.load(dy + r * F + c);
+  float fa[V], fg[V], fd[V], da[V], dg[V];
+  a.unpack(fa);
+  g.unpack(fg);
+  d.unpack(fd);
+#pragma unroll
+  for (int i = 0; i < V; ++i) {
+    da[i] = fd[i] * gelu_f(fg[i]);
+    dg[i] = fd[i] * fa[i] * gelu_grad_f(fg[i]);
+  }
+  a.pack(da);
+  g.pack(dg);
+  a.store(dx + r * 2 * F + c);
+  g.store(dx + r * 2 * F + F + c);
+}
+
+// Time token-shift on x[b, 1 + f*n, d]: the cls row is copied; in the body, feature chunk 0
+// ([0, d/3)) takes frame t+1, chunk 2 ([2d/3', 3d/3')) takes frame t-1, zero padded; the rest is
+// copied.  dir = +1 forward op, dir = -1 its transpose (the backward).
+template <typename T>
+__global__ void __launch_bounds__(256) token_shift_kernel(const T* __restrict__ x, T* __restrict__ y, int B, int f,
+                                                          int n, int d, int dir) {
+  const int64_t total = (int64_t)B * (1 + f * n) * d;
+  const int chunk = d / 3;
+  for (int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < total;
+       gid += (int64_t)gridDim.x * blockDim.x) {
+    const int col = (int)(gid % d);
+    const int64_t tok = gid / d;
+    const int t = (int)(tok % (1 + f * n));
+    T v = x[gid];
+    if (t > 0 && col < 3 * chunk) {
+      const int which = col / chunk;  // 0: from t+1, 1: unchanged, 2: from t-1
+      int shift = which == 0 ? 1 : (which == 2 ? -1 : 0);
+      shift *= dir;
+      if (shift != 0) {
+        const int fr = (t - 1) / n + shift;
+        v = (fr >= 0 && fr < f) ? x[gid + (int64_t)shift * n * d] : from_f<T>(0.f);
+      }
+    }
+    y[gid] = v;
+  }
+}
+
+}  // namespace meant
+
+using namespace meant;
+
+#define DISPATCH_T(dtype, CALL)                                   \
+  if (dtype == MEANT_DT_F32) { using T = float; CALL; }           \
+  else if (dtype == MEANT_DT_BF16) { using T = __nv_bfloat16; CALL; } \
+  else return MEANT_EUNSUPPORTED;
+
+static inline unsigned blocks_for(int64_t work, int per) { return (unsigned)((work + per - 1) / per); }
+
+extern "C" int meant_meanpool_fwd(const void* x, void* y, int64_t N, int S, int D, int dtype, cudaStream_t st) {
+  if (!x || !y || N < 0 || S <= 0 || D <= 0) return MEANT_EARG;
+  if (D % (dtype == MEANT_DT_F32 ? 4 : 8)) return MEANT_EUNSUPPORTED;
+  if (N == 0) return 0;
+  DISPATCH_T(dtype, (meanpool_fwd_kernel<T><<<blocks_for(N * (D / Vec16<T>::N), 256), 256, 0, st>>>(
+                        (const T*)x, (T*)y, N, S, D)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_meanpool_bwd(const void* dy, void* dx, int64_t N, int S, int D, int dtype, cudaStream_t st) {
+  if (!dy || !dx || N < 0 || S <= 0 || D <= 0) return MEANT_EARG;
+  if (D % (dtype == MEANT_DT_F32 ? 4 : 8)) return MEANT_EUNSUPPORTED;
+  if (N == 0) return 0;
+  DISPATCH_T(dtype, (meanpool_bwd_kernel<T><<<blocks_for(N * S * (D / Vec16<T>::N), 256), 256, 0, st>>>(
+                        (const T*)dy, (T*)dx, N, S, D)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_geglu_fwd(const void* x, void* y, int64_t rows, int F, int dtype, cudaStream_t st) {
+  if (!x || !y || rows < 0 || F <= 0) return MEANT_EARG;
+  if (F % (dtype == MEANT_DT_F32 ? 4 : 8)) return MEANT_EUNSUPPORTED;
+  if (rows == 0) return 0;
+  DISPATCH_T(dtype, (geglu_fwd_kernel<T><<<blocks_for(rows * (F / Vec16<T>::N), 256), 256, 0, st>>>(
+                        (const T*)x, (T*)y, rows, F)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_geglu_bwd(const void* dy, const void* x, void* dx, int64_t rows, int F, int dtype,
+                               cudaStream_t st) {
+  if (!dy || !x || !dx || rows < 0 || F <= 0) return MEANT_EARG;
+  if (F % (dtype == MEANT_DT_F32 ? 4 : 8)) return MEANT_EUNSUPPORTED;
+  if (rows == 0) return 0;
+  DISPATCH_T(dtype, (geglu_bwd_kernel<T><<<blocks_for(rows * (F / Vec16<T>::N), 256), 256, 0, st>>>(
+                        (const T*)dy, (const T*)x, (T*)dx, rows, F)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int transpose, int dtype,
+                                 cudaStream_t st) {
+  if (!x || !y || B <= 0 || f <= 0 || n <= 0 || d <= 0 || x == y) return MEANT_EARG;
+  const int64_t total = (int64_t)B * (1 + f * n) * d;
+  unsigned blocks = blocks_for(total, 256);
+  if (blocks > 148u * 16u) blocks = 148u * 16u;
+  DISPATCH_T(dtype, (token_shift_kernel<T><<<blocks, 256, 0, st>>>((const T*)x, (T*)y, B, f, n, d,
+                                                                    transpose ? -1 : 1)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}

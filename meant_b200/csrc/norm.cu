@@ -1,0 +1,398 @@
+// RMSNorm (reference semantics: utils/rms_norm.py:40-57, eps added to the RMS) and LayerNorm,
+// forward + backward, with the memory-bound neighbours of the MEANT encoder block fused in:
+//   * residual add before the norm          (meant/meant.py:116 `inter + input` -> encode2[0])
+//   * exact GELU before the norm            (meant/meant.py:107 GELU -> RMSNorm)
+//   * dropout after the norm                (meant/meant.py:105,107 Dropout(p), Dropout(0.5))
+// One warp per row, 128-bit coalesced loads, the row kept in registers (single HBM read),
+// warp-shuffle reductions, fp32 math.  HBM-bound: algorithmic bytes are listed in DESIGN.md.
+#include "common.cuh"
+
+namespace meant {
+
+struct NormArgs {
+  const void* x;      // [rows, d] input (pre-GELU input when pre_gelu)
+  const void* res;    // optional residual, added before the norm
+  const float* gain;  // [d] fp32
+  const float* bias;  // [d] fp32 (LayerNorm only)
+  void* y;            // [rows, d]
+  void* sum_out;      // optional: x + res (kept for the next residual / backward)
+  float* stat0;       // rms: 1/(rms+eps)   ln: mean
+  float* stat1;       // ln: rstd
+  int64_t rows;
+  int d;
+  float eps;
+  int pre_gelu;
+  uint32_t drop_thresh;  // 0 = no dropout
+  float drop_inv_keep;
+  uint64_t seed;
+};
+
+// ------------------------------------------------------------------ forward, row in registers
+template <typename T, int CHUNKS, bool LN>
+__global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
+  constexpr int V = Vec16<T>::N;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* __restrict__ x = static_cast<const T*>(a.x);
+  const T* __restrict__ res = static_cast<const T*>(a.res);
+  T* __restrict__ y = static_cast<T*>(a.y);
+  T* __restrict__ so = static_cast<T*>(a.sum_out);
+  float g[CHUNKS][V], bb[CHUNKS][V];
+#pragma unroll
+  for (int c = 0; c < CHUNKS; ++c) {
+    const int col = (lane + 32 * c) * V;
+#pragma unroll
+    for (int i = 0; i < V; ++i) {
+      g[c][i] = a.gain[col + i];
+      bb[c][i] = LN ? a.bias[col + i] : 0.f;
+    }
+  }
+  const float inv_d = 1.0f / (float)a.d;
+  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
+    const int64_t base = row * a.d;
+    float v[CHUNKS][V];
+    Vec16<T> t[CHUNKS], r[CHUNKS];
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) t[c].load(x + base + (lane + 32 * c) * V);
+    if (res) {
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c) r[c].load(res + base + (lane + 32 * c) * V);
+    }
+    float ss = 0.f, sm = 0.f;
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      t[c].unpack(v[c]);
+      if (a.pre_gelu) {
+#pragma unroll
+        for (int i = 0; i < V; ++i) v[c][i] = gelu_f(v[c][i]);
+      }
+      if (res) {
+        float rv[V];
+        r[c].unpack(rv);
+#pragma unroll
+        for (int i = 0; i < V; ++i) v[c][i] += rv[i];
+        if (so) {
+          // the sum is rounded to T once; the norm then uses the rounded value so that
+          // backward (which re-reads sum_out) sees exactly the forward's input
+          Vec16<T> o;
+          o.pack(v[c]);
+          o.store(so + base + (lane + 32 * c) * V);
+          o.unpack(v[c]);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < V; ++i) { ss += v[c][i] * v[c][i]; sm += v[c][i]; }
+    }
+    float mean = 0.f, rinv;
+    if (LN) {
+      mean = warp_sum(sm) * inv_d;
+      float var = 0.f;
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c)
+#pragma unroll
+        for (int i = 0; i < V; ++i) { const float dl = v[c][i] - mean; var += dl * dl; }
+      rinv = rsqrtf(warp_sum(var) * inv_d + a.eps);
+      if (lane == 0) { a.stat0[row] = mean; a.stat1[row] = rinv; }
+    } else {
+      ss = warp_sum(ss);
+      rinv = 1.0f / (sqrtf(ss) * sqrtf(inv_d) + a.eps);   // ||x|| * d^-1/2 + eps
+      if (lane == 0) a.stat0[row] = rinv;
+    }
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      float o[V];
+      const int col = (lane + 32 * c) * V;
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv);
+        if (a.drop_thresh) o[i] *= drop_keep(a.seed, (uint64_t)(base + col + i), a.drop_thresh, a.drop_inv_keep);
+      }
+      Vec16<T> ov;
+      ov.pack(o);
+      ov.store(y + base + col);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ forward, any d (two passes)
+template <typename T, bool LN>
+__global__ void __launch_bounds__(128) norm_fwd_generic_kernel(NormArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* __restrict__ x = static_cast<const T*>(a.x);
+  const T* __restrict__ res = static_cast<const T*>(a.res);
+  T* __restrict__ y = static_cast<T*>(a.y);
+  T* __restrict__ so = static_cast<T*>(a.sum_out);
+  const float inv_d = 1.0f / (float)a.d;
+  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
+    const int64_t base = row * a.d;
+    auto val = [&](int c) -> float {
+      float v = to_f(x[base + c]);
+      if (a.pre_gelu) v = gelu_f(v);
+      if (res) { v += to_f(res[base + c]); if (so) v = to_f(from_f<T>(v)); }
+      return v;
+    };
+    float ss = 0.f, sm = 0.f;
+    for (int c = lane; c < a.d; c += 32) { const float v = val(c); ss += v * v; sm += v; }
+    float mean = 0.f, rinv;
+    if (LN) {
+      mean = warp_sum(sm) * inv_d;
+      float var = 0.f;
+      for (int c = lane; c < a.d; c += 32) { const float dl = val(c) - mean; var += dl * dl; }
+      rinv = rsqrtf(warp_sum(var) * inv_d + a.eps);
+      if (lane == 0) { a.stat0[row] = mean; a.stat1[row] = rinv; }
+    } else {
+      rinv = 1.0f / (sqrtf(warp_sum(ss)) * sqrtf(inv_d) + a.eps);
+      if (lane == 0) a.stat0[row] = rinv;
+    }
+    for (int c = lane; c < a.d; c += 32) {
+      const float v = val(c);
+      if (res && so) so[base + c] = from_f<T>(v);
+      float o = LN ? (v - mean) * rinv * a.gain[c] + a.bias[c] : a.gain[c] * (v * rinv);
+      if (a.drop_thresh) o *= drop_keep(a.seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
+      y[base + c] = from_f<T>(o);
+    }
+  }
+}
+
+struct NormBwdArgs {
+  const void* dy;       // [rows, d]
+  const void* src;      // forward input of the norm: x, or pre-GELU u, or sum_out
+  const float* gain;
+  const float* stat0;
+  const float* stat1;
+  const void* dsum_in;  // optional gradient arriving at the same tensor from the residual path
+  void* dx;             // [rows, d]
+  float* dgain;         // [d] fp32, atomically accumulated (caller zeroes)
+  float* dbias;         // [d] fp32 (LayerNorm)
+  int64_t rows;
+  int d;
+  float eps;
+  int pre_gelu;
+  uint32_t drop_thresh;
+  float drop_inv_keep;
+  uint64_t seed;
+};
+
+// ------------------------------------------------------------------ backward, row in registers
+template <typename T, int CHUNKS, bool LN>
+__global__ void __launch_bounds__(128) norm_bwd_kernel(NormBwdArgs a) {
+  constexpr int V = Vec16<T>::N;
+  __shared__ float red[4][32 * CHUNKS * V + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* __restrict__ dy = static_cast<const T*>(a.dy);
+  const T* __restrict__ src = static_cast<const T*>(a.src);
+  const T* __restrict__ dsi = static_cast<const T*>(a.dsum_in);
+  T* __restrict__ dx = static_cast<T*>(a.dx);
+  float g[CHUNKS][V], dg[CHUNKS][V], db[CHUNKS][V];
+#pragma unroll
+  for (int c = 0; c < CHUNKS; ++c)
+#pragma unroll
+    for (int i = 0; i < V; ++i) { g[c][i] = a.gain[(lane + 32 * c) * V + i]; dg[c][i] = 0.f; db[c][i] = 0.f; }
+  const float inv_d = 1.0f / (float)a.d;
+  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
+    const int64_t base = row * a.d;
+    Vec16<T> tu[CHUNKS], tg[CHUNKS], ts[CHUNKS];
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      tu[c].load(src + base + (lane + 32 * c) * V);
+      tg[c].load(dy + base + (lane + 32 * c) * V);
+    }
+    if (dsi) {
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c) ts[c].load(dsi + base + (lane + 32 * c) * V);
+    }
+    float u[CHUNKS][V], s[CHUNKS][V], gy[CHUNKS][V];
+    const float mean = LN ? a.stat0[row] : 0.f;
+    const float rinv = LN ? a.stat1[row] : a.stat0[row];
+    float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      tu[c].unpack(u[c]);
+      tg[c].unpack(gy[c]);
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const int col = (lane + 32 * c) * V + i;
+        if (a.drop_thresh) gy[c][i] *= drop_keep(a.seed, (uint64_t)(base + col), a.drop_thresh, a.drop_inv_keep);
+        s[c][i] = a.pre_gelu ? gelu_f(u[c][i]) : u[c][i];
+        if (LN) s[c][i] = (s[c][i] - mean) * rinv;  // xhat
+        const float gd = g[c][i] * gy[c][i];
+        t1 += gd * s[c][i];
+        t2 += gd;
+        dg[c][i] += gy[c][i] * s[c][i] * (LN ? 1.f : rinv);
+        db[c][i] += gy[c][i];
+      }
+    }
+    t1 = warp_sum(t1);
+    float coef, m2 = 0.f;
+    if (LN) {
+      m2 = warp_sum(t2) * inv_d;
+      coef = t1 * inv_d;
+    } else {
+      const float rms = 1.0f / rinv - a.eps;
+      coef = rms > 0.f ? t1 * rinv * rinv * inv_d / rms : 0.f;
+    }
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) {
+      float o[V], sv[V];
+      if (dsi) ts[c].unpack(sv);
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const float gd = g[c][i] * gy[c][i];
+        float ds = LN ? rinv * (gd - m2 - s[c][i] * coef) : gd * rinv - s[c][i] * coef;
+        if (a.pre_gelu) ds *= gelu_grad_f(u[c][i]);
+        if (dsi) ds += sv[i];
+        o[i] = ds;
+      }
+      Vec16<T> ov;
+      ov.pack(o);
+      ov.store(dx + base + (lane + 32 * c) * V);
+    }
+  }
+  // block-level reduction of the per-warp column sums, then one atomic per column per block
+#pragma unroll 1
+  for (int pass = 0; pass < (LN ? 2 : 1); ++pass) {
+    __syncthreads();
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c)
+#pragma unroll
+      for (int i = 0; i < V; ++i) red[warp][(lane + 32 * c) * V + i] = pass ? db[c][i] : dg[c][i];
+    __syncthreads();
+    float* dst = pass ? a.dbias : a.dgain;
+    for (int col = threadIdx.x; col < a.d; col += 128)
+      atomicAdd(dst + col, red[0][col] + red[1][col] + red[2][col] + red[3][col]);
+  }
+}
+
+// ------------------------------------------------------------------ backward, any d
+template <typename T, bool LN>
+__global__ void __launch_bounds__(128) norm_bwd_generic_kernel(NormBwdArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const T* __restrict__ dy = static_cast<const T*>(a.dy);
+  const T* __restrict__ src = static_cast<const T*>(a.src);
+  const T* __restrict__ dsi = static_cast<const T*>(a.dsum_in);
+  T* __restrict__ dx = static_cast<T*>(a.dx);
+  const float inv_d = 1.0f / (float)a.d;
+  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
+    const int64_t base = row * a.d;
+    const float mean = LN ? a.stat0[row] : 0.f;
+    const float rinv = LN ? a.stat1[row] : a.stat0[row];
+    auto sval = [&](int c) -> float {
+      float v = to_f(src[base + c]);
+      if (a.pre_gelu) v = gelu_f(v);
+      return LN ? (v - mean) * rinv : v;
+    };
+    auto gval = [&](int c) -> float {
+      float v = to_f(dy[base + c]);
+      if (a.drop_thresh) v *= drop_keep(a.seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
+      return v;
+    };
+    float t1 = 0.f, t2 = 0.f;
+    for (int c = lane; c < a.d; c += 32) {
+      const float gd = a.gain[c] * gval(c);
+      t1 += gd * sval(c);
+      t2 += gd;
+    }
+    t1 = warp_sum(t1);
+    float coef, m2 = 0.f;
+    if (LN) { m2 = warp_sum(t2) * inv_d; coef = t1 * inv_d; }
+    else { const float rms = 1.0f / rinv - a.eps; coef = rms > 0.f ? t1 * rinv * rinv * inv_d / rms : 0.f; }
+    for (int c = lane; c < a.d; c += 32) {
+      const float s = sval(c), gy = gval(c), gd = a.gain[c] * gy;
+      float ds = LN ? rinv * (gd - m2 - s * coef) : gd * rinv - s * coef;
+      if (a.pre_gelu) ds *= gelu_grad_f(to_f(src[base + c]));
+      if (dsi) ds += to_f(dsi[base + c]);
+      dx[base + c] = from_f<T>(ds);
+      atomicAdd(a.dgain + c, gy * s * (LN ? 1.f : rinv));
+      if (LN) atomicAdd(a.dbias + c, gy);
+    }
+  }
+}
+
+static int grid_for(int64_t rows) {
+  int64_t blocks = (rows + 3) / 4;
+  const int64_t cap = 148 * 8;  // persistent-ish: <= 8 resident 128-thread CTAs per SM
+  return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
+}
+
+template <typename T, bool LN>
+static int launch_fwd(const NormArgs& a, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  const int g = grid_for(a.rows);
+  const bool vec_ok = (a.d % (32 * V) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(a.x) | reinterpret_cast<uintptr_t>(a.y) |
+                        reinterpret_cast<uintptr_t>(a.res) | reinterpret_cast<uintptr_t>(a.sum_out)) % 16 == 0);
+  const int chunks = vec_ok ? a.d / (32 * V) : 0;
+  switch (chunks) {
+    case 3: norm_fwd_kernel<T, 3, LN><<<g, 128, 0, st>>>(a); break;
+    case 6: norm_fwd_kernel<T, 6, LN><<<g, 128, 0, st>>>(a); break;
+    case 12: norm_fwd_kernel<T, 12, LN><<<g, 128, 0, st>>>(a); break;
+    default: norm_fwd_generic_kernel<T, LN><<<g, 128, 0, st>>>(a); break;
+  }
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+template <typename T, bool LN>
+static int launch_bwd(const NormBwdArgs& a, cudaStream_t st) {
+  constexpr int V = Vec16<T>::N;
+  int g = grid_for(a.rows);
+  if (g > 148 * 4) g = 148 * 4;  // fewer CTAs -> fewer dgain atomics
+  const bool vec_ok = (a.d % (32 * V) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(a.dy) | reinterpret_cast<uintptr_t>(a.src) |
+                        reinterpret_cast<uintptr_t>(a.dx) | reinterpret_cast<uintptr_t>(a.dsum_in)) % 16 == 0);
+  const int chunks = vec_ok ? a.d / (32 * V) : 0;
+  // CHUNKS * V <= 24 values per lane keeps the six per-lane arrays in registers
+  if (chunks == 3) norm_bwd_kernel<T, 3, LN><<<g, 128, 0, st>>>(a);
+  else if (chunks == 6 && V == 4) norm_bwd_kernel<T, (V == 4 ? 6 : 3), LN><<<g, 128, 0, st>>>(a);
+  else norm_bwd_generic_kernel<T, LN><<<g, 128, 0, st>>>(a);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace meant
+
+using namespace meant;
+
+extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* gain, void* y, void* sum_out,
+                                 float* rinv, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
+                                 uint64_t seed, int dtype, cudaStream_t stream) {
+  if (!x || !gain || !y || !rinv || rows < 0 || d <= 0 || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
+  if (rows == 0) return 0;
+  NormArgs a{x, res, gain, nullptr, y, sum_out, rinv, nullptr, rows, d, eps, pre_gelu,
+             drop_p > 0.f ? (uint32_t)(drop_p * 4294967296.0) : 0u, 1.0f / (1.0f - drop_p), seed};
+  if (dtype == MEANT_DT_F32) return launch_fwd<float, false>(a, stream);
+  if (dtype == MEANT_DT_BF16) return launch_fwd<__nv_bfloat16, false>(a, stream);
+  return MEANT_EUNSUPPORTED;
+}
+
+extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv,
+                                 const void* dsum_in, void* dx, float* dgain, int64_t rows, int d, float eps,
+                                 int pre_gelu, float drop_p, uint64_t seed, int dtype, cudaStream_t stream) {
+  if (!dy || !src || !gain || !rinv || !dx || !dgain || rows < 0 || d <= 0) return MEANT_EARG;
+  if (rows == 0) return 0;
+  NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, nullptr, rows, d, eps, pre_gelu,
+                drop_p > 0.f ? (uint32_t)(drop_p * 4294967296.0) : 0u, 1.0f / (1.0f - drop_p), seed};
+  if (dtype == MEANT_DT_F32) return launch_bwd<float, false>(a, stream);
+  if (dtype == MEANT_DT_BF16) return launch_bwd<__nv_bfloat16, false>(a, stream);
+  return MEANT_EUNSUPPORTED;
+}
+
+extern "C" int meant_layernorm_fwd(const void* x, const float* gain, const float* bias, void* y, float* mean,
+                                   float* rstd, int64_t rows, int d, float eps, int dtype, cudaStream_t stream) {
+  if (!x || !gain || !bias || !y || !mean || !rstd || rows < 0 || d <= 0) return MEANT_EARG;
+  if (rows == 0) return 0;
+  NormArgs a{x, nullptr, gain, bias, y, nullptr, mean, rstd, rows, d, eps, 0, 0u, 1.0f, 0};
+  if (dtype == MEANT_DT_F32) return launch_fwd<float, true>(a, stream);
+  if (dtype == MEANT_DT_BF16) return launch_fwd<__nv_bfloat16, true>(a, stream);
+  return MEANT_EUNSUPPORTED;
+}
+
+extern "C" int meant_layernorm_bwd(const void* dy, const void* x, const float* gain, const float* mean,
+                                   const float* rstd, void* dx, float* dgain, float* dbias, int64_t rows, int d,
+                                   int dtype, cudaStream_t stream) {
+  if (!dy || !x || !gain || !mean || !rstd || !dx || !dgain || !dbias || rows < 0 || d <= 0) return MEANT_EARG;
+  if (rows == 0) return 0;
+  NormBwdArgs a{dy, x, gain, mean, rstd, nullptr, dx, dgain, dbias, rows, d, 0.f, 0, 0u, 1.0f, 0};
+  if (dtype == MEANT_DT_F32) return launch_bwd<float, true>(a, stream);
+  if (dtype == MEANT_DT_BF16) return launch_bwd<__nv_bfloat16, true>(a, stream);
+  return MEANT_EUNSUPPORTED;
+}

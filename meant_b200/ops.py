@@ -1,0 +1,331 @@
+"""torch.autograd wrappers over the C ABI (include/meant_b200.h).
+
+torch is the plumbing here (device memory, streams, autograd graph); every op below runs a
+hand-written sm_100a kernel from libmeant_b200.so and raises if that is impossible.
+"""
+import math
+
+import torch
+
+from . import _native as nv
+from ._native import AttnArgs, HeadView
+
+
+def compute_dtype(x: torch.Tensor) -> torch.dtype:
+    """bf16 under torch.autocast('cuda', dtype=torch.bfloat16), else the tensor's dtype."""
+    if torch.is_autocast_enabled("cuda"):
+        dt = torch.get_autocast_dtype("cuda")
+        if dt != torch.bfloat16:
+            raise RuntimeError(
+                f"meant_b200 computes in bfloat16 or float32; autocast dtype {dt} is not supported "
+                "(the reference's fp16 autocast + GradScaler maps to torch.autocast('cuda', torch.bfloat16))")
+        return dt
+    if x.dtype not in (torch.float32, torch.bfloat16):
+        raise RuntimeError(f"meant_b200 computes in bfloat16 or float32, got {x.dtype}")
+    return x.dtype
+
+
+def _prep(x, dtype):
+    nv.require_cuda(x)
+    return x.to(dtype).contiguous()
+
+
+def _prep_rows(x, dtype):
+    """Like _prep but keeps strided [N, S, W] views whose rows are dense (sliced projections)."""
+    if x is None:
+        return None
+    nv.require_cuda(x)
+    x = x.to(dtype)
+    return x if x.dim() == 3 and x.stride(-1) == 1 and x.data_ptr() % 16 == 0 else x.contiguous()
+
+
+def _f32(t):
+    return t.detach().float().contiguous()
+
+
+# ------------------------------------------------------------------------------ RMSNorm
+class _RMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, res, gain, eps, pre_gelu, drop_p, seed):
+        dtype = compute_dtype(x)
+        x2 = _prep(x, dtype)
+        d = x2.shape[-1]
+        rows = x2.numel() // d
+        r2 = _prep(res, dtype) if res is not None else None
+        g32 = _f32(gain)
+        y = torch.empty_like(x2)
+        s = torch.empty_like(x2) if r2 is not None else None
+        rinv = torch.empty(rows, dtype=torch.float32, device=x2.device)
+        nv.check(nv.lib().meant_rmsnorm_fwd(nv.ptr(x2), nv.ptr(r2), nv.ptr(g32), nv.ptr(y), nv.ptr(s),
+                                            nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed,
+                                            nv.dt(x2), nv.stream()), "meant_rmsnorm_fwd")
+        ctx.save_for_backward(s if r2 is not None else x2, g32, rinv)
+        ctx.cfg = (eps, int(pre_gelu), drop_p, seed, res is not None, gain.dtype, x.dtype,
+                   res.dtype if res is not None else None)
+        if r2 is None:
+            return y
+        return y, s
+
+    @staticmethod
+    def backward(ctx, dy, dsum=None):
+        src, g32, rinv = ctx.saved_tensors
+        eps, pre_gelu, drop_p, seed, has_res, gdt, xdt, rdt = ctx.cfg
+        d = src.shape[-1]
+        rows = src.numel() // d
+        dy = torch.zeros_like(src) if dy is None else dy.to(src.dtype).contiguous()
+        ds = dsum.to(src.dtype).contiguous() if dsum is not None else None
+        dx = torch.empty_like(src)
+        dgain = torch.zeros(d, dtype=torch.float32, device=src.device)
+        nv.check(nv.lib().meant_rmsnorm_bwd(nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv), nv.ptr(ds),
+                                            nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
+                                            nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+        return dx.to(xdt), (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
+
+
+def _seed():
+    # drawn from torch's CPU generator so torch.manual_seed() makes dropout reproducible
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+
+def rms_norm(x, gain, eps=1e-8, residual=None, pre_gelu=False, drop_p=0.0):
+    """y = gain * s / (rms(s) + eps), s = gelu?(x) (+ residual); returns y, or (y, s) when a
+    residual is given.  drop_p > 0 applies inverted dropout to y (training only: the caller
+    passes 0 in eval mode)."""
+    seed = _seed() if drop_p > 0.0 else 0
+    return _RMSNormFn.apply(x, residual, gain, float(eps), bool(pre_gelu), float(drop_p), seed)
+
+
+# ---------------------------------------------------------------------------- LayerNorm
+class _LayerNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        dtype = compute_dtype(x)
+        x2 = _prep(x, dtype)
+        d = x2.shape[-1]
+        rows = x2.numel() // d
+        w32, b32 = _f32(weight), _f32(bias)
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x2.device)
+        rstd = torch.empty_like(mean)
+        nv.check(nv.lib().meant_layernorm_fwd(nv.ptr(x2), nv.ptr(w32), nv.ptr(b32), nv.ptr(y), nv.ptr(mean),
+                                              nv.ptr(rstd), rows, d, eps, nv.dt(x2), nv.stream()),
+                 "meant_layernorm_fwd")
+        ctx.save_for_backward(x2, w32, mean, rstd)
+        ctx.cfg = (weight.dtype, x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w32, mean, rstd = ctx.saved_tensors
+        wdt, xdt = ctx.cfg
+        d = x2.shape[-1]
+        rows = x2.numel() // d
+        dy = dy.to(x2.dtype).contiguous()
+        dx = torch.empty_like(x2)
+        dw = torch.zeros(d, dtype=torch.float32, device=x2.device)
+        db = torch.zeros_like(dw)
+        nv.check(nv.lib().meant_layernorm_bwd(nv.ptr(dy), nv.ptr(x2), nv.ptr(w32), nv.ptr(mean), nv.ptr(rstd),
+                                              nv.ptr(dx), nv.ptr(dw), nv.ptr(db), rows, d, nv.dt(x2),
+                                              nv.stream()), "meant_layernorm_bwd")
+        return dx.to(xdt), dw.to(wdt), db.to(wdt), None
+
+
+def layer_norm(x, weight, bias, eps=1e-5):
+    return _LayerNormFn.apply(x, weight, bias, float(eps))
+
+
+# ---------------------------------------------------------------------------- attention
+def _view(t, col0, heads, dh, n2_count=1, group=None):
+    """HeadView of columns [col0, col0 + heads*dh) of a [N, S, W] tensor (last stride 1)."""
+    assert t.stride(-1) == 1
+    es = t.element_size()
+    if group is None:
+        return HeadView(t.data_ptr() + col0 * es, t.stride(0), 0, t.stride(1), dh)
+    sn1, sn2, ss = group
+    return HeadView(t.data_ptr() + col0 * es, sn1, sn2, ss, dh)
+
+
+class _AttnFn(torch.autograd.Function):
+    """mode 'qkv'  : t0 = [N, S, 3*dim] packed (q | k | v), t1 = t2 = None
+       mode 'q_kv' : t0 = [N, Sq, dim], t1 = [N, Sk, 2*dim] packed (k | v)
+       mode 'q_k_v': three [N, S*, dim] tensors."""
+
+    @staticmethod
+    def forward(ctx, t0, t1, t2, mode, heads, scale, causal, rot, pos_is_head, key_mask, impl):
+        dtype = compute_dtype(t0)
+        t0, t1, t2 = (_prep_rows(t, dtype) for t in (t0, t1, t2))
+        if mode == "qkv":
+            dim = t0.shape[-1] // 3
+            srcs = ((t0, 0), (t0, dim), (t0, 2 * dim))
+        elif mode == "q_kv":
+            dim = t0.shape[-1]
+            srcs = ((t0, 0), (t1, 0), (t1, dim))
+        else:
+            dim = t0.shape[-1]
+            srcs = ((t0, 0), (t1, 0), (t2, 0))
+        if dim % heads:
+            raise ValueError(f"dim {dim} is not divisible by heads {heads}")
+        dh = dim // heads
+        n, sq = t0.shape[0], t0.shape[1]
+        sk = srcs[1][0].shape[1]
+        out = torch.empty(n, sq, dim, dtype=dtype, device=t0.device)
+        lse = torch.empty(n, heads, sq, dtype=torch.float32, device=t0.device)
+        a = AttnArgs()
+        a.q, a.k, a.v = (_view(t, c, heads, dh) for t, c in srcs)
+        a.o = _view(out, 0, heads, dh)
+        a.lse = nv.ptr(lse)
+        tabs = None
+        if rot is not None:
+            tabs = tuple(r.contiguous() for r in rot)
+            a.qcos, a.qsin, a.kcos, a.ksin = (nv.ptr(r) for r in tabs)
+            a.rot_dim = tabs[0].shape[-1]
+            need = heads if pos_is_head else max(sq, sk)
+            if tabs[0].shape[0] < need or a.rot_dim > dh:
+                raise ValueError("rotary tables do not cover the positions / head size")
+        km = None
+        if key_mask is not None:
+            km = key_mask.to(device=t0.device, dtype=torch.float32).contiguous()
+            if km.shape != (n, sk):
+                raise ValueError(f"attention_mask must be [{n}, {sk}], got {tuple(km.shape)}")
+            a.key_mask = nv.ptr(km)
+        a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
+        a.pos_is_head, a.causal, a.scale = int(pos_is_head), int(causal), float(scale)
+        nv.check(nv.lib().meant_attn_fwd(a, nv.dt(t0), impl, nv.stream()), "meant_attn_fwd")
+        ctx.save_for_backward(t0, t1, t2, out, lse, km, *(tabs or ()))
+        ctx.cfg = (mode, heads, float(scale), int(causal), int(pos_is_head), impl, rot is not None)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        t0, t1, t2, out, lse, km, *tabs = ctx.saved_tensors
+        mode, heads, scale, causal, pos_is_head, impl, has_rot = ctx.cfg
+        dout = dout.to(out.dtype).contiguous()
+        g0 = torch.empty_like(t0)
+        g1 = torch.empty_like(t1) if t1 is not None else None
+        g2 = torch.empty_like(t2) if t2 is not None else None
+        if mode == "qkv":
+            dim = t0.shape[-1] // 3
+            srcs = ((t0, 0), (t0, dim), (t0, 2 * dim))
+            dsts = ((g0, 0), (g0, dim), (g0, 2 * dim))
+        elif mode == "q_kv":
+            dim = t0.shape[-1]
+            srcs = ((t0, 0), (t1, 0), (t1, dim))
+            dsts = ((g0, 0), (g1, 0), (g1, dim))
+        else:
+            dim = t0.shape[-1]
+            srcs = ((t0, 0), (t1, 0), (t2, 0))
+            dsts = ((g0, 0), (g1, 0), (g2, 0))
+        dh = dim // heads
+        n, sq, sk = t0.shape[0], t0.shape[1], srcs[1][0].shape[1]
+        delta = torch.empty_like(lse)
+        a = AttnArgs()
+        a.q, a.k, a.v = (_view(t, c, heads, dh) for t, c in srcs)
+        a.dq, a.dk, a.dv = (_view(t, c, heads, dh) for t, c in dsts)
+        a.o = _view(dout, 0, heads, dh)
+        a.out_saved = _view(out, 0, heads, dh)
+        a.lse, a.delta = nv.ptr(lse), nv.ptr(delta)
+        if has_rot:
+            a.qcos, a.qsin, a.kcos, a.ksin = (nv.ptr(r) for r in tabs)
+            a.rot_dim = tabs[0].shape[-1]
+        if km is not None:
+            a.key_mask = nv.ptr(km)
+        a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
+        a.pos_is_head, a.causal, a.scale = pos_is_head, causal, scale
+        nv.check(nv.lib().meant_attn_bwd(a, nv.dt(t0), impl, nv.stream()), "meant_attn_bwd")
+        return g0, g1, g2, None, None, None, None, None, None, None, None
+
+
+def attention(qkv=None, q=None, kv=None, k=None, v=None, *, heads, scale, causal=False, rot=None,
+              pos_is_head=False, key_mask=None, impl=nv.IMPL_AUTO):
+    """softmax((Rq q)(Rk k)^T * scale + masks) v on packed `b s (h d)` projections.
+    Returns [N, Sq, dim] in `b s (h d)` layout (no rearrange is materialised)."""
+    if qkv is not None:
+        return _AttnFn.apply(qkv, None, None, "qkv", heads, scale, causal, rot, pos_is_head, key_mask, impl)
+    if kv is not None:
+        return _AttnFn.apply(q, kv, None, "q_kv", heads, scale, causal, rot, pos_is_head, key_mask, impl)
+    return _AttnFn.apply(q, k, v, "q_k_v", heads, scale, causal, rot, pos_is_head, key_mask, impl)
+
+
+# ------------------------------------------------------------------- pooling, GEGLU, shift
+class _MeanPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        dtype = compute_dtype(x)
+        x2 = _prep(x, dtype)
+        n, s, d = x2.shape
+        y = torch.empty(n, d, dtype=dtype, device=x2.device)
+        nv.check(nv.lib().meant_meanpool_fwd(nv.ptr(x2), nv.ptr(y), n, s, d, nv.dt(x2), nv.stream()),
+                 "meant_meanpool_fwd")
+        ctx.cfg = (n, s, d, x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        n, s, d, xdt = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty(n, s, d, dtype=dy.dtype, device=dy.device)
+        nv.check(nv.lib().meant_meanpool_bwd(nv.ptr(dy), nv.ptr(dx), n, s, d, nv.dt(dy), nv.stream()),
+                 "meant_meanpool_bwd")
+        return dx.to(xdt)
+
+
+def mean_pool(x):
+    """mean over axis 1 of [N, S, D] (meant/meant.py:231)."""
+    return _MeanPoolFn.apply(x)
+
+
+class _GegluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        dtype = compute_dtype(x)
+        x2 = _prep(x, dtype)
+        f = x2.shape[-1] // 2
+        rows = x2.numel() // (2 * f)
+        y = torch.empty(*x2.shape[:-1], f, dtype=dtype, device=x2.device)
+        nv.check(nv.lib().meant_geglu_fwd(nv.ptr(x2), nv.ptr(y), rows, f, nv.dt(x2), nv.stream()),
+                 "meant_geglu_fwd")
+        ctx.save_for_backward(x2)
+        ctx.xdt = x.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x2,) = ctx.saved_tensors
+        f = x2.shape[-1] // 2
+        rows = x2.numel() // (2 * f)
+        dy = dy.to(x2.dtype).contiguous()
+        dx = torch.empty_like(x2)
+        nv.check(nv.lib().meant_geglu_bwd(nv.ptr(dy), nv.ptr(x2), nv.ptr(dx), rows, f, nv.dt(x2), nv.stream()),
+                 "meant_geglu_bwd")
+        return dx.to(ctx.xdt)
+
+
+def geglu(x):
+    return _GegluFn.apply(x)
+
+
+class _TokenShiftFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, frames):
+        dtype = compute_dtype(x)
+        x2 = _prep(x, dtype)
+        b, ntok, d = x2.shape
+        n = (ntok - 1) // frames
+        y = torch.empty_like(x2)
+        nv.check(nv.lib().meant_token_shift(nv.ptr(x2), nv.ptr(y), b, frames, n, d, 0, nv.dt(x2), nv.stream()),
+                 "meant_token_shift")
+        ctx.cfg = (b, frames, n, d, x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        b, frames, n, d, xdt = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty_like(dy)
+        nv.check(nv.lib().meant_token_shift(nv.ptr(dy), nv.ptr(dx), b, frames, n, d, 1, nv.dt(dy), nv.stream()),
+                 "meant_token_shift")
+        return dx.to(xdt), None
+
+
+def token_shift(x, frames):
+    return _TokenShiftFn.apply(x, frames)
