@@ -1,0 +1,100 @@
+"""Data-parallel gradient exchange for the MEANT training step: one process per GPU, flat
+gradient buckets all-reduced (NCCL over NVLink 5 / NVSwitch) as soon as backward has produced
+them, overlapping the rest of backward.  The reference has no distributed code at all
+(only nn.DataParallel in pretrain_mlm.py:330); this is the B200-native replacement.
+
+Design
+  * parameters are walked in REVERSE registration order (head -> temporal -> encoders ->
+    embedding: the order backward produces gradients) and packed into ~bucket_mb buckets;
+  * every parameter's .grad is a view into its bucket's flat buffer (no pack/unpack copies);
+  * a post-accumulate-grad hook counts arrivals; the last arrival launches
+    all_reduce(bucket, AVG, async_op=True) -- NCCL runs it on its own stream;
+  * finish() waits for the outstanding handles before the optimizer reads the gradients.
+The same code runs on gloo (CPU tensors) for the world_size-2 tests.
+"""
+import torch
+import torch.distributed as dist
+
+
+class BucketedGradAllReduce:
+    def __init__(self, params, bucket_mb: float = 25.0, group=None, grad_dtype=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.params = [p for p in params if p.requires_grad]
+        self.buckets = []          # [(flat tensor, [params])]
+        self._bucket_of = {}
+        self._pending = []
+        self._handles = []
+        cap = int(bucket_mb * 1024 * 1024)
+        cur, cur_bytes = [], 0
+        for p in reversed(self.params):
+            nbytes = p.numel() * (torch.empty((), dtype=grad_dtype or p.dtype).element_size())
+            if cur and cur_bytes + nbytes > cap:
+                self._seal(cur, grad_dtype)
+                cur, cur_bytes = [], 0
+            cur.append(p)
+            cur_bytes += nbytes
+        if cur:
+            self._seal(cur, grad_dtype)
+        self._pending = [len(ps) for _, ps in self.buckets]
+        self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
+
+    def _seal(self, ps, grad_dtype):
+        dtype = grad_dtype or ps[0].dtype
+        flat = torch.zeros(sum(p.numel() for p in ps), dtype=dtype, device=ps[0].device)
+        off = 0
+        for p in ps:
+            p.grad = flat[off:off + p.numel()].view_as(p)
+            off += p.numel()
+            self._bucket_of[p] = len(self.buckets)
+        self.buckets.append((flat, ps))
+
+    def zero_grad(self):
+        """Zero the flat buffers in place (gradients stay views) and re-arm the counters."""
+        for flat, ps in self.buckets:
+            flat.zero_()
+            for p in ps:
+                if p.grad is None or p.grad.data_ptr() < flat.data_ptr() or \
+                        p.grad.data_ptr() >= flat.data_ptr() + flat.numel() * flat.element_size():
+                    raise RuntimeError("a gradient was detached from its bucket (do not set .grad = None)")
+        self._pending = [len(ps) for _, ps in self.buckets]
+        self._handles = []
+
+    def _on_grad(self, p):
+        b = self._bucket_of[p]
+        self._pending[b] -= 1
+        if self._pending[b] == 0 and self.world > 1:
+            flat = self.buckets[b][0]
+            if flat.is_cuda:
+                self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
+            else:  # gloo has no AVG
+                flat.div_(self.world)
+                self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+
+    def finish(self):
+        """Wait for every bucket; buckets whose parameters got no gradient this step are reduced
+        here so that all ranks issue the same collectives."""
+        if self.world > 1:
+            for b, left in enumerate(self._pending):
+                if left > 0:
+                    flat = self.buckets[b][0]
+                    if not flat.is_cuda:
+                        flat.div_(self.world)
+                    self._handles.append(dist.all_reduce(
+                        flat, op=dist.ReduceOp.AVG if flat.is_cuda else dist.ReduceOp.SUM, group=self.group,
+                        async_op=True))
+                    self._pending[b] = 0
+        for h in self._handles:
+            h.wait()
+        self._handles = []
+
+    def bucket_bytes(self):
+        return [flat.numel() * flat.element_size() for flat, _ in self.buckets]
+
+
+def broadcast_parameters(module, src=0, group=None):
+    """Make every rank start from rank `src`'s weights (what DDP's constructor does)."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    for t in list(module.parameters()) + list(module.buffers()):
+        dist.broadcast(t.data, src=src, group=group)

@@ -179,8 +179,8 @@ class _AttnFn(torch.autograd.Function):
             tabs = tuple(r.contiguous() for r in rot)
             a.qcos, a.qsin, a.kcos, a.ksin = (nv.ptr(r) for r in tabs)
             a.rot_dim = tabs[0].shape[-1]
-            need = heads if pos_is_head else max(sq, sk)
-            if tabs[0].shape[0] < need or a.rot_dim > dh:
+            need_q, need_k = (heads, heads) if pos_is_head else (sq, sk)
+            if tabs[0].shape[0] < need_q or tabs[2].shape[0] < need_k or a.rot_dim > dh:
                 raise ValueError("rotary tables do not cover the positions / head size")
         km = None
         if key_mask is not None:

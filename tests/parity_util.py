@@ -85,3 +85,21 @@ def cosine(a, b):
     if na == 0 and nb == 0:
         return 1.0
     return float(torch.dot(a, b) / (na * nb).clamp_min(1e-300))
+
+
+def compare_grads(mine, ref, min_cos=0.999, what=""):
+    """Per-tensor gradient check.  Tensors whose true gradient is (numerically) zero -- e.g. the
+    key bias of single-query softmax attention, which shifts every score equally -- are noise
+    in both implementations: for those only the magnitude is bounded."""
+    top = max(float(g.norm()) for g in ref.values()) if ref else 0.0
+    worst = 1.0
+    for k, g in ref.items():
+        assert k in mine, f"{what}: no gradient for {k}"
+        gn = float(g.norm())
+        if gn <= 1e-5 * top:
+            assert float(mine[k].norm()) <= 2e-2 * top + 1e-12, f"{what}: {k} should be ~0"
+            continue
+        c = cosine(mine[k], g)
+        worst = min(worst, c)
+        assert c >= min_cos, f"{what}: grad cosine {k}: {c}"
+    return worst
