@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""MEANT lag-12 training-step benchmark (BASELINE.json metric: train samples/sec).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): meant_tweet, lag 12, S=128 Stocknet-shaped synthetic
+text, bf16 autocast, forward + CrossEntropy + backward + grad-clip + AdamW, one process per GPU,
+the batch sharded per rank, gradients all-reduced in buckets over NCCL (weak scaling).
+Prints ONE JSON line on rank 0 (contract in the task statement; extra keys: roofline,
+roofline_extra, cpu_baseline, e2e, clocks, gpu_launches).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+LAG, SEQ, VOCAB, DIM, HEADS, CLASSES = 12, 128, 64001, 768, 8, 2
+METRIC, UNIT = "MEANT lag-12 train samples/sec", "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=64, help="samples per GPU per step")
+    ap.add_argument("--encoders", type=int, default=12, help="languageEncoder depth (reference default 12)")
+    ap.add_argument("--cpu-batch", type=int, default=2, help="samples per CPU-baseline step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--attn-impl", default="auto", choices=["auto", "exact", "tcgen05"])
+    return ap.parse_args()
+
+
+def workload_config(args, n):
+    return {"workload": "meant_tweet lag=12 S=128 text+price-shaped synthetic batch (BASELINE configs[1])",
+            "lag": LAG, "seq_len": SEQ, "dim": DIM, "heads": HEADS, "vocab": VOCAB,
+            "num_encoders": args.encoders, "batch_per_gpu": args.batch, "global_batch": args.batch * n,
+            "parallelism": f"dp{n}", "optimizer": "AdamW(fused) + clip_grad_norm 1.0", "mode": "train (dropout on)",
+            "l2": "no flush needed: each step streams >10 GB of activations/weights, far above the 126 MB L2"}
+
+
+def synth_batch(batch, rank, device="cpu", pin=False):
+    g = torch.Generator().manual_seed(1234 + rank)
+    tweets = torch.randint(0, VOCAB, (batch, LAG, SEQ), generator=g)
+    cut = torch.randint(0, SEQ // 4 + 1, (batch, LAG, 1), generator=g)
+    mask = (torch.arange(SEQ).view(1, 1, SEQ) < (SEQ - cut)).float()
+    labels = torch.randint(0, CLASSES, (batch,), generator=g)
+    out = (tweets, mask, labels)
+    if pin:
+        out = tuple(t.pin_memory() for t in out)
+    return tuple(t.to(device) for t in out)
+
+
+# --------------------------------------------------------------------------------- CPU arm
+def cpu_reference_run(args, steps, warmup):
+    """The reference algorithm on the host cores: the oracle port (oracle/, a restatement of the
+    reference's PyTorch code pinned to reference-generated goldens; /root/reference itself is
+    Python and cannot travel to the GPU box).  Same model config, bounded batch."""
+    from oracle import meant_models as mm
+    import torch.nn.functional as F
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    from oracle.params import make_params
+    p = make_params("meant_tweet_l12", encoders=args.encoders, vocab=VOCAB)
+    leaves = [v for v in p.values() if v.requires_grad]
+    opt = torch.optim.AdamW(leaves, lr=5e-5)
+    tweets, mask, labels = synth_batch(args.cpu_batch, 0)
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        out = mm.meant_tweet_forward(p, tweets, mask, HEADS)
+        loss = F.cross_entropy(out, labels)
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(leaves, 1.0)
+        opt.step()
+        if it >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    return {"value": args.cpu_batch / sec, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{steps} steps of {args.cpu_batch} samples (fwd+bwd+clip+AdamW, fp32, eval-mode "
+                      f"dropout, {args.encoders} encoders), {sec:.2f} s/step"}, sec
+
+
+# ------------------------------------------------------------------------------ clock sampling
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown," \
+        "clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------ GPU arm
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return d["hbm_gbs"], d["bf16_tflops"], d["bf16_tflops_sustained"], "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
+def kernel_stats(timers):
+    out = {}
+    for name, evs in timers.items():
+        ms = [a.elapsed_time(b) for a, b in evs]
+        out[name] = (sum(ms) / len(ms), len(ms))
+    return out
+
+
+def rooflines(args, stats, steps):
+    """Roofline objects from the live CUDA-event timings of this run.  Algorithmic work per
+    launch: causal attention fwd 2*S^2*Dh*H FLOP per sequence (the masked
+    upper triangle is not counted), bwd 2x fwd; RMSNorm fwd 2*T*d*2 B (+1 tensor read for the
+    residual form, +1 write for the kept sum), bwd 3*T*d*2 B (+1 read for the residual gradient)."""
+    hbm, tf_burst, tf_sus, src = peaks()
+    nseq, tokens = args.batch * LAG, args.batch * LAG * SEQ
+    dh = DIM // HEADS
+    flops_fwd = 2.0 * SEQ * SEQ * dh * HEADS * nseq
+    main, extra = None, []
+    for name, (ms, count) in sorted(stats.items()):
+        if name.startswith("attn_fwd/S128x128") or name.startswith("attn_bwd/S128x128"):
+            fl = flops_fwd * (2.0 if "bwd" in name else 1.0)
+            ach = fl / (ms * 1e-3) / 1e12
+            r = {"kernel": name, "bound": "tensor", "achieved": round(ach, 2), "peak": tf_sus, "unit": "TFLOP/s",
+                 "frac": round(ach / tf_sus, 4), "traffic": None, "avg_ms": round(ms, 4),
+                 "launches_per_step": count / steps, "peak_source": src + ", sustained"}
+            if "fwd" in name:
+                main = r
+            else:
+                extra.append(r)
+        elif name.startswith("rmsnorm_") and "/d768/" in name:
+            res, bwd = "/res1" in name, "bwd" in name
+            tensors = (3 + res) if bwd else (2 + 2 * res)
+            byts = tensors * tokens * DIM * 2
+            ach = byts / (ms * 1e-3) / 1e9
+            extra.append({"kernel": name, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
+                          "frac": round(ach / hbm, 4), "traffic": None, "avg_ms": round(ms, 4),
+                          "launches_per_step": count / steps, "peak_source": src})
+    return main, extra
+
+
+def gpu_run(args):
+    import torch.distributed as dist
+    from torch import nn
+    import meant_b200 as mb
+    from meant_b200 import _native as nv
+    from meant_b200.train import TrainStep
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (meant_b200 has no CPU path); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if args.attn_impl != "auto":
+        import meant_b200.ops as ops
+        ops.DEFAULT_ATTN_IMPL = {"exact": nv.IMPL_EXACT, "tcgen05": nv.IMPL_TCGEN05}[args.attn_impl]
+    torch.manual_seed(0)
+    model = mb.meant_tweet(DIM, 4, LAG, CLASSES, nn.Embedding(VOCAB, DIM), num_encoders=args.encoders).to(dev)
+    model.train()
+    step = TrainStep(model, bf16=True)
+    h_tweets, h_mask, h_labels = synth_batch(args.batch, rank, pin=True)
+    d_tweets, d_mask, d_labels = (t.to(dev) for t in (h_tweets, h_mask, h_labels))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(args.warmup):
+        step(d_labels, d_tweets, d_mask)
+    # ---- timed region 1: device-resident inputs ("value")
+    sampler = ClockSampler(local) if rank == 0 else None
+    barrier()
+    if sampler:
+        sampler.start()
+    nv.reset_launch_count()
+    nv.enable_timers(rank == 0)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step(d_labels, d_tweets, d_mask)
+    e1.record()
+    barrier()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = nv.launch_count()
+    stats = kernel_stats(nv.timers()) if rank == 0 else {}
+    nv.enable_timers(False)
+    # ---- timed region 2: host buffers in, loss out, every step ("e2e")
+    barrier()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(args.steps):
+        tw, mk, lb = (t.to(dev, non_blocking=True) for t in (h_tweets, h_mask, h_labels))
+        loss_host = float(step(lb, tw, mk).item())
+    e3.record()
+    barrier()
+    ms_e2e = max_over_ranks(e2.elapsed_time(e3))
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        n = world
+        total = args.batch * n * args.steps
+        main, extra = rooflines(args, stats, args.steps)
+        line = {"metric": METRIC, "value": round(total / (ms * 1e-3), 2), "unit": UNIT, "n_gpus": n,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+                "data": "synthetic (seeded token ids + padding masks, random-init weights)",
+                "config": workload_config(args, n),
+                "e2e": {"value": round(total / (ms_e2e * 1e-3), 2), "unit": UNIT,
+                        "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in (h_tweets, h_mask, h_labels)),
+                        "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
+                "gpu_launches": int(launches), "clocks": clocks, "roofline": main, "roofline_extra": extra,
+                "final_loss": loss_host, "native_library": os.path.relpath(nv.lib_path(), ROOT)}
+        if n == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"], _ = cpu_reference_run(args, steps=2, warmup=1)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def reference_run(args):
+    """--impl reference: the reference algorithm's CPU path (oracle port) on the host cores.
+    Under torchrun only rank 0 works."""
+    if int(os.environ.get("RANK", 0)) != 0:
+        return
+    base, sec = cpu_reference_run(args, steps=args.steps, warmup=args.warmup)
+    cfg = workload_config(args, args.gpus)
+    cfg["note"] = "CPU arm: same model/config, bounded batch per step (cpu_baseline.sample)"
+    print(json.dumps({"impl": "reference", "metric": METRIC, "value": round(base["value"], 4), "unit": UNIT,
+                      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+                      "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True, "scaling": "weak",
+                      "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                      "cpu_baseline": base,
+                      "e2e": {"value": round(base["value"], 4), "unit": UNIT, "h2d_bytes_per_step": 0,
+                              "d2h_bytes_per_step": 0}}), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        reference_run(a)
+    else:
+        gpu_run(a)

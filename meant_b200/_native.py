@@ -106,3 +106,28 @@ def launch_count() -> int:
 
 def reset_launch_count():
     lib().meant_reset_launch_count()
+
+
+# ---- optional per-kernel CUDA-event timing (bench.py): events are recorded on the launching
+# stream around the C call, so the measured interval is that kernel's launch(es) only.
+_timers = None
+
+
+def enable_timers(on=True):
+    global _timers
+    _timers = {} if on else None
+
+
+def timers():
+    return _timers
+
+
+def timed(name, fn, *args):
+    if _timers is None:
+        return fn(*args)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    r = fn(*args)
+    e1.record()
+    _timers.setdefault(name, []).append((e0, e1))
+    return r

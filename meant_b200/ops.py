@@ -56,9 +56,10 @@ class _RMSNormFn(torch.autograd.Function):
         y = torch.empty_like(x2)
         s = torch.empty_like(x2) if r2 is not None else None
         rinv = torch.empty(rows, dtype=torch.float32, device=x2.device)
-        nv.check(nv.lib().meant_rmsnorm_fwd(nv.ptr(x2), nv.ptr(r2), nv.ptr(g32), nv.ptr(y), nv.ptr(s),
-                                            nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed,
-                                            nv.dt(x2), nv.stream()), "meant_rmsnorm_fwd")
+        tag = f"rmsnorm_fwd/d{d}/res{int(r2 is not None)}/gelu{int(pre_gelu)}"
+        nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_fwd, nv.ptr(x2), nv.ptr(r2), nv.ptr(g32), nv.ptr(y), nv.ptr(s),
+                          nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed, nv.dt(x2), nv.stream()),
+                 "meant_rmsnorm_fwd")
         ctx.save_for_backward(s if r2 is not None else x2, g32, rinv)
         ctx.cfg = (eps, int(pre_gelu), drop_p, seed, res is not None, gain.dtype, x.dtype,
                    res.dtype if res is not None else None)
@@ -76,9 +77,10 @@ class _RMSNormFn(torch.autograd.Function):
         ds = dsum.to(src.dtype).contiguous() if dsum is not None else None
         dx = torch.empty_like(src)
         dgain = torch.zeros(d, dtype=torch.float32, device=src.device)
-        nv.check(nv.lib().meant_rmsnorm_bwd(nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv), nv.ptr(ds),
-                                            nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
-                                            nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+        tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}"
+        nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_bwd, nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv),
+                          nv.ptr(ds), nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
+                          nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
         return dx.to(xdt), (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
 
 
@@ -190,7 +192,8 @@ class _AttnFn(torch.autograd.Function):
             a.key_mask = nv.ptr(km)
         a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
         a.pos_is_head, a.causal, a.scale = int(pos_is_head), int(causal), float(scale)
-        nv.check(nv.lib().meant_attn_fwd(a, nv.dt(t0), impl, nv.stream()), "meant_attn_fwd")
+        nv.check(nv.timed(f"attn_fwd/S{sq}x{sk}/Dh{dh}/c{int(causal)}", nv.lib().meant_attn_fwd, a, nv.dt(t0), impl, nv.stream()),
+                 "meant_attn_fwd")
         ctx.save_for_backward(t0, t1, t2, out, lse, km, *(tabs or ()))
         ctx.cfg = (mode, heads, float(scale), int(causal), int(pos_is_head), impl, rot is not None)
         return out
@@ -231,14 +234,19 @@ class _AttnFn(torch.autograd.Function):
             a.key_mask = nv.ptr(km)
         a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
         a.pos_is_head, a.causal, a.scale = pos_is_head, causal, scale
-        nv.check(nv.lib().meant_attn_bwd(a, nv.dt(t0), impl, nv.stream()), "meant_attn_bwd")
+        nv.check(nv.timed(f"attn_bwd/S{sq}x{sk}/Dh{dh}/c{causal}", nv.lib().meant_attn_bwd, a, nv.dt(t0), impl, nv.stream()),
+                 "meant_attn_bwd")
         return g0, g1, g2, None, None, None, None, None, None, None, None
 
 
+DEFAULT_ATTN_IMPL = nv.IMPL_AUTO   # bench/tests may force IMPL_EXACT or IMPL_TCGEN05
+
+
 def attention(qkv=None, q=None, kv=None, k=None, v=None, *, heads, scale, causal=False, rot=None,
-              pos_is_head=False, key_mask=None, impl=nv.IMPL_AUTO):
+              pos_is_head=False, key_mask=None, impl=None):
     """softmax((Rq q)(Rk k)^T * scale + masks) v on packed `b s (h d)` projections.
     Returns [N, Sq, dim] in `b s (h d)` layout (no rearrange is materialised)."""
+    impl = DEFAULT_ATTN_IMPL if impl is None else impl
     if qkv is not None:
         return _AttnFn.apply(qkv, None, None, "qkv", heads, scale, causal, rot, pos_is_head, key_mask, impl)
     if kv is not None:
