@@ -113,6 +113,12 @@ int meant_geglu_bwd(const void* dy, const void* x, void* dx, int64_t rows, int F
 int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int transpose, int dtype,
                       meant_stream_t stream);
 
+/* ---- tcgen05 self-test: D[128,N] (fp32) = op(A) op(B)^T for one bf16 tile; a_mn / b_mn select
+ *      MN-major operands (A given as [K,128], B as [K,N]) instead of K-major ([128,K], [N,K]).
+ *      Exists so the tests can pin the descriptor conventions the attention kernels rely on. */
+int meant_tc_probe(const void* A, const void* B, float* D, int N, int K, int a_mn, int b_mn,
+                   meant_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
