@@ -1,0 +1,403 @@
+// Fused xPos/rotary flash attention on tcgen05 tensor cores (sm_100a), bf16 in / fp32 accumulate.
+//
+// Forward, one CTA per (sequence, head, 128-query tile), 128 threads, thread t <-> query row t
+// <-> TMEM lane t (softmax is thread-local, no shuffles):
+//   stage   Q, K (rotated + xPos-scaled in registers on the way in) and V as 16-byte chunks into
+//           the shared "chunk layout" (tc_utils.cuh) straight from the packed `b s (h d)` projections
+//   MMA 1   S = Q K^T            (A, B K-major)                    -> TMEM cols [0,128)
+//   softmax scale, causal / padding mask, online max/sum in fp32; P (bf16) -> shared memory
+//   MMA 2   PV = P V             (A K-major, B = V MN-major: no transpose copy) -> TMEM cols [128,128+DH)
+//   O accumulates in registers across key tiles; epilogue writes `b s (h d)` and the LSE.
+// Backward (Sq, Sk <= 128: the text path), one CTA per (sequence, head), recompute based:
+//   S = Q K^T, dP = dO V^T -> P, dS (bf16, shared) -> dV = P^T dO, dK = dS^T Q, dQ = dS K,
+//   every transposed operand read MN-major from the buffer that was staged once; dQ/dK are
+//   un-rotated (transpose rotation) in the epilogue.
+// Work per sequence and the roofline that bounds it: DESIGN.md.
+#include "attn_common.cuh"
+#include "tc_utils.cuh"
+#include <math_constants.h>
+
+namespace meant {
+
+constexpr int TQ = 128;                       // query rows per CTA == TMEM lanes
+constexpr int TK = 128;                       // keys per tile
+constexpr uint32_t CS128 = 128 * 16 + 16;     // chunk stride of a 128-row chunk-layout buffer
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+// Stage rows [s0, s0+128) of a head view into chunk layout, optionally rotating pairs with the
+// per-element tables (cos/sin already carry the xPos scale).  Lanes walk 16-byte chunks of a
+// row first, so global reads are contiguous DH*2-byte segments.
+template <int DH>
+__device__ __forceinline__ void stage_rows(uint8_t* smem, const HeadView& v, int n, int n2c, int h, int s0, int S,
+                                           const float* __restrict__ cs, const float* __restrict__ sn, int rot_dim,
+                                           int pos_is_head) {
+  constexpr int CPR = DH / 8;
+  for (int idx = threadIdx.x; idx < 128 * CPR; idx += 128) {
+    const int r = idx / CPR, ch = idx - r * CPR;
+    const int srow = s0 + r;
+    uint4 raw = make_uint4(0u, 0u, 0u, 0u);
+    if (srow < S) {
+      raw = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(v, n, n2c, srow, h) + ch * 8);
+      if (cs != nullptr && ch * 8 < rot_dim) {
+        const int pos = pos_is_head ? h : srow;
+        const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + ch * 8);
+        const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + ch * 8);
+        const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+        __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+        float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+        float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+        h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+        h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+        h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+        h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+      }
+    }
+    *reinterpret_cast<uint4*>(smem + ch * CS128 + r * 16) = raw;
+  }
+}
+
+// K-major operand (rows = M/N, cols = K) / MN-major operand (rows = K, cols = M/N) descriptors of
+// a 128-row chunk-layout buffer at K-step ks (16 K-elements per MMA).
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int ks) {
+  return tc::make_desc(base + ks * 2 * CS128, CS128, 128);
+}
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int ks) {
+  return tc::make_desc(base + ks * 256, 128, CS128);
+}
+
+__device__ __forceinline__ float masked_score(float s, float scale, const float* mrow, int kj, bool valid) {
+  float x = s * scale;
+  if (mrow != nullptr && valid) x += (1.0f - __ldg(mrow + kj)) * -1e9f;   // meant/xPosAttention.py:54-56
+  return valid ? x * LOG2E : -CUDART_INF_F;
+}
+
+template <int DH>
+struct FwdSmem {
+  static constexpr uint32_t OPER = (DH / 8) * CS128;       // Q, K or V tile
+  static constexpr uint32_t PBUF = (TK / 8) * CS128;       // P tile
+  static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, P = 3 * OPER, TOTAL = 3 * OPER + PBUF;
+};
+
+template <int DH>
+__global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t bar_s, bar_o;
+  __shared__ uint32_t tmem_slot;
+  using L = FwdSmem<DH>;
+  const int t = threadIdx.x, warp = t >> 5;
+  const int q0 = blockIdx.x * TQ, h = blockIdx.y, n = blockIdx.z;
+  if (t == 0) {
+    tc::mbar_init(&bar_s, 1);
+    tc::mbar_init(&bar_o, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
+  stage_rows<DH>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+
+  const int qi = q0 + t;
+  const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+  float m_run = -CUDART_INF_F, l_run = 0.f;
+  float o_acc[DH];
+#pragma unroll
+  for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
+  const int last_q = min(q0 + TQ, a.Sq) - 1;
+  const int n_tiles = (a.Sk + TK - 1) / TK;
+  uint32_t phase = 0, tmem = 0;
+  const uint32_t sq = tc::smem_u32(smem + L::Q), sk = tc::smem_u32(smem + L::K), sv = tc::smem_u32(smem + L::V),
+                 sp = tc::smem_u32(smem + L::P);
+  for (int kt = 0; kt < n_tiles; ++kt) {
+    const int k0 = kt * TK;
+    if (a.causal && k0 > last_q) break;
+    stage_rows<DH>(smem + L::K, a.k, n, a.n2_count, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    stage_rows<DH>(smem + L::V, a.v, n, a.n2_count, h, k0, a.Sk, nullptr, nullptr, 0, 0);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    tmem = tmem_slot;
+    if (t == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
+#pragma unroll
+      for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+      tc::mma_commit(&bar_s);
+    }
+    tc::mbar_wait(&bar_s, phase);
+    tc::fence_after_sync();
+    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    // pass 1: row max
+    float m_tile = -CUDART_INF_F;
+#pragma unroll 1
+    for (int c0 = 0; c0 < TK; c0 += 16) {
+      float s[16];
+      tc::tmem_ld16(lane_base + c0, s);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int kj = k0 + c0 + i;
+        const bool valid = kj < a.Sk && (!a.causal || kj <= qi);
+        m_tile = fmaxf(m_tile, masked_score(s[i], a.scale, mrow, kj, valid));
+      }
+    }
+    const float m_new = fmaxf(m_run, m_tile);
+    const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
+    const float corr = exp2f(m_run - m_use);   // m_run = -inf -> 0
+    // pass 2: P = exp2(x - m), bf16 -> shared (row t, 16-byte chunks), row sum
+    float l_tile = 0.f;
+#pragma unroll 1
+    for (int c0 = 0; c0 < TK; c0 += 16) {
+      float s[16];
+      tc::tmem_ld16(lane_base + c0, s);
+      tc::tmem_ld_wait();
+      uint4 pk[2];
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) {
+        const int kj = k0 + c0 + i;
+        const bool v0 = kj < a.Sk && (!a.causal || kj <= qi);
+        const bool v1 = kj + 1 < a.Sk && (!a.causal || kj + 1 <= qi);
+        const float p0 = exp2f(masked_score(s[i], a.scale, mrow, kj, v0) - m_use);
+        const float p1 = exp2f(masked_score(s[i + 1], a.scale, mrow, kj + 1, v1) - m_use);
+        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+        ph[i >> 1] = pb;
+        const float2 back = __bfloat1622float2(pb);   // sum what the tensor core will see
+        l_tile += back.x + back.y;
+      }
+      *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk[0];
+      *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
+    }
+    l_run = l_run * corr + l_tile;
+    m_run = m_new;
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (t == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(TQ, DH, 0, 1);
+#pragma unroll
+      for (int ks = 0; ks < TK / 16; ++ks)
+        tc::mma_ss(tmem + 128, desc_kmajor(sp, ks), desc_mnmajor(sv, ks), idesc, ks > 0);
+      tc::mma_commit(&bar_o);
+    }
+    tc::mbar_wait(&bar_o, phase);
+    tc::fence_after_sync();
+#pragma unroll
+    for (int c0 = 0; c0 < DH; c0 += 16) {
+      float pv[16];
+      tc::tmem_ld16(lane_base + 128 + c0, pv);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) o_acc[c0 + i] = o_acc[c0 + i] * corr + pv[i];
+    }
+    phase ^= 1;
+  }
+  if (qi < a.Sq) {
+    const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+    __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
+#pragma unroll
+    for (int c0 = 0; c0 < DH; c0 += 8) {
+      uint4 pk;
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 8; i += 2) ph[i >> 1] = __floats2bfloat162_rn(o_acc[c0 + i] * inv, o_acc[c0 + i + 1] * inv);
+      *reinterpret_cast<uint4*>(op + c0) = pk;
+    }
+    if (a.lse) a.lse[((int64_t)n * a.H + h) * a.Sq + qi] = m_run * LN2 + logf(l_run);
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem_slot, 256);
+}
+
+// ------------------------------------------------------------------------------------ backward
+template <int DH>
+struct BwdSmem {
+  static constexpr uint32_t OPER = (DH / 8) * CS128;
+  static constexpr uint32_t PBUF = (TK / 8) * CS128;
+  static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, DO = 3 * OPER, P = 4 * OPER, DS = 4 * OPER + PBUF,
+                            TOTAL = 4 * OPER + 2 * PBUF;
+};
+
+// un-rotate (transpose rotation) 16 consecutive features [c0, c0+16) of a gradient row in place
+__device__ __forceinline__ void unrot16(float* g, const float* cs, const float* sn, int pos, int rot_dim, int c0) {
+#pragma unroll
+  for (int i = 0; i < 16; i += 2)
+    if (c0 + i < rot_dim) unrot_pair(g[i], g[i + 1], cs, sn, pos, rot_dim, c0 + i);
+}
+
+template <int DH>
+__global__ void __launch_bounds__(128, 1) attn_tc_bwd_kernel(AttnArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t bar1, bar2;
+  __shared__ uint32_t tmem_slot;
+  using L = BwdSmem<DH>;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 384, T_DQ = 0;
+  const int t = threadIdx.x, warp = t >> 5;
+  const int h = blockIdx.y, n = blockIdx.z;
+  if (t == 0) {
+    tc::mbar_init(&bar1, 1);
+    tc::mbar_init(&bar2, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  stage_rows<DH>(smem + L::Q, a.q, n, a.n2_count, h, 0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+  stage_rows<DH>(smem + L::K, a.k, n, a.n2_count, h, 0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+  stage_rows<DH>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk, nullptr, nullptr, 0, 0);
+  stage_rows<DH>(smem + L::DO, a.o, n, a.n2_count, h, 0, a.Sq, nullptr, nullptr, 0, 0);
+  // delta_t = <dO_t, O_t>, lse_t (thread t owns query row t)
+  float delta = 0.f, lse2 = 0.f;
+  if (t < a.Sq) {
+    const __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, t, h);
+    const __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, t, h);
+#pragma unroll
+    for (int c0 = 0; c0 < DH; c0 += 8) {
+      const uint4 ov = *reinterpret_cast<const uint4*>(op + c0), gv = *reinterpret_cast<const uint4*>(gp + c0);
+      const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 x = __bfloat1622float2(o2[i]), y = __bfloat1622float2(g2[i]);
+        delta += x.x * y.x + x.y * y.y;
+      }
+    }
+    const int64_t li = ((int64_t)n * a.H + h) * a.Sq + t;
+    lse2 = a.lse[li] * LOG2E;
+    a.delta[li] = delta;
+  }
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const uint32_t sq = tc::smem_u32(smem + L::Q), sk = tc::smem_u32(smem + L::K), sv = tc::smem_u32(smem + L::V),
+                 sdo = tc::smem_u32(smem + L::DO), sp = tc::smem_u32(smem + L::P), sds = tc::smem_u32(smem + L::DS);
+  if (t == 0) {
+    constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
+#pragma unroll
+    for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+#pragma unroll
+    for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_kmajor(sdo, ks), desc_kmajor(sv, ks), idesc, ks > 0);
+    tc::mma_commit(&bar1);
+  }
+  tc::mbar_wait(&bar1, 0);
+  tc::fence_after_sync();
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+#pragma unroll 1
+  for (int c0 = 0; c0 < TK; c0 += 16) {
+    float s[16], dp[16];
+    tc::tmem_ld16(lane_base + T_S + c0, s);
+    tc::tmem_ld16(lane_base + T_DP + c0, dp);
+    tc::tmem_ld_wait();
+    uint4 pk[2], dk[2];
+    __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
+    __nv_bfloat162* dh = reinterpret_cast<__nv_bfloat162*>(dk);
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+      float p[2], ds[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int kj = c0 + i + j;
+        const bool valid = t < a.Sq && kj < a.Sk && (!a.causal || kj <= t);
+        p[j] = valid ? exp2f(masked_score(s[i + j], a.scale, mrow, kj, true) - lse2) : 0.f;
+        ds[j] = p[j] * (dp[i + j] - delta) * a.scale;
+      }
+      ph[i >> 1] = __floats2bfloat162_rn(p[0], p[1]);
+      dh[i >> 1] = __floats2bfloat162_rn(ds[0], ds[1]);
+    }
+    *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk[0];
+    *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
+    *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8) * CS128 + t * 16) = dk[0];
+    *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8 + 1) * CS128 + t * 16) = dk[1];
+  }
+  tc::fence_async_smem();
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  if (t == 0) {
+    constexpr uint32_t id_t = tc::make_idesc(TK, DH, 1, 1);   // A^T (MN-major) x B (MN-major)
+    constexpr uint32_t id_n = tc::make_idesc(TQ, DH, 0, 1);   // A (K-major)    x B (MN-major)
+#pragma unroll
+    for (int ks = 0; ks < TQ / 16; ++ks)      // dV = P^T dO   (K = queries)
+      tc::mma_ss(tmem + T_DV, desc_mnmajor(sp, ks), desc_mnmajor(sdo, ks), id_t, ks > 0);
+#pragma unroll
+    for (int ks = 0; ks < TQ / 16; ++ks)      // dK = dS^T Q
+      tc::mma_ss(tmem + T_DK, desc_mnmajor(sds, ks), desc_mnmajor(sq, ks), id_t, ks > 0);
+#pragma unroll
+    for (int ks = 0; ks < TK / 16; ++ks)      // dQ = dS K     (K = keys)
+      tc::mma_ss(tmem + T_DQ, desc_kmajor(sds, ks), desc_mnmajor(sk, ks), id_n, ks > 0);
+    tc::mma_commit(&bar2);
+  }
+  tc::mbar_wait(&bar2, 0);
+  tc::fence_after_sync();
+  // epilogue: row t of dV / dK is key t, row t of dQ is query t
+  auto store_row = [&](uint32_t tcol, __nv_bfloat16* dst, const float* cs, const float* sn, int pos) {
+#pragma unroll
+    for (int c0 = 0; c0 < DH; c0 += 16) {
+      float g[16];
+      tc::tmem_ld16(lane_base + tcol + c0, g);
+      tc::tmem_ld_wait();
+      if (cs != nullptr) unrot16(g, cs, sn, pos, a.rot_dim, c0);
+      uint4 pk[2];
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) ph[i >> 1] = __floats2bfloat162_rn(g[i], g[i + 1]);
+      if (dst != nullptr) {
+        *reinterpret_cast<uint4*>(dst + c0) = pk[0];
+        *reinterpret_cast<uint4*>(dst + c0 + 8) = pk[1];
+      }
+    }
+  };
+  const bool krow = t < a.Sk, qrow = t < a.Sq;
+  store_row(T_DV, krow ? view_ptr<__nv_bfloat16>(a.dv, n, a.n2_count, t, h) : nullptr, nullptr, nullptr, 0);
+  store_row(T_DK, krow ? view_ptr<__nv_bfloat16>(a.dk, n, a.n2_count, t, h) : nullptr, a.kcos, a.ksin,
+            a.pos_is_head ? h : min(t, a.Sk - 1));
+  store_row(T_DQ, qrow ? view_ptr<__nv_bfloat16>(a.dq, n, a.n2_count, t, h) : nullptr, a.qcos, a.qsin,
+            a.pos_is_head ? h : min(t, a.Sq - 1));
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// ------------------------------------------------------------------------------------ host side
+static bool view_ok(const HeadView& v) {
+  return v.p != nullptr && (reinterpret_cast<uintptr_t>(v.p) % 16 == 0) && v.sn1 % 8 == 0 && v.sn2 % 8 == 0 &&
+         v.ss % 8 == 0 && v.sh % 8 == 0;
+}
+
+int attn_tc_supported(const AttnArgs& a, int dtype, int backward) {
+  if (dtype != MEANT_DT_BF16) return 0;
+  if (a.Dh != 64 && a.Dh != 96) return 0;
+  if (a.N <= 0 || a.H <= 0 || a.Sq <= 0 || a.Sk <= 0 || a.n2_count <= 0 || a.N > 65535 || a.H > 65535) return 0;
+  if (a.rot_dim % 8 != 0 || a.rot_dim > a.Dh) return 0;
+  if (a.qcos && (!a.qsin || !a.kcos || !a.ksin)) return 0;
+  if (!view_ok(a.q) || !view_ok(a.k) || !view_ok(a.v) || !view_ok(a.o)) return 0;
+  if (backward) {
+    if (a.Sq > TQ || a.Sk > TK) return 0;   // multi-tile backward: exact path for now
+    if (!view_ok(a.dq) || !view_ok(a.dk) || !view_ok(a.dv) || !view_ok(a.out_saved) || !a.lse || !a.delta) return 0;
+  }
+  return 1;
+}
+
+template <typename Kern>
+static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  kern<<<grid, 128, smem, st>>>(a);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
+  dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
+  if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st);
+  return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st);
+}
+
+int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
+  dim3 grid(1, a.H, a.N);
+  if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
+  return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);
+}
+
+}  // namespace meant
