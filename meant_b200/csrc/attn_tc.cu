@@ -360,6 +360,11 @@ __global__ void __launch_bounds__(128, 1) attn_tc_bwd_kernel(AttnArgs a) {
 }
 
 // ------------------------------------------------------------------------------------ host side
+// attn_tc2.cu: persistent warp-specialised kernels for single-tile problems (Sq, Sk <= 128)
+int attn_tc2_supported(const AttnArgs& a, int backward);
+int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st);
+int attn_tc2_bwd(const AttnArgs& a, cudaStream_t st);
+
 static bool view_ok(const HeadView& v) {
   return v.p != nullptr && (reinterpret_cast<uintptr_t>(v.p) % 16 == 0) && v.sn1 % 8 == 0 && v.sn2 % 8 == 0 &&
          v.ss % 8 == 0 && v.sh % 8 == 0;
@@ -389,12 +394,14 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
 }
 
 int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
+  if (attn_tc2_supported(a, 0)) return attn_tc2_fwd(a, st);
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st);
 }
 
 int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
+  if (attn_tc2_supported(a, 1)) return attn_tc2_bwd(a, st);
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);
