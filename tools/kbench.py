@@ -1,0 +1,109 @@
+#!/usr/bin/env python
+"""Kernel micro-benchmarks through the C ABI (CUDA events on the launching stream, inputs larger
+than L2 or an L2 flush between iterations).  Used for the ncu captures under profiles/.
+
+    python tools/kbench.py attn  [--n 768] [--s 128] [--dh 96] [--iters 20]
+    python tools/kbench.py norm  [--rows 98304] [--d 768]
+"""
+import argparse
+import math
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from meant_b200 import ops, RotaryEmbedding, _native as nv  # noqa: E402
+
+
+def timeit(fn, iters, flush=None):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(iters):
+        if flush is not None:
+            flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    ms.sort()
+    return ms[len(ms) // 2], ms[0]
+
+
+def attn(args):
+    heads, dh, n, s = args.heads, args.dh, args.n, args.s
+    dim = heads * dh
+    torch.manual_seed(0)
+    qkv = torch.randn(n, s, 3 * dim, device="cuda").bfloat16().requires_grad_(True)
+    rot = RotaryEmbedding(dim=48 if dh == 96 else dh, use_xpos=dh == 96).tables(s, "cuda") if not args.norot else None
+    cut = torch.randint(0, s // 4 + 1, (n, 1), device="cuda")
+    mask = (torch.arange(s, device="cuda")[None] < (s - cut)).float() if args.causal else None
+    scale = 1.0 / math.sqrt(dim)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    impl = {"auto": nv.IMPL_AUTO, "exact": nv.IMPL_EXACT, "tcgen05": nv.IMPL_TCGEN05}[args.impl]
+
+    def fwd():
+        return ops.attention(qkv, heads=heads, scale=scale, causal=args.causal, rot=rot, key_mask=mask, impl=impl)
+
+    out = fwd()
+    dout = torch.randn_like(out)
+    f_med, f_min = timeit(lambda: ops.attention(qkv.detach(), heads=heads, scale=scale, causal=args.causal, rot=rot,
+                                                key_mask=mask, impl=impl), args.iters, flush)
+
+    def bwd():
+        qkv.grad = None
+        out.backward(dout, retain_graph=True)
+
+    b_med, b_min = timeit(bwd, args.iters, flush)
+    # algorithmic work: fwd reads q,k,v + writes o; bwd reads q,k,v,dO (+lse) + writes dq,dk,dv
+    tile = n * s * dim * 2
+    fl = (2.0 if args.causal else 4.0) * s * s * dh * heads * n
+    print(f"attn n={n} s={s} dh={dh} causal={args.causal}: fwd {f_med*1e3:.1f} us (min {f_min*1e3:.1f}) "
+          f"{4*tile/f_med/1e6:.0f} GB/s {fl/f_med/1e9:.1f} TFLOP/s | bwd(autograd, incl. torch glue) {b_med*1e3:.1f} us "
+          f"(min {b_min*1e3:.1f}) {7*tile/b_med/1e6:.0f} GB/s {2*fl/b_med/1e9:.1f} TFLOP/s")
+
+
+def norm(args):
+    rows, d = args.rows, args.d
+    x = torch.randn(rows, d, device="cuda").bfloat16().requires_grad_(True)
+    res = torch.randn(rows, d, device="cuda").bfloat16()
+    g = torch.ones(d, device="cuda", requires_grad=True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    byts = rows * d * 2
+    for name, kw, tf, tb in (("plain", {}, 2, 3), ("gelu", {"pre_gelu": True}, 2, 3), ("res", {"residual": res}, 4, 4)):
+        f_med, f_min = timeit(lambda: ops.rms_norm(x.detach(), g.detach(), **kw), args.iters, flush)
+        y = ops.rms_norm(x, g, **kw)
+        outs = y if isinstance(y, tuple) else (y,)
+        douts = tuple(torch.randn_like(o) for o in outs)
+
+        def bwd():
+            x.grad = None
+            g.grad = None
+            torch.autograd.backward(outs, douts, retain_graph=True)
+
+        b_med, b_min = timeit(bwd, args.iters, flush)
+        print(f"rmsnorm {name} rows={rows} d={d}: fwd {f_med*1e3:.1f} us {tf*byts/f_med/1e6:.0f} GB/s | "
+              f"bwd(autograd) {b_med*1e3:.1f} us {tb*byts/b_med/1e6:.0f} GB/s")
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what", choices=["attn", "norm"])
+    ap.add_argument("--n", type=int, default=768)
+    ap.add_argument("--s", type=int, default=128)
+    ap.add_argument("--dh", type=int, default=96)
+    ap.add_argument("--heads", type=int, default=8)
+    ap.add_argument("--rows", type=int, default=98304)
+    ap.add_argument("--d", type=int, default=768)
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--causal", type=int, default=1)
+    ap.add_argument("--norot", action="store_true")
+    ap.add_argument("--impl", default="auto")
+    a = ap.parse_args()
+    a.causal = bool(a.causal)
+    {"attn": attn, "norm": norm}[a.what](a)
