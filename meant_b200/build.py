@@ -19,6 +19,8 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--use_fast_math=false", "-Xptxas", "-v"]
 FLAGS.remove("--use_fast_math=false")  # exact erf/exp/div: parity first
+if os.environ.get("MEANT_PROF"):         # in-kernel phase timers (tools/kbench.py --prof); never set for product builds
+    FLAGS.append("-DMEANT_PROF")
 
 
 def sources():

@@ -6,16 +6,18 @@
 // (consecutive CTAs take the heads of one sequence, so the packed `b s (h d)` rows they read
 // are contiguous in DRAM).  384 threads, two roles:
 //   loader warps 8-11  cp.async (LDGSTS, 16 B, zero-filled past S) Q/K/V[/dO] tiles straight from
-//                      the packed projections into the shared "chunk layout" (tc_utils.cuh),
-//                      several items ahead; rotate + xPos-scale Q and K rows IN PLACE from
-//                      per-thread register tables (thread <-> row, fp16 pairs, loaded once);
-//                      issue the first MMA(s) of the item; later drain the staged results to
-//                      global memory with coalesced 16-byte stores (un-rotating dQ/dK first).
-//   compute warps 0-7  warps w and w+4 share TMEM lanes (query rows) 32(w%4).. and split the key
-//                      columns in interleaved 32-column blocks (balanced under the causal mask);
-//                      softmax (forward) or P/dS recompute (backward) straight out of TMEM with
-//                      one shared-memory exchange of the row max / row sums, bf16 P/dS to shared
-//                      memory, issue the dependent MMAs, move accumulators TMEM -> bf16 -> staging.
+//                      the packed projections into the shared "chunk layout" (tc_utils.cuh), up to
+//                      three items ahead, completion signalled by cp.async.mbarrier.arrive; the
+//                      padding-mask bias / LSE row; later drain the staged results to global
+//                      memory with coalesced 16-byte stores.
+//   compute warps 0-7  warps w and w+4 share TMEM lanes (query rows) 32(w%4).. : thread (row t, half)
+//                      rotates + xPos-scales row t of Q (half 0) or K (half 1) IN PLACE from
+//                      per-thread register tables (fp16 pairs, loaded once), issues the MMAs,
+//                      and the halves split the key columns in interleaved 32-column blocks
+//                      (balanced under the causal mask) for the softmax (forward) or the P/dS
+//                      recompute (backward) straight out of TMEM, with one shared-memory exchange
+//                      of the row max / row sums; accumulators go TMEM -> (un-rotate dQ/dK in
+//                      fp32 registers) -> bf16 -> staging.
 // Hand-offs are mbarriers (tcgen05.commit for MMA completion, mbarrier.arrive for data), never
 // __syncthreads, so loads of item j+1/j+2, the tensor core on item j and the stores of item
 // j-1 overlap.  Both kernels are HBM-bound at S = 128 (see DESIGN.md for the byte counts).
@@ -27,11 +29,29 @@
 namespace meant {
 namespace t2 {
 
-constexpr uint32_t CS = 128 * 16 + 16;   // chunk stride of a 128-row chunk-layout buffer
+constexpr uint32_t CS = 128 * 16 + 16;   // chunk stride of a 128-row chunk-layout buffer (+16: lanes walking chunks hit distinct banks)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr int BAR_C = 1, BAR_L = 2;      // named barriers of the compute (256 threads) / loader (128) groups
 constexpr int NC = 256, NL = 128, NT = NC + NL;
+
+// Optional in-kernel phase timing (build with -DMEANT_PROF): CTA 0 accumulates clock64 deltas per phase
+// for one compute thread (slots 0..15) and one loader thread (slots 16..31); read with meant_debug_prof().
+#ifdef MEANT_PROF
+__device__ unsigned long long g_prof[64];
+struct Prof {
+  long long last; bool on; int base;
+  __device__ __forceinline__ void init(bool enable, int b) { on = enable; base = b; last = clock64(); }
+  __device__ __forceinline__ void tick(int slot) {
+    if (on) { const long long now = clock64(); atomicAdd(&g_prof[base + slot], (unsigned long long)(now - last)); last = now; }
+  }
+};
+#else
+struct Prof {
+  __device__ __forceinline__ void init(bool, int) {}
+  __device__ __forceinline__ void tick(int) {}
+};
+#endif
 
 template <int DH>
 struct Geo {
@@ -49,32 +69,49 @@ __device__ __forceinline__ const __nv_bfloat16* head_base(const HeadView& v, int
   return static_cast<const __nv_bfloat16*>(v.p) + (int64_t)n1 * v.sn1 + (int64_t)n2 * v.sn2 + (int64_t)h * v.sh;
 }
 
-// 128 threads: rows [0,128) of head (n, h) -> chunk layout at shared address sbase; rows >= S are zero filled.
+// Loader thread t of 128 moves chunks idx = t + 128 k (k < CPR) of every 128 x DH tile: lanes walk the 16-byte
+// chunks of a row first, so a warp reads ~2.7 whole rows (full 64-byte segments, few 128-byte lines).  The
+// (row, chunk) split is the same for every tile and item, so it is computed once.  (tools/ldbench.cu: this
+// map moves 3.9 TB/s through LDGSTS; 8-lane groups filling one core matrix from 8 rows only 3.2 TB/s.)
 template <int DH>
-__device__ __forceinline__ void issue_tile(uint32_t sbase, const HeadView& v, int n, int n2c, int h, int S, int t) {
-  constexpr int CPR = DH / 8;
+struct ChunkMap {
+  static constexpr int CPR = DH / 8;
+  int rc[CPR];                                     // row | chunk << 8
+  __device__ __forceinline__ void init(int t) {
+#pragma unroll
+    for (int k = 0; k < CPR; ++k) {
+      const int idx = t + k * 128, r = idx / CPR, ch = idx - r * CPR;
+      rc[k] = r | (ch << 8);
+    }
+  }
+  __device__ __forceinline__ int row(int k) const { return rc[k] & 0xff; }
+  __device__ __forceinline__ int gcol(int k) const { return (rc[k] >> 8) * 8; }                      // element column
+  __device__ __forceinline__ uint32_t soff(int k) const { return (rc[k] >> 8) * CS + (rc[k] & 0xff) * 16; }   // chunk layout
+  __device__ __forceinline__ uint32_t stg(int k) const { return (rc[k] & 0xff) * Geo<DH>::PITCH + (rc[k] >> 8) * 16; }
+};
+
+// rows [0,128) of head (n, h) -> chunk layout at shared address sbase; rows >= S are zero filled.
+template <int DH>
+__device__ __forceinline__ void issue_tile(const ChunkMap<DH>& cm, uint32_t sbase, const HeadView& v, int n, int n2c, int h, int S) {
   const __nv_bfloat16* base = head_base(v, n, n2c, h);
-#pragma unroll 4
-  for (int k = 0; k < CPR; ++k) {
-    const int idx = t + k * 128;
-    const int r = idx / CPR, ch = idx - r * CPR;
-    const bool ok = r < S;
-    tc::cp_async16(sbase + ch * CS + r * 16, base + (int64_t)(ok ? r : 0) * v.ss + ch * 8, ok ? 16u : 0u);
+  const int ss = (int)v.ss;
+#pragma unroll
+  for (int k = 0; k < DH / 8; ++k) {
+    const bool ok = cm.row(k) < S;
+    tc::cp_async16(sbase + cm.soff(k), base + (ok ? cm.row(k) * ss : 0) + cm.gcol(k), ok ? 16u : 0u);
   }
 }
 
-// 128 threads: staged rows (row-major, PITCH bytes apart) -> head (n, h) of a global view, coalesced.
+// staged rows (row-major, PITCH bytes apart) -> head (n, h) of a global view, coalesced.
 template <int DH>
-__device__ __forceinline__ void drain_rows(const uint8_t* stg, const HeadView& v, int n, int n2c, int h, int S, int t) {
-  constexpr int CPR = DH / 8;
+__device__ __forceinline__ void drain_rows(const ChunkMap<DH>& cm, const uint8_t* stg, const HeadView& v, int n, int n2c, int h, int S) {
   __nv_bfloat16* base = const_cast<__nv_bfloat16*>(head_base(v, n, n2c, h));
-#pragma unroll 4
-  for (int k = 0; k < CPR; ++k) {
-    const int idx = t + k * 128;
-    const int r = idx / CPR, ch = idx - r * CPR;
-    if (r < S) {
-      const uint4 val = *reinterpret_cast<const uint4*>(stg + r * Geo<DH>::PITCH + ch * 16);
-      *reinterpret_cast<uint4*>(base + (int64_t)r * v.ss + ch * 8) = val;
+  const int ss = (int)v.ss;
+#pragma unroll
+  for (int k = 0; k < DH / 8; ++k) {
+    if (cm.row(k) < S) {
+      const uint4 val = *reinterpret_cast<const uint4*>(stg + cm.stg(k));
+      *reinterpret_cast<uint4*>(base + cm.row(k) * ss + cm.gcol(k)) = val;
     }
   }
 }
@@ -151,6 +188,37 @@ __device__ __forceinline__ void stage_acc_cols(uint32_t taddr, uint8_t* dst, flo
   }
 }
 
+// Full accumulator row (DH fp32 columns) -> un-rotate the first rc chunks in fp32 registers -> bf16 row at dst
+template <int DH, int RC>
+__device__ __forceinline__ void stage_acc_unrot(uint32_t taddr, uint8_t* dst, int rc, const RotTab<RC>& T) {
+#pragma unroll
+  for (int c0 = 0; c0 < DH; c0 += 32) {
+    float o[32];
+    tc::tmem_ld32(taddr + c0, o);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ch = c0 / 8 + q;
+      uint4 pk;
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float g0 = o[q * 8 + 2 * i], g1 = o[q * 8 + 2 * i + 1];
+        if (ch < RC) {
+          if (ch < rc) {
+            const float2 c = __half22float2(T.c[(ch < RC ? ch : 0) * 4 + i]), s = __half22float2(T.s[(ch < RC ? ch : 0) * 4 + i]);
+            const float y0 = g0 * c.x + g1 * s.y, y1 = g1 * c.y - g0 * s.x;
+            g0 = y0;
+            g1 = y1;
+          }
+        }
+        ph[i] = __floats2bfloat162_rn(g0, g1);
+      }
+      *reinterpret_cast<uint4*>(dst + ch * 16) = pk;
+    }
+  }
+}
+
 // additive key bias in the exp2 domain: padding mask (meant/xPosAttention.py:54-56) and keys past Sk
 __device__ __forceinline__ float key_bias2(float mval, int k, int Sk) {
   return k < Sk ? (1.0f - mval) * -1e9f * LOG2E : -CUDART_INF_F;
@@ -165,7 +233,7 @@ struct FwdL {
   static constexpr uint32_t AUX = NST * STAGE;                 // [NST][128] fp32 additive key bias (exp2 domain)
   static constexpr uint32_t RED = AUX + NST * 512;             // [2][2][128] fp32 row max / row sum exchange
   static constexpr uint32_t BARS = RED + 2048;
-  static constexpr uint32_t TOTAL = BARS + 128;
+  static constexpr uint32_t TOTAL = BARS + 256;
   static_assert(G::PBUF <= 2 * G::OPER && 128 * G::PITCH <= 2 * G::OPER, "P / staging must fit in Q | K");
 };
 
@@ -179,14 +247,16 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
   constexpr int HALF = DH / 2;                                 // accumulator columns per compute half
   // TMEM: one 128-column buffer per stage: S, then (once P is in shared memory) O over its first DH columns
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
-  uint64_t *s_full = bars, *aux_ready = bars + NST, *o_staged = bars + 2 * NST, *o_full = bars + 3 * NST;
+  uint64_t *landed = bars, *s_full = bars + NST, *o_full = bars + 2 * NST, *o_staged = bars + 3 * NST,
+           *aux_ready = bars + 4 * NST;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < NST; ++i) {
-      tc::mbar_init(&s_full[i], 1);
+      tc::mbar_init(&landed[i], NL);
       tc::mbar_init(&aux_ready[i], NL);
-      tc::mbar_init(&o_staged[i], NC);
+      tc::mbar_init(&s_full[i], 1);
       tc::mbar_init(&o_full[i], 1);
+      tc::mbar_init(&o_staged[i], NC);
     }
     tc::fence_mbar_init();
   }
@@ -202,65 +272,76 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
 
   if (tid >= NC) {
     // ------------------------------------------------------------------ loader group
-    tc::reg_inc<216>();   // 96 table registers live here; the compute warps give theirs up (no local-memory spills)
     const int t = tid - NC;
-    RotTab<RC> tq, tk;
-    int cur_h = -1;
-    if (rc && !a.pos_is_head) {
-      load_tab<RC>(tq, a.qcos, a.qsin, min(t, a.Sq - 1), a.rot_dim);
-      load_tab<RC>(tk, a.kcos, a.ksin, min(t, a.Sk - 1), a.rot_dim);
-    }
-    // cp.async the three tiles of item j; returns this thread's padding-mask value (consumed later by post_aux)
-    auto issue = [&](int j) -> float {
+    ChunkMap<DH> cm;
+    cm.init(t);
+    Prof pf;
+    pf.init(blockIdx.x == 0 && t == 0, 16);
+    for (int j = 0; j < n_my; ++j) {
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
+      pf.tick(0);
+      if (j >= NST) {   // the stage still holds item j - NST: drain its staged output first
+        const int pitem = item - NST * (int)gridDim.x, pn = pitem / a.H, ph = pitem - pn * a.H;
+        tc::mbar_wait(&o_staged[st], ((j - NST) / NST) & 1);
+        pf.tick(1);
+        drain_rows<DH>(cm, smem + st * L::STAGE, a.o, pn, a.n2_count, ph, a.Sq);
+        pf.tick(2);
+        tc::bar_sync(BAR_L, NL);    // every staged row has been read before the stage is refilled
+        pf.tick(3);
+      }
       float mval = 1.f;
       if (a.key_mask && t < a.Sk) mval = __ldg(a.key_mask + (int64_t)n * a.Sk + t);
       const uint32_t sb = s0 + st * L::STAGE;
-      issue_tile<DH>(sb, a.q, n, a.n2_count, h, a.Sq, t);
-      issue_tile<DH>(sb + G::OPER, a.k, n, a.n2_count, h, a.Sk, t);
-      issue_tile<DH>(sb + 2 * G::OPER, a.v, n, a.n2_count, h, a.Sk, t);
-      tc::cp_async_commit();
-      return mval;
-    };
-    auto post_aux = [&](int j, float mval) {
-      const int st = j % NST;
+      issue_tile<DH>(cm, sb, a.q, n, a.n2_count, h, a.Sq);
+      issue_tile<DH>(cm, sb + G::OPER, a.k, n, a.n2_count, h, a.Sk);
+      issue_tile<DH>(cm, sb + 2 * G::OPER, a.v, n, a.n2_count, h, a.Sk);
+      tc::cp_async_arrive(&landed[st]);                           // fires when this thread's copies have landed
+      pf.tick(4);
       reinterpret_cast<float*>(smem + L::AUX + st * 512)[t] = key_bias2(mval, t, a.Sk);
       tc::mbar_arrive(&aux_ready[st]);
-    };
-    auto copy_out = [&](int j) {
+      pf.tick(5);
+    }
+    for (int j = max(0, n_my - NST); j < n_my; ++j) {
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
       tc::mbar_wait(&o_staged[st], (j / NST) & 1);
-      drain_rows<DH>(smem + st * L::STAGE, a.o, n, a.n2_count, h, a.Sq, t);
-      tc::bar_sync(BAR_L, NL);    // every staged row has been read before the stage is refilled
-    };
-    float mnext = issue(0);
-    post_aux(0, mnext);
-    for (int j = 0; j < n_my; ++j) {
+      drain_rows<DH>(cm, smem + st * L::STAGE, a.o, n, a.n2_count, h, a.Sq);
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;                    // TMEM lane quarter / column half
+    const int t = rg * 32 + lane;                                 // query row (and the Q or K row this thread rotates)
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    float* red_max = reinterpret_cast<float*>(smem + L::RED);     // [2][128]
+    float* red_sum = red_max + 256;                               // [2][128]
+    int nblk = (a.Sk + 31) >> 5;                                  // 32-key blocks with any unmasked key for this warp's rows
+    if (a.causal) nblk = min(nblk, rg + 1);
+    RotTab<RC> tab;                                               // half 0: q tables, half 1: k tables
+    const float* tcs = half ? a.kcos : a.qcos;
+    const float* tsn = half ? a.ksin : a.qsin;
+    int cur_h = -1;
+    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
+    // rotate item j's Q / K rows in place, then start its score MMA
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
+    auto prepare = [&](int j) {
       const int st = j % NST;
-      const bool more = j + 1 < n_my;
-      if (more) {
-        if (j + 1 >= NST) copy_out(j + 1 - NST);
-        mnext = issue(j + 1);
-        tc::cp_async_wait<1>();
-      } else {
-        tc::cp_async_wait<0>();
-      }
-      tc::bar_sync(BAR_L, NL);      // item j's tiles have landed for every loader thread
+      pf.tick(8);
+      tc::mbar_wait(&landed[st], (j / NST) & 1);
+      pf.tick(9);
       if (rc) {
         if (a.pos_is_head) {
-          const int item = blockIdx.x + j * gridDim.x, h = item % a.H;
-          if (h != cur_h) {
-            load_tab<RC>(tq, a.qcos, a.qsin, h, a.rot_dim);
-            load_tab<RC>(tk, a.kcos, a.ksin, h, a.rot_dim);
-            cur_h = h;
-          }
+          const int h = (blockIdx.x + j * gridDim.x) % a.H;
+          if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + st * L::STAGE + t * 16, CS, rc, tq);
-        rot_row<RC, false>(smem + st * L::STAGE + G::OPER + t * 16, CS, rc, tk);
+        rot_row<RC, false>(smem + st * L::STAGE + half * G::OPER + t * 16, CS, rc, tab);
       }
       tc::fence_async_smem();
-      tc::bar_sync(BAR_L, NL);
-      if (t == 0) {
+      tc::fence_before_sync();
+      pf.tick(10);
+      tc::bar_sync(BAR_C, NC);
+      pf.tick(11);
+      if (tid == 0) {
         tc::fence_after_sync();
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
         const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
@@ -268,29 +349,19 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
         for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
         tc::mma_commit(&s_full[st]);
       }
-      if (more) post_aux(j + 1, mnext);
-    }
-    for (int j = max(0, n_my - NST); j < n_my; ++j) copy_out(j);
-  } else {
-    // ------------------------------------------------------------------ compute group
-    tc::reg_dec<144>();
-    const int rg = warp & 3, half = warp >> 2;                    // TMEM lane quarter / column half
-    const int t = rg * 32 + lane;                                 // query row
-    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
-    const float scale2 = a.scale * LOG2E;
-    float* red_max = reinterpret_cast<float*>(smem + L::RED);     // [2][128]
-    float* red_sum = red_max + 256;                               // [2][128]
-    int nblk = (a.Sk + 31) >> 5;                                  // 32-key blocks with any unmasked key for this warp's rows
-    if (a.causal) nblk = min(nblk, rg + 1);
+    };
+    if (n_my > 0) prepare(0);
     for (int j = 0; j < n_my; ++j) {
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
       const uint32_t par = (j / NST) & 1;
+      pf.tick(0);
       tc::mbar_wait(&aux_ready[st], par);
       tc::mbar_wait(&s_full[st], par);
       tc::fence_after_sync();
+      pf.tick(1);
       const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + st * 512);
       const uint32_t ts = lane_base + st * 128;
-      float x[64];
+      // two passes over the scores in TMEM (re-reading them is cheaper than 64 live registers per thread)
       float m = -CUDART_INF_F;
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
@@ -299,39 +370,49 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
           float sv[32];
           tc::tmem_ld32(ts + blk * 32, sv);
           tc::tmem_ld_wait();
-          const bool diag = a.causal && blk == rg;
+          const int lim = (a.causal && blk == rg) ? lane : 31;      // diagonal block: keys after the query are masked
 #pragma unroll
           for (int e = 0; e < 32; e += 4) {
             const float4 b = b4[(blk * 32 + e) >> 2];
             const float bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-              float v = fmaf(sv[e + u], scale2, bb[u]);
-              if (diag && e + u > lane) v = -CUDART_INF_F;
-              x[i * 32 + e + u] = v;
-              m = fmaxf(m, v);
+              const float v = fmaf(sv[e + u], scale2, bb[u]);
+              m = fmaxf(m, e + u > lim ? -CUDART_INF_F : v);
             }
           }
         }
       }
       red_max[half * 128 + t] = m;
+      pf.tick(2);
       tc::bar_sync(BAR_C, NC);
+      pf.tick(3);
       m = fmaxf(m, red_max[(half ^ 1) * 128 + t]);
       const float m_use = m == -CUDART_INF_F ? 0.f : m;
-      float l = 0.f;
+      float l0 = 0.f, l1 = 0.f;
       uint8_t* pbuf = smem + st * L::STAGE;                         // P over the consumed Q | K
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
         if (blk < nblk) {
+          float sv[32];
+          tc::tmem_ld32(ts + blk * 32, sv);
+          tc::tmem_ld_wait();
+          const int lim = (a.causal && blk == rg) ? lane : 31;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
+            const float4 ba = b4[(blk * 32 + q * 8) >> 2], bc = b4[((blk * 32 + q * 8) >> 2) + 1];
+            const float bb[8] = {ba.x, ba.y, ba.z, ba.w, bc.x, bc.y, bc.z, bc.w};
             uint4 pk;
             __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-              const float p0 = tc::ex2(x[i * 32 + q * 8 + 2 * u] - m_use), p1 = tc::ex2(x[i * 32 + q * 8 + 2 * u + 1] - m_use);
-              l += p0 + p1;
+              const int e = q * 8 + 2 * u;
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u]) - m_use), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1]) - m_use);
+              if (e > lim) p0 = 0.f;
+              if (e + 1 > lim) p1 = 0.f;
+              l0 += p0;
+              l1 += p1;
               ph[u] = __floats2bfloat162_rn(p0, p1);
             }
             *reinterpret_cast<uint4*>(pbuf + (blk * 4 + q) * CS + t * 16) = pk;
@@ -341,10 +422,13 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
           for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(pbuf + (blk * 4 + q) * CS + t * 16) = make_uint4(0u, 0u, 0u, 0u);
         }
       }
+      float l = l0 + l1;
       red_sum[half * 128 + t] = l;
       tc::fence_async_smem();
       tc::fence_before_sync();
+      pf.tick(4);
       tc::bar_sync(BAR_C, NC);
+      pf.tick(5);
       if (tid == 0) {
         tc::fence_after_sync();
         constexpr uint32_t idesc = tc::make_idesc(128, DH, 0, 1);
@@ -353,12 +437,16 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
         tc::mma_commit(&o_full[st]);
       }
       l += red_sum[(half ^ 1) * 128 + t];
+      if (j + 1 < n_my) prepare(j + 1);                             // next item's rotation + score MMA hide the PV latency
+      pf.tick(12);
       tc::mbar_wait(&o_full[st], par);
       tc::fence_after_sync();
+      pf.tick(6);
       stage_acc_cols<HALF>(ts + half * HALF, smem + st * L::STAGE + t * G::PITCH + half * HALF * 2, l > 0.f ? 1.0f / l : 0.f);
       if (half == 0 && t < a.Sq && a.lse) a.lse[((int64_t)n * a.H + h) * a.Sq + t] = m_use * LN2 + logf(l);
       tc::fence_before_sync();
       tc::mbar_arrive(&o_staged[st]);
+      pf.tick(7);
     }
   }
   tc::fence_before_sync();
@@ -371,7 +459,8 @@ template <int DH>
 struct BwdL {
   using G = Geo<DH>;
   static constexpr uint32_t Q = 0, K = G::OPER, V = 2 * G::OPER, DO = 3 * G::OPER, P = 4 * G::OPER, DS = P + G::PBUF;
-  static constexpr uint32_t AUX = DS + G::PBUF;                // bias2[128] | lse*log2e[128] | delta exchange [2][128]
+  static constexpr uint32_t STG_Z = DS + G::PBUF;              // dK staging (dQ stages over P, dV over dS)
+  static constexpr uint32_t AUX = STG_Z + 128 * G::PITCH;      // bias2[128] | lse*log2e[128] | delta exchange [2][128]
   static constexpr uint32_t BARS = AUX + 2048;
   static constexpr uint32_t TOTAL = BARS + 128;
   static_assert(128 * G::PITCH <= G::PBUF, "gradient staging must fit in the P / dS buffers");
@@ -386,17 +475,17 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
   constexpr int HALF = DH / 2;
   constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 352, T_DQ = 0;   // dQ reuses the consumed S columns
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
-  uint64_t *sdp_full = bars, *grads_full = bars + 1, *aux_ready = bars + 2, *staged_x = bars + 3, *staged_y = bars + 4,
-           *x_free = bars + 5, *y_free = bars + 6;
+  uint64_t *landed_qk = bars, *landed_dv = bars + 1, *sdp_full = bars + 2, *grads_full = bars + 3, *staged = bars + 4,
+           *stg_free = bars + 5, *aux_ready = bars + 6;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
+    tc::mbar_init(landed_qk, NL);
+    tc::mbar_init(landed_dv, NL);
+    tc::mbar_init(aux_ready, NL);
     tc::mbar_init(sdp_full, 1);
     tc::mbar_init(grads_full, 1);
-    tc::mbar_init(aux_ready, NL);
-    tc::mbar_init(staged_x, NC);
-    tc::mbar_init(staged_y, NC);
-    tc::mbar_init(x_free, NL);
-    tc::mbar_init(y_free, NL);
+    tc::mbar_init(staged, NC);
+    tc::mbar_init(stg_free, NL);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
@@ -408,84 +497,55 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
   const int rc = a.qcos ? a.rot_dim / 8 : 0;
   const uint32_t s0 = tc::smem_u32(smem);
   const uint32_t sq = s0 + L::Q, sk = s0 + L::K, sv = s0 + L::V, sdo = s0 + L::DO, sp = s0 + L::P, sds = s0 + L::DS;
-  uint8_t* stg_x = smem + L::P;     // gradient staging areas (free once the gradient MMAs are done)
-  uint8_t* stg_y = smem + L::DS;
+  uint8_t* stg_x = smem + L::P;       // dQ staging (free once the gradient MMAs are done)
+  uint8_t* stg_y = smem + L::DS;      // dV staging
+  uint8_t* stg_z = smem + L::STG_Z;   // dK staging
   float* aux_bias = reinterpret_cast<float*>(smem + L::AUX);
   float* aux_lse2 = aux_bias + 128;
   float* red_delta = aux_bias + 256;                                // [2][128]
 
   if (tid >= NC) {
     // ------------------------------------------------------------------ loader group
-    tc::reg_inc<216>();   // 96 table registers live here; the compute warps give theirs up (no local-memory spills)
     const int t = tid - NC;
-    RotTab<RC> tq, tk;
-    int cur_h = -1;
-    if (rc && !a.pos_is_head) {
-      load_tab<RC>(tq, a.qcos, a.qsin, min(t, a.Sq - 1), a.rot_dim);
-      load_tab<RC>(tk, a.kcos, a.ksin, min(t, a.Sk - 1), a.rot_dim);
-    }
-    auto tabs_for = [&](int h) {
-      if (rc && a.pos_is_head && h != cur_h) {
-        load_tab<RC>(tq, a.qcos, a.qsin, h, a.rot_dim);
-        load_tab<RC>(tk, a.kcos, a.ksin, h, a.rot_dim);
-        cur_h = h;
-      }
-    };
-    uint32_t xs = 0, ys = 0;
-    // drain the three gradients of item j as the compute group stages them: dQ (X), dV (Y), dK (X)
-    auto service = [&](int j) {
+    ChunkMap<DH> cm;
+    cm.init(t);
+    Prof pf;
+    pf.init(blockIdx.x == 0 && t == 0, 16);
+    auto drain = [&](int j) {   // the three gradients of item j, staged by the compute group
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H;
-      tabs_for(h);
-      tc::mbar_wait(staged_x, xs & 1); ++xs;
-      if (rc) { rot_row<RC, true>(stg_x + t * G::PITCH, 16, rc, tq); tc::bar_sync(BAR_L, NL); }
-      drain_rows<DH>(stg_x, a.dq, n, a.n2_count, h, a.Sq, t);
-      tc::mbar_arrive(x_free);
-      tc::mbar_wait(staged_y, ys & 1); ++ys;
-      drain_rows<DH>(stg_y, a.dv, n, a.n2_count, h, a.Sk, t);
-      tc::mbar_arrive(y_free);
-      tc::mbar_wait(staged_x, xs & 1); ++xs;
-      if (rc) { rot_row<RC, true>(stg_x + t * G::PITCH, 16, rc, tk); tc::bar_sync(BAR_L, NL); }
-      drain_rows<DH>(stg_x, a.dk, n, a.n2_count, h, a.Sk, t);
-      tc::mbar_arrive(x_free);
+      pf.tick(4);
+      tc::mbar_wait(staged, j & 1);
+      pf.tick(5);
+      drain_rows<DH>(cm, stg_x, a.dq, n, a.n2_count, h, a.Sq);
+      drain_rows<DH>(cm, stg_y, a.dv, n, a.n2_count, h, a.Sk);
+      drain_rows<DH>(cm, stg_z, a.dk, n, a.n2_count, h, a.Sk);
+      tc::mbar_arrive(stg_free);
+      pf.tick(6);
     };
     for (int j = 0; j < n_my; ++j) {
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H;
+      pf.tick(0);
       if (j > 0) tc::mbar_wait(grads_full, (j - 1) & 1);           // operand tiles of item j-1 are consumed
+      pf.tick(1);
       float mval = 1.f, lse = 0.f;
       if (a.key_mask && t < a.Sk) mval = __ldg(a.key_mask + (int64_t)n * a.Sk + t);
       if (t < a.Sq) lse = __ldg(a.lse + ((int64_t)n * a.H + h) * a.Sq + t);
-      issue_tile<DH>(sq, a.q, n, a.n2_count, h, a.Sq, t);
-      issue_tile<DH>(sk, a.k, n, a.n2_count, h, a.Sk, t);
-      issue_tile<DH>(sv, a.v, n, a.n2_count, h, a.Sk, t);
-      issue_tile<DH>(sdo, a.o, n, a.n2_count, h, a.Sq, t);
-      tc::cp_async_commit();
-      if (j > 0) service(j - 1);
+      issue_tile<DH>(cm, sq, a.q, n, a.n2_count, h, a.Sq);
+      issue_tile<DH>(cm, sk, a.k, n, a.n2_count, h, a.Sk);
+      tc::cp_async_arrive(landed_qk);
+      issue_tile<DH>(cm, sdo, a.o, n, a.n2_count, h, a.Sq);
+      issue_tile<DH>(cm, sv, a.v, n, a.n2_count, h, a.Sk);
+      tc::cp_async_arrive(landed_dv);
+      pf.tick(2);
       aux_bias[t] = key_bias2(mval, t, a.Sk);
       aux_lse2[t] = lse * LOG2E;
       tc::mbar_arrive(aux_ready);
-      tc::cp_async_wait<0>();
-      tc::bar_sync(BAR_L, NL);
-      if (rc) {
-        tabs_for(h);
-        rot_row<RC, false>(smem + L::Q + t * 16, CS, rc, tq);
-        rot_row<RC, false>(smem + L::K + t * 16, CS, rc, tk);
-      }
-      tc::fence_async_smem();
-      tc::bar_sync(BAR_L, NL);
-      if (t == 0) {
-        tc::fence_after_sync();
-        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
-#pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
-#pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_kmajor(sdo, ks), desc_kmajor(sv, ks), idesc, ks > 0);
-        tc::mma_commit(sdp_full);
-      }
+      pf.tick(3);
+      if (j > 0) drain(j - 1);
     }
-    if (n_my > 0) service(n_my - 1);
+    if (n_my > 0) drain(n_my - 1);
   } else {
     // ------------------------------------------------------------------ compute group
-    tc::reg_dec<144>();
     const int rg = warp & 3, half = warp >> 2;
     const int t = rg * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
@@ -494,11 +554,36 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
     const bool qrow = t < a.Sq;
     int nblk = (a.Sk + 31) >> 5;
     if (a.causal) nblk = min(nblk, rg + 1);
-    uint8_t* my_x = stg_x + t * G::PITCH + half * HALF * 2;
-    uint8_t* my_y = stg_y + t * G::PITCH + half * HALF * 2;
-    uint32_t xu = 0, yu = 0;
+    RotTab<RC> tab;                                               // half 0: q tables (Q, dQ), half 1: k tables (K, dK)
+    const float* tcs = half ? a.kcos : a.qcos;
+    const float* tsn = half ? a.ksin : a.qsin;
+    int cur_h = -1;
+    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
     for (int j = 0; j < n_my; ++j) {
+      // ---- rotate Q / K rows in place, start S = Q K^T and dP = dO V^T
+      tc::mbar_wait(landed_qk, j & 1);
+      if (rc) {
+        if (a.pos_is_head) {
+          const int h = (blockIdx.x + j * gridDim.x) % a.H;
+          if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
+        }
+        rot_row<RC, false>(smem + (half ? L::K : L::Q) + t * 16, CS, rc, tab);
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::bar_sync(BAR_C, NC);
+      if (tid == 0) {
+        tc::fence_after_sync();
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+        tc::mbar_wait(landed_dv, j & 1);                            // dO and V follow Q and K through the loader
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_kmajor(sdo, ks), desc_kmajor(sv, ks), idesc, ks > 0);
+        tc::mma_commit(sdp_full);
+      }
       tc::mbar_wait(aux_ready, j & 1);
+      if (j > 0) tc::mbar_wait(stg_free, (j - 1) & 1);              // P / dS double as the previous item's staging
       tc::mbar_wait(sdp_full, j & 1);
       tc::fence_after_sync();
       const float lse2 = aux_lse2[t];
@@ -508,25 +593,28 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
         if (blk < nblk) {
-          float sv32[32], dp[32];
-          tc::tmem_ld32(lane_base + T_S + blk * 32, sv32);
-          tc::tmem_ld32(lane_base + T_DP + blk * 32, dp);
-          tc::tmem_ld_wait();
-          const bool diag = a.causal && blk == rg;
+          const int lim = !qrow ? -1 : ((a.causal && blk == rg) ? lane : 31);
 #pragma unroll
-          for (int e = 0; e < 32; e += 4) {
-            const float4 b = b4[(blk * 32 + e) >> 2];
-            const float bb[4] = {b.x, b.y, b.z, b.w};
-            float p[4];
+          for (int hb = 0; hb < 2; ++hb) {                          // 16 columns at a time keeps the live set small
+            float sv16[16], dp[16];
+            tc::tmem_ld16(lane_base + T_S + blk * 32 + hb * 16, sv16);
+            tc::tmem_ld16(lane_base + T_DP + blk * 32 + hb * 16, dp);
+            tc::tmem_ld_wait();
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              p[u] = tc::ex2(fmaf(sv32[e + u], scale2, bb[u]) - lse2);
-              if (!qrow || (diag && e + u > lane)) p[u] = 0.f;
-              delta = fmaf(p[u], dp[e + u], delta);
+            for (int e = 0; e < 16; e += 4) {
+              const float4 b = b4[(blk * 32 + hb * 16 + e) >> 2];
+              const float bb[4] = {b.x, b.y, b.z, b.w};
+              float p[4];
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                p[u] = tc::ex2(fmaf(sv16[e + u], scale2, bb[u]) - lse2);
+                if (hb * 16 + e + u > lim) p[u] = 0.f;
+                delta = fmaf(p[u], dp[e + u], delta);
+              }
+              const __nv_bfloat162 p01 = __floats2bfloat162_rn(p[0], p[1]), p23 = __floats2bfloat162_rn(p[2], p[3]);
+              pk[i * 16 + hb * 8 + e / 2] = *reinterpret_cast<const uint32_t*>(&p01);
+              pk[i * 16 + hb * 8 + e / 2 + 1] = *reinterpret_cast<const uint32_t*>(&p23);
             }
-            const __nv_bfloat162 p01 = __floats2bfloat162_rn(p[0], p[1]), p23 = __floats2bfloat162_rn(p[2], p[3]);
-            pk[i * 16 + e / 2] = *reinterpret_cast<const uint32_t*>(&p01);
-            pk[i * 16 + e / 2 + 1] = *reinterpret_cast<const uint32_t*>(&p23);
           }
         } else {
 #pragma unroll
@@ -543,25 +631,28 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
-        uint32_t dsk[16];
-        if (blk < nblk) {
-          float dp[32];
-          tc::tmem_ld32(lane_base + T_DP + blk * 32, dp);
-          tc::tmem_ld_wait();
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const float2 p = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk[i * 16 + e]));
-            const __nv_bfloat162 d2 = __floats2bfloat162_rn(p.x * (dp[2 * e] - delta) * scale, p.y * (dp[2 * e + 1] - delta) * scale);
-            dsk[e] = *reinterpret_cast<const uint32_t*>(&d2);
+        for (int hb = 0; hb < 2; ++hb) {
+          uint32_t dsk[8];
+          if (blk < nblk) {
+            float dp[16];
+            tc::tmem_ld16(lane_base + T_DP + blk * 32 + hb * 16, dp);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float2 p = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk[i * 16 + hb * 8 + e]));
+              const __nv_bfloat162 d2 = __floats2bfloat162_rn(p.x * (dp[2 * e] - delta) * scale, p.y * (dp[2 * e + 1] - delta) * scale);
+              dsk[e] = *reinterpret_cast<const uint32_t*>(&d2);
+            }
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) dsk[e] = 0u;
           }
-        } else {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) dsk[e] = 0u;
+          for (int q = 0; q < 2; ++q)
+            *reinterpret_cast<uint4*>(smem + L::DS + (blk * 4 + hb * 2 + q) * CS + t * 16) =
+                make_uint4(dsk[q * 4], dsk[q * 4 + 1], dsk[q * 4 + 2], dsk[q * 4 + 3]);
         }
-#pragma unroll
-        for (int q = 0; q < 4; ++q)
-          *reinterpret_cast<uint4*>(smem + L::DS + (blk * 4 + q) * CS + t * 16) =
-              make_uint4(dsk[q * 4], dsk[q * 4 + 1], dsk[q * 4 + 2], dsk[q * 4 + 3]);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
@@ -578,22 +669,12 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       }
       tc::mbar_wait(grads_full, j & 1);
       tc::fence_after_sync();
-      // dQ first: it frees the S columns for the next item's score MMA
-      if (xu >= 1) tc::mbar_wait(x_free, (xu - 1) & 1);
-      ++xu;
-      stage_acc_cols<HALF>(lane_base + T_DQ + half * HALF, my_x, 1.0f);
+      // half 0 owns the dQ row, half 1 the dK row (each un-rotates with its own table); dV is split by columns
+      if (half == 0) stage_acc_unrot<DH, RC>(lane_base + T_DQ, stg_x + t * G::PITCH, rc, tab);
+      else           stage_acc_unrot<DH, RC>(lane_base + T_DK, stg_z + t * G::PITCH, rc, tab);
+      stage_acc_cols<HALF>(lane_base + T_DV + half * HALF, stg_y + t * G::PITCH + half * HALF * 2, 1.0f);
       tc::fence_before_sync();
-      tc::mbar_arrive(staged_x);
-      if (yu >= 1) tc::mbar_wait(y_free, (yu - 1) & 1);
-      ++yu;
-      stage_acc_cols<HALF>(lane_base + T_DV + half * HALF, my_y, 1.0f);
-      tc::fence_before_sync();
-      tc::mbar_arrive(staged_y);
-      tc::mbar_wait(x_free, (xu - 1) & 1);
-      ++xu;
-      stage_acc_cols<HALF>(lane_base + T_DK + half * HALF, my_x, 1.0f);
-      tc::fence_before_sync();
-      tc::mbar_arrive(staged_x);
+      tc::mbar_arrive(staged);
     }
   }
   tc::fence_before_sync();
@@ -625,6 +706,9 @@ int attn_tc2_supported(const AttnArgs& a, int backward) {
     if (al % 8 != 0) return 0;
   }
   if (backward && !a.lse) return 0;
+  const HeadView* vs[7] = {&a.q, &a.k, &a.v, &a.o, &a.dq, &a.dk, &a.dv};
+  for (int i = 0; i < (backward ? 7 : 4); ++i)
+    if (vs[i]->ss <= 0 || vs[i]->ss >= (1 << 23)) return 0;   // row offsets are computed in 32 bits
   return 1;
 }
 
@@ -638,6 +722,23 @@ static int launch2(Kern kern, size_t smem, const AttnArgs& a, cudaStream_t st) {
   MEANT_LAUNCH_CHECK();
   return 0;
 }
+
+}  // namespace meant
+extern "C" int meant_debug_prof(unsigned long long* out64, int reset) {
+#ifdef MEANT_PROF
+  cudaDeviceSynchronize();
+  if (out64 && cudaMemcpyFromSymbol(out64, meant::t2::g_prof, sizeof(unsigned long long) * 64) != cudaSuccess) return -1;
+  if (reset) {
+    unsigned long long z[64] = {0};
+    cudaMemcpyToSymbol(meant::t2::g_prof, z, sizeof(z));
+  }
+  return 1;
+#else
+  (void)out64; (void)reset;
+  return 0;
+#endif
+}
+namespace meant {
 
 int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st) {
   if (a.Dh == 96) return launch2(t2::attn2_fwd_kernel<96, 6>, t2::FwdL<96>::TOTAL, a, st);

@@ -35,6 +35,20 @@ def timeit(fn, iters, flush=None):
     return ms[len(ms) // 2], ms[0]
 
 
+def prof(tag, items, launches):
+    """Phase timers of CTA 0 (library built with MEANT_PROF=1): cycles per item per phase."""
+    import ctypes
+    fn = getattr(nv.lib(), "meant_debug_prof", None)
+    if fn is None:
+        return
+    buf = (ctypes.c_ulonglong * 64)()
+    fn.restype = ctypes.c_int
+    if fn(buf, 1) != 1:
+        return
+    per = launches * ((items + 147) // 148)
+    print(f"  prof {tag}: compute", [round(buf[i] / per) for i in range(16)], "loader", [round(buf[16 + i] / per) for i in range(16)])
+
+
 def attn(args):
     heads, dh, n, s = args.heads, args.dh, args.n, args.s
     dim = heads * dh
@@ -52,14 +66,17 @@ def attn(args):
 
     out = fwd()
     dout = torch.randn_like(out)
+    prof("warm", 1, 1)
     f_med, f_min = timeit(lambda: ops.attention(qkv.detach(), heads=heads, scale=scale, causal=args.causal, rot=rot,
                                                 key_mask=mask, impl=impl), args.iters, flush)
+    prof("fwd", n * heads, 3 + args.iters)
 
     def bwd():
         qkv.grad = None
         out.backward(dout, retain_graph=True)
 
     b_med, b_min = timeit(bwd, args.iters, flush)
+    prof("bwd", n * heads, 3 + args.iters)
     # algorithmic work: fwd reads q,k,v + writes o; bwd reads q,k,v,dO (+lse) + writes dq,dk,dv
     tile = n * s * dim * 2
     fl = (2.0 if args.causal else 4.0) * s * s * dh * heads * n
