@@ -69,23 +69,55 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
-// exact (erf) GELU, as nn.GELU() in the reference (meant/meant.py:64,107)
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// GELU of nn.GELU() (exact erf form, meant/meant.py:64,107) and its derivative.  erf comes from
+// Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, i.e. fp32 round-off level) on the SFU: one ex2 and one
+// rcp per element instead of erff's ~40 instructions, which made the GELU-fused norm kernels
+// issue-bound rather than HBM-bound.  exp(-x^2/2) is shared between the erf tail and the Gaussian pdf.
+__device__ __forceinline__ void gelu_parts(float x, float& cdf, float& pdf) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  float e, t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));   // exp(-x^2/2)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float poly = fmaf(t, 1.061405429f, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float tail = 0.5f * poly * t * e;              // (1 - erf(z)) / 2
+  cdf = x >= 0.f ? 1.0f - tail : tail;
+  pdf = 0.39894228040143268f * e;
+}
+__device__ __forceinline__ float gelu_f(float x) {
+  float cdf, pdf;
+  gelu_parts(x, cdf, pdf);
+  return x * cdf;
+}
 __device__ __forceinline__ float gelu_grad_f(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  float cdf, pdf;
+  gelu_parts(x, cdf, pdf);
+  return fmaf(x, pdf, cdf);
 }
 
-// Counter-based dropout mask: keep iff hash(seed, idx) >= p * 2^32.  Regenerated in backward.
-__device__ __forceinline__ uint32_t mix32(uint64_t seed, uint64_t idx) {
-  uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
-  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-  return (uint32_t)((z ^ (z >> 31)) >> 32);
+// Counter-based dropout mask, regenerated in backward: one 32-bit hash per PAIR of consecutive
+// elements, 16 bits each; element kept iff its 16 bits >= p * 65536.
+__device__ __forceinline__ uint32_t hash_pair(uint64_t seed, uint64_t pair_idx) {
+  uint32_t h = ((uint32_t)pair_idx ^ (uint32_t)seed) + ((uint32_t)(pair_idx >> 32) * 0x9E3779B1u + (uint32_t)(seed >> 32));
+  h ^= h >> 16;
+  h *= 0x85EBCA6Bu;
+  h ^= h >> 13;
+  h *= 0xC2B2AE35u;
+  h ^= h >> 16;
+  return h;
 }
-__device__ __forceinline__ float drop_keep(uint64_t seed, uint64_t idx, uint32_t thresh, float inv_keep) {
-  return mix32(seed, idx) >= thresh ? inv_keep : 0.0f;
+// multipliers (inv_keep or 0) for elements 2 * pair_idx and 2 * pair_idx + 1
+__device__ __forceinline__ void drop_pair(uint64_t seed, uint64_t pair_idx, uint32_t thr16, float inv_keep, float& k0, float& k1) {
+  const uint32_t h = hash_pair(seed, pair_idx);
+  k0 = (h & 0xffffu) >= thr16 ? inv_keep : 0.0f;
+  k1 = (h >> 16) >= thr16 ? inv_keep : 0.0f;
+}
+__device__ __forceinline__ float drop_keep(uint64_t seed, uint64_t idx, uint32_t thr16, float inv_keep) {
+  float k0, k1;
+  drop_pair(seed, idx >> 1, thr16, inv_keep, k0, k1);
+  return (idx & 1) ? k1 : k0;
 }
 
 }  // namespace meant

@@ -102,9 +102,15 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
       float o[V];
       const int col = (lane + 32 * c) * V;
 #pragma unroll
-      for (int i = 0; i < V; ++i) {
-        o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv);
-        if (a.drop_thresh) o[i] *= drop_keep(a.seed, (uint64_t)(base + col + i), a.drop_thresh, a.drop_inv_keep);
+      for (int i = 0; i < V; ++i) o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv);
+      if (a.drop_thresh) {
+#pragma unroll
+        for (int i = 0; i < V; i += 2) {
+          float k0, k1;
+          drop_pair(a.seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
+          o[i] *= k0;
+          o[i + 1] *= k1;
+        }
       }
       Vec16<T> ov;
       ov.pack(o);
@@ -173,8 +179,11 @@ struct NormBwdArgs {
 };
 
 // ------------------------------------------------------------------ backward, row in registers
-template <typename T, int CHUNKS, bool LN>
-__global__ void __launch_bounds__(128) norm_bwd_kernel(NormBwdArgs a) {
+// The row stays PACKED (bf16/fp32 vectors) between the two sweeps, so only the gain, the per-column
+// gradient accumulators and (GELU form) the activation / its derivative live in fp32 registers:
+// 3-4 CTAs of 4 warps per SM keep >= 36 KB of loads in flight.
+template <typename T, int CHUNKS, bool LN, bool GELU>
+__global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(NormBwdArgs a) {
   constexpr int V = Vec16<T>::N;
   __shared__ float red[4][32 * CHUNKS * V + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -200,25 +209,42 @@ __global__ void __launch_bounds__(128) norm_bwd_kernel(NormBwdArgs a) {
 #pragma unroll
       for (int c = 0; c < CHUNKS; ++c) ts[c].load(dsi + base + (lane + 32 * c) * V);
     }
-    float u[CHUNKS][V], s[CHUNKS][V], gy[CHUNKS][V];
     const float mean = LN ? a.stat0[row] : 0.f;
     const float rinv = LN ? a.stat1[row] : a.stat0[row];
+    float sk[GELU ? CHUNKS : 1][V], gk[GELU ? CHUNKS : 1][V];   // GELU form: activation and its derivative
     float t1 = 0.f, t2 = 0.f;
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
-      tu[c].unpack(u[c]);
-      tg[c].unpack(gy[c]);
+      float u[V], gy[V];
+      tu[c].unpack(u);
+      tg[c].unpack(gy);
+      if (a.drop_thresh) {
+#pragma unroll
+        for (int i = 0; i < V; i += 2) {
+          float k0, k1;
+          drop_pair(a.seed, (uint64_t)(base + (lane + 32 * c) * V + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
+          gy[i] *= k0;
+          gy[i + 1] *= k1;
+        }
+        tg[c].pack(gy);     // the second sweep re-reads the masked gradient (exact: 0 or a power-of-two scale for p = 0.5;
+                            // otherwise one extra rounding of dy * inv_keep to T, as if dropout's backward had run in T)
+      }
 #pragma unroll
       for (int i = 0; i < V; ++i) {
-        const int col = (lane + 32 * c) * V + i;
-        if (a.drop_thresh) gy[c][i] *= drop_keep(a.seed, (uint64_t)(base + col), a.drop_thresh, a.drop_inv_keep);
-        s[c][i] = a.pre_gelu ? gelu_f(u[c][i]) : u[c][i];
-        if (LN) s[c][i] = (s[c][i] - mean) * rinv;  // xhat
-        const float gd = g[c][i] * gy[c][i];
-        t1 += gd * s[c][i];
+        float sv = u[i];
+        if (GELU) {
+          float cdf, pdf;
+          gelu_parts(u[i], cdf, pdf);
+          sv = u[i] * cdf;
+          sk[c][i] = sv;
+          gk[c][i] = fmaf(u[i], pdf, cdf);
+        }
+        if (LN) sv = (sv - mean) * rinv;  // xhat
+        const float gd = g[c][i] * gy[i];
+        t1 = fmaf(gd, sv, t1);
         t2 += gd;
-        dg[c][i] += gy[c][i] * s[c][i] * (LN ? 1.f : rinv);
-        db[c][i] += gy[c][i];
+        dg[c][i] = fmaf(gy[i], sv * (LN ? 1.f : rinv), dg[c][i]);
+        db[c][i] += gy[i];
       }
     }
     t1 = warp_sum(t1);
@@ -232,13 +258,17 @@ __global__ void __launch_bounds__(128) norm_bwd_kernel(NormBwdArgs a) {
     }
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
-      float o[V], sv[V];
+      float u[V], gy[V], o[V], sv[V];
+      tu[c].unpack(u);
+      tg[c].unpack(gy);
       if (dsi) ts[c].unpack(sv);
 #pragma unroll
       for (int i = 0; i < V; ++i) {
-        const float gd = g[c][i] * gy[c][i];
-        float ds = LN ? rinv * (gd - m2 - s[c][i] * coef) : gd * rinv - s[c][i] * coef;
-        if (a.pre_gelu) ds *= gelu_grad_f(u[c][i]);
+        float s1 = GELU ? sk[c][i] : u[i];
+        if (LN) s1 = (s1 - mean) * rinv;
+        const float gd = g[c][i] * gy[i];
+        float ds = LN ? rinv * (gd - m2 - s1 * coef) : gd * rinv - s1 * coef;
+        if (GELU) ds *= gk[c][i];
         if (dsi) ds += sv[i];
         o[i] = ds;
       }
@@ -307,6 +337,12 @@ __global__ void __launch_bounds__(128) norm_bwd_generic_kernel(NormBwdArgs a) {
   }
 }
 
+static uint32_t drop_thr16(float p) {   // 16-bit keep threshold (common.cuh: drop_pair); 0 = dropout off
+  if (!(p > 0.f)) return 0u;
+  const uint32_t t = (uint32_t)(p * 65536.0f + 0.5f);
+  return t < 1u ? 1u : (t > 65535u ? 65535u : t);
+}
+
 static int grid_for(int64_t rows) {
   int64_t blocks = (rows + 3) / 4;
   const int64_t cap = 148 * 8;  // persistent-ish: <= 8 resident 128-thread CTAs per SM
@@ -335,14 +371,20 @@ template <typename T, bool LN>
 static int launch_bwd(const NormBwdArgs& a, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   int g = grid_for(a.rows);
-  if (g > 148 * 4) g = 148 * 4;  // fewer CTAs -> fewer dgain atomics
+  if (g > 148 * 4) g = 148 * (a.pre_gelu ? 3 : 4);  // one resident wave: fewer dgain atomics
   const bool vec_ok = (a.d % (32 * V) == 0) &&
                       ((reinterpret_cast<uintptr_t>(a.dy) | reinterpret_cast<uintptr_t>(a.src) |
                         reinterpret_cast<uintptr_t>(a.dx) | reinterpret_cast<uintptr_t>(a.dsum_in)) % 16 == 0);
   const int chunks = vec_ok ? a.d / (32 * V) : 0;
-  // CHUNKS * V <= 24 values per lane keeps the six per-lane arrays in registers
-  if (chunks == 3) norm_bwd_kernel<T, 3, LN><<<g, 128, 0, st>>>(a);
-  else if (chunks == 6 && V == 4) norm_bwd_kernel<T, (V == 4 ? 6 : 3), LN><<<g, 128, 0, st>>>(a);
+  // CHUNKS * V <= 24 values per lane keeps the per-lane arrays in registers
+  const bool gelu = a.pre_gelu != 0;
+  bool done = false;
+  if constexpr (!LN) {
+    if (chunks == 3 && gelu) { norm_bwd_kernel<T, 3, false, true><<<g, 128, 0, st>>>(a); done = true; }
+  }
+  if (done) {}
+  else if (chunks == 3 && !gelu) norm_bwd_kernel<T, 3, LN, false><<<g, 128, 0, st>>>(a);
+  else if (chunks == 6 && V == 4 && !gelu) norm_bwd_kernel<T, (V == 4 ? 6 : 3), LN, false><<<g, 128, 0, st>>>(a);
   else norm_bwd_generic_kernel<T, LN><<<g, 128, 0, st>>>(a);
   MEANT_LAUNCH_CHECK();
   return 0;
@@ -358,7 +400,7 @@ extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* ga
   if (!x || !gain || !y || !rinv || rows < 0 || d <= 0 || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
   if (rows == 0) return 0;
   NormArgs a{x, res, gain, nullptr, y, sum_out, rinv, nullptr, rows, d, eps, pre_gelu,
-             drop_p > 0.f ? (uint32_t)(drop_p * 4294967296.0) : 0u, 1.0f / (1.0f - drop_p), seed};
+             drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed};
   if (dtype == MEANT_DT_F32) return launch_fwd<float, false>(a, stream);
   if (dtype == MEANT_DT_BF16) return launch_fwd<__nv_bfloat16, false>(a, stream);
   return MEANT_EUNSUPPORTED;
@@ -370,7 +412,7 @@ extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* g
   if (!dy || !src || !gain || !rinv || !dx || !dgain || rows < 0 || d <= 0) return MEANT_EARG;
   if (rows == 0) return 0;
   NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, nullptr, rows, d, eps, pre_gelu,
-                drop_p > 0.f ? (uint32_t)(drop_p * 4294967296.0) : 0u, 1.0f / (1.0f - drop_p), seed};
+                drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed};
   if (dtype == MEANT_DT_F32) return launch_bwd<float, false>(a, stream);
   if (dtype == MEANT_DT_BF16) return launch_bwd<__nv_bfloat16, false>(a, stream);
   return MEANT_EUNSUPPORTED;
