@@ -145,11 +145,18 @@ def kernel_stats(timers):
     return out
 
 
+# ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch of the dominant kernels at THIS workload
+# (profiles/r1d_attn2_full_summary.txt; N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
+NCU_TRAFFIC = {"attn_fwd": 583.4e6, "attn_bwd": 1021.0e6}
+
+
 def rooflines(args, stats, steps):
-    """Roofline objects from the live CUDA-event timings of this run.  Algorithmic work per
-    launch: causal attention fwd 2*S^2*Dh*H FLOP per sequence (the masked
-    upper triangle is not counted), bwd 2x fwd; RMSNorm fwd 2*T*d*2 B (+1 tensor read for the
-    residual form, +1 write for the kept sum), bwd 3*T*d*2 B (+1 read for the residual gradient)."""
+    """Roofline objects from the live CUDA-event timings of this run.
+    Attention at S=128 is HBM-bound on B200 (65 FLOP/B against a ridge of ~209): algorithmic bytes per
+    (sequence, head) = q,k,v read + o written + LSE = 4*S*Dh*2 + 4*S forward, q,k,v,dO read + dq,dk,dv written
+    + LSE = 7*S*Dh*2 + 4*S backward.  Its tensor-core fraction (the north star's other figure; causal FLOPs
+    2*S^2*Dh*H per sequence, backward 2x) is listed in roofline_extra.  RMSNorm fwd 2*T*d*2 B (+1 tensor read
+    for the residual form, +1 write for the kept sum), bwd 3*T*d*2 B (+1 read for the residual gradient)."""
     hbm, tf_burst, tf_sus, src = peaks()
     nseq, tokens = args.batch * LAG, args.batch * LAG * SEQ
     dh = DIM // HEADS
@@ -157,12 +164,21 @@ def rooflines(args, stats, steps):
     main, extra = None, []
     for name, (ms, count) in sorted(stats.items()):
         if name.startswith("attn_fwd/S128x128") or name.startswith("attn_bwd/S128x128"):
-            fl = flops_fwd * (2.0 if "bwd" in name else 1.0)
-            ach = fl / (ms * 1e-3) / 1e12
-            r = {"kernel": name, "bound": "tensor", "achieved": round(ach, 2), "peak": tf_sus, "unit": "TFLOP/s",
-                 "frac": round(ach / tf_sus, 4), "traffic": None, "avg_ms": round(ms, 4),
-                 "launches_per_step": count / steps, "peak_source": src + ", sustained"}
-            if "fwd" in name:
+            bwd = "bwd" in name
+            byts = nseq * HEADS * ((7 if bwd else 4) * SEQ * dh * 2 + 4 * SEQ)
+            ach = byts / (ms * 1e-3) / 1e9
+            scale_n = nseq / 768.0
+            r = {"kernel": name, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
+                 "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["attn_bwd" if bwd else "attn_fwd"] * scale_n,
+                 "avg_ms": round(ms, 4), "launches_per_step": count / steps, "peak_source": src,
+                 "algorithmic_bytes_per_launch": byts}
+            fl = flops_fwd * (2.0 if bwd else 1.0)
+            tf = fl / (ms * 1e-3) / 1e12
+            extra.append({"kernel": name, "bound": "tensor", "achieved": round(tf, 2), "peak": tf_sus,
+                          "unit": "TFLOP/s", "frac": round(tf / tf_sus, 4), "traffic": None, "avg_ms": round(ms, 4),
+                          "peak_source": src + ", sustained",
+                          "note": "S=128 attention is HBM-bound (65 FLOP/B); tensor fraction listed for the north star"})
+            if not bwd:
                 main = r
             else:
                 extra.append(r)
