@@ -30,7 +30,7 @@ class attention(nn.Module):
         qkv = _packed_qkv(self, input)
         o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
                           rot=self.pos_emb.tables(n, input.device))
-        return self.dropout(self.multi_mad(o))
+        return self.dropout(ops.linear(o, self.multi_mad.weight, self.multi_mad.bias))
 
 
 class flash_attention(nn.Module):
@@ -52,4 +52,4 @@ class flash_attention(nn.Module):
         qkv = _packed_qkv(self, input)
         o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / self.dim, causal=bool(self.mask),
                           rot=self.pos_emb.tables(self.num_heads, input.device), pos_is_head=True)
-        return self.multi_mad(o)
+        return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)

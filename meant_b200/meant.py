@@ -20,20 +20,28 @@ def _drop_p(mod: nn.Module) -> float:
     return float(mod.p) if mod.training else 0.0
 
 
-def _fused_block(x, norm_a, lin_a, attn, norm_b, drop_b, lin_b, norm_c, lin_c, norm_d, drop_d, lin_d):
+def _lin(mod, x):
+    return ops.linear(x, mod.weight, mod.bias)
+
+
+def _fused_block(x, res_in, norm_a, lin_a, attn, norm_b, drop_b, lin_b, norm_c, lin_c, norm_d, drop_d, lin_d):
     """One MEANT encoder block (meant/meant.py:66-75 / :109-120) as 7 GEMMs + 5 fused kernels:
-         RMSNorm | Linear | attention (QKV GEMM, fused rotary flash kernel, out GEMM)
+         [residual add +] RMSNorm | Linear | attention (QKV GEMM, fused rotary flash kernel, out GEMM)
          RMSNorm(+dropout) | Linear | [residual add + RMSNorm] | Linear
-         [GELU + RMSNorm + dropout] | Linear | residual add
-    Returns (branch, residual): the caller adds them (or fuses the add into the next block)."""
-    h = ops.rms_norm(x, norm_a.scale, norm_a.eps)
-    h = attn(lin_a(h))
+         [GELU + RMSNorm + dropout] | Linear
+    The block input is x (+ res_in: the previous block's un-added (branch, residual) pair, so that its
+    final add runs inside this block's first norm kernel).  Returns (branch, residual) un-added."""
+    if res_in is None:
+        h, xin = ops.rms_norm(x, norm_a.scale, norm_a.eps), x
+    else:
+        h, xin = ops.rms_norm(x, norm_a.scale, norm_a.eps, residual=res_in)
+    h = attn(_lin(lin_a, h))
     h = ops.rms_norm(h, norm_b.scale, norm_b.eps, drop_p=drop_b)
-    h = lin_b(h)
-    g, r = ops.rms_norm(h, norm_c.scale, norm_c.eps, residual=x)       # r = h + x
-    g = lin_c(g)
+    h = _lin(lin_b, h)
+    g, r = ops.rms_norm(h, norm_c.scale, norm_c.eps, residual=xin)     # r = h + block input
+    g = _lin(lin_c, g)
     g = ops.rms_norm(g, norm_d.scale, norm_d.eps, pre_gelu=True, drop_p=drop_d)
-    return lin_d(g), r
+    return _lin(lin_d, g), r
 
 
 class visionEncoder(nn.Module):
@@ -48,9 +56,12 @@ class visionEncoder(nn.Module):
         self.encode2 = nn.ModuleList([RMSNorm(dim), nn.Linear(dim, dim), nn.GELU(), RMSNorm(dim),
                                       nn.Linear(dim, dim)])
 
-    def forward(self, input):
+    def forward_fused(self, x, res_in=None):
         e, e2 = self.encode, self.encode2
-        branch, resid = _fused_block(input, e[0], e[1], e[2], e[3], 0.0, e[4], e2[0], e2[1], e2[3], 0.0, e2[4])
+        return _fused_block(x, res_in, e[0], e[1], e[2], e[3], 0.0, e[4], e2[0], e2[1], e2[3], 0.0, e2[4])
+
+    def forward(self, input):
+        branch, resid = self.forward_fused(input)
         return branch + resid
 
 
@@ -66,13 +77,16 @@ class languageEncoder(nn.Module):
         self.encode2 = nn.ModuleList([RMSNorm(dim), nn.Linear(dim, dim), nn.GELU(), RMSNorm(dim), nn.Dropout(),
                                       nn.Linear(dim, dim)])
 
-    def forward(self, input, attention_mask=None):
+    def forward_fused(self, x, res_in=None, attention_mask=None):
         e, e2 = self.encode, self.encode2
         att = e[2]
         # the reference forwards the padding mask only to the eager class (meant/meant.py:112-115)
         call = (lambda t: att(t, attention_mask)) if type(att).__name__ == 'xPosAttention' else att
-        branch, resid = _fused_block(input, e[0], e[1], call, e[3], _drop_p(e[4]), e[5],
-                                     e2[0], e2[1], e2[3], _drop_p(e2[4]), e2[5])
+        return _fused_block(x, res_in, e[0], e[1], call, e[3], _drop_p(e[4]), e[5],
+                            e2[0], e2[1], e2[3], _drop_p(e2[4]), e2[5])
+
+    def forward(self, input, attention_mask=None):
+        branch, resid = self.forward_fused(input, None, attention_mask)
         return branch + resid
 
 
@@ -112,10 +126,17 @@ class _PatchRearrange(nn.Module):
 
 
 def _run_stack(encoders, x, *extra):
+    """Run a ModuleList of encoder blocks; the add that closes block i is fused into block i+1's first norm."""
     x = x.to(ops.compute_dtype(x))   # one cast of the residual stream (bf16 under autocast)
+    res = None
     for enc in encoders:
-        x = enc(x, *extra)
-    return x
+        if hasattr(enc, "forward_fused"):
+            x, res = enc.forward_fused(x, res, *extra)
+        else:
+            if res is not None:
+                x, res = x + res, None
+            x = enc(x, *extra)
+    return x if res is None else x + res
 
 
 class meant(nn.Module):

@@ -97,6 +97,14 @@ def rms_norm(x, gain, eps=1e-8, residual=None, pre_gelu=False, drop_p=0.0):
     return _RMSNormFn.apply(x, residual, gain, float(eps), bool(pre_gelu), float(drop_p), seed)
 
 
+# ------------------------------------------------------------------------------- Linear
+def linear(x, weight, bias=None):
+    """nn.Linear forward (meant/meant.py:102,106,107): a plain library GEMM (cuBLASLt through torch) until the
+    hand-written tcgen05 GEMM with fused epilogues lands.  A Python autograd wrapper with its
+    own bias-gradient kernel was measured slower end to end (host launch overhead), see DESIGN.md 5."""
+    return torch.nn.functional.linear(x, weight, bias)
+
+
 # ---------------------------------------------------------------------------- LayerNorm
 class _LayerNormFn(torch.autograd.Function):
     @staticmethod

@@ -17,7 +17,7 @@ def _packed_qkv(mod, x):
     is (q | v | k).  Parameters stay three separate nn.Linear modules (state_dict contract)."""
     w = torch.cat((mod.q.weight, mod.v.weight, mod.k.weight), dim=0)
     b = torch.cat((mod.q.bias, mod.v.bias, mod.k.bias), dim=0)
-    return F.linear(x, w, b)
+    return ops.linear(x, w, b)
 
 
 class xPosAttention(nn.Module):
@@ -41,7 +41,7 @@ class xPosAttention(nn.Module):
         qkv = _packed_qkv(self, input)
         o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
                           causal=bool(self.mask), rot=self.xPos.tables(s, input.device), key_mask=attention_mask)
-        return self.multi_mad(o)
+        return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)
 
 
 class xPosAttention_flash(nn.Module):
@@ -65,4 +65,4 @@ class xPosAttention_flash(nn.Module):
         qkv = _packed_qkv(self, input)
         o = ops.attention(qkv, heads=self.num_heads, scale=self.Dh ** -0.5, causal=bool(self.mask),
                           rot=self.xPos.tables(self.num_heads, input.device), pos_is_head=True)
-        return self.multi_mad(o)
+        return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)
