@@ -119,6 +119,11 @@ int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int tr
 int meant_tc_probe(const void* A, const void* B, float* D, int N, int K, int a_mn, int b_mn,
                    meant_stream_t stream);
 
+/* Same tile with SWIZZLED operand sub-tiles (64-column SWIZZLE_128B, or one 32-column SWIZZLE_64B), the
+ * layout the attention kernels fill with cp.async; an MN-major B wider than a sub-tile is issued per sub-tile. */
+int meant_tc_probe_sw(const void* A, const void* B, float* D, int N, int K, int a_mn, int b_mn,
+                      meant_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,7 @@ SIGNATURES = {
     "meant_geglu_bwd": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "meant_token_shift": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
     "meant_tc_probe": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
+    "meant_tc_probe_sw": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
 }
 
 _lib = None

@@ -28,6 +28,26 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
   return d;                // base_offset 0, lbo_mode 0, layout_type 0 (SWIZZLE_NONE)
 }
 
+// Swizzled operand tiles ("sub-tiles"): R rows of 128 B (64 bf16, SWIZZLE_128B, layout type 2) or of 64 B
+// (32 bf16, SWIZZLE_64B, layout type 4); the 16-byte chunk c of row r sits at
+//     r * 128 + ((c ^ (r & 7)) << 4)            (128 B rows, tile base 1024-byte aligned)
+//     r *  64 + ((c ^ ((r >> 1) & 3)) << 4)     ( 64 B rows)
+// which is Swizzle<3,4,3> / Swizzle<2,4,3> on the byte address.  The same tile is
+//   * a K-major operand  (rows = M/N, cols = K): SBO = 8 rows, K step of 16 elements = +32 B on the start address
+//   * an MN-major operand (rows = K, cols = M/N): SBO = 8 rows (K groups), LBO = distance to the next
+//     64- (32-) column sub-tile in the M/N direction, K step of 16 rows = +16 rows on the start address.
+__device__ __forceinline__ uint64_t make_desc_sw(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)(layout_type & 7) << 61;
+  return d;
+}
+__device__ __forceinline__ uint32_t sw128_off(int r, int c) { return (uint32_t)(r * 128 + ((c ^ (r & 7)) << 4)); }
+__device__ __forceinline__ uint32_t sw64_off(int r, int c) { return (uint32_t)(r * 64 + ((c ^ ((r >> 1) & 3)) << 4)); }
+
 // ---- instruction descriptor, kind::f16, bf16 x bf16 -> f32 -------------------------------
 __host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |

@@ -145,6 +145,29 @@ __global__ void k_cpasync_cm(const uint8_t* g, int ntiles, int spin_mode, int* s
   if (t == 0 && blockIdx.x == 0 && spin_mode) *(volatile int*)sink = 77;
 }
 
+// mode 1c: cp.async 16 B into UMMA-ready swizzled tiles: columns 0-63 -> [128 rows x 128 B] SWIZZLE_128B,
+// columns 64-95 -> [128 rows x 64 B] SWIZZLE_64B; lanes walk the 12 chunks of a row (row-contiguous global reads).
+__global__ void k_cpasync_sw(const uint8_t* g, int ntiles, int* sink) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int nthr = blockDim.x, t = threadIdx.x;
+  const int per = ROWS * 12 / nthr;
+  const uint32_t s0 = smem_u32(smem);
+  int j = 0;
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++j) {
+    const uint8_t* base = tile_base(g, tile, 0);
+    const uint32_t sb = s0 + (j & 3) * 24576;
+    for (int k = 0; k < per; ++k) {
+      const int idx = t + k * nthr, r = idx / 12, ch = idx % 12;
+      const uint32_t off = ch < 8 ? r * 128 + ((ch ^ (r & 7)) << 4) : 16384 + r * 64 + ((((ch - 8) ^ ((r >> 1) & 3))) << 4);
+      cpa16(sb + off, base + (size_t)r * PITCH + ch * 16);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 3;" ::: "memory");
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (smem[t] == 0x7f && smem[t + 1] == 0x11) *sink = 1;
+}
+
 // mode 2: cp.async.bulk, rows of 192 B (contiguous = 0) or whole contiguous tiles (contiguous = 1), 4-stage ring
 __global__ void k_bulk(const uint8_t* g, int ntiles, int contiguous, int* sink) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -237,6 +260,12 @@ int main() {
   run("cp.async16 core-matrix map, 128 thr", [&] { k_cpasync_cm<<<sms, 128, 3 * 12 * 2048 + 1024>>>(g, ntiles, 0, sink); }, ntiles);
   run("cp.async16 core-matrix map + 256 idle thr", [&] { k_cpasync_cm<<<sms, 384, 3 * 12 * 2048 + 1024>>>(g, ntiles, 0, sink); }, ntiles);
   run("cp.async16 core-matrix map + 256 spinning", [&] { cudaMemset(sink, 0, 4); k_cpasync_cm<<<sms, 384, 3 * 12 * 2048 + 1024>>>(g, ntiles, 1, sink); }, ntiles);
+  cudaFuncSetAttribute(k_cpasync_sw, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 24576 + 1024);
+  for (int nthr : {128, 256})  {
+    char nm[96];
+    snprintf(nm, 96, "cp.async16 %d thr, SW128|SW64 tiles", nthr);
+    run(nm, [&] { k_cpasync_sw<<<sms, nthr, 4 * 24576 + 1024>>>(g, ntiles, sink); }, ntiles);
+  }
   run("cp.async.bulk 192 B rows, 4 stages", [&] { k_bulk<<<sms, 128, 4 * TILE + 1024>>>(g, ntiles, 0, sink); }, ntiles);
   run("cp.async.bulk 24 KB contiguous, 4 stages", [&] { k_bulk<<<sms, 128, 4 * TILE + 1024>>>(g, ntiles, 1, sink); }, ntiles);
   run("cp.async.bulk 192 B rows, 2 CTA/SM", [&] { k_bulk<<<2 * sms, 128, 4 * TILE + 1024>>>(g, ntiles, 0, sink); }, ntiles);
