@@ -6,7 +6,8 @@
 // (consecutive CTAs take the heads of one sequence, so the packed `b s (h d)` rows they read
 // are contiguous in DRAM).  384 threads, two roles:
 //   loader warps 8-11  cp.async (LDGSTS, 16 B, zero-filled past S) Q/K/V[/dO] tiles straight from
-//                      the packed projections into the shared "chunk layout" (tc_utils.cuh), up to
+//                      the packed projections into SWIZZLE_128B / SWIZZLE_64B operand sub-tiles
+//                      (whole rows written contiguously, read by the tensor core as is), up to
 //                      three items ahead, completion signalled by cp.async.mbarrier.arrive; the
 //                      padding-mask bias / LSE row; later drain the staged results to global
 //                      memory with coalesced 16-byte stores.
@@ -29,7 +30,8 @@
 namespace meant {
 namespace t2 {
 
-constexpr uint32_t CS = 128 * 16 + 16;   // chunk stride of a 128-row chunk-layout buffer (+16: lanes walking chunks hit distinct banks)
+constexpr uint32_t SUB_A = 128 * 128;     // 128 rows x 64 columns, SWIZZLE_128B sub-tile
+constexpr uint32_t SUB_B = 128 * 64;      // 128 rows x 32 columns, SWIZZLE_64B sub-tile
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr int BAR_C = 1, BAR_L = 2;      // named barriers of the compute (256 threads) / loader (128) groups
@@ -56,13 +58,41 @@ struct Prof {
 template <int DH>
 struct Geo {
   static constexpr int CPR = DH / 8;                 // 16-byte chunks per row
-  static constexpr uint32_t OPER = CPR * CS;         // one 128 x DH operand tile
-  static constexpr uint32_t PBUF = 16 * CS;          // one 128 x 128 P / dS tile
+  static constexpr bool TAIL = DH > 64;              // columns [64, 96) live in a SWIZZLE_64B sub-tile
+  static constexpr uint32_t OPER = SUB_A + (TAIL ? SUB_B : 0u);   // one 128 x DH operand tile
+  static constexpr uint32_t PBUF = 2 * SUB_A;        // one 128 x 128 P / dS tile (two SWIZZLE_128B sub-tiles)
   static constexpr uint32_t PITCH = DH * 2 + 16;     // staging row pitch (bank-conflict free)
+  static_assert(DH == 64 || DH == 96, "operand tile = one 64-column sub-tile (+ one 32-column sub-tile)");
 };
 
-__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, int ks) { return tc::make_desc(base + ks * 2 * CS, CS, 128); }
-__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, int ks) { return tc::make_desc(base + ks * 256, 128, CS); }
+// Shared-memory operand layout (conventions verified by tc_probe.cu::tc_probe_sw_kernel): every tile is a
+// set of 128-row sub-tiles whose rows are contiguous (128 B: SWIZZLE_128B, 64 B: SWIZZLE_64B) with the
+// 16-byte chunks of a row XOR-permuted, so that a row-walking cp.async stream writes whole rows (6.6 TB/s
+// through LDGSTS, tools/ldbench.cu) and the tensor core reads the tile without a transposing copy.
+// byte offset of 16-byte chunk ch of row r in a 128 x DH operand tile
+__device__ __forceinline__ uint32_t oper_off(int r, int ch) {
+  return ch < 8 ? tc::sw128_off(r, ch) : SUB_A + tc::sw64_off(r, ch - 8);
+}
+// byte offset of 16-byte chunk c (8 columns) of row r in a 128 x 128 P / dS tile
+__device__ __forceinline__ uint32_t pbuf_off(int r, int c) { return (c >> 3) * SUB_A + tc::sw128_off(r, c & 7); }
+
+// K-major view (K = head dimension) of an operand tile, K-step ks of 16 columns
+__device__ __forceinline__ uint64_t desc_oper_k(uint32_t base, int ks) {
+  return ks < 4 ? tc::make_desc_sw(base + ks * 32, 16, 1024, 2) : tc::make_desc_sw(base + SUB_A + (ks - 4) * 32, 16, 512, 4);
+}
+// MN-major view (K = rows) of an operand tile, K-step ks of 16 rows: columns [0, 64) / [64, 96)
+__device__ __forceinline__ uint64_t desc_oper_mn_a(uint32_t base, int ks) { return tc::make_desc_sw(base + ks * 2048, SUB_A, 1024, 2); }
+__device__ __forceinline__ uint64_t desc_oper_mn_b(uint32_t base, int ks) { return tc::make_desc_sw(base + SUB_A + ks * 1024, SUB_B, 512, 4); }
+// P / dS tile: K-major (K = key columns) and MN-major (K = query rows; the two sub-tiles are LBO apart)
+__device__ __forceinline__ uint64_t desc_p_k(uint32_t base, int ks) { return tc::make_desc_sw(base + (ks >> 2) * SUB_A + (ks & 3) * 32, 16, 1024, 2); }
+__device__ __forceinline__ uint64_t desc_p_mn(uint32_t base, int ks) { return tc::make_desc_sw(base + ks * 2048, SUB_A, 1024, 2); }
+
+// D[128 x DH] (+)= A * B with B an MN-major operand tile: one MMA per sub-tile (N = 64, then N = 32)
+template <int DH>
+__device__ __forceinline__ void mma_oper_mn(uint32_t tmem_d, uint64_t adesc, uint32_t sb, int ks, int a_mn, bool acc) {
+  tc::mma_ss(tmem_d, adesc, desc_oper_mn_a(sb, ks), tc::make_idesc(128, 64, a_mn, 1), acc);
+  if (Geo<DH>::TAIL) tc::mma_ss(tmem_d + 64, adesc, desc_oper_mn_b(sb, ks), tc::make_idesc(128, 32, a_mn, 1), acc);
+}
 
 __device__ __forceinline__ const __nv_bfloat16* head_base(const HeadView& v, int n, int n2c, int h) {
   const int n1 = n / n2c, n2 = n - n1 * n2c;
@@ -70,27 +100,27 @@ __device__ __forceinline__ const __nv_bfloat16* head_base(const HeadView& v, int
 }
 
 // Loader thread t of 128 moves chunks idx = t + 128 k (k < CPR) of every 128 x DH tile: lanes walk the 16-byte
-// chunks of a row first, so a warp reads ~2.7 whole rows (full 64-byte segments, few 128-byte lines).  The
-// (row, chunk) split is the same for every tile and item, so it is computed once.  (tools/ldbench.cu: this
-// map moves 3.9 TB/s through LDGSTS; 8-lane groups filling one core matrix from 8 rows only 3.2 TB/s.)
+// chunks of a row first, so a warp reads ~2.7 whole rows (full 64-byte segments, few 128-byte lines) and
+// writes them to contiguous (swizzled) shared rows.  The (row, chunk, shared offset) split is the same for
+// every tile and item, so it is computed once.
 template <int DH>
 struct ChunkMap {
   static constexpr int CPR = DH / 8;
-  int rc[CPR];                                     // row | chunk << 8
+  int rc[CPR];                                     // row | chunk << 8 | shared offset << 16
   __device__ __forceinline__ void init(int t) {
 #pragma unroll
     for (int k = 0; k < CPR; ++k) {
       const int idx = t + k * 128, r = idx / CPR, ch = idx - r * CPR;
-      rc[k] = r | (ch << 8);
+      rc[k] = r | (ch << 8) | (int)(oper_off(r, ch) << 16);
     }
   }
   __device__ __forceinline__ int row(int k) const { return rc[k] & 0xff; }
-  __device__ __forceinline__ int gcol(int k) const { return (rc[k] >> 8) * 8; }                      // element column
-  __device__ __forceinline__ uint32_t soff(int k) const { return (rc[k] >> 8) * CS + (rc[k] & 0xff) * 16; }   // chunk layout
-  __device__ __forceinline__ uint32_t stg(int k) const { return (rc[k] & 0xff) * Geo<DH>::PITCH + (rc[k] >> 8) * 16; }
+  __device__ __forceinline__ int gcol(int k) const { return ((rc[k] >> 8) & 0xff) * 8; }             // element column
+  __device__ __forceinline__ uint32_t soff(int k) const { return (uint32_t)rc[k] >> 16; }            // swizzled operand tile
+  __device__ __forceinline__ uint32_t stg(int k) const { return (rc[k] & 0xff) * Geo<DH>::PITCH + ((rc[k] >> 8) & 0xff) * 16; }
 };
 
-// rows [0,128) of head (n, h) -> chunk layout at shared address sbase; rows >= S are zero filled.
+// rows [0,128) of head (n, h) -> swizzled operand tile at shared address sbase; rows >= S are zero filled.
 template <int DH>
 __device__ __forceinline__ void issue_tile(const ChunkMap<DH>& cm, uint32_t sbase, const HeadView& v, int n, int n2c, int h, int S) {
   const __nv_bfloat16* base = head_base(v, n, n2c, h);
@@ -137,13 +167,14 @@ __device__ __forceinline__ void load_tab(RotTab<RC>& T, const float* cs, const f
 }
 
 // Rotate (INV = false) or un-rotate (transpose rotation, INV = true) the first rc chunks of one
-// row in place; chunk ch of the row lives at row_ptr + ch * chunk_stride.
+// row r of an operand tile in place (RC <= 8: the rotated chunks all live in the SWIZZLE_128B sub-tile).
 template <int RC, bool INV>
-__device__ __forceinline__ void rot_row(uint8_t* row_ptr, uint32_t chunk_stride, int rc, const RotTab<RC>& T) {
+__device__ __forceinline__ void rot_row(uint8_t* tile, int r, int rc, const RotTab<RC>& T) {
+  static_assert(RC <= 8, "rotated chunks must stay in the first sub-tile");
 #pragma unroll
   for (int ch = 0; ch < RC; ++ch) {
     if (ch < rc) {
-      uint4* p = reinterpret_cast<uint4*>(row_ptr + ch * chunk_stride);
+      uint4* p = reinterpret_cast<uint4*>(tile + tc::sw128_off(r, ch));
       uint4 raw = *p;
       __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
 #pragma unroll
@@ -233,14 +264,15 @@ struct FwdL {
   static constexpr uint32_t AUX = NST * STAGE;                 // [NST][128] fp32 additive key bias (exp2 domain)
   static constexpr uint32_t RED = AUX + NST * 512;             // [2][2][128] fp32 row max / row sum exchange
   static constexpr uint32_t BARS = RED + 2048;
-  static constexpr uint32_t TOTAL = BARS + 256;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;          // + alignment slack
   static_assert(G::PBUF <= 2 * G::OPER && 128 * G::PITCH <= 2 * G::OPER, "P / staging must fit in Q | K");
 };
 
 template <int DH, int RC>
 __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_items) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
   using L = FwdL<DH>;
   using G = Geo<DH>;
   constexpr int NST = L::NST;
@@ -334,7 +366,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
           if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + st * L::STAGE + half * G::OPER + t * 16, CS, rc, tab);
+        rot_row<RC, false>(smem + st * L::STAGE + half * G::OPER, t, rc, tab);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
@@ -346,7 +378,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
         const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
 #pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
         tc::mma_commit(&s_full[st]);
       }
     };
@@ -415,11 +447,11 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
               l1 += p1;
               ph[u] = __floats2bfloat162_rn(p0, p1);
             }
-            *reinterpret_cast<uint4*>(pbuf + (blk * 4 + q) * CS + t * 16) = pk;
+            *reinterpret_cast<uint4*>(pbuf + pbuf_off(t, blk * 4 + q)) = pk;
           }
         } else if (blk * 32 < n_s) {
 #pragma unroll
-          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(pbuf + (blk * 4 + q) * CS + t * 16) = make_uint4(0u, 0u, 0u, 0u);
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(pbuf + pbuf_off(t, blk * 4 + q)) = make_uint4(0u, 0u, 0u, 0u);
         }
       }
       float l = l0 + l1;
@@ -431,9 +463,8 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       pf.tick(5);
       if (tid == 0) {
         tc::fence_after_sync();
-        constexpr uint32_t idesc = tc::make_idesc(128, DH, 0, 1);
         const uint32_t sp = s0 + st * L::STAGE, sv = sp + 2 * G::OPER;
-        for (int ks = 0; ks < n_s / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_kmajor(sp, ks), desc_mnmajor(sv, ks), idesc, ks > 0);
+        for (int ks = 0; ks < n_s / 16; ++ks) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
         tc::mma_commit(&o_full[st]);
       }
       l += red_sum[(half ^ 1) * 128 + t];
@@ -462,14 +493,15 @@ struct BwdL {
   static constexpr uint32_t STG_Z = DS + G::PBUF;              // dK staging (dQ stages over P, dV over dS)
   static constexpr uint32_t AUX = STG_Z + 128 * G::PITCH;      // bias2[128] | lse*log2e[128] | delta exchange [2][128]
   static constexpr uint32_t BARS = AUX + 2048;
-  static constexpr uint32_t TOTAL = BARS + 128;
+  static constexpr uint32_t TOTAL = BARS + 128 + 1024;          // + alignment slack
   static_assert(128 * G::PITCH <= G::PBUF, "gradient staging must fit in the P / dS buffers");
 };
 
 template <int DH, int RC>
 __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_items) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
   using L = BwdL<DH>;
   using G = Geo<DH>;
   constexpr int HALF = DH / 2;
@@ -567,7 +599,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
           if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + (half ? L::K : L::Q) + t * 16, CS, rc, tab);
+        rot_row<RC, false>(smem + (half ? L::K : L::Q), t, rc, tab);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
@@ -576,10 +608,10 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
         tc::fence_after_sync();
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
 #pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
         tc::mbar_wait(landed_dv, j & 1);                            // dO and V follow Q and K through the loader
 #pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_kmajor(sdo, ks), desc_kmajor(sv, ks), idesc, ks > 0);
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
         tc::mma_commit(sdp_full);
       }
       tc::mbar_wait(aux_ready, j & 1);
@@ -622,7 +654,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q)
-          *reinterpret_cast<uint4*>(smem + L::P + (blk * 4 + q) * CS + t * 16) =
+          *reinterpret_cast<uint4*>(smem + L::P + pbuf_off(t, blk * 4 + q)) =
               make_uint4(pk[i * 16 + q * 4], pk[i * 16 + q * 4 + 1], pk[i * 16 + q * 4 + 2], pk[i * 16 + q * 4 + 3]);
       }
       red_delta[half * 128 + t] = delta;
@@ -650,7 +682,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
           }
 #pragma unroll
           for (int q = 0; q < 2; ++q)
-            *reinterpret_cast<uint4*>(smem + L::DS + (blk * 4 + hb * 2 + q) * CS + t * 16) =
+            *reinterpret_cast<uint4*>(smem + L::DS + pbuf_off(t, blk * 4 + hb * 2 + q)) =
                 make_uint4(dsk[q * 4], dsk[q * 4 + 1], dsk[q * 4 + 2], dsk[q * 4 + 3]);
         }
       }
@@ -659,12 +691,10 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       tc::bar_sync(BAR_C, NC);
       if (tid == 0) {
         tc::fence_after_sync();
-        constexpr uint32_t id_t = tc::make_idesc(128, DH, 1, 1);     // A^T (MN-major) x B (MN-major)
-        constexpr uint32_t id_n = tc::make_idesc(128, DH, 0, 1);     // A (K-major)    x B (MN-major)
         const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
-        for (int ks = 0; ks < kq; ++ks) tc::mma_ss(tmem + T_DV, desc_mnmajor(sp, ks), desc_mnmajor(sdo, ks), id_t, ks > 0);   // dV = P^T dO
-        for (int ks = 0; ks < kq; ++ks) tc::mma_ss(tmem + T_DK, desc_mnmajor(sds, ks), desc_mnmajor(sq, ks), id_t, ks > 0);   // dK = dS^T Q
-        for (int ks = 0; ks < kk; ++ks) tc::mma_ss(tmem + T_DQ, desc_kmajor(sds, ks), desc_mnmajor(sk, ks), id_n, ks > 0);    // dQ = dS K
+        for (int ks = 0; ks < kq; ++ks) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
+        for (int ks = 0; ks < kq; ++ks) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
+        for (int ks = 0; ks < kk; ++ks) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);     // dQ = dS K
         tc::mma_commit(grads_full);
       }
       tc::mbar_wait(grads_full, j & 1);
