@@ -32,7 +32,7 @@ enum { MEANT_F32 = 0, MEANT_BF16 = 1 };
 enum { MEANT_IMPL_AUTO = 0, MEANT_IMPL_EXACT = 1, MEANT_IMPL_TCGEN05 = 2 };
 
 /* ---- library ------------------------------------------------------------------------- */
-int meant_version(void);                 /* ABI version, bumped on any signature change   */
+int meant_version(void);                 /* ABI version (2), bumped on any signature change */
 int64_t meant_launch_count(void);        /* kernels launched by this library so far       */
 void meant_reset_launch_count(void);
 
@@ -41,17 +41,19 @@ void meant_reset_launch_count(void);
  *   res/sum_out : s = x + res is normalised and also written to sum_out
  *                 (meant/meant.py:116,120 residual adds feeding encode2[0] / the next block)
  *   pre_gelu    : s = gelu(x), exact erf form (meant/meant.py:107 GELU -> RMSNorm)
- *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107)
+ *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107);
+ *                 seed_dev (optional, device memory) is added to seed when the kernel runs, so a
+ *                 captured CUDA graph draws a fresh mask on every replay
  * rinv[rows] receives 1/(rms+eps) for the backward pass.                                  */
 int meant_rmsnorm_fwd(const void* x, const void* res, const float* gain, void* y, void* sum_out, float* rinv,
-                      int64_t rows, int d, float eps, int pre_gelu, float drop_p, uint64_t seed, int dtype,
-                      meant_stream_t stream);
+                      int64_t rows, int d, float eps, int pre_gelu, float drop_p, uint64_t seed,
+                      const uint64_t* seed_dev, int dtype, meant_stream_t stream);
 /* src = the forward's normalised-input source: x (plain), x (pre_gelu: pre-activation) or
  * sum_out (residual form).  dsum_in (optional) is added to dx: the gradient that reaches the
  * same tensor through the residual path.  dgain[d] (fp32) is ACCUMULATED atomically.       */
 int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv, const void* dsum_in,
                       void* dx, float* dgain, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
-                      uint64_t seed, int dtype, meant_stream_t stream);
+                      uint64_t seed, const uint64_t* seed_dev, int dtype, meant_stream_t stream);
 
 /* ---- LayerNorm: nn.LayerNorm heads (meant/meant_tweet.py:143, meant/meant_vision.py:143) and
  *      TimeSformer PreNorm (src/meant/timesformer_pytorch.py:17-25) ------------------------ */
@@ -112,6 +114,11 @@ int meant_geglu_bwd(const void* dy, const void* x, void* dx, int64_t rows, int F
  *      transpose != 0 applies the adjoint (backward) ---------------------------------------- */
 int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int transpose, int dtype,
                       meant_stream_t stream);
+
+/* ---- bias gradient of nn.Linear (the q/k/v, multi_mad and MLP Linears of meant/xPosAttention.py:24-28,
+ *      meant/meant.py:61-66):  db[c] (fp32, overwritten) = sum_r dy[r*ld + c] ------------------------- */
+int meant_bias_grad(const void* dy, float* db, int64_t rows, int cols, int64_t ld, int dtype,
+                    meant_stream_t stream);
 
 /* ---- tcgen05 self-test: D[128,N] (fp32) = op(A) op(B)^T for one bf16 tile; a_mn / b_mn select
  *      MN-major operands (A given as [K,128], B as [K,N]) instead of K-major ([128,K], [N,K]).

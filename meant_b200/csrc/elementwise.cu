@@ -135,6 +135,59 @@ __global__ void __launch_bounds__(256) token_shift_kernel(const T* __restrict__ 
   }
 }
 
+
+// Bias gradient of a Linear layer: db[c] = sum over rows of dy[r, c] (what autograd's sum-to-size does for
+// the q/k/v, multi_mad and MLP biases: meant/xPosAttention.py:24-28, meant/meant.py:61-66).  A pure
+// streaming read: 32 x 8 threads, each keeps 8 independent 16-byte loads in flight over its row lane of
+// the CTA's row slab, partial sums meet in shared memory and one atomicAdd per column leaves the CTA.
+template <typename T>
+__global__ void __launch_bounds__(256) bias_grad_kernel(const T* __restrict__ dy, float* __restrict__ db, int64_t rows,
+                                                        int cols, int64_t ld, int rows_per_cta) {
+  constexpr int V = Vec16<T>::N;
+  __shared__ float red[8][32 * V + 1];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + tx) * V;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_cta;
+  const int64_t r1 = r0 + rows_per_cta < rows ? r0 + rows_per_cta : rows;
+  float acc[V];
+#pragma unroll
+  for (int i = 0; i < V; ++i) acc[i] = 0.f;
+  if (col < cols) {
+    const T* p = dy + col;
+    int64_t r = r0 + ty;
+    for (; r + 56 < r1; r += 64) {
+      Vec16<T> v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u].load(p + (r + 8 * u) * ld);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        float f[V];
+        v[u].unpack(f);
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] += f[i];
+      }
+    }
+    for (; r < r1; r += 8) {
+      Vec16<T> v;
+      v.load(p + r * ld);
+      float f[V];
+      v.unpack(f);
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] += f[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < V; ++i) red[ty][tx * V + i] = acc[i];
+  __syncthreads();
+  const int c = threadIdx.x;
+  if (c < 32 * V && blockIdx.x * 32 * V + c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += red[y][c];
+    atomicAdd(db + blockIdx.x * 32 * V + c, t);
+  }
+}
+
 }  // namespace meant
 
 using namespace meant;
@@ -195,6 +248,25 @@ extern "C" int meant_token_shift(const void* x, void* y, int B, int f, int n, in
   if (blocks > 148u * 16u) blocks = 148u * 16u;
   DISPATCH_T(dtype, (token_shift_kernel<T><<<blocks, 256, 0, st>>>((const T*)x, (T*)y, B, f, n, d,
                                                                     transpose ? -1 : 1)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_bias_grad(const void* dy, float* db, int64_t rows, int cols, int64_t ld, int dtype,
+                               cudaStream_t st) {
+  if ((!dy && rows != 0) || !db || rows < 0 || cols <= 0 || ld < cols) return MEANT_EARG;
+  const int v = dtype == MEANT_DT_F32 ? 4 : 8;
+  if (cols % v || ld % v || ((uintptr_t)dy & 15)) return MEANT_EUNSUPPORTED;
+  cudaError_t e = cudaMemsetAsync(db, 0, sizeof(float) * cols, st);
+  if (e != cudaSuccess) return (int)e;
+  if (rows == 0) return 0;
+  const unsigned gx = blocks_for(cols, 32 * v);
+  // ~4 CTAs per SM in flight, slabs of at least 64 rows
+  int64_t slabs = (148 * 4 + gx - 1) / gx;
+  if (slabs > (rows + 63) / 64) slabs = (rows + 63) / 64;
+  const int rows_per_cta = (int)(((rows + slabs - 1) / slabs + 7) / 8 * 8);
+  dim3 grid(gx, blocks_for(rows, rows_per_cta));
+  DISPATCH_T(dtype, (bias_grad_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, db, rows, cols, ld, rows_per_cta)));
   MEANT_LAUNCH_CHECK();
   return 0;
 }

@@ -25,11 +25,14 @@ struct NormArgs {
   uint32_t drop_thresh;  // 0 = no dropout
   float drop_inv_keep;
   uint64_t seed;
+  const unsigned long long* seed_dev;   // optional device-resident addend (CUDA-graph replays advance it)
 };
 
 // ------------------------------------------------------------------ forward, row in registers
 template <typename T, int CHUNKS, bool LN>
 __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
+  uint64_t seed = a.seed;
+  if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   constexpr int V = Vec16<T>::N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const T* __restrict__ x = static_cast<const T*>(a.x);
@@ -107,7 +110,7 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
 #pragma unroll
         for (int i = 0; i < V; i += 2) {
           float k0, k1;
-          drop_pair(a.seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
+          drop_pair(seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
           o[i] *= k0;
           o[i + 1] *= k1;
         }
@@ -122,6 +125,8 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
 // ------------------------------------------------------------------ forward, any d (two passes)
 template <typename T, bool LN>
 __global__ void __launch_bounds__(128) norm_fwd_generic_kernel(NormArgs a) {
+  uint64_t seed = a.seed;
+  if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const T* __restrict__ x = static_cast<const T*>(a.x);
   const T* __restrict__ res = static_cast<const T*>(a.res);
@@ -153,7 +158,7 @@ __global__ void __launch_bounds__(128) norm_fwd_generic_kernel(NormArgs a) {
       const float v = val(c);
       if (res && so) so[base + c] = from_f<T>(v);
       float o = LN ? (v - mean) * rinv * a.gain[c] + a.bias[c] : a.gain[c] * (v * rinv);
-      if (a.drop_thresh) o *= drop_keep(a.seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
+      if (a.drop_thresh) o *= drop_keep(seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
       y[base + c] = from_f<T>(o);
     }
   }
@@ -176,6 +181,7 @@ struct NormBwdArgs {
   uint32_t drop_thresh;
   float drop_inv_keep;
   uint64_t seed;
+  const unsigned long long* seed_dev;   // optional device-resident addend (CUDA-graph replays advance it)
 };
 
 // ------------------------------------------------------------------ backward, row in registers
@@ -184,6 +190,8 @@ struct NormBwdArgs {
 // 3-4 CTAs of 4 warps per SM keep >= 36 KB of loads in flight.
 template <typename T, int CHUNKS, bool LN, bool GELU>
 __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(NormBwdArgs a) {
+  uint64_t seed = a.seed;
+  if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   constexpr int V = Vec16<T>::N;
   __shared__ float red[4][32 * CHUNKS * V + 1];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -222,7 +230,7 @@ __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(Nor
 #pragma unroll
         for (int i = 0; i < V; i += 2) {
           float k0, k1;
-          drop_pair(a.seed, (uint64_t)(base + (lane + 32 * c) * V + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
+          drop_pair(seed, (uint64_t)(base + (lane + 32 * c) * V + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
           gy[i] *= k0;
           gy[i + 1] *= k1;
         }
@@ -295,6 +303,8 @@ __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(Nor
 // ------------------------------------------------------------------ backward, any d
 template <typename T, bool LN>
 __global__ void __launch_bounds__(128) norm_bwd_generic_kernel(NormBwdArgs a) {
+  uint64_t seed = a.seed;
+  if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const T* __restrict__ dy = static_cast<const T*>(a.dy);
   const T* __restrict__ src = static_cast<const T*>(a.src);
@@ -312,7 +322,7 @@ __global__ void __launch_bounds__(128) norm_bwd_generic_kernel(NormBwdArgs a) {
     };
     auto gval = [&](int c) -> float {
       float v = to_f(dy[base + c]);
-      if (a.drop_thresh) v *= drop_keep(a.seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
+      if (a.drop_thresh) v *= drop_keep(seed, (uint64_t)(base + c), a.drop_thresh, a.drop_inv_keep);
       return v;
     };
     float t1 = 0.f, t2 = 0.f;
@@ -396,11 +406,12 @@ using namespace meant;
 
 extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* gain, void* y, void* sum_out,
                                  float* rinv, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
-                                 uint64_t seed, int dtype, cudaStream_t stream) {
+                                 uint64_t seed, const uint64_t* seed_dev, int dtype, cudaStream_t stream) {
   if (!x || !gain || !y || !rinv || rows < 0 || d <= 0 || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
   if (rows == 0) return 0;
   NormArgs a{x, res, gain, nullptr, y, sum_out, rinv, nullptr, rows, d, eps, pre_gelu,
-             drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed};
+             drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
+             reinterpret_cast<const unsigned long long*>(seed_dev)};
   if (dtype == MEANT_DT_F32) return launch_fwd<float, false>(a, stream);
   if (dtype == MEANT_DT_BF16) return launch_fwd<__nv_bfloat16, false>(a, stream);
   return MEANT_EUNSUPPORTED;
@@ -408,11 +419,13 @@ extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* ga
 
 extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv,
                                  const void* dsum_in, void* dx, float* dgain, int64_t rows, int d, float eps,
-                                 int pre_gelu, float drop_p, uint64_t seed, int dtype, cudaStream_t stream) {
+                                 int pre_gelu, float drop_p, uint64_t seed, const uint64_t* seed_dev, int dtype,
+                                 cudaStream_t stream) {
   if (!dy || !src || !gain || !rinv || !dx || !dgain || rows < 0 || d <= 0) return MEANT_EARG;
   if (rows == 0) return 0;
   NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, nullptr, rows, d, eps, pre_gelu,
-                drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed};
+                drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
+             reinterpret_cast<const unsigned long long*>(seed_dev)};
   if (dtype == MEANT_DT_F32) return launch_bwd<float, false>(a, stream);
   if (dtype == MEANT_DT_BF16) return launch_bwd<__nv_bfloat16, false>(a, stream);
   return MEANT_EUNSUPPORTED;

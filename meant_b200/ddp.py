@@ -6,9 +6,12 @@ them, overlapping the rest of backward.  The reference has no distributed code a
 Design
   * parameters are walked in REVERSE registration order (head -> temporal -> encoders ->
     embedding: the order backward produces gradients) and packed into ~bucket_mb buckets;
-  * every parameter's .grad is a view into its bucket's flat buffer (no pack/unpack copies);
-  * a post-accumulate-grad hook counts arrivals; the last arrival launches
-    all_reduce(bucket, AVG, async_op=True) -- NCCL runs it on its own stream;
+  * gradients are produced by autograd as usual (.grad starts the step as None, so the first
+    arrival is a move, not a zero-fill plus an add per parameter); a post-accumulate-grad hook
+    counts arrivals, and the last arrival of a bucket packs the bucket's gradients into its flat
+    buffer with ONE multi-tensor copy, re-points every .grad at its slice of the buffer and
+    launches all_reduce(bucket, AVG, async_op=True) -- NCCL runs it on its own stream;
+  * with one rank nothing is packed at all: the optimizer reads the autograd tensors;
   * finish() waits for the outstanding handles before the optimizer reads the gradients.
 The same code runs on gloo (CPU tensors) for the world_size-2 tests.
 """
@@ -25,6 +28,7 @@ class BucketedGradAllReduce:
         self._bucket_of = {}
         self._pending = []
         self._handles = []
+        self._views, self._numel = [], []
         cap = int(bucket_mb * 1024 * 1024)
         cur, cur_bytes = [], 0
         for p in reversed(self.params):
@@ -41,55 +45,62 @@ class BucketedGradAllReduce:
 
     def _seal(self, ps, grad_dtype):
         dtype = grad_dtype or ps[0].dtype
-        flat = torch.zeros(sum(p.numel() for p in ps), dtype=dtype, device=ps[0].device)
-        off = 0
+        flat = torch.empty(sum(p.numel() for p in ps), dtype=dtype, device=ps[0].device) if self.world > 1 else None
+        views, off = [], 0
         for p in ps:
-            p.grad = flat[off:off + p.numel()].view_as(p)
+            if flat is not None:
+                views.append(flat[off:off + p.numel()].view_as(p))
             off += p.numel()
             self._bucket_of[p] = len(self.buckets)
+        self._views.append(views)
+        self._numel.append(off)
         self.buckets.append((flat, ps))
 
     def zero_grad(self):
-        """Zero the flat buffers in place (gradients stay views) and re-arm the counters."""
-        for flat, ps in self.buckets:
-            flat.zero_()
-            for p in ps:
-                if p.grad is None or p.grad.data_ptr() < flat.data_ptr() or \
-                        p.grad.data_ptr() >= flat.data_ptr() + flat.numel() * flat.element_size():
-                    raise RuntimeError("a gradient was detached from its bucket (do not set .grad = None)")
+        """Drop the gradients (autograd then moves instead of accumulating) and re-arm the counters."""
+        for p in self.params:
+            p.grad = None
         self._pending = [len(ps) for _, ps in self.buckets]
         self._handles = []
+
+    def _reduce(self, b):
+        """Pack bucket b (parameters without a gradient this step contribute zeros and keep .grad = None
+        only if no rank produced one -- every rank must see the same set), then all-reduce it."""
+        flat, ps = self.buckets[b]
+        views = self._views[b]
+        have = [(v, p) for v, p in zip(views, ps) if p.grad is not None]
+        if len(have) != len(ps):
+            flat.zero_()
+        if have:
+            torch._foreach_copy_([v for v, _ in have], [p.grad for _, p in have])
+        for v, p in have:
+            p.grad = v
+        if flat.is_cuda:
+            self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
+        else:  # gloo has no AVG
+            flat.div_(self.world)
+            self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
 
     def _on_grad(self, p):
         b = self._bucket_of[p]
         self._pending[b] -= 1
         if self._pending[b] == 0 and self.world > 1:
-            flat = self.buckets[b][0]
-            if flat.is_cuda:
-                self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
-            else:  # gloo has no AVG
-                flat.div_(self.world)
-                self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            self._reduce(b)
 
     def finish(self):
-        """Wait for every bucket; buckets whose parameters got no gradient this step are reduced
+        """Wait for every bucket; buckets some of whose parameters got no gradient this step are reduced
         here so that all ranks issue the same collectives."""
         if self.world > 1:
             for b, left in enumerate(self._pending):
                 if left > 0:
-                    flat = self.buckets[b][0]
-                    if not flat.is_cuda:
-                        flat.div_(self.world)
-                    self._handles.append(dist.all_reduce(
-                        flat, op=dist.ReduceOp.AVG if flat.is_cuda else dist.ReduceOp.SUM, group=self.group,
-                        async_op=True))
+                    self._reduce(b)
                     self._pending[b] = 0
         for h in self._handles:
             h.wait()
         self._handles = []
 
     def bucket_bytes(self):
-        return [flat.numel() * flat.element_size() for flat, _ in self.buckets]
+        return [n * ps[0].element_size() for n, (_, ps) in zip(self._numel, self.buckets)]
 
 
 def broadcast_parameters(module, src=0, group=None):

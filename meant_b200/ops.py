@@ -57,9 +57,11 @@ class _RMSNormFn(torch.autograd.Function):
         s = torch.empty_like(x2) if r2 is not None else None
         rinv = torch.empty(rows, dtype=torch.float32, device=x2.device)
         tag = f"rmsnorm_fwd/d{d}/res{int(r2 is not None)}/gelu{int(pre_gelu)}"
+        sdev = _graph_seed if drop_p > 0.0 else None
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_fwd, nv.ptr(x2), nv.ptr(r2), nv.ptr(g32), nv.ptr(y), nv.ptr(s),
-                          nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed, nv.dt(x2), nv.stream()),
-                 "meant_rmsnorm_fwd")
+                          nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed, nv.ptr(sdev), nv.dt(x2),
+                          nv.stream()), "meant_rmsnorm_fwd")
+        ctx.sdev = sdev
         ctx.save_for_backward(s if r2 is not None else x2, g32, rinv)
         ctx.cfg = (eps, int(pre_gelu), drop_p, seed, res is not None, gain.dtype, x.dtype,
                    res.dtype if res is not None else None)
@@ -80,8 +82,18 @@ class _RMSNormFn(torch.autograd.Function):
         tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}"
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_bwd, nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv),
                           nv.ptr(ds), nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
-                          nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+                          nv.ptr(ctx.sdev), nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
         return dx.to(xdt), (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
+
+
+# Device-resident int64 added to every dropout seed by the kernels.  train.TrainStep sets it while a step is
+# captured into a CUDA graph (and advances it inside the graph), so replays draw fresh masks.
+_graph_seed = None
+
+
+def set_graph_seed(t):
+    global _graph_seed
+    _graph_seed = t
 
 
 def _seed():
@@ -98,10 +110,70 @@ def rms_norm(x, gain, eps=1e-8, residual=None, pre_gelu=False, drop_p=0.0):
 
 
 # ------------------------------------------------------------------------------- Linear
+def _mm_f32(a, b):
+    """a @ b with an fp32 result straight from the GEMM epilogue (weight gradients: saves the bf16 -> fp32 pass)."""
+    if a.dtype == torch.float32:
+        return torch.mm(a, b)
+    try:
+        return torch.mm(a, b, out_dtype=torch.float32)
+    except (TypeError, RuntimeError):
+        return torch.mm(a, b).float()
+
+
+class _LinearFn(torch.autograd.Function):
+    """nn.Linear (meant/xPosAttention.py:24-28, meant/meant.py:61-66).  The GEMMs are plain library GEMMs
+    (cuBLASLt through torch: SURVEY 8f); what is ours is the backward's bias gradient -- one streaming
+    column-sum kernel instead of autograd's generic reduction -- and the fp32 weight gradient written by the
+    GEMM itself.  Worth it only when launches are not host-bound (TrainStep(graph=True))."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        dtype = compute_dtype(x)
+        nv.require_cuda(x, weight, bias)
+        with torch.autocast("cuda", enabled=False):
+            xc, wc = x.to(dtype), weight.to(dtype)
+            y = torch.nn.functional.linear(xc, wc, bias.to(dtype) if bias is not None else None)
+        ctx.save_for_backward(xc, wc)
+        ctx.cfg = (x.dtype, weight.dtype, bias.dtype if bias is not None else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, wc = ctx.saved_tensors
+        xdt, wdt, bdt = ctx.cfg
+        n_out, n_in = wc.shape
+        with torch.autocast("cuda", enabled=False):
+            dy2 = dy.to(wc.dtype).reshape(-1, n_out)
+            if dy2.stride(-1) != 1 or dy2.stride(0) % 8 or dy2.data_ptr() % 16:
+                dy2 = dy2.contiguous()
+            x2 = xc.reshape(-1, n_in)
+            dx = dw = db = None
+            if ctx.needs_input_grad[0]:
+                dx = torch.mm(dy2, wc).view(xc.shape).to(xdt)
+            if ctx.needs_input_grad[1]:
+                dw = _mm_f32(dy2.t(), x2).to(wdt)
+            if bdt is not None and ctx.needs_input_grad[2]:
+                db32 = torch.empty(n_out, dtype=torch.float32, device=dy2.device)
+                nv.check(nv.timed(f"bias_grad/r{dy2.shape[0]}/c{n_out}", nv.lib().meant_bias_grad, nv.ptr(dy2), nv.ptr(db32),
+                                  dy2.shape[0], n_out, dy2.stride(0), nv.dt(dy2), nv.stream()), "meant_bias_grad")
+                db = db32.to(bdt)
+        return dx, dw, db
+
+
+_fused_linear = False
+
+
+def use_fused_linear(on=True):
+    """Route ops.linear through _LinearFn (set by TrainStep(graph=True); see _LinearFn)."""
+    global _fused_linear
+    _fused_linear = bool(on)
+
+
 def linear(x, weight, bias=None):
-    """nn.Linear forward (meant/meant.py:102,106,107): a plain library GEMM (cuBLASLt through torch) until the
-    hand-written tcgen05 GEMM with fused epilogues lands.  A Python autograd wrapper with its
-    own bias-gradient kernel was measured slower end to end (host launch overhead), see DESIGN.md 5."""
+    """nn.Linear forward (meant/meant.py:102,106,107)."""
+    if _fused_linear and bias is not None and x.is_cuda and torch.is_grad_enabled() and \
+            (weight.shape[0] % 8 == 0) and x.numel() // x.shape[-1] >= 1024:
+        return _LinearFn.apply(x, weight, bias)
     return torch.nn.functional.linear(x, weight, bias)
 
 

@@ -9,8 +9,14 @@ from .ddp import BucketedGradAllReduce, broadcast_parameters
 
 
 class TrainStep:
+    """graph=True (one rank, CUDA): after `graph_warmup` eager steps the whole step -- zero_grad, autocast
+    forward, loss, backward, clip, AdamW -- is captured once into a CUDA graph and replayed, so the ~2000
+    launches of a step cost no host time; inputs are copied into static buffers, dropout masks advance through
+    a device-resident seed (ops.set_graph_seed), and the bias-gradient kernel replaces autograd's reduction
+    (ops.use_fused_linear).  Input shapes and non-tensor arguments must not change between calls."""
+
     def __init__(self, model, lr=5e-5, betas=(0.9, 0.999), weight_decay=0.0, max_grad_norm=1.0,
-                 bucket_mb=25.0, bf16=True, group=None):
+                 bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3):
         self.model = model
         self.bf16 = bf16
         self.max_grad_norm = max_grad_norm
@@ -18,10 +24,17 @@ class TrainStep:
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group)
         fused = self.params[0].is_cuda
-        self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused)
+        self.graph = bool(graph) and fused and self.reducer.world == 1
+        self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused,
+                                     capturable=self.graph)
+        self._graph_warmup, self._calls = int(graph_warmup), 0
+        self._g = self._static = self._loss = self._seed_t = None
+        self.launches_per_replay = 0            # native-library launches captured in one step
+        if self.graph:
+            from . import ops
+            ops.use_fused_linear(True)
 
-    def __call__(self, labels, *args, **kwargs):
-        """One optimisation step; returns the (device) loss tensor."""
+    def _step(self, labels, args, kwargs):
         self.reducer.zero_grad()
         device_type = "cuda" if self.params[0].is_cuda else "cpu"
         with torch.autocast(device_type, dtype=torch.bfloat16, enabled=self.bf16 and device_type == "cuda"):
@@ -33,3 +46,47 @@ class TrainStep:
             torch.nn.utils.clip_grad_norm_(self.params, self.max_grad_norm, foreach=True)
         self.opt.step()
         return loss.detach()
+
+    def _capture(self, labels, args, kwargs):
+        from . import ops, _native as nv
+        clone = lambda v: v.clone() if torch.is_tensor(v) else v
+        self._static = (clone(labels), tuple(clone(a) for a in args), {k: clone(v) for k, v in kwargs.items()})
+        self._seed_t = torch.zeros(1, dtype=torch.int64, device=labels.device)
+        torch.cuda.synchronize()
+        self._g = torch.cuda.CUDAGraph()
+        ops.set_graph_seed(self._seed_t)
+        n0 = nv.launch_count()
+        try:
+            with torch.cuda.graph(self._g):
+                self._seed_t.add_(0x1E3779B97F4A7C15)     # every replay shifts all dropout seeds
+                self._loss = self._step(self._static[0], self._static[1], self._static[2])
+        finally:
+            ops.set_graph_seed(None)
+        self.launches_per_replay = nv.launch_count() - n0
+
+    def _load(self, labels, args, kwargs):
+        s_labels, s_args, s_kwargs = self._static
+        pairs = [(s_labels, labels)] + list(zip(s_args, args)) + [(s_kwargs[k], kwargs[k]) for k in s_kwargs]
+        if len(args) != len(s_args) or set(kwargs) != set(s_kwargs):
+            raise ValueError("TrainStep(graph=True): the call signature changed after capture")
+        for dst, src in pairs:
+            if torch.is_tensor(dst):
+                if not torch.is_tensor(src) or src.shape != dst.shape or src.dtype != dst.dtype:
+                    raise ValueError("TrainStep(graph=True): input shapes / dtypes are fixed after capture")
+                if src.data_ptr() != dst.data_ptr():
+                    dst.copy_(src, non_blocking=True)
+            elif dst is not src and dst != src:
+                raise ValueError("TrainStep(graph=True): non-tensor arguments are fixed after capture")
+
+    def __call__(self, labels, *args, **kwargs):
+        """One optimisation step; returns the (device) loss tensor (graph mode: a static tensor the next
+        call overwrites)."""
+        self._calls += 1
+        if not self.graph or self._calls <= self._graph_warmup:
+            return self._step(labels, args, kwargs)
+        if self._g is None:
+            self._capture(labels, args, kwargs)
+        else:
+            self._load(labels, args, kwargs)
+        self._g.replay()
+        return self._loss

@@ -30,12 +30,12 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/meant_b200.h but not exported"
     assert set(names) == set(nv.SIGNATURES), set(names) ^ set(nv.SIGNATURES)
-    assert lib.meant_version() == 1
+    assert lib.meant_version() == 2
 
 
 def test_argument_errors_are_codes_not_crashes():
     lib = nv.lib()
-    assert lib.meant_rmsnorm_fwd(None, None, None, None, None, None, 4, 768, 1e-8, 0, 0.0, 0, nv.F32, None) == -1
+    assert lib.meant_rmsnorm_fwd(None, None, None, None, None, None, 4, 768, 1e-8, 0, 0.0, 0, None, nv.F32, None) == -1
     assert lib.meant_layernorm_fwd(None, None, None, None, None, None, 4, 768, 1e-5, nv.F32, None) == -1
     assert lib.meant_meanpool_fwd(None, None, 1, 1, 8, nv.F32, None) == -1
     assert lib.meant_attn_fwd(None, nv.F32, 0, None) == -1

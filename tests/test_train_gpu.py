@@ -1,0 +1,136 @@
+"""GPU tests of the training-step plumbing around the hot path: the bias-gradient kernel (meant_bias_grad),
+the Linear autograd wrapper that uses it, device-side dropout seeds and the CUDA-graph TrainStep."""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from meant_b200 import _native as nv
+    return nv
+
+
+@pytest.mark.parametrize("rows,cols,dtype", [(4097, 768, torch.bfloat16), (98304, 768, torch.bfloat16),
+                                             (1000, 2304, torch.bfloat16), (63, 8, torch.bfloat16),
+                                             (513, 772, torch.float32), (0, 768, torch.bfloat16)])
+def test_bias_grad_matches_column_sum(rows, cols, dtype):
+    nv = _lib()
+    torch.manual_seed(rows + cols)
+    dy = torch.randn(rows, cols, device="cuda").to(dtype)
+    db = torch.full((cols,), 7.0, device="cuda")
+    rc = nv.lib().meant_bias_grad(nv.ptr(dy), nv.ptr(db), rows, cols, cols, nv.dt(dy), nv.stream())
+    assert rc == 0
+    ref = dy.double().sum(0)
+    tol = 1e-3 * max(1.0, rows ** 0.5)
+    assert float((db.double() - ref).abs().max()) <= tol
+
+
+def test_bias_grad_strided_rows_and_argument_errors():
+    nv = _lib()
+    wide = torch.randn(2000, 3 * 768, device="cuda").bfloat16()
+    dy = wide[:, 768:1536]                                   # the k slice of a packed qkv gradient
+    db = torch.empty(768, device="cuda")
+    assert nv.lib().meant_bias_grad(nv.ptr(dy), nv.ptr(db), 2000, 768, wide.stride(0), nv.dt(dy), nv.stream()) == 0
+    assert float((db.double() - dy.double().sum(0)).abs().max()) < 0.1
+    assert nv.lib().meant_bias_grad(None, nv.ptr(db), 4, 768, 768, nv.BF16, None) == -1
+    assert nv.lib().meant_bias_grad(nv.ptr(dy), nv.ptr(db), 4, 766, 768, nv.BF16, None) == -2     # cols % 8
+
+
+@pytest.mark.parametrize("autocast", [True, False])
+def test_fused_linear_matches_autograd(autocast):
+    from meant_b200 import ops
+    torch.manual_seed(0)
+    lin = nn.Linear(768, 1536).cuda()
+    x = torch.randn(16, 128, 768, device="cuda", requires_grad=True)
+    dy = torch.randn(16, 128, 1536, device="cuda")
+
+    def run(fused):
+        ops.use_fused_linear(fused)
+        try:
+            for t in (x, lin.weight, lin.bias):
+                t.grad = None
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+                y = ops.linear(x, lin.weight, lin.bias)
+            y.backward(dy.to(y.dtype))
+            return y.detach().float(), x.grad.clone(), lin.weight.grad.clone(), lin.bias.grad.clone()
+        finally:
+            ops.use_fused_linear(False)
+
+    got, ref = run(True), run(False)
+    tol = 2e-2 if autocast else 2e-3          # fp32 GEMMs may use TF32 on either side
+    for g, r in zip(got, ref):
+        assert g.dtype == r.dtype and g.shape == r.shape
+        assert float((g - r).abs().max()) <= tol * max(1.0, float(r.abs().max()))
+
+
+def test_device_seed_advances_dropout_masks():
+    from meant_b200 import ops
+    x = torch.randn(256, 768, device="cuda").bfloat16()
+    g = torch.ones(768, device="cuda")
+    seed_t = torch.zeros(1, dtype=torch.int64, device="cuda")
+    ops.set_graph_seed(seed_t)
+    try:
+        torch.manual_seed(3)
+        a = ops.rms_norm(x, g, drop_p=0.5)
+        seed_t.add_(12345)
+        torch.manual_seed(3)                  # same host seed: only the device addend differs
+        b = ops.rms_norm(x, g, drop_p=0.5)
+        seed_t.sub_(12345)
+        torch.manual_seed(3)
+        c = ops.rms_norm(x, g, drop_p=0.5)
+    finally:
+        ops.set_graph_seed(None)
+    assert torch.equal(a, c)
+    assert not torch.equal(a == 0, b == 0)
+    assert 0.45 < float((b == 0).float().mean()) < 0.55
+
+
+def _tiny_model():
+    import meant_b200 as mb
+    torch.manual_seed(0)
+    return mb.meant_tweet(768, 4, 3, 2, nn.Embedding(1000, 768), num_encoders=2).cuda()
+
+
+def _batch(seed):
+    g = torch.Generator().manual_seed(seed)
+    tweets = torch.randint(0, 1000, (8, 3, 128), generator=g).cuda()
+    mask = (torch.arange(128).view(1, 1, 128) < 100).float().expand(8, 3, 128).contiguous().cuda()
+    labels = torch.randint(0, 2, (8,), generator=g).cuda()
+    return labels, tweets, mask
+
+
+def test_graph_step_follows_eager_trajectory():
+    """eval() switches the dropouts off, so the captured step must reproduce the eager one step for step
+    (fresh inputs every step: the static buffers really are reloaded)."""
+    from meant_b200 import ops
+    from meant_b200.train import TrainStep
+    losses = {}
+    try:
+        for mode in (False, True):
+            model = _tiny_model().eval()
+            step = TrainStep(model, lr=1e-4, bf16=True, graph=mode, graph_warmup=2)
+            losses[mode] = [float(step(*_batch(k))) for k in range(6)]
+            if mode:
+                assert step._g is not None and step.launches_per_replay > 20
+    finally:
+        ops.use_fused_linear(False)
+    for a, b in zip(losses[False], losses[True]):
+        assert abs(a - b) <= 5e-3 * max(1.0, abs(a)), (losses[False], losses[True])
+
+
+def test_graph_step_train_mode_runs_and_learns():
+    from meant_b200 import ops
+    from meant_b200.train import TrainStep
+    try:
+        model = _tiny_model().train()
+        step = TrainStep(model, lr=2e-4, bf16=True, graph=True, graph_warmup=2)
+        batch = _batch(0)
+        losses = [float(step(*batch)) for _ in range(12)]
+    finally:
+        ops.use_fused_linear(False)
+    assert all(l == l for l in losses)                       # finite
+    assert len(set(round(l, 6) for l in losses[3:])) > 1     # replays are not frozen
+    assert min(losses[6:]) < losses[0]
