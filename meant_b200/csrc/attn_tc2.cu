@@ -36,6 +36,9 @@ constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 constexpr int BAR_C = 1, BAR_L = 2;      // named barriers of the compute (256 threads) / loader (128) groups
 constexpr int NC = 256, NL = 128, NT = NC + NL;
+// The thread that issues the MMAs: lane 0 of warp 4 (row group 0, column half 1), the compute warp that has no
+// key block under the causal mask, so the serial issue code hides in its idle time.
+constexpr int ISSUER = 128;
 
 // Optional in-kernel phase timing (build with -DMEANT_PROF): CTA 0 accumulates clock64 deltas per phase
 // for one compute thread (slots 0..15) and one loader thread (slots 16..31); read with meant_debug_prof().
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       pf.tick(10);
       tc::bar_sync(BAR_C, NC);
       pf.tick(11);
-      if (tid == 0) {
+      if (tid == ISSUER) {
         tc::fence_after_sync();
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
         const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
@@ -461,10 +464,12 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       pf.tick(4);
       tc::bar_sync(BAR_C, NC);
       pf.tick(5);
-      if (tid == 0) {
+      if (tid == ISSUER) {
         tc::fence_after_sync();
         const uint32_t sp = s0 + st * L::STAGE, sv = sp + 2 * G::OPER;
-        for (int ks = 0; ks < n_s / 16; ++ks) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks * 16 < n_s) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
         tc::mma_commit(&o_full[st]);
       }
       l += red_sum[(half ^ 1) * 128 + t];
@@ -591,9 +596,13 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
     const float* tsn = half ? a.ksin : a.qsin;
     int cur_h = -1;
     if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
+    Prof pc;
+    pc.init(blockIdx.x == 0 && tid == 96, 0);
     for (int j = 0; j < n_my; ++j) {
+      pc.tick(0);
       // ---- rotate Q / K rows in place, start S = Q K^T and dP = dO V^T
       tc::mbar_wait(landed_qk, j & 1);
+      pc.tick(1);
       if (rc) {
         if (a.pos_is_head) {
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
@@ -603,8 +612,10 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
+      pc.tick(2);
       tc::bar_sync(BAR_C, NC);
-      if (tid == 0) {
+      pc.tick(3);
+      if (tid == ISSUER) {
         tc::fence_after_sync();
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
 #pragma unroll
@@ -618,6 +629,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       if (j > 0) tc::mbar_wait(stg_free, (j - 1) & 1);              // P / dS double as the previous item's staging
       tc::mbar_wait(sdp_full, j & 1);
       tc::fence_after_sync();
+      pc.tick(4);
       const float lse2 = aux_lse2[t];
       uint32_t pk[32];                                              // this thread's 64 columns of P, bf16 pairs
       float delta = 0.f;                                            // rowsum(P * dP) == rowsum(dO * O)
@@ -658,7 +670,9 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
               make_uint4(pk[i * 16 + q * 4], pk[i * 16 + q * 4 + 1], pk[i * 16 + q * 4 + 2], pk[i * 16 + q * 4 + 3]);
       }
       red_delta[half * 128 + t] = delta;
+      pc.tick(5);
       tc::bar_sync(BAR_C, NC);
+      pc.tick(6);
       delta += red_delta[(half ^ 1) * 128 + t];
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
@@ -688,23 +702,33 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
+      pc.tick(7);
       tc::bar_sync(BAR_C, NC);
-      if (tid == 0) {
+      pc.tick(8);
+      if (tid == ISSUER) {
         tc::fence_after_sync();
         const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
-        for (int ks = 0; ks < kq; ++ks) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
-        for (int ks = 0; ks < kq; ++ks) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
-        for (int ks = 0; ks < kk; ++ks) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);     // dQ = dS K
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
         tc::mma_commit(grads_full);
       }
       tc::mbar_wait(grads_full, j & 1);
       tc::fence_after_sync();
+      pc.tick(9);
       // half 0 owns the dQ row, half 1 the dK row (each un-rotates with its own table); dV is split by columns
       if (half == 0) stage_acc_unrot<DH, RC>(lane_base + T_DQ, stg_x + t * G::PITCH, rc, tab);
       else           stage_acc_unrot<DH, RC>(lane_base + T_DK, stg_z + t * G::PITCH, rc, tab);
       stage_acc_cols<HALF>(lane_base + T_DV + half * HALF, stg_y + t * G::PITCH + half * HALF * 2, 1.0f);
       tc::fence_before_sync();
       tc::mbar_arrive(staged);
+      pc.tick(10);
     }
   }
   tc::fence_before_sync();
