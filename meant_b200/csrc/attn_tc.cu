@@ -394,14 +394,20 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
 }
 
 int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
-  if (attn_tc2_supported(a, 0)) return attn_tc2_fwd(a, st);
+  if (attn_tc2_supported(a, 0)) {
+    const int r2 = attn_tc2_fwd(a, st);
+    if (r2 != MEANT_EUNSUPPORTED) return r2;     // views TMA cannot describe fall through to the multi-tile kernel
+  }
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st);
 }
 
 int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
-  if (attn_tc2_supported(a, 1)) return attn_tc2_bwd(a, st);
+  if (attn_tc2_supported(a, 1)) {
+    const int r2 = attn_tc2_bwd(a, st);
+    if (r2 != MEANT_EUNSUPPORTED) return r2;
+  }
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);

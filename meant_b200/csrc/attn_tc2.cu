@@ -4,27 +4,32 @@
 //
 // One CTA per SM walks (sequence, head) work items blockIdx.x, blockIdx.x + gridDim.x, ...
 // (consecutive CTAs take the heads of one sequence, so the packed `b s (h d)` rows they read
-// are contiguous in DRAM).  384 threads, two roles:
-//   loader warps 8-11  cp.async (LDGSTS, 16 B, zero-filled past S) Q/K/V[/dO] tiles straight from
-//                      the packed projections into SWIZZLE_128B / SWIZZLE_64B operand sub-tiles
-//                      (whole rows written contiguously, read by the tensor core as is), up to
-//                      three items ahead, completion signalled by cp.async.mbarrier.arrive; the
-//                      padding-mask bias / LSE row; later drain the staged results to global
-//                      memory with coalesced 16-byte stores.
+// are contiguous in DRAM).  320 threads, three roles:
+//   producer warp 8    one thread drives TMA: Q/K/V[/dO] head tiles go from the packed projections
+//                      (5-D tensor maps over the head views, rows past S zero-filled) straight into
+//                      SWIZZLE_128B / SWIZZLE_64B operand sub-tiles, completion counted in bytes on an
+//                      mbarrier; staged results leave through TMA stores.  The warp also turns the
+//                      padding-mask row (and, backward, the LSE row) into per-item shared vectors.
+//   MMA warp 9         one thread waits for "operands rotated" / "P written" and issues the
+//                      tcgen05.mma chains, so no computing warp ever stalls on instruction issue.
 //   compute warps 0-7  warps w and w+4 share TMEM lanes (query rows) 32(w%4).. : thread (row t, half)
 //                      rotates + xPos-scales row t of Q (half 0) or K (half 1) IN PLACE from
-//                      per-thread register tables (fp16 pairs, loaded once), issues the MMAs,
-//                      and the halves split the key columns in interleaved 32-column blocks
-//                      (balanced under the causal mask) for the softmax (forward) or the P/dS
-//                      recompute (backward) straight out of TMEM, with one shared-memory exchange
-//                      of the row max / row sums; accumulators go TMEM -> (un-rotate dQ/dK in
-//                      fp32 registers) -> bf16 -> staging.
-// Hand-offs are mbarriers (tcgen05.commit for MMA completion, mbarrier.arrive for data), never
-// __syncthreads, so loads of item j+1/j+2, the tensor core on item j and the stores of item
-// j-1 overlap.  Both kernels are HBM-bound at S = 128 (see DESIGN.md for the byte counts).
+//                      per-thread register tables (fp16 pairs, loaded once), and the halves split
+//                      the key columns in interleaved 32-column blocks (balanced under the causal
+//                      mask) for the softmax (forward) or the P/dS recompute (backward) straight out
+//                      of TMEM, exchanging the row max / row sums through shared memory behind a
+//                      64-thread named barrier; accumulators go TMEM -> (un-rotate dQ/dK in fp32
+//                      registers) -> bf16 -> swizzled staging tile.
+// Every hand-off is an mbarrier (tcgen05.commit for MMA completion, expect_tx for TMA, arrive for
+// data), never __syncthreads: loads of the next items, the tensor core, the softmax of item j and
+// the stores of item j-1 overlap.  Forward keeps three Q|K|V stages in flight; backward double
+// buffers Q|K and recycles V / dO as soon as their last MMA has run.  Both kernels are HBM-bound
+// at S = 128 (see DESIGN.md for the byte counts).
 #include "attn_common.cuh"
 #include "tc_utils.cuh"
+#include "tma_utils.cuh"
 #include <cuda_fp16.h>
+#include <string.h>
 #include <math_constants.h>
 
 namespace meant {
@@ -34,11 +39,7 @@ constexpr uint32_t SUB_A = 128 * 128;     // 128 rows x 64 columns, SWIZZLE_128B
 constexpr uint32_t SUB_B = 128 * 64;      // 128 rows x 32 columns, SWIZZLE_64B sub-tile
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
-constexpr int BAR_C = 1, BAR_L = 2;      // named barriers of the compute (256 threads) / loader (128) groups
-constexpr int NC = 256, NL = 128, NT = NC + NL;
-// The thread that issues the MMAs: lane 0 of warp 4 (row group 0, column half 1), the compute warp that has no
-// key block under the causal mask, so the serial issue code hides in its idle time.
-constexpr int ISSUER = 128;
+constexpr int NC = 256;                  // compute threads (warps 0-7)
 
 // Optional in-kernel phase timing (build with -DMEANT_PROF): CTA 0 accumulates clock64 deltas per phase
 // for one compute thread (slots 0..15) and one loader thread (slots 16..31); read with meant_debug_prof().
@@ -64,7 +65,6 @@ struct Geo {
   static constexpr bool TAIL = DH > 64;              // columns [64, 96) live in a SWIZZLE_64B sub-tile
   static constexpr uint32_t OPER = SUB_A + (TAIL ? SUB_B : 0u);   // one 128 x DH operand tile
   static constexpr uint32_t PBUF = 2 * SUB_A;        // one 128 x 128 P / dS tile (two SWIZZLE_128B sub-tiles)
-  static constexpr uint32_t PITCH = DH * 2 + 16;     // staging row pitch (bank-conflict free)
   static_assert(DH == 64 || DH == 96, "operand tile = one 64-column sub-tile (+ one 32-column sub-tile)");
 };
 
@@ -95,58 +95,6 @@ template <int DH>
 __device__ __forceinline__ void mma_oper_mn(uint32_t tmem_d, uint64_t adesc, uint32_t sb, int ks, int a_mn, bool acc) {
   tc::mma_ss(tmem_d, adesc, desc_oper_mn_a(sb, ks), tc::make_idesc(128, 64, a_mn, 1), acc);
   if (Geo<DH>::TAIL) tc::mma_ss(tmem_d + 64, adesc, desc_oper_mn_b(sb, ks), tc::make_idesc(128, 32, a_mn, 1), acc);
-}
-
-__device__ __forceinline__ const __nv_bfloat16* head_base(const HeadView& v, int n, int n2c, int h) {
-  const int n1 = n / n2c, n2 = n - n1 * n2c;
-  return static_cast<const __nv_bfloat16*>(v.p) + (int64_t)n1 * v.sn1 + (int64_t)n2 * v.sn2 + (int64_t)h * v.sh;
-}
-
-// Loader thread t of 128 moves chunks idx = t + 128 k (k < CPR) of every 128 x DH tile: lanes walk the 16-byte
-// chunks of a row first, so a warp reads ~2.7 whole rows (full 64-byte segments, few 128-byte lines) and
-// writes them to contiguous (swizzled) shared rows.  The (row, chunk, shared offset) split is the same for
-// every tile and item, so it is computed once.
-template <int DH>
-struct ChunkMap {
-  static constexpr int CPR = DH / 8;
-  int rc[CPR];                                     // row | chunk << 8 | shared offset << 16
-  __device__ __forceinline__ void init(int t) {
-#pragma unroll
-    for (int k = 0; k < CPR; ++k) {
-      const int idx = t + k * 128, r = idx / CPR, ch = idx - r * CPR;
-      rc[k] = r | (ch << 8) | (int)(oper_off(r, ch) << 16);
-    }
-  }
-  __device__ __forceinline__ int row(int k) const { return rc[k] & 0xff; }
-  __device__ __forceinline__ int gcol(int k) const { return ((rc[k] >> 8) & 0xff) * 8; }             // element column
-  __device__ __forceinline__ uint32_t soff(int k) const { return (uint32_t)rc[k] >> 16; }            // swizzled operand tile
-  __device__ __forceinline__ uint32_t stg(int k) const { return (rc[k] & 0xff) * Geo<DH>::PITCH + ((rc[k] >> 8) & 0xff) * 16; }
-};
-
-// rows [0,128) of head (n, h) -> swizzled operand tile at shared address sbase; rows >= S are zero filled.
-template <int DH>
-__device__ __forceinline__ void issue_tile(const ChunkMap<DH>& cm, uint32_t sbase, const HeadView& v, int n, int n2c, int h, int S) {
-  const __nv_bfloat16* base = head_base(v, n, n2c, h);
-  const int ss = (int)v.ss;
-#pragma unroll
-  for (int k = 0; k < DH / 8; ++k) {
-    const bool ok = cm.row(k) < S;
-    tc::cp_async16(sbase + cm.soff(k), base + (ok ? cm.row(k) * ss : 0) + cm.gcol(k), ok ? 16u : 0u);
-  }
-}
-
-// staged rows (row-major, PITCH bytes apart) -> head (n, h) of a global view, coalesced.
-template <int DH>
-__device__ __forceinline__ void drain_rows(const ChunkMap<DH>& cm, const uint8_t* stg, const HeadView& v, int n, int n2c, int h, int S) {
-  __nv_bfloat16* base = const_cast<__nv_bfloat16*>(head_base(v, n, n2c, h));
-  const int ss = (int)v.ss;
-#pragma unroll
-  for (int k = 0; k < DH / 8; ++k) {
-    if (cm.row(k) < S) {
-      const uint4 val = *reinterpret_cast<const uint4*>(stg + cm.stg(k));
-      *reinterpret_cast<uint4*>(base + cm.row(k) * ss + cm.gcol(k)) = val;
-    }
-  }
 }
 
 // Per-thread rotation table of one position: (C[2i], C[2i+1]) / (S[2i], S[2i+1]) pairs in fp16
@@ -194,65 +142,6 @@ __device__ __forceinline__ void rot_row(uint8_t* tile, int r, int rc, const RotT
   }
 }
 
-// TMEM accumulator (this thread's lane, NCOL fp32 columns from taddr; NCOL = 32 or 48) -> bf16 at dst
-template <int NCOL>
-__device__ __forceinline__ void stage_acc_cols(uint32_t taddr, uint8_t* dst, float mul) {
-  float o[32];
-  tc::tmem_ld32(taddr, o);
-  tc::tmem_ld_wait();
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    uint4 pk;
-    __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(o[q * 8 + 2 * i] * mul, o[q * 8 + 2 * i + 1] * mul);
-    *reinterpret_cast<uint4*>(dst + q * 16) = pk;
-  }
-  if (NCOL > 32) {
-    tc::tmem_ld16(taddr + 32, o);
-    tc::tmem_ld_wait();
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      uint4 pk;
-      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(o[q * 8 + 2 * i] * mul, o[q * 8 + 2 * i + 1] * mul);
-      *reinterpret_cast<uint4*>(dst + 64 + q * 16) = pk;
-    }
-  }
-}
-
-// Full accumulator row (DH fp32 columns) -> un-rotate the first rc chunks in fp32 registers -> bf16 row at dst
-template <int DH, int RC>
-__device__ __forceinline__ void stage_acc_unrot(uint32_t taddr, uint8_t* dst, int rc, const RotTab<RC>& T) {
-#pragma unroll
-  for (int c0 = 0; c0 < DH; c0 += 32) {
-    float o[32];
-    tc::tmem_ld32(taddr + c0, o);
-    tc::tmem_ld_wait();
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int ch = c0 / 8 + q;
-      uint4 pk;
-      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        float g0 = o[q * 8 + 2 * i], g1 = o[q * 8 + 2 * i + 1];
-        if (ch < RC) {
-          if (ch < rc) {
-            const float2 c = __half22float2(T.c[(ch < RC ? ch : 0) * 4 + i]), s = __half22float2(T.s[(ch < RC ? ch : 0) * 4 + i]);
-            const float y0 = g0 * c.x + g1 * s.y, y1 = g1 * c.y - g0 * s.x;
-            g0 = y0;
-            g1 = y1;
-          }
-        }
-        ph[i] = __floats2bfloat162_rn(g0, g1);
-      }
-      *reinterpret_cast<uint4*>(dst + ch * 16) = pk;
-    }
-  }
-}
-
 // additive key bias in the exp2 domain: padding mask (meant/xPosAttention.py:54-56) and keys past Sk
 __device__ __forceinline__ float key_bias2(float mval, int k, int Sk) {
   return k < Sk ? (1.0f - mval) * -1e9f * LOG2E : -CUDART_INF_F;
@@ -268,11 +157,46 @@ struct FwdL {
   static constexpr uint32_t RED = AUX + NST * 512;             // [2][2][128] fp32 row max / row sum exchange
   static constexpr uint32_t BARS = RED + 2048;
   static constexpr uint32_t TOTAL = BARS + 256 + 1024;          // + alignment slack
-  static_assert(G::PBUF <= 2 * G::OPER && 128 * G::PITCH <= 2 * G::OPER, "P / staging must fit in Q | K");
+  static_assert(G::PBUF <= 2 * G::OPER, "P must fit in Q | K");
 };
 
+// thread roles of the forward kernel: 8 compute warps, one producer warp (TMA loads / stores, key bias), one
+// MMA-issue warp -- nobody who computes ever waits for an instruction issue, nobody who issues ever computes
+constexpr int F_PROD = NC / 32, F_MMA = F_PROD + 1, F_NT = NC + 64;
+constexpr int BAR_PAIR = 3;              // named barriers 3..6: the two warps that share a TMEM lane quarter
+
+struct FwdMaps { CUtensorMap m[8]; };    // q, k, v, o  x  (columns [0,64) SWIZZLE_128B, columns [64,96) SWIZZLE_64B)
+
+// this thread's accumulator columns [c0, c0 + 8 * NCH) of row t (NCH = 4 or 6 chunks) -> bf16 -> swizzled operand tile
+template <int NCH>
+__device__ __forceinline__ void stage_acc_sw(uint32_t taddr, uint8_t* tile, int t, int ch0, float mul) {
+  float o[32];
+  tc::tmem_ld32(taddr, o);
+  tc::tmem_ld_wait();
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint4 pk;
+    __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(o[q * 8 + 2 * i] * mul, o[q * 8 + 2 * i + 1] * mul);
+    *reinterpret_cast<uint4*>(tile + oper_off(t, ch0 + q)) = pk;
+  }
+  if (NCH > 4) {
+    tc::tmem_ld16(taddr + 32, o);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      uint4 pk;
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(o[q * 8 + 2 * i] * mul, o[q * 8 + 2 * i + 1] * mul);
+      *reinterpret_cast<uint4*>(tile + oper_off(t, ch0 + 4 + q)) = pk;
+    }
+  }
+}
+
 template <int DH, int RC>
-__global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_items) {
+__global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_items, const __grid_constant__ FwdMaps maps) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
   uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
@@ -283,15 +207,17 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
   // TMEM: one 128-column buffer per stage: S, then (once P is in shared memory) O over its first DH columns
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *landed = bars, *s_full = bars + NST, *o_full = bars + 2 * NST, *o_staged = bars + 3 * NST,
-           *aux_ready = bars + 4 * NST;
+           *aux_ready = bars + 4 * NST, *rot_done = bars + 5 * NST, *p_ready = bars + 6 * NST;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < NST; ++i) {
-      tc::mbar_init(&landed[i], NL);
-      tc::mbar_init(&aux_ready[i], NL);
+      tc::mbar_init(&landed[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);
       tc::mbar_init(&s_full[i], 1);
       tc::mbar_init(&o_full[i], 1);
       tc::mbar_init(&o_staged[i], NC);
+      tc::mbar_init(&rot_done[i], NC);
+      tc::mbar_init(&p_ready[i], NC);
     }
     tc::fence_mbar_init();
   }
@@ -305,41 +231,94 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
   const uint32_t s0 = tc::smem_u32(smem);
   const int n_s = (a.Sk + 15) & ~15;                            // PV K extent (keys, rounded to one MMA K step)
 
-  if (tid >= NC) {
-    // ------------------------------------------------------------------ loader group
-    const int t = tid - NC;
-    ChunkMap<DH> cm;
-    cm.init(t);
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
     Prof pf;
-    pf.init(blockIdx.x == 0 && t == 0, 16);
+    pf.init(blockIdx.x == 0 && lane == 0, 16);
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    auto store_out = [&](int item, int st) {                      // staged O of `item` -> global (lane 0)
+      const int n = item / a.H, h = item - n * a.H, n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      const uint32_t sb = s0 + st * L::STAGE;
+      tma::store_box(&maps.m[6], sb, 0, h, 0, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[7], sb + SUB_A, 64, h, 0, n2, n1);
+      tma::store_commit();
+    };
     for (int j = 0; j < n_my; ++j) {
       const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
+      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
       pf.tick(0);
-      if (j >= NST) {   // the stage still holds item j - NST: drain its staged output first
-        const int pitem = item - NST * (int)gridDim.x, pn = pitem / a.H, ph = pitem - pn * a.H;
+      if (j >= NST) {   // the stage still holds item j - NST: its staged output goes out first
         tc::mbar_wait(&o_staged[st], ((j - NST) / NST) & 1);
         pf.tick(1);
-        drain_rows<DH>(cm, smem + st * L::STAGE, a.o, pn, a.n2_count, ph, a.Sq);
+        if (lane == 0) {
+          store_out(item - NST * (int)gridDim.x, st);
+          tma::store_wait_read<0>();                              // the stage may be overwritten now
+        }
         pf.tick(2);
-        tc::bar_sync(BAR_L, NL);    // every staged row has been read before the stage is refilled
-        pf.tick(3);
       }
-      float mval = 1.f;
-      if (a.key_mask && t < a.Sk) mval = __ldg(a.key_mask + (int64_t)n * a.Sk + t);
-      const uint32_t sb = s0 + st * L::STAGE;
-      issue_tile<DH>(cm, sb, a.q, n, a.n2_count, h, a.Sq);
-      issue_tile<DH>(cm, sb + G::OPER, a.k, n, a.n2_count, h, a.Sk);
-      issue_tile<DH>(cm, sb + 2 * G::OPER, a.v, n, a.n2_count, h, a.Sk);
-      tc::cp_async_arrive(&landed[st]);                           // fires when this thread's copies have landed
-      pf.tick(4);
-      reinterpret_cast<float*>(smem + L::AUX + st * 512)[t] = key_bias2(mval, t, a.Sk);
+      if (lane == 0) {
+        const uint32_t sb = s0 + st * L::STAGE;
+        tma::mbar_expect_tx(&landed[st], 3 * G::OPER);
+#pragma unroll
+        for (int v = 0; v < 3; ++v) {
+          tma::load_box(sb + v * G::OPER, &maps.m[2 * v], &landed[st], 0, h, 0, n2, n1);
+          if (G::TAIL) tma::load_box(sb + v * G::OPER + SUB_A, &maps.m[2 * v + 1], &landed[st], 64, h, 0, n2, n1);
+        }
+      }
+      pf.tick(3);
+      float4 mv = make_float4(1.f, 1.f, 1.f, 1.f);
+      const int k0 = lane * 4;
+      if (a.key_mask) {
+        const float* mrow = a.key_mask + (int64_t)n * a.Sk;
+        if (k0 + 3 < a.Sk && (a.Sk & 3) == 0) mv = __ldg(reinterpret_cast<const float4*>(mrow + k0));
+        else {
+          if (k0 < a.Sk) mv.x = __ldg(mrow + k0);
+          if (k0 + 1 < a.Sk) mv.y = __ldg(mrow + k0 + 1);
+          if (k0 + 2 < a.Sk) mv.z = __ldg(mrow + k0 + 2);
+          if (k0 + 3 < a.Sk) mv.w = __ldg(mrow + k0 + 3);
+        }
+      }
+      reinterpret_cast<float4*>(smem + L::AUX + st * 512)[lane] =
+          make_float4(key_bias2(mv.x, k0, a.Sk), key_bias2(mv.y, k0 + 1, a.Sk), key_bias2(mv.z, k0 + 2, a.Sk),
+                      key_bias2(mv.w, k0 + 3, a.Sk));
       tc::mbar_arrive(&aux_ready[st]);
-      pf.tick(5);
+      pf.tick(4);
     }
     for (int j = max(0, n_my - NST); j < n_my; ++j) {
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
+      const int st = j % NST;
       tc::mbar_wait(&o_staged[st], (j / NST) & 1);
-      drain_rows<DH>(cm, smem + st * L::STAGE, a.o, n, a.n2_count, h, a.Sq);
+      if (lane == 0) store_out(blockIdx.x + j * gridDim.x, st);
+    }
+    if (lane == 0) tma::store_wait_all();
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      auto issue_s = [&](int j) {
+        const int st = j % NST;
+        tc::mbar_wait(&rot_done[st], (j / NST) & 1);
+        tc::fence_after_sync();
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+        const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
+        tc::mma_commit(&s_full[st]);
+      };
+      if (n_my > 0) issue_s(0);
+      for (int j = 0; j < n_my; ++j) {
+        const int st = j % NST;
+        tc::mbar_wait(&p_ready[st], (j / NST) & 1);
+        tc::fence_after_sync();
+        const uint32_t sp = s0 + st * L::STAGE, sv = sp + 2 * G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks * 16 < n_s) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
+        tc::mma_commit(&o_full[st]);
+        if (j + 1 < n_my) issue_s(j + 1);
+      }
     }
   } else {
     // ------------------------------------------------------------------ compute group
@@ -356,9 +335,9 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
     const float* tsn = half ? a.ksin : a.qsin;
     int cur_h = -1;
     if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
-    // rotate item j's Q / K rows in place, then start its score MMA
     Prof pf;
     pf.init(blockIdx.x == 0 && tid == 96, 0);
+    // rotate item j's Q / K rows in place and hand the stage to the MMA warp
     auto prepare = [&](int j) {
       const int st = j % NST;
       pf.tick(8);
@@ -373,17 +352,8 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
+      tc::mbar_arrive(&rot_done[st]);
       pf.tick(10);
-      tc::bar_sync(BAR_C, NC);
-      pf.tick(11);
-      if (tid == ISSUER) {
-        tc::fence_after_sync();
-        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
-        const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
-#pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
-        tc::mma_commit(&s_full[st]);
-      }
     };
     if (n_my > 0) prepare(0);
     for (int j = 0; j < n_my; ++j) {
@@ -420,7 +390,7 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       }
       red_max[half * 128 + t] = m;
       pf.tick(2);
-      tc::bar_sync(BAR_C, NC);
+      tc::bar_sync(BAR_PAIR + rg, 64);                              // the two halves of this row group only
       pf.tick(3);
       m = fmaxf(m, red_max[(half ^ 1) * 128 + t]);
       const float m_use = m == -CUDART_INF_F ? 0.f : m;
@@ -461,25 +431,18 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
       red_sum[half * 128 + t] = l;
       tc::fence_async_smem();
       tc::fence_before_sync();
+      tc::mbar_arrive(&p_ready[st]);                                // the MMA warp starts O = P V
       pf.tick(4);
-      tc::bar_sync(BAR_C, NC);
-      pf.tick(5);
-      if (tid == ISSUER) {
-        tc::fence_after_sync();
-        const uint32_t sp = s0 + st * L::STAGE, sv = sp + 2 * G::OPER;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks * 16 < n_s) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
-        tc::mma_commit(&o_full[st]);
-      }
+      if (j + 1 < n_my) prepare(j + 1);                             // next item's rotation hides the PV latency
+      tc::bar_sync(BAR_PAIR + rg, 64);
       l += red_sum[(half ^ 1) * 128 + t];
-      if (j + 1 < n_my) prepare(j + 1);                             // next item's rotation + score MMA hide the PV latency
-      pf.tick(12);
+      pf.tick(5);
       tc::mbar_wait(&o_full[st], par);
       tc::fence_after_sync();
       pf.tick(6);
-      stage_acc_cols<HALF>(ts + half * HALF, smem + st * L::STAGE + t * G::PITCH + half * HALF * 2, l > 0.f ? 1.0f / l : 0.f);
+      stage_acc_sw<G::CPR / 2>(ts + half * HALF, smem + st * L::STAGE, t, half * (G::CPR / 2), l > 0.f ? 1.0f / l : 0.f);
       if (half == 0 && t < a.Sq && a.lse) a.lse[((int64_t)n * a.H + h) * a.Sq + t] = m_use * LN2 + logf(l);
+      tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(&o_staged[st]);
       pf.tick(7);
@@ -491,19 +454,58 @@ __global__ void __launch_bounds__(NT, 1) attn2_fwd_kernel(AttnArgs a, int n_item
 }
 
 // ============================================================================== backward
+// Shared memory: the Q | K pair is double buffered (item j+1's pair lands while item j computes); V is free for the
+// next item as soon as dP = dO V^T has run, dO as soon as the gradient MMAs have; P and dS are single.  The three
+// gradient tiles are staged (swizzled operand layout, what the TMA store expects) over buffers that are dead by
+// then: dQ over P, dV over dS, dK over this item's Q.
 template <int DH>
 struct BwdL {
   using G = Geo<DH>;
-  static constexpr uint32_t Q = 0, K = G::OPER, V = 2 * G::OPER, DO = 3 * G::OPER, P = 4 * G::OPER, DS = P + G::PBUF;
-  static constexpr uint32_t STG_Z = DS + G::PBUF;              // dK staging (dQ stages over P, dV over dS)
-  static constexpr uint32_t AUX = STG_Z + 128 * G::PITCH;      // bias2[128] | lse*log2e[128] | delta exchange [2][128]
-  static constexpr uint32_t BARS = AUX + 2048;
+  static constexpr uint32_t QK = 0;                            // [2][Q | K]
+  static constexpr uint32_t V = 4 * G::OPER, DO = 5 * G::OPER, P = 6 * G::OPER, DS = P + G::PBUF;
+  static constexpr uint32_t AUX = DS + G::PBUF;                // [2][bias2[128] | lse*log2e[128]], then delta exchange [2][128]
+  static constexpr uint32_t RED = AUX + 2048;
+  static constexpr uint32_t BARS = RED + 1024;
   static constexpr uint32_t TOTAL = BARS + 128 + 1024;          // + alignment slack
-  static_assert(128 * G::PITCH <= G::PBUF, "gradient staging must fit in the P / dS buffers");
+  static_assert(G::OPER <= G::PBUF, "gradient staging must fit in the P / dS buffers");
+  static_assert(TOTAL <= 232448, "exceeds the 227 KB of shared memory a CTA can opt in to");
 };
 
+struct BwdMaps { CUtensorMap m[14]; };   // q, k, v, dO (loads), dq, dk, dv (stores)  x  (SWIZZLE_128B part, SWIZZLE_64B part)
+
+// Full accumulator row (DH fp32 columns) -> un-rotate the first rc chunks in fp32 registers -> bf16 -> swizzled tile row t
 template <int DH, int RC>
-__global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_items) {
+__device__ __forceinline__ void stage_acc_unrot_sw(uint32_t taddr, uint8_t* tile, int t, int rc, const RotTab<RC>& T) {
+#pragma unroll
+  for (int c0 = 0; c0 < DH; c0 += 32) {
+    float o[32];
+    tc::tmem_ld32(taddr + c0, o);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int ch = c0 / 8 + q;
+      uint4 pk;
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float g0 = o[q * 8 + 2 * i], g1 = o[q * 8 + 2 * i + 1];
+        if (ch < RC) {
+          if (ch < rc) {
+            const float2 c = __half22float2(T.c[(ch < RC ? ch : 0) * 4 + i]), s = __half22float2(T.s[(ch < RC ? ch : 0) * 4 + i]);
+            const float y0 = g0 * c.x + g1 * s.y, y1 = g1 * c.y - g0 * s.x;
+            g0 = y0;
+            g1 = y1;
+          }
+        }
+        ph[i] = __floats2bfloat162_rn(g0, g1);
+      }
+      *reinterpret_cast<uint4*>(tile + oper_off(t, ch)) = pk;
+    }
+  }
+}
+
+template <int DH, int RC>
+__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMaps maps) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
   uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
@@ -512,17 +514,22 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
   constexpr int HALF = DH / 2;
   constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 352, T_DQ = 0;   // dQ reuses the consumed S columns
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
-  uint64_t *landed_qk = bars, *landed_dv = bars + 1, *sdp_full = bars + 2, *grads_full = bars + 3, *staged = bars + 4,
-           *stg_free = bars + 5, *aux_ready = bars + 6;
+  uint64_t *landed_qk = bars, *aux_ready = bars + 2, *rot_done = bars + 4, *landed_v = bars + 6, *landed_do = bars + 7,
+           *sdp_full = bars + 8, *pds_ready = bars + 9, *grads_full = bars + 10, *staged = bars + 11, *stg_free = bars + 12;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    tc::mbar_init(landed_qk, NL);
-    tc::mbar_init(landed_dv, NL);
-    tc::mbar_init(aux_ready, NL);
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&landed_qk[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);
+      tc::mbar_init(&rot_done[i], NC);
+    }
+    tc::mbar_init(landed_v, 1);
+    tc::mbar_init(landed_do, 1);
     tc::mbar_init(sdp_full, 1);
+    tc::mbar_init(pds_ready, NC);
     tc::mbar_init(grads_full, 1);
     tc::mbar_init(staged, NC);
-    tc::mbar_init(stg_free, NL);
+    tc::mbar_init(stg_free, 1);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
@@ -533,61 +540,138 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
   const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int rc = a.qcos ? a.rot_dim / 8 : 0;
   const uint32_t s0 = tc::smem_u32(smem);
-  const uint32_t sq = s0 + L::Q, sk = s0 + L::K, sv = s0 + L::V, sdo = s0 + L::DO, sp = s0 + L::P, sds = s0 + L::DS;
-  uint8_t* stg_x = smem + L::P;       // dQ staging (free once the gradient MMAs are done)
-  uint8_t* stg_y = smem + L::DS;      // dV staging
-  uint8_t* stg_z = smem + L::STG_Z;   // dK staging
-  float* aux_bias = reinterpret_cast<float*>(smem + L::AUX);
-  float* aux_lse2 = aux_bias + 128;
-  float* red_delta = aux_bias + 256;                                // [2][128]
+  const uint32_t sv = s0 + L::V, sdo = s0 + L::DO, sp = s0 + L::P, sds = s0 + L::DS;
 
-  if (tid >= NC) {
-    // ------------------------------------------------------------------ loader group
-    const int t = tid - NC;
-    ChunkMap<DH> cm;
-    cm.init(t);
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
     Prof pf;
-    pf.init(blockIdx.x == 0 && t == 0, 16);
-    auto drain = [&](int j) {   // the three gradients of item j, staged by the compute group
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H;
-      pf.tick(4);
-      tc::mbar_wait(staged, j & 1);
-      pf.tick(5);
-      drain_rows<DH>(cm, stg_x, a.dq, n, a.n2_count, h, a.Sq);
-      drain_rows<DH>(cm, stg_y, a.dv, n, a.n2_count, h, a.Sk);
-      drain_rows<DH>(cm, stg_z, a.dk, n, a.n2_count, h, a.Sk);
-      tc::mbar_arrive(stg_free);
-      pf.tick(6);
+    pf.init(blockIdx.x == 0 && lane == 0, 16);
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 14; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    auto coords = [&](int j, int& h, int& n2, int& n1) {
+      const int item = blockIdx.x + j * gridDim.x, n = item / a.H;
+      h = item - n * a.H;
+      n1 = n / a.n2_count;
+      n2 = n - n1 * a.n2_count;
+    };
+    auto load_tile = [&](int view, uint32_t dst, uint64_t* bar, int h, int n2, int n1) {
+      tma::load_box(dst, &maps.m[2 * view], bar, 0, h, 0, n2, n1);
+      if (G::TAIL) tma::load_box(dst + SUB_A, &maps.m[2 * view + 1], bar, 64, h, 0, n2, n1);
+    };
+    auto store_tile = [&](int view, uint32_t src, int h, int n2, int n1) {
+      tma::store_box(&maps.m[2 * view], src, 0, h, 0, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[2 * view + 1], src + SUB_A, 64, h, 0, n2, n1);
+    };
+    auto store_grads = [&](int j) {                               // staged gradients of item j -> global (lane 0)
+      int h, n2, n1;
+      coords(j, h, n2, n1);
+      store_tile(4, sp, h, n2, n1);                               // dq
+      store_tile(5, s0 + L::QK + (j & 1) * 2 * G::OPER, h, n2, n1);   // dk (over this item's Q)
+      store_tile(6, sds, h, n2, n1);                              // dv
+      tma::store_commit();
     };
     for (int j = 0; j < n_my; ++j) {
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H;
+      const int b = j & 1;
+      int h, n2, n1;
+      coords(j, h, n2, n1);
+      const int n = n1 * a.n2_count + n2;
       pf.tick(0);
-      if (j > 0) tc::mbar_wait(grads_full, (j - 1) & 1);           // operand tiles of item j-1 are consumed
+      if (lane == 0) {       // Q | K pair b: item j-2's dK staging left it in program order (store_wait_read below)
+        const uint32_t sq = s0 + L::QK + b * 2 * G::OPER;
+        tma::mbar_expect_tx(&landed_qk[b], 2 * G::OPER);
+        load_tile(0, sq, &landed_qk[b], h, n2, n1);
+        load_tile(1, sq + G::OPER, &landed_qk[b], h, n2, n1);
+      }
       pf.tick(1);
-      float mval = 1.f, lse = 0.f;
-      if (a.key_mask && t < a.Sk) mval = __ldg(a.key_mask + (int64_t)n * a.Sk + t);
-      if (t < a.Sq) lse = __ldg(a.lse + ((int64_t)n * a.H + h) * a.Sq + t);
-      issue_tile<DH>(cm, sq, a.q, n, a.n2_count, h, a.Sq);
-      issue_tile<DH>(cm, sk, a.k, n, a.n2_count, h, a.Sk);
-      tc::cp_async_arrive(landed_qk);
-      issue_tile<DH>(cm, sdo, a.o, n, a.n2_count, h, a.Sq);
-      issue_tile<DH>(cm, sv, a.v, n, a.n2_count, h, a.Sk);
-      tc::cp_async_arrive(landed_dv);
+      if (j > 0) tc::mbar_wait(sdp_full, (j - 1) & 1);            // V is free once dP of the previous item has run
       pf.tick(2);
-      aux_bias[t] = key_bias2(mval, t, a.Sk);
-      aux_lse2[t] = lse * LOG2E;
-      tc::mbar_arrive(aux_ready);
+      if (lane == 0) {
+        tma::mbar_expect_tx(landed_v, G::OPER);
+        load_tile(2, sv, landed_v, h, n2, n1);
+      }
+      {
+        const int k0 = lane * 4;
+        float mv[4] = {1.f, 1.f, 1.f, 1.f}, ls[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+        const float* lrow = a.lse + ((int64_t)n * a.H + h) * a.Sq;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (mrow && k0 + u < a.Sk) mv[u] = __ldg(mrow + k0 + u);
+          if (k0 + u < a.Sq) ls[u] = __ldg(lrow + k0 + u);
+        }
+        float* aux = reinterpret_cast<float*>(smem + L::AUX + b * 1024);
+        reinterpret_cast<float4*>(aux)[lane] = make_float4(key_bias2(mv[0], k0, a.Sk), key_bias2(mv[1], k0 + 1, a.Sk),
+                                                           key_bias2(mv[2], k0 + 2, a.Sk), key_bias2(mv[3], k0 + 3, a.Sk));
+        reinterpret_cast<float4*>(aux + 128)[lane] = make_float4(ls[0] * LOG2E, ls[1] * LOG2E, ls[2] * LOG2E, ls[3] * LOG2E);
+        tc::mbar_arrive(&aux_ready[b]);
+      }
       pf.tick(3);
-      if (j > 0) drain(j - 1);
+      if (j > 0) tc::mbar_wait(grads_full, (j - 1) & 1);          // dO is free once the previous gradient MMAs have run
+      pf.tick(4);
+      if (lane == 0) {
+        tma::mbar_expect_tx(landed_do, G::OPER);
+        load_tile(3, sdo, landed_do, h, n2, n1);
+      }
+      if (j > 0) {
+        tc::mbar_wait(staged, (j - 1) & 1);
+        pf.tick(5);
+        if (lane == 0) {
+          store_grads(j - 1);
+          tma::store_wait_read<0>();
+          tc::mbar_arrive(stg_free);                              // P / dS (and that item's Q | K pair) may be rewritten
+        }
+        pf.tick(6);
+      }
     }
-    if (n_my > 0) drain(n_my - 1);
+    if (n_my > 0) {
+      tc::mbar_wait(staged, (n_my - 1) & 1);
+      if (lane == 0) {
+        store_grads(n_my - 1);
+        tma::store_wait_all();
+      }
+    }
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      for (int j = 0; j < n_my; ++j) {
+        const int b = j & 1;
+        const uint32_t sq = s0 + L::QK + b * 2 * G::OPER, sk = sq + G::OPER;
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+        tc::mbar_wait(&rot_done[b], (j >> 1) & 1);
+        if (j > 0) tc::mbar_wait(staged, (j - 1) & 1);            // dQ of the previous item has left the S columns
+        tc::fence_after_sync();
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
+        tc::mbar_wait(landed_v, j & 1);
+        tc::mbar_wait(landed_do, j & 1);
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
+        tc::mma_commit(sdp_full);
+        tc::mbar_wait(pds_ready, j & 1);
+        tc::fence_after_sync();
+        const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
+        tc::mma_commit(grads_full);
+      }
+    }
   } else {
     // ------------------------------------------------------------------ compute group
     const int rg = warp & 3, half = warp >> 2;
     const int t = rg * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
     const float scale = a.scale, scale2 = a.scale * LOG2E;
-    const float4* b4 = reinterpret_cast<const float4*>(aux_bias);
+    float* red_delta = reinterpret_cast<float*>(smem + L::RED);
     const bool qrow = t < a.Sq;
     int nblk = (a.Sk + 31) >> 5;
     if (a.causal) nblk = min(nblk, rg + 1);
@@ -598,39 +682,37 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
     if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
     Prof pc;
     pc.init(blockIdx.x == 0 && tid == 96, 0);
-    for (int j = 0; j < n_my; ++j) {
-      pc.tick(0);
-      // ---- rotate Q / K rows in place, start S = Q K^T and dP = dO V^T
-      tc::mbar_wait(landed_qk, j & 1);
-      pc.tick(1);
+    // rotate item j's Q / K rows in place (buffer j & 1) and hand the pair to the MMA warp
+    auto prepare = [&](int j) {
+      const int b = j & 1;
+      pc.tick(8);
+      tc::mbar_wait(&landed_qk[b], (j >> 1) & 1);
+      pc.tick(9);
       if (rc) {
         if (a.pos_is_head) {
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
           if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + (half ? L::K : L::Q), t, rc, tab);
+        rot_row<RC, false>(smem + L::QK + (b * 2 + half) * G::OPER, t, rc, tab);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
-      pc.tick(2);
-      tc::bar_sync(BAR_C, NC);
-      pc.tick(3);
-      if (tid == ISSUER) {
-        tc::fence_after_sync();
-        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
-#pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
-        tc::mbar_wait(landed_dv, j & 1);                            // dO and V follow Q and K through the loader
-#pragma unroll
-        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
-        tc::mma_commit(sdp_full);
-      }
-      tc::mbar_wait(aux_ready, j & 1);
+      tc::mbar_arrive(&rot_done[b]);
+      pc.tick(10);
+    };
+    if (n_my > 0) prepare(0);
+    for (int j = 0; j < n_my; ++j) {
+      const int b = j & 1;
+      const float* aux = reinterpret_cast<const float*>(smem + L::AUX + b * 1024);
+      const float4* b4 = reinterpret_cast<const float4*>(aux);
+      pc.tick(0);
+      tc::mbar_wait(&aux_ready[b], (j >> 1) & 1);
       if (j > 0) tc::mbar_wait(stg_free, (j - 1) & 1);              // P / dS double as the previous item's staging
+      pc.tick(1);
       tc::mbar_wait(sdp_full, j & 1);
       tc::fence_after_sync();
-      pc.tick(4);
-      const float lse2 = aux_lse2[t];
+      pc.tick(2);
+      const float lse2 = aux[128 + t];
       uint32_t pk[32];                                              // this thread's 64 columns of P, bf16 pairs
       float delta = 0.f;                                            // rowsum(P * dP) == rowsum(dO * O)
 #pragma unroll
@@ -646,8 +728,8 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
             tc::tmem_ld_wait();
 #pragma unroll
             for (int e = 0; e < 16; e += 4) {
-              const float4 b = b4[(blk * 32 + hb * 16 + e) >> 2];
-              const float bb[4] = {b.x, b.y, b.z, b.w};
+              const float4 bq = b4[(blk * 32 + hb * 16 + e) >> 2];
+              const float bb[4] = {bq.x, bq.y, bq.z, bq.w};
               float p[4];
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
@@ -670,9 +752,9 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
               make_uint4(pk[i * 16 + q * 4], pk[i * 16 + q * 4 + 1], pk[i * 16 + q * 4 + 2], pk[i * 16 + q * 4 + 3]);
       }
       red_delta[half * 128 + t] = delta;
-      pc.tick(5);
-      tc::bar_sync(BAR_C, NC);
-      pc.tick(6);
+      pc.tick(3);
+      tc::bar_sync(BAR_PAIR + rg, 64);                              // the two halves of this row group only
+      pc.tick(4);
       delta += red_delta[(half ^ 1) * 128 + t];
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
@@ -702,33 +784,23 @@ __global__ void __launch_bounds__(NT, 1) attn2_bwd_kernel(AttnArgs a, int n_item
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
-      pc.tick(7);
-      tc::bar_sync(BAR_C, NC);
-      pc.tick(8);
-      if (tid == ISSUER) {
-        tc::fence_after_sync();
-        const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < kq) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
-        tc::mma_commit(grads_full);
-      }
+      tc::mbar_arrive(pds_ready);                                   // the MMA warp starts dV, dK, dQ
+      pc.tick(5);
+      // next item's rotation hides the gradient MMAs (head-indexed tables are still needed to un-rotate this item)
+      if (j + 1 < n_my && !a.pos_is_head) prepare(j + 1);
+      pc.tick(6);
       tc::mbar_wait(grads_full, j & 1);
       tc::fence_after_sync();
-      pc.tick(9);
+      pc.tick(7);
       // half 0 owns the dQ row, half 1 the dK row (each un-rotates with its own table); dV is split by columns
-      if (half == 0) stage_acc_unrot<DH, RC>(lane_base + T_DQ, stg_x + t * G::PITCH, rc, tab);
-      else           stage_acc_unrot<DH, RC>(lane_base + T_DK, stg_z + t * G::PITCH, rc, tab);
-      stage_acc_cols<HALF>(lane_base + T_DV + half * HALF, stg_y + t * G::PITCH + half * HALF * 2, 1.0f);
+      if (half == 0) stage_acc_unrot_sw<DH, RC>(lane_base + T_DQ, smem + L::P, t, rc, tab);
+      else           stage_acc_unrot_sw<DH, RC>(lane_base + T_DK, smem + L::QK + b * 2 * G::OPER, t, rc, tab);
+      stage_acc_sw<G::CPR / 2>(lane_base + T_DV + half * HALF, smem + L::DS, t, half * (G::CPR / 2), 1.0f);
+      tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(staged);
-      pc.tick(10);
+      if (j + 1 < n_my && a.pos_is_head) prepare(j + 1);
+      pc.tick(11);
     }
   }
   tc::fence_before_sync();
@@ -766,13 +838,24 @@ int attn_tc2_supported(const AttnArgs& a, int backward) {
   return 1;
 }
 
-template <typename Kern>
-static int launch2(Kern kern, size_t smem, const AttnArgs& a, cudaStream_t st) {
+// tensor maps for `count` head views (a 64-column SWIZZLE_128B map and, for Dh = 96, a 32-column SWIZZLE_64B map each)
+template <int DH>
+static int build_maps(CUtensorMap* m, const AttnArgs& a, const HeadView* const* vs, const int* seq, int count) {
+  for (int i = 0; i < count; ++i) {
+    int rc = tma::make_head_map(&m[2 * i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 64);
+    if (rc == 0 && DH > 64) rc = tma::make_head_map(&m[2 * i + 1], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 32);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+template <typename Kern, typename Maps>
+static int launch2(Kern kern, size_t smem, const AttnArgs& a, const Maps& maps, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
   const int64_t items = (int64_t)a.N * a.H;
   const int grid = (int)(items < num_sms() ? items : num_sms());
-  kern<<<grid, t2::NT, smem, st>>>(a, (int)items);
+  kern<<<grid, t2::F_NT, smem, st>>>(a, (int)items, maps);
   MEANT_LAUNCH_CHECK();
   return 0;
 }
@@ -794,14 +877,36 @@ extern "C" int meant_debug_prof(unsigned long long* out64, int reset) {
 }
 namespace meant {
 
+// forward: tensor maps for the q, k, v loads and the o store, then one persistent CTA per SM
+template <int DH, int RC>
+static int launch_fwd(const AttnArgs& a, cudaStream_t st) {
+  t2::FwdMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const HeadView* vs[4] = {&a.q, &a.k, &a.v, &a.o};
+  const int seq[4] = {a.Sq, a.Sk, a.Sk, a.Sq};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 4)) return rc;
+  return launch2(t2::attn2_fwd_kernel<DH, RC>, t2::FwdL<DH>::TOTAL, a, maps, st);
+}
+
+template <int DH, int RC>
+static int launch_bwd(const AttnArgs& a, cudaStream_t st) {
+  t2::BwdMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const HeadView* vs[7] = {&a.q, &a.k, &a.v, &a.o, &a.dq, &a.dk, &a.dv};
+  const int seq[7] = {a.Sq, a.Sk, a.Sk, a.Sq, a.Sq, a.Sk, a.Sk};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7)) return rc;
+  return launch2(t2::attn2_bwd_kernel<DH, RC>, t2::BwdL<DH>::TOTAL, a, maps, st);
+}
+
+// MEANT_EUNSUPPORTED: a view the tensor maps cannot describe (the caller falls back to the multi-tile kernels)
 int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st) {
-  if (a.Dh == 96) return launch2(t2::attn2_fwd_kernel<96, 6>, t2::FwdL<96>::TOTAL, a, st);
-  return launch2(t2::attn2_fwd_kernel<64, 8>, t2::FwdL<64>::TOTAL, a, st);
+  if (a.Dh == 96) return launch_fwd<96, 6>(a, st);
+  return launch_fwd<64, 8>(a, st);
 }
 
 int attn_tc2_bwd(const AttnArgs& a, cudaStream_t st) {
-  if (a.Dh == 96) return launch2(t2::attn2_bwd_kernel<96, 6>, t2::BwdL<96>::TOTAL, a, st);
-  return launch2(t2::attn2_bwd_kernel<64, 8>, t2::BwdL<64>::TOTAL, a, st);
+  if (a.Dh == 96) return launch_bwd<96, 6>(a, st);
+  return launch_bwd<64, 8>(a, st);
 }
 
 }  // namespace meant
