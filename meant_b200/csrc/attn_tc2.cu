@@ -457,7 +457,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 // Shared memory: the Q | K pair is double buffered (item j+1's pair lands while item j computes); V is free for the
 // next item as soon as dP = dO V^T has run, dO as soon as the gradient MMAs have; P and dS are single.  The three
 // gradient tiles are staged (swizzled operand layout, what the TMA store expects) over buffers that are dead by
-// then: dQ over P, dV over dS, dK over this item's Q.
+// then: dQ over this item's K (dead once dQ = dS K has run), dK over its Q, dV over dS -- the Q | K pair is not
+// needed again for two items, so only dV's store stands between this item and the next one's dS.
 template <int DH>
 struct BwdL {
   using G = Geo<DH>;
@@ -515,7 +516,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
   constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 352, T_DQ = 0;   // dQ reuses the consumed S columns
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *landed_qk = bars, *aux_ready = bars + 2, *rot_done = bars + 4, *landed_v = bars + 6, *landed_do = bars + 7,
-           *sdp_full = bars + 8, *pds_ready = bars + 9, *grads_full = bars + 10, *staged = bars + 11, *stg_free = bars + 12;
+           *sdp_full = bars + 8, *pds_ready = bars + 9, *grads_full = bars + 10, *staged = bars + 11, *stg_free = bars + 12,
+           *dq_full = bars + 13, *dq_staged = bars + 14;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
@@ -530,6 +532,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
     tc::mbar_init(grads_full, 1);
     tc::mbar_init(staged, NC);
     tc::mbar_init(stg_free, 1);
+    tc::mbar_init(dq_full, 1);
+    tc::mbar_init(dq_staged, NC / 2);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
@@ -568,9 +572,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
     auto store_grads = [&](int j) {                               // staged gradients of item j -> global (lane 0)
       int h, n2, n1;
       coords(j, h, n2, n1);
-      store_tile(4, sp, h, n2, n1);                               // dq
-      store_tile(5, s0 + L::QK + (j & 1) * 2 * G::OPER, h, n2, n1);   // dk (over this item's Q)
-      store_tile(6, sds, h, n2, n1);                              // dv
+      const uint32_t sq = s0 + L::QK + (j & 1) * 2 * G::OPER;
+      store_tile(6, sds, h, n2, n1);                              // dv (over dS): its own group, released first
+      tma::store_commit();
+      store_tile(4, sq + G::OPER, h, n2, n1);                     // dq (over this item's K)
+      store_tile(5, sq, h, n2, n1);                               // dk (over this item's Q)
       tma::store_commit();
     };
     for (int j = 0; j < n_my; ++j) {
@@ -579,7 +585,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       coords(j, h, n2, n1);
       const int n = n1 * a.n2_count + n2;
       pf.tick(0);
-      if (lane == 0) {       // Q | K pair b: item j-2's dK staging left it in program order (store_wait_read below)
+      if (lane == 0) {       // Q | K pair b still holds item j-2's dQ / dK staging until those stores have read it
+        if (j >= 2) tma::store_wait_read<0>();
         const uint32_t sq = s0 + L::QK + b * 2 * G::OPER;
         tma::mbar_expect_tx(&landed_qk[b], 2 * G::OPER);
         load_tile(0, sq, &landed_qk[b], h, n2, n1);
@@ -620,8 +627,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         pf.tick(5);
         if (lane == 0) {
           store_grads(j - 1);
-          tma::store_wait_read<0>();
-          tc::mbar_arrive(stg_free);                              // P / dS (and that item's Q | K pair) may be rewritten
+          tma::store_wait_read<1>();                              // the dV group has left dS
+          tc::mbar_arrive(stg_free);
         }
         pf.tick(6);
       }
@@ -641,7 +648,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         const uint32_t sq = s0 + L::QK + b * 2 * G::OPER, sk = sq + G::OPER;
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
         tc::mbar_wait(&rot_done[b], (j >> 1) & 1);
-        if (j > 0) tc::mbar_wait(staged, (j - 1) & 1);            // dQ of the previous item has left the S columns
+        if (j > 0) tc::mbar_wait(dq_staged, (j - 1) & 1);         // dQ of the previous item has left the S columns
         tc::fence_after_sync();
 #pragma unroll
         for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
@@ -655,13 +662,14 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
+          if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
+        tc::mma_commit(dq_full);                                  // dQ can be staged while dK, dV still run
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
           if (ks < kq) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
         tc::mma_commit(grads_full);
       }
     }
@@ -707,7 +715,6 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       const float4* b4 = reinterpret_cast<const float4*>(aux);
       pc.tick(0);
       tc::mbar_wait(&aux_ready[b], (j >> 1) & 1);
-      if (j > 0) tc::mbar_wait(stg_free, (j - 1) & 1);              // P / dS double as the previous item's staging
       pc.tick(1);
       tc::mbar_wait(sdp_full, j & 1);
       tc::fence_after_sync();
@@ -756,6 +763,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       tc::bar_sync(BAR_PAIR + rg, 64);                              // the two halves of this row group only
       pc.tick(4);
       delta += red_delta[(half ^ 1) * 128 + t];
+      if (j > 0) tc::mbar_wait(stg_free, (j - 1) & 1);              // dS doubles as the previous item's dV staging
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
@@ -789,12 +797,23 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       // next item's rotation hides the gradient MMAs (head-indexed tables are still needed to un-rotate this item)
       if (j + 1 < n_my && !a.pos_is_head) prepare(j + 1);
       pc.tick(6);
-      tc::mbar_wait(grads_full, j & 1);
-      tc::fence_after_sync();
-      pc.tick(7);
       // half 0 owns the dQ row, half 1 the dK row (each un-rotates with its own table); dV is split by columns
-      if (half == 0) stage_acc_unrot_sw<DH, RC>(lane_base + T_DQ, smem + L::P, t, rc, tab);
-      else           stage_acc_unrot_sw<DH, RC>(lane_base + T_DK, smem + L::QK + b * 2 * G::OPER, t, rc, tab);
+      uint8_t* pair = smem + L::QK + b * 2 * G::OPER;
+      if (half == 0) {
+        tc::mbar_wait(dq_full, j & 1);
+        tc::fence_after_sync();
+        pc.tick(7);
+        stage_acc_unrot_sw<DH, RC>(lane_base + T_DQ, pair + G::OPER, t, rc, tab);      // over K
+        tc::fence_before_sync();
+        tc::mbar_arrive(dq_staged);                                 // the S columns are free for the next item
+        tc::mbar_wait(grads_full, j & 1);
+        tc::fence_after_sync();
+      } else {
+        tc::mbar_wait(grads_full, j & 1);
+        tc::fence_after_sync();
+        pc.tick(7);
+        stage_acc_unrot_sw<DH, RC>(lane_base + T_DK, pair, t, rc, tab);                 // over Q
+      }
       stage_acc_sw<G::CPR / 2>(lane_base + T_DV + half * HALF, smem + L::DS, t, half * (G::CPR / 2), 1.0f);
       tc::fence_async_smem();
       tc::fence_before_sync();
