@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--cpu-batch", type=int, default=2, help="samples per CPU-baseline step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--attn-impl", default="auto", choices=["auto", "exact", "tcgen05"])
-    ap.add_argument("--graph", type=int, default=1, help="capture the step into a CUDA graph (single rank only)")
+    ap.add_argument("--graph", type=int, default=1, help="capture the step into a CUDA graph")
     return ap.parse_args()
 
 
@@ -48,7 +48,7 @@ def workload_config(args, n):
             "lag": LAG, "seq_len": SEQ, "dim": DIM, "heads": HEADS, "vocab": VOCAB,
             "num_encoders": args.encoders, "batch_per_gpu": args.batch, "global_batch": args.batch * n,
             "parallelism": f"dp{n}", "optimizer": "AdamW(fused) + clip_grad_norm 1.0", "mode": "train (dropout on)",
-            "launch": "whole step replayed from one CUDA graph" if (args.graph and n == 1) else "eager launches",
+            "launch": "whole step (incl. the NCCL gradient all-reduces) replayed from one CUDA graph" if args.graph else "eager launches",
             "l2": "no flush needed: each step streams >10 GB of activations/weights, far above the 126 MB L2"}
 
 
@@ -224,7 +224,7 @@ def gpu_run(args):
     torch.manual_seed(0)
     model = mb.meant_tweet(DIM, 4, LAG, CLASSES, nn.Embedding(VOCAB, DIM), num_encoders=args.encoders).to(dev)
     model.train()
-    step = TrainStep(model, bf16=True, graph=bool(args.graph) and world == 1, graph_warmup=min(3, args.warmup))
+    step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=min(3, args.warmup))
     h_tweets, h_mask, h_labels = synth_batch(args.batch, rank, pin=True)
     d_tweets, d_mask, d_labels = (t.to(dev) for t in (h_tweets, h_mask, h_labels))
 
@@ -305,7 +305,12 @@ def gpu_run(args):
         if n == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"], _ = cpu_reference_run(args, steps=2, warmup=1)
         print(json.dumps(line), flush=True)
+    step.close()           # the graph holds NCCL kernels: it has to go before the communicator does
     if world > 1:
+        barrier()
+        sys.stdout.flush()
+        if step.graph:
+            os._exit(0)    # communicator teardown after graph capture can block; every rank is done and in step
         dist.destroy_process_group()
 
 

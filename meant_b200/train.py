@@ -9,9 +9,10 @@ from .ddp import BucketedGradAllReduce, broadcast_parameters
 
 
 class TrainStep:
-    """graph=True (one rank, CUDA): after `graph_warmup` eager steps the whole step -- zero_grad, autocast
-    forward, loss, backward, clip, AdamW -- is captured once into a CUDA graph and replayed, so the ~2000
-    launches of a step cost no host time; inputs are copied into static buffers, dropout masks advance through
+    """graph=True (CUDA): after `graph_warmup` eager steps the whole step -- zero_grad, autocast forward, loss,
+    backward, the bucketed NCCL gradient all-reduces (captured on NCCL's stream, still overlapping backward),
+    clip, AdamW -- is captured once into a CUDA graph and replayed, so the ~2000 launches of a step cost no
+    host time; inputs are copied into static buffers, dropout masks advance through
     a device-resident seed (ops.set_graph_seed), and the bias-gradient kernel replaces autograd's reduction
     (ops.use_fused_linear).  Input shapes and non-tensor arguments must not change between calls."""
 
@@ -24,7 +25,7 @@ class TrainStep:
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group)
         fused = self.params[0].is_cuda
-        self.graph = bool(graph) and fused and self.reducer.world == 1
+        self.graph = bool(graph) and fused
         self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused,
                                      capturable=self.graph)
         self._graph_warmup, self._calls = int(graph_warmup), 0
@@ -77,6 +78,13 @@ class TrainStep:
                     dst.copy_(src, non_blocking=True)
             elif dst is not src and dst != src:
                 raise ValueError("TrainStep(graph=True): non-tensor arguments are fixed after capture")
+
+    def close(self):
+        """Release the captured graph (NCCL communicators cannot be destroyed while a graph holds their kernels)."""
+        if self._g is not None:
+            torch.cuda.synchronize()
+            self._g.reset()
+            self._g, self._calls = None, 0
 
     def __call__(self, labels, *args, **kwargs):
         """One optimisation step; returns the (device) loss tensor (graph mode: a static tensor the next
