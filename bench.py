@@ -148,8 +148,8 @@ def kernel_stats(timers):
 
 
 # ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch of the dominant kernels at THIS workload
-# (profiles/r1d_attn2_full_summary.txt; N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
-NCU_TRAFFIC = {"attn_fwd": 583.4e6, "attn_bwd": 1021.0e6}
+# (profiles/r1h_attn2_summary.txt; N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
+NCU_TRAFFIC = {"attn_fwd": 581.6e6, "attn_bwd": 1017.6e6}
 
 
 def rooflines(args, stats, steps):

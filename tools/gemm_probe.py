@@ -1,0 +1,28 @@
+import torch, torch.nn.functional as F
+torch.manual_seed(0)
+M=98304
+flush = torch.empty(256<<20, dtype=torch.uint8, device="cuda")
+def t(fn, it=20):
+    for _ in range(3): fn()
+    torch.cuda.synchronize()
+    ms=[]
+    for _ in range(it):
+        flush.zero_()
+        a,b=torch.cuda.Event(enable_timing=True),torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize(); ms.append(a.elapsed_time(b))
+    ms.sort(); return ms[len(ms)//2]*1e3
+for n_in,n_out in ((768,768),(768,2304)):
+    x=torch.randn(M,n_in,device="cuda").bfloat16(); w=torch.randn(n_out,n_in,device="cuda").bfloat16()*0.02; b=torch.randn(n_out,device="cuda").bfloat16()
+    wt=w.t().contiguous(); dy=torch.randn(M,n_out,device="cuda").bfloat16()
+    fl=2*M*n_in*n_out
+    r={}
+    r["linear TN+bias"]=t(lambda: F.linear(x,w,b))
+    r["addmm NN+bias"]=t(lambda: torch.addmm(b,x,wt))
+    r["mm NN nobias"]=t(lambda: torch.mm(x,wt))
+    r["linear nobias"]=t(lambda: F.linear(x,w))
+    r["dx = dy@w (NN)"]=t(lambda: torch.mm(dy,w))
+    r["dx = dy@wt.t() (NT)"]=t(lambda: torch.mm(dy,wt.t()))
+    r["dw = dy.t()@x bf16"]=t(lambda: torch.mm(dy.t(),x))
+    r["dw f32 out"]=t(lambda: torch.mm(dy.t(),x,out_dtype=torch.float32))
+    r["dwT = x.t()@dy bf16"]=t(lambda: torch.mm(x.t(),dy))
+    for k,v in r.items(): print(f"{n_in}->{n_out} {k:24s} {v:8.1f} us  {fl/v/1e6:7.1f} TF/s")
