@@ -32,7 +32,7 @@ enum { MEANT_F32 = 0, MEANT_BF16 = 1 };
 enum { MEANT_IMPL_AUTO = 0, MEANT_IMPL_EXACT = 1, MEANT_IMPL_TCGEN05 = 2 };
 
 /* ---- library ------------------------------------------------------------------------- */
-int meant_version(void);                 /* ABI version (2), bumped on any signature change */
+int meant_version(void);                 /* ABI version (3), bumped on any signature change */
 int64_t meant_launch_count(void);        /* kernels launched by this library so far       */
 void meant_reset_launch_count(void);
 
@@ -50,10 +50,12 @@ int meant_rmsnorm_fwd(const void* x, const void* res, const float* gain, void* y
                       const uint64_t* seed_dev, int dtype, meant_stream_t stream);
 /* src = the forward's normalised-input source: x (plain), x (pre_gelu: pre-activation) or
  * sum_out (residual form).  dsum_in (optional) is added to dx: the gradient that reaches the
- * same tensor through the residual path.  dgain[d] (fp32) is ACCUMULATED atomically.       */
+ * same tensor through the residual path.  dgain[d] (fp32) is ACCUMULATED atomically.
+ * dxsum[d] (optional, fp32, zero on entry) receives sum_rows dx: when x came out of an nn.Linear this is that
+ * layer's bias gradient, produced here instead of by a separate reduction over dx.           */
 int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv, const void* dsum_in,
                       void* dx, float* dgain, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
-                      uint64_t seed, const uint64_t* seed_dev, int dtype, meant_stream_t stream);
+                      uint64_t seed, const uint64_t* seed_dev, float* dxsum, int dtype, meant_stream_t stream);
 
 /* ---- LayerNorm: nn.LayerNorm heads (meant/meant_tweet.py:143, meant/meant_vision.py:143) and
  *      TimeSformer PreNorm (src/meant/timesformer_pytorch.py:17-25) ------------------------ */
@@ -119,6 +121,15 @@ int meant_token_shift(const void* x, void* y, int B, int f, int n, int d, int tr
  *      meant/meant.py:61-66):  db[c] (fp32, overwritten) = sum_r dy[r*ld + c] ------------------------- */
 int meant_bias_grad(const void* dy, float* db, int64_t rows, int cols, int64_t ld, int dtype,
                     meant_stream_t stream);
+
+/* ---- token embedding (the `embedding` module of the model constructors, meant/meant_tweet.py:152 `mod(words)`;
+ *      nn.Embedding semantics without padding_idx / max_norm): out[t, :] = W[ids[t], :] cast to `dtype`;
+ *      backward: dW (fp32 [vocab, D], overwritten) = scatter-add of dy rows.  Ids outside [0, vocab) read as a
+ *      zero row and contribute nothing (torch raises a device assert instead). ------------------------------ */
+int meant_embedding_fwd(const int64_t* ids, const float* W, void* out, int64_t tokens, int D, int64_t vocab,
+                        int dtype, meant_stream_t stream);
+int meant_embedding_bwd(const int64_t* ids, const void* dy, float* dW, int64_t tokens, int D, int64_t vocab,
+                        int dtype, meant_stream_t stream);
 
 /* ---- tcgen05 self-test: D[128,N] (fp32) = op(A) op(B)^T for one bf16 tile; a_mn / b_mn select
  *      MN-major operands (A given as [K,128], B as [K,N]) instead of K-major ([128,K], [N,K]).

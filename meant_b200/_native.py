@@ -36,8 +36,10 @@ SIGNATURES = {
     "meant_launch_count": (i64, []),
     "meant_reset_launch_count": (None, []),
     "meant_rmsnorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, f32, u64, vp, i32, vp]),
-    "meant_rmsnorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, f32, u64, vp, i32, vp]),
+    "meant_rmsnorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, f32, u64, vp, vp, i32, vp]),
     "meant_bias_grad": (i32, [vp, vp, i64, i32, i64, i32, vp]),
+    "meant_embedding_fwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
+    "meant_embedding_bwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
     "meant_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp]),
     "meant_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "meant_attn_fwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),

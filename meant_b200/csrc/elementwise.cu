@@ -188,6 +188,57 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const T* __restrict__ dy
   }
 }
 
+// Token embedding lookup (the `embedding` module handed to the model constructors: meant/meant_tweet.py:152,
+// nn.Embedding in bench / tests): out[t, :] = T(W[ids[t], :]) -- the gather writes the compute dtype directly, so no
+// fp32 [tokens, dim] intermediate exists.  One warp per token, 16-byte loads.  Ids outside [0, vocab) give a zero row.
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_fwd_kernel(const int64_t* __restrict__ ids, const float* __restrict__ W,
+                                                            T* __restrict__ out, int64_t tokens, int D, int64_t vocab) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t t = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); t < tokens; t += (int64_t)gridDim.x * 8) {
+    const int64_t id = ids[t];
+    const bool ok = id >= 0 && id < vocab;
+    const float4* src = reinterpret_cast<const float4*>(W + (ok ? id : 0) * D);
+    for (int c = lane; c < D / 4; c += 32) {
+      float4 v = ok ? __ldg(src + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+      if constexpr (sizeof(T) == 4) {
+        reinterpret_cast<float4*>(out + t * D)[c] = v;
+      } else {
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+        uint2 pk;
+        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+        reinterpret_cast<uint2*>(out + t * D)[c] = pk;
+      }
+    }
+  }
+}
+
+// dW[ids[t], :] += dy[t, :]  (dW fp32, zero-filled by the entry point): one warp per token, one 16-byte vector
+// reduction (red.global.add.v4.f32) per 4 columns -- no sort, no segmented scan.
+template <typename T>
+__global__ void __launch_bounds__(256) embedding_bwd_kernel(const int64_t* __restrict__ ids, const T* __restrict__ dy,
+                                                            float* __restrict__ dW, int64_t tokens, int D, int64_t vocab) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t t = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); t < tokens; t += (int64_t)gridDim.x * 8) {
+    const int64_t id = ids[t];
+    if (id < 0 || id >= vocab) continue;
+    float4* dst = reinterpret_cast<float4*>(dW + id * D);
+    for (int c = lane; c < D / 4; c += 32) {
+      float4 v;
+      if constexpr (sizeof(T) == 4) {
+        v = reinterpret_cast<const float4*>(dy + t * D)[c];
+      } else {
+        const uint2 pk = reinterpret_cast<const uint2*>(dy + t * D)[c];
+        const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
+        const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
+        v = make_float4(lo.x, lo.y, hi.x, hi.y);
+      }
+      atomicAdd(dst + c, v);
+    }
+  }
+}
+
 }  // namespace meant
 
 using namespace meant;
@@ -267,6 +318,32 @@ extern "C" int meant_bias_grad(const void* dy, float* db, int64_t rows, int cols
   const int rows_per_cta = (int)(((rows + slabs - 1) / slabs + 7) / 8 * 8);
   dim3 grid(gx, blocks_for(rows, rows_per_cta));
   DISPATCH_T(dtype, (bias_grad_kernel<T><<<grid, 256, 0, st>>>((const T*)dy, db, rows, cols, ld, rows_per_cta)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_embedding_fwd(const int64_t* ids, const float* W, void* out, int64_t tokens, int D, int64_t vocab,
+                                   int dtype, cudaStream_t st) {
+  if (!ids || !W || !out || tokens < 0 || D <= 0 || vocab <= 0) return MEANT_EARG;
+  if (D % 4 || ((uintptr_t)W & 15) || ((uintptr_t)out & 15)) return MEANT_EUNSUPPORTED;
+  if (tokens == 0) return 0;
+  unsigned blocks = blocks_for(tokens, 8);
+  if (blocks > 148u * 16u) blocks = 148u * 16u;
+  DISPATCH_T(dtype, (embedding_fwd_kernel<T><<<blocks, 256, 0, st>>>(ids, W, (T*)out, tokens, D, vocab)));
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int meant_embedding_bwd(const int64_t* ids, const void* dy, float* dW, int64_t tokens, int D, int64_t vocab,
+                                   int dtype, cudaStream_t st) {
+  if (!ids || !dy || !dW || tokens < 0 || D <= 0 || vocab <= 0) return MEANT_EARG;
+  if (D % 4 || ((uintptr_t)dW & 15) || ((uintptr_t)dy & 15)) return MEANT_EUNSUPPORTED;
+  cudaError_t e = cudaMemsetAsync(dW, 0, sizeof(float) * (size_t)vocab * D, st);
+  if (e != cudaSuccess) return (int)e;
+  if (tokens == 0) return 0;
+  unsigned blocks = blocks_for(tokens, 8);
+  if (blocks > 148u * 16u) blocks = 148u * 16u;
+  DISPATCH_T(dtype, (embedding_bwd_kernel<T><<<blocks, 256, 0, st>>>(ids, (const T*)dy, dW, tokens, D, vocab)));
   MEANT_LAUNCH_CHECK();
   return 0;
 }

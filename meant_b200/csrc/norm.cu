@@ -188,8 +188,10 @@ struct NormBwdArgs {
 // The row stays PACKED (bf16/fp32 vectors) between the two sweeps, so only the gain, the per-column
 // gradient accumulators and (GELU form) the activation / its derivative live in fp32 registers:
 // 3-4 CTAs of 4 warps per SM keep >= 36 KB of loads in flight.
-template <typename T, int CHUNKS, bool LN, bool GELU>
-__global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(NormBwdArgs a) {
+// COLSUM (RMSNorm only): also accumulate sum_rows dx into a.dbias -- the bias gradient of the Linear that produced x.
+template <typename T, int CHUNKS, bool LN, bool GELU, bool COLSUM = false>
+__global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_kernel(NormBwdArgs a) {
+  static_assert(!(LN && COLSUM), "the dbias accumulators serve LayerNorm's bias OR the column sum of dx");
   uint64_t seed = a.seed;
   if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   constexpr int V = Vec16<T>::N;
@@ -252,7 +254,7 @@ __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(Nor
         t1 = fmaf(gd, sv, t1);
         t2 += gd;
         dg[c][i] = fmaf(gy[i], sv * (LN ? 1.f : rinv), dg[c][i]);
-        db[c][i] += gy[i];
+        if (LN) db[c][i] += gy[i];
       }
     }
     t1 = warp_sum(t1);
@@ -279,6 +281,7 @@ __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(Nor
         if (GELU) ds *= gk[c][i];
         if (dsi) ds += sv[i];
         o[i] = ds;
+        if (COLSUM) db[c][i] += ds;
       }
       Vec16<T> ov;
       ov.pack(o);
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(128, (GELU || LN) ? 3 : 4) norm_bwd_kernel(Nor
   }
   // block-level reduction of the per-warp column sums, then one atomic per column per block
 #pragma unroll 1
-  for (int pass = 0; pass < (LN ? 2 : 1); ++pass) {
+  for (int pass = 0; pass < ((LN || COLSUM) ? 2 : 1); ++pass) {
     __syncthreads();
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c)
@@ -390,7 +393,15 @@ static int launch_bwd(const NormBwdArgs& a, cudaStream_t st) {
   const bool gelu = a.pre_gelu != 0;
   bool done = false;
   if constexpr (!LN) {
-    if (chunks == 3 && gelu) { norm_bwd_kernel<T, 3, false, true><<<g, 128, 0, st>>>(a); done = true; }
+    const bool colsum = a.dbias != nullptr;
+    if (chunks == 3 && colsum) {
+      if (g > 148 * 3) g = 148 * 3;
+      if (gelu) norm_bwd_kernel<T, 3, false, true, true><<<g, 128, 0, st>>>(a);
+      else      norm_bwd_kernel<T, 3, false, false, true><<<g, 128, 0, st>>>(a);
+      done = true;
+    } else if (colsum) {
+      return MEANT_EUNSUPPORTED;    // the entry point falls back to a separate column-sum launch
+    } else if (chunks == 3 && gelu) { norm_bwd_kernel<T, 3, false, true><<<g, 128, 0, st>>>(a); done = true; }
   }
   if (done) {}
   else if (chunks == 3 && !gelu) norm_bwd_kernel<T, 3, LN, false><<<g, 128, 0, st>>>(a);
@@ -419,16 +430,21 @@ extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* ga
 
 extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* gain, const float* rinv,
                                  const void* dsum_in, void* dx, float* dgain, int64_t rows, int d, float eps,
-                                 int pre_gelu, float drop_p, uint64_t seed, const uint64_t* seed_dev, int dtype,
-                                 cudaStream_t stream) {
+                                 int pre_gelu, float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dxsum,
+                                 int dtype, cudaStream_t stream) {
   if (!dy || !src || !gain || !rinv || !dx || !dgain || rows < 0 || d <= 0) return MEANT_EARG;
   if (rows == 0) return 0;
-  NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, nullptr, rows, d, eps, pre_gelu,
+  NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, dxsum, rows, d, eps, pre_gelu,
                 drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
-             reinterpret_cast<const unsigned long long*>(seed_dev)};
-  if (dtype == MEANT_DT_F32) return launch_bwd<float, false>(a, stream);
-  if (dtype == MEANT_DT_BF16) return launch_bwd<__nv_bfloat16, false>(a, stream);
-  return MEANT_EUNSUPPORTED;
+                reinterpret_cast<const unsigned long long*>(seed_dev)};
+  if (dtype != MEANT_DT_F32 && dtype != MEANT_DT_BF16) return MEANT_EUNSUPPORTED;
+  int rc = dtype == MEANT_DT_F32 ? launch_bwd<float, false>(a, stream) : launch_bwd<__nv_bfloat16, false>(a, stream);
+  if (rc == MEANT_EUNSUPPORTED && dxsum) {   // row shapes without a fused column sum: one extra streaming pass over dx
+    a.dbias = nullptr;
+    rc = dtype == MEANT_DT_F32 ? launch_bwd<float, false>(a, stream) : launch_bwd<__nv_bfloat16, false>(a, stream);
+    if (rc == 0) rc = meant_bias_grad(dx, dxsum, rows, d, d, dtype, stream);
+  }
+  return rc;
 }
 
 extern "C" int meant_layernorm_fwd(const void* x, const float* gain, const float* bias, void* y, float* mean,

@@ -170,7 +170,7 @@ class meant(nn.Module):
         b = images.shape[0]
         words = tweets.reshape(b * self.lag, tweets.shape[2])
         for mod in self.embedding:
-            words = mod(words)
+            words = ops.embed(mod, words)
         if attention_mask is not None:
             attention_mask = attention_mask.reshape(b * self.lag, attention_mask.shape[2])
         words = _run_stack(self.languageEncoders, words, attention_mask)

@@ -49,7 +49,7 @@ class meant_tweet(nn.Module):
         if attention_mask is not None:   # the reference requires it (meant/meant_tweet.py:150)
             attention_mask = attention_mask.reshape(b * self.lag, attention_mask.shape[2])
         for mod in self.embedding:
-            words = mod(words)
+            words = ops.embed(mod, words)
         words = _run_stack(self.languageEncoders, words, attention_mask)
         t = ops.mean_pool(words).view(b, self.lag, -1)
         for enc in self.temporal_encoding:

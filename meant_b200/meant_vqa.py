@@ -34,7 +34,7 @@ class meant_vqa(nn.Module):
         words = kw.get("input_ids", tweets)
         images = kw.get("pixels", images)
         for mod in self.embedding:
-            words = mod(words)
+            words = ops.embed(mod, words)
         words = _run_stack(self.languageEncoders, words, attention_mask)
         img = _run_stack(self.visionEncoders, self.patchEmbed(images))
         t = torch.cat((ops.mean_pool(words), ops.mean_pool(img)), dim=1)
@@ -55,5 +55,5 @@ class meant_language_pretrainer(nn.Module):
 
     def forward(self, words, attention_mask=None):
         for mod in self.embedding:
-            words = mod(words)
+            words = ops.embed(mod, words)
         return self.mlm_head(_run_stack(self.languageEncoders, words, attention_mask))

@@ -79,10 +79,15 @@ class _RMSNormFn(torch.autograd.Function):
         ds = dsum.to(src.dtype).contiguous() if dsum is not None else None
         dx = torch.empty_like(src)
         dgain = torch.zeros(d, dtype=torch.float32, device=src.device)
-        tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}"
+        # with the Linear wrapper active the kernel also sums dx over rows: if x came out of a Linear, that is the
+        # layer's bias gradient (picked up by _LinearFn.backward through the tag below)
+        dxsum = torch.zeros(d, dtype=torch.float32, device=src.device) if _fused_linear and xdt == src.dtype else None
+        tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}" + ("/colsum" if dxsum is not None else "")
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_bwd, nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv),
                           nv.ptr(ds), nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
-                          nv.ptr(ctx.sdev), nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+                          nv.ptr(ctx.sdev), nv.ptr(dxsum), nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+        if dxsum is not None:
+            dx._meant_colsum = (dxsum, dx._version)     # valid only while dx is not modified (version check)
         return dx.to(xdt), (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
 
 
@@ -142,6 +147,9 @@ class _LinearFn(torch.autograd.Function):
         xc, wc = ctx.saved_tensors
         xdt, wdt, bdt = ctx.cfg
         n_out, n_in = wc.shape
+        colsum = getattr(dy, "_meant_colsum", None)       # left by _RMSNormFn.backward: sum_rows of this very tensor
+        if colsum is not None and (colsum[1] != dy._version or colsum[0].numel() != n_out or dy.dtype != wc.dtype):
+            colsum = None
         with torch.autocast("cuda", enabled=False):
             dy2 = dy.to(wc.dtype).reshape(-1, n_out)
             if dy2.stride(-1) != 1 or dy2.stride(0) % 8 or dy2.data_ptr() % 16:
@@ -152,7 +160,9 @@ class _LinearFn(torch.autograd.Function):
                 dx = torch.mm(dy2, wc).view(xc.shape).to(xdt)
             if ctx.needs_input_grad[1]:
                 dw = _mm_f32(dy2.t(), x2).to(wdt)
-            if bdt is not None and ctx.needs_input_grad[2]:
+            if bdt is not None and ctx.needs_input_grad[2] and colsum is not None:
+                db = colsum[0].to(bdt)
+            elif bdt is not None and ctx.needs_input_grad[2]:
                 db32 = torch.empty(n_out, dtype=torch.float32, device=dy2.device)
                 nv.check(nv.timed(f"bias_grad/r{dy2.shape[0]}/c{n_out}", nv.lib().meant_bias_grad, nv.ptr(dy2), nv.ptr(db32),
                                   dy2.shape[0], n_out, dy2.stride(0), nv.dt(dy2), nv.stream()), "meant_bias_grad")
@@ -175,6 +185,41 @@ def linear(x, weight, bias=None):
             (weight.shape[0] % 8 == 0) and x.numel() // x.shape[-1] >= 1024:
         return _LinearFn.apply(x, weight, bias)
     return torch.nn.functional.linear(x, weight, bias)
+
+
+# ---------------------------------------------------------------------------- Embedding
+class _EmbeddingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, weight, dtype):
+        ids2 = ids.reshape(-1).contiguous()
+        out = torch.empty(ids2.numel(), weight.shape[1], dtype=dtype, device=weight.device)
+        nv.check(nv.lib().meant_embedding_fwd(nv.ptr(ids2), nv.ptr(weight), nv.ptr(out), ids2.numel(), weight.shape[1],
+                                              weight.shape[0], nv.dt(out), nv.stream()), "meant_embedding_fwd")
+        ctx.save_for_backward(ids2)
+        ctx.shape = weight.shape
+        return out.view(*ids.shape, weight.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        (ids2,) = ctx.saved_tensors
+        dy2 = dy.reshape(-1, ctx.shape[1]).contiguous()
+        dw = torch.empty(ctx.shape, dtype=torch.float32, device=dy.device)
+        nv.check(nv.timed(f"embedding_bwd/t{ids2.numel()}", nv.lib().meant_embedding_bwd, nv.ptr(ids2), nv.ptr(dy2),
+                          nv.ptr(dw), ids2.numel(), ctx.shape[1], ctx.shape[0], nv.dt(dy2), nv.stream()),
+                 "meant_embedding_bwd")
+        return None, dw, None
+
+
+def embed(mod, ids):
+    """The model's `embedding` module applied to token ids (meant/meant_tweet.py:152).  A plain nn.Embedding on the
+    GPU runs the gather kernel, which writes the compute dtype directly, and a scatter-add backward; any other module
+    (e.g. a full BERT embedding block) is called as is."""
+    w = getattr(mod, "weight", None)
+    if type(mod) is torch.nn.Embedding and mod.padding_idx is None and mod.max_norm is None and not mod.sparse \
+            and not mod.scale_grad_by_freq and w.is_cuda and w.dtype == torch.float32 and w.shape[1] % 8 == 0 \
+            and w.is_contiguous() and ids.dtype == torch.int64:
+        return _EmbeddingFn.apply(ids, w, compute_dtype(w))
+    return mod(ids)
 
 
 # ---------------------------------------------------------------------------- LayerNorm

@@ -134,3 +134,64 @@ def test_graph_step_train_mode_runs_and_learns():
     assert all(l == l for l in losses)                       # finite
     assert len(set(round(l, 6) for l in losses[3:])) > 1     # replays are not frozen
     assert min(losses[6:]) < losses[0]
+
+
+@pytest.mark.parametrize("autocast", [True, False])
+def test_embedding_matches_torch(autocast):
+    from meant_b200 import ops
+    torch.manual_seed(1)
+    emb = nn.Embedding(5000, 768).cuda()
+    ids = torch.randint(0, 5000, (7, 3, 128), device="cuda")
+    ids[0, 0, :64] = 17                                      # heavy collisions on one row
+    dy = torch.randn(7, 3, 128, 768, device="cuda")
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast):
+        got = ops.embed(emb, ids)
+    assert got.dtype == (torch.bfloat16 if autocast else torch.float32)
+    ref = emb(ids)
+    assert torch.equal(got.float(), ref.to(got.dtype).float())
+    got.backward(dy.to(got.dtype))
+    g = emb.weight.grad.clone()
+    emb.weight.grad = None
+    ref.backward(dy.to(got.dtype).float())
+    assert float((g - emb.weight.grad).abs().max()) <= 1e-3 * max(1.0, float(emb.weight.grad.abs().max()))
+
+
+def test_embedding_other_modules_pass_through():
+    from meant_b200 import ops
+    emb = nn.Sequential(nn.Embedding(100, 64), nn.LayerNorm(64)).cuda()
+    ids = torch.randint(0, 100, (2, 5), device="cuda")
+    assert torch.equal(ops.embed(emb, ids), emb(ids))
+
+
+def test_norm_backward_supplies_linear_bias_gradient():
+    """Linear -> RMSNorm(+GELU/dropout/residual): with the Linear wrapper active the norm's backward kernel also
+    sums dx over rows and the Linear's backward uses it instead of launching the column-sum kernel."""
+    from meant_b200 import ops
+    nv = _lib()
+    torch.manual_seed(0)
+    lin = nn.Linear(768, 768).cuda()
+    gain = torch.rand(768, device="cuda", requires_grad=True)
+    x = torch.randn(4096, 768, device="cuda", requires_grad=True)
+    res = torch.randn(4096, 768, device="cuda").bfloat16()
+    dz = torch.randn(4096, 768, device="cuda").bfloat16()
+
+    def run(fused, **kw):
+        ops.use_fused_linear(fused)
+        try:
+            for t in (x, lin.weight, lin.bias, gain):
+                t.grad = None
+            nv.reset_launch_count()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                z = ops.rms_norm(ops.linear(x, lin.weight, lin.bias), gain, **kw)
+            z = z[0] if isinstance(z, tuple) else z
+            z.backward(dz)
+            return lin.bias.grad.clone(), x.grad.clone(), nv.launch_count()
+        finally:
+            ops.use_fused_linear(False)
+
+    for kw in ({}, {"pre_gelu": True}, {"residual": res}):
+        b1, x1, n1 = run(True, **kw)
+        b0, x0, n0 = run(False, **kw)
+        assert n1 == 2                                   # norm forward + norm backward: no bias_grad launch
+        assert float((b1 - b0).abs().max()) <= 2e-2 * max(1.0, float(b0.abs().max()))
+        assert float((x1 - x0).abs().max()) <= 2e-2 * max(1.0, float(x0.abs().max()))
