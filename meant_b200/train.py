@@ -24,7 +24,7 @@ class TrainStep:
         broadcast_parameters(model, 0, group)
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group)
-        fused = self.params[0].is_cuda
+        fused = self._fused = self.params[0].is_cuda
         self.graph = bool(graph) and fused
         self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused,
                                      capturable=self.graph)
@@ -43,7 +43,13 @@ class TrainStep:
         loss = F.cross_entropy(out.float(), labels)
         loss.backward()
         self.reducer.finish()
-        if self.max_grad_norm:
+        if self.max_grad_norm and self._fused:
+            # clip_grad_norm_ without its own pass over the gradients: fused AdamW divides every gradient by
+            # `grad_scale` (and writes it back) inside its update kernel, so the clip coefficient rides along
+            grads = [p.grad for p in self.params if p.grad is not None]
+            total = torch.linalg.vector_norm(torch.stack(torch._foreach_norm(grads)))
+            self.opt.grad_scale = torch.clamp((total + 1e-6) / self.max_grad_norm, min=1.0).float().reshape(())
+        elif self.max_grad_norm:
             torch.nn.utils.clip_grad_norm_(self.params, self.max_grad_norm, foreach=True)
         self.opt.step()
         return loss.detach()

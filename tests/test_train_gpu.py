@@ -195,3 +195,25 @@ def test_norm_backward_supplies_linear_bias_gradient():
         assert n1 == 2                                   # norm forward + norm backward: no bias_grad launch
         assert float((b1 - b0).abs().max()) <= 2e-2 * max(1.0, float(b0.abs().max()))
         assert float((x1 - x0).abs().max()) <= 2e-2 * max(1.0, float(x0.abs().max()))
+
+
+def test_clip_folded_into_adamw_matches_clip_grad_norm():
+    from meant_b200.train import TrainStep
+    torch.manual_seed(0)
+    ref = nn.Sequential(nn.Linear(64, 64), nn.Tanh(), nn.Linear(64, 3)).cuda()
+    mine = nn.Sequential(nn.Linear(64, 64), nn.Tanh(), nn.Linear(64, 3)).cuda()
+    mine.load_state_dict(ref.state_dict())
+    x = torch.randn(32, 64, device="cuda") * 30.0            # large gradients: the clip is active
+    y = torch.randint(0, 3, (32,), device="cuda")
+    opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.0, fused=True)
+    step = TrainStep(mine, lr=1e-2, bf16=False, max_grad_norm=1.0)
+    for _ in range(3):
+        opt.zero_grad()
+        F.cross_entropy(ref(x), y).backward()
+        norm = torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+        opt.step()
+        step(y, x)
+    assert float(norm) > 1.0
+    for a, b in zip(ref.parameters(), mine.parameters()):
+        assert torch.allclose(a, b, atol=1e-6, rtol=1e-5)
+        assert torch.allclose(a.grad, b.grad, atol=1e-7, rtol=1e-4)       # the clipped gradient is written back
