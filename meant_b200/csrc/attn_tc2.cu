@@ -120,23 +120,39 @@ __device__ __forceinline__ void load_tab(RotTab<RC>& T, const float* cs, const f
 // Rotate (INV = false) or un-rotate (transpose rotation, INV = true) the first rc chunks of one
 // row r of an operand tile in place (RC <= 8: the rotated chunks all live in the SWIZZLE_128B sub-tile).
 template <int RC, bool INV>
+__device__ __forceinline__ void rot_chunk(uint4& raw, int ch, const RotTab<RC>& T) {
+  __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 x = __bfloat1622float2(h2[i]);
+    const float2 c = __half22float2(T.c[ch * 4 + i]), s = __half22float2(T.s[ch * 4 + i]);
+    float y0, y1;
+    if (!INV) { y0 = x.x * c.x - x.y * s.x; y1 = x.y * c.y + x.x * s.y; }
+    else      { y0 = x.x * c.x + x.y * s.y; y1 = x.y * c.y - x.x * s.x; }
+    h2[i] = __floats2bfloat162_rn(y0, y1);
+  }
+}
+
+template <int RC, bool INV>
 __device__ __forceinline__ void rot_row(uint8_t* tile, int r, int rc, const RotTab<RC>& T) {
   static_assert(RC <= 8, "rotated chunks must stay in the first sub-tile");
+  if (rc == RC) {          // the usual case (rot_dim = 48 of Dh = 96, full Dh = 64): all loads first, no guards
+    uint4 raw[RC];
+#pragma unroll
+    for (int ch = 0; ch < RC; ++ch) raw[ch] = *reinterpret_cast<const uint4*>(tile + tc::sw128_off(r, ch));
+#pragma unroll
+    for (int ch = 0; ch < RC; ++ch) {
+      rot_chunk<RC, INV>(raw[ch], ch, T);
+      *reinterpret_cast<uint4*>(tile + tc::sw128_off(r, ch)) = raw[ch];
+    }
+    return;
+  }
 #pragma unroll
   for (int ch = 0; ch < RC; ++ch) {
     if (ch < rc) {
       uint4* p = reinterpret_cast<uint4*>(tile + tc::sw128_off(r, ch));
       uint4 raw = *p;
-      __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float2 x = __bfloat1622float2(h2[i]);
-        const float2 c = __half22float2(T.c[ch * 4 + i]), s = __half22float2(T.s[ch * 4 + i]);
-        float y0, y1;
-        if (!INV) { y0 = x.x * c.x - x.y * s.x; y1 = x.y * c.y + x.x * s.y; }
-        else      { y0 = x.x * c.x + x.y * s.y; y1 = x.y * c.y - x.x * s.x; }
-        h2[i] = __floats2bfloat162_rn(y0, y1);
-      }
+      rot_chunk<RC, INV>(raw, ch, T);
       *p = raw;
     }
   }
@@ -375,16 +391,20 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
           float sv[32];
           tc::tmem_ld32(ts + blk * 32, sv);
           tc::tmem_ld_wait();
-          const int lim = (a.causal && blk == rg) ? lane : 31;      // diagonal block: keys after the query are masked
+          const bool diag = a.causal && blk == rg;                  // diagonal block: keys after the query are masked
 #pragma unroll
           for (int e = 0; e < 32; e += 4) {
             const float4 b = b4[(blk * 32 + e) >> 2];
             const float bb[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const float v = fmaf(sv[e + u], scale2, bb[u]);
-              m = fmaxf(m, e + u > lim ? -CUDART_INF_F : v);
-            }
+            for (int u = 0; u < 4; ++u) sv[e + u] = fmaf(sv[e + u], scale2, bb[u]);
+          }
+          if (diag) {                                               // warp-uniform
+#pragma unroll
+            for (int e = 0; e < 32; ++e) m = fmaxf(m, e > lane ? -CUDART_INF_F : sv[e]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) m = fmaxf(m, sv[e]);
           }
         }
       }
@@ -403,7 +423,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
           float sv[32];
           tc::tmem_ld32(ts + blk * 32, sv);
           tc::tmem_ld_wait();
-          const int lim = (a.causal && blk == rg) ? lane : 31;
+          const bool diag = a.causal && blk == rg;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const float4 ba = b4[(blk * 32 + q * 8) >> 2], bc = b4[((blk * 32 + q * 8) >> 2) + 1];
@@ -413,9 +433,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int e = q * 8 + 2 * u;
-              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u]) - m_use), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1]) - m_use);
-              if (e > lim) p0 = 0.f;
-              if (e + 1 > lim) p1 = 0.f;
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - m_use)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - m_use));
+              if (diag) {                                           // warp-uniform: off-diagonal blocks skip the masking
+                if (e > lane) p0 = 0.f;
+                if (e + 1 > lane) p1 = 0.f;
+              }
               l0 += p0;
               l1 += p1;
               ph[u] = __floats2bfloat162_rn(p0, p1);
@@ -727,6 +749,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         const int blk = 2 * i + half;
         if (blk < nblk) {
           const int lim = !qrow ? -1 : ((a.causal && blk == rg) ? lane : 31);
+          const bool masked = (a.causal && blk == rg) || rg * 32 + 31 >= a.Sq;   // warp-uniform: most blocks skip the test
 #pragma unroll
           for (int hb = 0; hb < 2; ++hb) {                          // 16 columns at a time keeps the live set small
             float sv16[16], dp[16];
@@ -741,7 +764,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
                 p[u] = tc::ex2(fmaf(sv16[e + u], scale2, bb[u]) - lse2);
-                if (hb * 16 + e + u > lim) p[u] = 0.f;
+                if (masked && hb * 16 + e + u > lim) p[u] = 0.f;
                 delta = fmaf(p[u], dp[e + u], delta);
               }
               const __nv_bfloat162 p01 = __floats2bfloat162_rn(p[0], p[1]), p23 = __floats2bfloat162_rn(p[2], p[3]);
