@@ -476,8 +476,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 }
 
 // ============================================================================== backward
-// Shared memory: the Q | K pair is double buffered (item j+1's pair lands while item j computes); V is free for the
-// next item as soon as dP = dO V^T has run, dO as soon as the gradient MMAs have; P and dS are single.  The three
+// Shared memory: the Q | K pair is double buffered (item j+1's pair lands while item j computes).  V and dO swap two
+// slots: V(j)'s slot is free as soon as dP = dO V^T has run and takes dO(j+1); dO(j)'s slot is free as soon as
+// dV = P^T dO has run (issued right after pass 1, under pass 2) and takes V(j+1).  P and dS are single.  The three
 // gradient tiles are staged (swizzled operand layout, what the TMA store expects) over buffers that are dead by
 // then: dQ over this item's K (dead once dQ = dS K has run), dK over its Q, dV over dS -- the Q | K pair is not
 // needed again for two items, so only dV's store stands between this item and the next one's dS.
@@ -485,11 +486,12 @@ template <int DH>
 struct BwdL {
   using G = Geo<DH>;
   static constexpr uint32_t QK = 0;                            // [2][Q | K]
-  static constexpr uint32_t V = 4 * G::OPER, DO = 5 * G::OPER, P = 6 * G::OPER, DS = P + G::PBUF;
+  static constexpr uint32_t VD = 4 * G::OPER;                  // [2]: V(j) in slot j & 1, dO(j) in the other one
+  static constexpr uint32_t P = 6 * G::OPER, DS = P + G::PBUF;
   static constexpr uint32_t AUX = DS + G::PBUF;                // [2][bias2[128] | lse*log2e[128]], then delta exchange [2][128]
   static constexpr uint32_t RED = AUX + 2048;
   static constexpr uint32_t BARS = RED + 1024;
-  static constexpr uint32_t TOTAL = BARS + 128 + 1024;          // + alignment slack
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;          // + alignment slack
   static_assert(G::OPER <= G::PBUF, "gradient staging must fit in the P / dS buffers");
   static_assert(TOTAL <= 232448, "exceeds the 227 KB of shared memory a CTA can opt in to");
 };
@@ -539,7 +541,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
   uint64_t *landed_qk = bars, *aux_ready = bars + 2, *rot_done = bars + 4, *landed_v = bars + 6, *landed_do = bars + 7,
            *sdp_full = bars + 8, *pds_ready = bars + 9, *grads_full = bars + 10, *staged = bars + 11, *stg_free = bars + 12,
-           *dq_full = bars + 13, *dq_staged = bars + 14;
+           *dq_full = bars + 13, *dq_staged = bars + 14, *p_ready = bars + 15, *dv_done = bars + 16;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
@@ -556,6 +558,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
     tc::mbar_init(stg_free, 1);
     tc::mbar_init(dq_full, 1);
     tc::mbar_init(dq_staged, NC / 2);
+    tc::mbar_init(p_ready, NC);
+    tc::mbar_init(dv_done, 1);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
@@ -566,7 +570,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
   const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int rc = a.qcos ? a.rot_dim / 8 : 0;
   const uint32_t s0 = tc::smem_u32(smem);
-  const uint32_t sv = s0 + L::V, sdo = s0 + L::DO, sp = s0 + L::P, sds = s0 + L::DS;
+  const uint32_t svd = s0 + L::VD, sp = s0 + L::P, sds = s0 + L::DS;
 
   if (warp == F_PROD) {
     // ------------------------------------------------------------------ producer warp
@@ -615,11 +619,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         load_tile(1, sq + G::OPER, &landed_qk[b], h, n2, n1);
       }
       pf.tick(1);
-      if (j > 0) tc::mbar_wait(sdp_full, (j - 1) & 1);            // V is free once dP of the previous item has run
+      if (j > 0) tc::mbar_wait(sdp_full, (j - 1) & 1);            // V(j-1)'s slot is free once dP of that item has run
       pf.tick(2);
       if (lane == 0) {
-        tma::mbar_expect_tx(landed_v, G::OPER);
-        load_tile(2, sv, landed_v, h, n2, n1);
+        tma::mbar_expect_tx(landed_do, G::OPER);
+        load_tile(3, svd + (b ^ 1) * G::OPER, landed_do, h, n2, n1);
       }
       {
         const int k0 = lane * 4;
@@ -638,11 +642,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         tc::mbar_arrive(&aux_ready[b]);
       }
       pf.tick(3);
-      if (j > 0) tc::mbar_wait(grads_full, (j - 1) & 1);          // dO is free once the previous gradient MMAs have run
+      if (j > 0) tc::mbar_wait(dv_done, (j - 1) & 1);             // dO(j-1)'s slot is free once dV of that item has run
       pf.tick(4);
       if (lane == 0) {
-        tma::mbar_expect_tx(landed_do, G::OPER);
-        load_tile(3, sdo, landed_do, h, n2, n1);
+        tma::mbar_expect_tx(landed_v, G::OPER);
+        load_tile(2, svd + b * G::OPER, landed_v, h, n2, n1);
       }
       if (j > 0) {
         tc::mbar_wait(staged, (j - 1) & 1);
@@ -668,6 +672,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       for (int j = 0; j < n_my; ++j) {
         const int b = j & 1;
         const uint32_t sq = s0 + L::QK + b * 2 * G::OPER, sk = sq + G::OPER;
+        const uint32_t sv = svd + b * G::OPER, sdo = svd + (b ^ 1) * G::OPER;
         constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
         tc::mbar_wait(&rot_done[b], (j >> 1) & 1);
         if (j > 0) tc::mbar_wait(dq_staged, (j - 1) & 1);         // dQ of the previous item has left the S columns
@@ -679,9 +684,15 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
         for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
         tc::mma_commit(sdp_full);
+        const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
+        tc::mbar_wait(p_ready, j & 1);                            // P is complete after pass 1: dV runs under pass 2
+        tc::fence_after_sync();
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
+        tc::mma_commit(dv_done);
         tc::mbar_wait(pds_ready, j & 1);
         tc::fence_after_sync();
-        const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
           if (ks < kk) mma_oper_mn<DH>(tmem + T_DQ, desc_p_k(sds, ks), sk, ks, 0, ks > 0);    // dQ = dS K
@@ -689,9 +700,6 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
           if (ks < kq) mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, ks > 0);   // dK = dS^T Q
-#pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          if (ks < kq) mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, ks > 0);   // dV = P^T dO
         tc::mma_commit(grads_full);
       }
     }
@@ -782,6 +790,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
               make_uint4(pk[i * 16 + q * 4], pk[i * 16 + q * 4 + 1], pk[i * 16 + q * 4 + 2], pk[i * 16 + q * 4 + 3]);
       }
       red_delta[half * 128 + t] = delta;
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(p_ready);                                     // the MMA warp starts dV = P^T dO
       pc.tick(3);
       tc::bar_sync(BAR_PAIR + rg, 64);                              // the two halves of this row group only
       pc.tick(4);

@@ -73,28 +73,41 @@ __device__ __forceinline__ float warp_max(float v) {
 // Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, i.e. fp32 round-off level) on the SFU: one ex2 and one
 // rcp per element instead of erff's ~40 instructions, which made the GELU-fused norm kernels
 // issue-bound rather than HBM-bound.  exp(-x^2/2) is shared between the erf tail and the Gaussian pdf.
+// tail = (1 - erf(|x| / sqrt 2)) / 2 and e = exp(-x^2 / 2): the 1/sqrt 2 and the 1/2 are folded into the constants.
+__device__ __forceinline__ void gelu_tail(float x, float& tail, float& e) {
+  float t;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170f));               // exp(-x^2/2)
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(fabsf(x), 0.3275911f * 0.70710678118654752f, 1.0f)));
+  float poly = fmaf(t, 0.5f * 1.061405429f, 0.5f * -1.453152027f);
+  poly = fmaf(poly, t, 0.5f * 1.421413741f);
+  poly = fmaf(poly, t, 0.5f * -0.284496736f);
+  poly = fmaf(poly, t, 0.5f * 0.254829592f);
+  tail = poly * t * e;
+}
 __device__ __forceinline__ void gelu_parts(float x, float& cdf, float& pdf) {
-  const float z = fabsf(x) * 0.70710678118654752f;
-  float e, t;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-z * z * 1.4426950408889634f));   // exp(-x^2/2)
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
-  float poly = fmaf(t, 1.061405429f, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float tail = 0.5f * poly * t * e;              // (1 - erf(z)) / 2
+  float tail, e;
+  gelu_tail(x, tail, e);
   cdf = x >= 0.f ? 1.0f - tail : tail;
   pdf = 0.39894228040143268f * e;
 }
+// x * cdf(x) = max(x, 0) - |x| * tail
 __device__ __forceinline__ float gelu_f(float x) {
-  float cdf, pdf;
-  gelu_parts(x, cdf, pdf);
-  return x * cdf;
+  float tail, e;
+  gelu_tail(x, tail, e);
+  return fmaf(-fabsf(x), tail, fmaxf(x, 0.f));
 }
 __device__ __forceinline__ float gelu_grad_f(float x) {
   float cdf, pdf;
   gelu_parts(x, cdf, pdf);
   return fmaf(x, pdf, cdf);
+}
+// activation and derivative together (the GELU-fused norm backward)
+__device__ __forceinline__ void gelu_val_grad(float x, float& val, float& grad) {
+  float tail, e;
+  gelu_tail(x, tail, e);
+  val = fmaf(-fabsf(x), tail, fmaxf(x, 0.f));
+  const float cdf = x >= 0.f ? 1.0f - tail : tail;
+  grad = fmaf(x * 0.39894228040143268f, e, cdf);
 }
 
 // Counter-based dropout mask, regenerated in backward: one 32-bit hash per PAIR of consecutive
@@ -113,6 +126,12 @@ __device__ __forceinline__ void drop_pair(uint64_t seed, uint64_t pair_idx, uint
   const uint32_t h = hash_pair(seed, pair_idx);
   k0 = (h & 0xffffu) >= thr16 ? inv_keep : 0.0f;
   k1 = (h >> 16) >= thr16 ? inv_keep : 0.0f;
+}
+// keep flags only (callers that fold inv_keep into a per-row / per-column factor)
+__device__ __forceinline__ void drop_pair_keep(uint64_t seed, uint64_t pair_idx, uint32_t thr16, bool& k0, bool& k1) {
+  const uint32_t h = hash_pair(seed, pair_idx);
+  k0 = (h & 0xffffu) >= thr16;
+  k1 = (h >> 16) >= thr16;
 }
 __device__ __forceinline__ float drop_keep(uint64_t seed, uint64_t idx, uint32_t thr16, float inv_keep) {
   float k0, k1;

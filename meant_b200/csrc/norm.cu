@@ -100,19 +100,21 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
       rinv = 1.0f / (sqrtf(ss) * sqrtf(inv_d) + a.eps);   // ||x|| * d^-1/2 + eps
       if (lane == 0) a.stat0[row] = rinv;
     }
+    // inverted dropout: the 1/(1-p) rides in the row factor, the mask is a select (LayerNorm is never dropped)
+    const float rinv_o = (!LN && a.drop_thresh) ? rinv * a.drop_inv_keep : rinv;
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
       float o[V];
       const int col = (lane + 32 * c) * V;
 #pragma unroll
-      for (int i = 0; i < V; ++i) o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv);
-      if (a.drop_thresh) {
+      for (int i = 0; i < V; ++i) o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv_o);
+      if (!LN && a.drop_thresh) {
 #pragma unroll
         for (int i = 0; i < V; i += 2) {
-          float k0, k1;
-          drop_pair(seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
-          o[i] *= k0;
-          o[i + 1] *= k1;
+          bool k0, k1;
+          drop_pair_keep(seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, k0, k1);
+          o[i] = k0 ? o[i] : 0.f;
+          o[i + 1] = k1 ? o[i + 1] : 0.f;
         }
       }
       Vec16<T> ov;
@@ -243,11 +245,8 @@ __global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_
       for (int i = 0; i < V; ++i) {
         float sv = u[i];
         if (GELU) {
-          float cdf, pdf;
-          gelu_parts(u[i], cdf, pdf);
-          sv = u[i] * cdf;
+          gelu_val_grad(u[i], sv, gk[c][i]);
           sk[c][i] = sv;
-          gk[c][i] = fmaf(u[i], pdf, cdf);
         }
         if (LN) sv = (sv - mean) * rinv;  // xhat
         const float gd = g[c][i] * gy[i];
