@@ -43,6 +43,44 @@ def _f32(t):
     return t.detach().float().contiguous()
 
 
+# ---- per-step state installed by train.TrainStep (inactive otherwise) ------------------------------------------
+# _shadow: {id(param): (param, bf16 copy)} refreshed once per step with ONE multi-tensor cast instead of one cast
+# kernel per Linear per step; ("packed", id(wq), id(wv), id(wk)) -> (packed weight, packed bias) for the fused q|v|k
+# projection.  _arena: a zeroed fp32 buffer handed out in slices for the small per-column accumulators of the norm
+# backward kernels (one fill per step instead of ~100).
+_shadow = None
+_arena = None
+_arena_off = 0
+
+
+def set_weight_shadows(d):
+    global _shadow
+    _shadow = d
+
+
+def _shadow_of(p, dtype):
+    if _shadow is None or p is None:
+        return None
+    e = _shadow.get(id(p))
+    return e[1] if e is not None and e[0] is p and e[1].dtype == dtype else None
+
+
+def set_zero_arena(buf):
+    """buf: fp32 tensor that the caller zeroes at the start of every step (None switches the arena off)."""
+    global _arena, _arena_off
+    _arena, _arena_off = buf, 0
+
+
+def _zeros(n, device):
+    global _arena_off
+    if _arena is not None and _arena.device == device:
+        start = (_arena_off + 63) // 64 * 64
+        if start + n <= _arena.numel():
+            _arena_off = start + n
+            return _arena[start:start + n]
+    return torch.zeros(n, dtype=torch.float32, device=device)
+
+
 # ------------------------------------------------------------------------------ RMSNorm
 class _RMSNormFn(torch.autograd.Function):
     @staticmethod
@@ -78,10 +116,10 @@ class _RMSNormFn(torch.autograd.Function):
         dy = torch.zeros_like(src) if dy is None else dy.to(src.dtype).contiguous()
         ds = dsum.to(src.dtype).contiguous() if dsum is not None else None
         dx = torch.empty_like(src)
-        dgain = torch.zeros(d, dtype=torch.float32, device=src.device)
+        dgain = _zeros(d, src.device)
         # with the Linear wrapper active the kernel also sums dx over rows: if x came out of a Linear, that is the
         # layer's bias gradient (picked up by _LinearFn.backward through the tag below)
-        dxsum = torch.zeros(d, dtype=torch.float32, device=src.device) if _fused_linear and xdt == src.dtype else None
+        dxsum = _zeros(d, src.device) if _fused_linear and xdt == src.dtype else None
         tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}" + ("/colsum" if dxsum is not None else "")
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_bwd, nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv),
                           nv.ptr(ds), nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
@@ -136,8 +174,12 @@ class _LinearFn(torch.autograd.Function):
         dtype = compute_dtype(x)
         nv.require_cuda(x, weight, bias)
         with torch.autocast("cuda", enabled=False):
-            xc, wc = x.to(dtype), weight.to(dtype)
-            y = torch.nn.functional.linear(xc, wc, bias.to(dtype) if bias is not None else None)
+            xc = x.to(dtype)
+            wc = _shadow_of(weight, dtype)
+            wc = weight.to(dtype) if wc is None else wc
+            bc = _shadow_of(bias, dtype)
+            bc = (bias.to(dtype) if bias is not None else None) if bc is None else bc
+            y = torch.nn.functional.linear(xc, wc, bc)
         ctx.save_for_backward(xc, wc)
         ctx.cfg = (x.dtype, weight.dtype, bias.dtype if bias is not None else None)
         return y
@@ -168,6 +210,56 @@ class _LinearFn(torch.autograd.Function):
                                   dy2.shape[0], n_out, dy2.stride(0), nv.dt(dy2), nv.stream()), "meant_bias_grad")
                 db = db32.to(bdt)
         return dx, dw, db
+
+
+class _Linear3Fn(torch.autograd.Function):
+    """Three nn.Linear layers over the same input as ONE GEMM (the q | v | k projection: the parameters stay three
+    separate modules, meant/xPosAttention.py:24-27).  With TrainStep's weight shadows the packed bf16 weight already
+    exists (the three shadows are row blocks of one buffer), so no concatenation runs at all."""
+
+    @staticmethod
+    def forward(ctx, x, w0, w1, w2, b0, b1, b2):
+        dtype = compute_dtype(x)
+        nv.require_cuda(x, w0)
+        packed = _shadow.get(("packed", id(w0), id(w1), id(w2))) if _shadow is not None else None
+        with torch.autocast("cuda", enabled=False):
+            if packed is not None and packed[0].dtype == dtype and packed[2][0] is w0:
+                wc, bc = packed[0], packed[1]
+            else:
+                wc, bc = torch.cat((w0, w1, w2)).to(dtype), torch.cat((b0, b1, b2)).to(dtype)
+            xc = x.to(dtype)
+            y = torch.nn.functional.linear(xc, wc, bc)
+        ctx.save_for_backward(xc, wc)
+        ctx.cfg = (x.dtype, w0.dtype, b0.dtype, (w0.shape[0], w1.shape[0], w2.shape[0]))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        xc, wc = ctx.saved_tensors
+        xdt, wdt, bdt, sizes = ctx.cfg
+        n_out, n_in = wc.shape
+        with torch.autocast("cuda", enabled=False):
+            dy2 = dy.to(wc.dtype).reshape(-1, n_out)
+            if dy2.stride(-1) != 1 or dy2.stride(0) % 8 or dy2.data_ptr() % 16:
+                dy2 = dy2.contiguous()
+            dx = torch.mm(dy2, wc).view(xc.shape).to(xdt) if ctx.needs_input_grad[0] else None
+            dw = _mm_f32(dy2.t(), xc.reshape(-1, n_in)).to(wdt).split(sizes, 0)
+            db32 = torch.empty(n_out, dtype=torch.float32, device=dy2.device)
+            nv.check(nv.timed(f"bias_grad/r{dy2.shape[0]}/c{n_out}", nv.lib().meant_bias_grad, nv.ptr(dy2), nv.ptr(db32),
+                              dy2.shape[0], n_out, dy2.stride(0), nv.dt(dy2), nv.stream()), "meant_bias_grad")
+            db = db32.to(bdt).split(sizes)
+        return (dx,) + tuple(dw) + tuple(db)
+
+
+def linear3(x, m0, m1, m2):
+    """cat(m0(x), m1(x), m2(x)) along the feature axis for three nn.Linear modules, as one GEMM."""
+    if _fused_linear and x.is_cuda and torch.is_grad_enabled() and m0.bias is not None and m1.bias is not None \
+            and m2.bias is not None and x.numel() // x.shape[-1] >= 1024 and m0.weight.shape[0] % 8 == 0 \
+            and m1.weight.shape[0] % 8 == 0:
+        return _Linear3Fn.apply(x, m0.weight, m1.weight, m2.weight, m0.bias, m1.bias, m2.bias)
+    w = torch.cat((m0.weight, m1.weight, m2.weight), dim=0)
+    b = torch.cat((m0.bias, m1.bias, m2.bias), dim=0)
+    return linear(x, w, b)
 
 
 _fused_linear = False

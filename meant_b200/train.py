@@ -31,11 +31,61 @@ class TrainStep:
         self._graph_warmup, self._calls = int(graph_warmup), 0
         self._g = self._static = self._loss = self._seed_t = None
         self.launches_per_replay = 0            # native-library launches captured in one step
+        self._shadow_src = self._shadow_dst = self._shadows = self._arena = None
         if self.graph:
             from . import ops
             ops.use_fused_linear(True)
+            if bf16:
+                self._build_shadows()
+            self._arena = torch.zeros(1 << 20, dtype=torch.float32, device=self.params[0].device)
+
+    def _build_shadows(self):
+        """bf16 copies of every nn.Linear weight / bias, refreshed by ONE multi-tensor cast per step; the q, v, k
+        shadows of an attention module are row blocks of one packed buffer (ops.linear3 uses it as is)."""
+        import torch.nn as nn
+        shadows, src, dst, seen = {}, [], [], set()
+
+        def add(p, view):
+            shadows[id(p)] = (p, view)
+            src.append(p.detach())
+            dst.append(view)
+            seen.add(id(p))
+
+        for m in self.model.modules():
+            trio = [getattr(m, n, None) for n in ("q", "v", "k")]
+            if all(isinstance(t, nn.Linear) and t.bias is not None and t.weight.is_cuda for t in trio) and \
+                    len({t.weight.shape[1] for t in trio}) == 1 and not any(id(t.weight) in seen for t in trio):
+                rows = [t.weight.shape[0] for t in trio]
+                pw = torch.empty(sum(rows), trio[0].weight.shape[1], dtype=torch.bfloat16, device=trio[0].weight.device)
+                pb = torch.empty(sum(rows), dtype=torch.bfloat16, device=pw.device)
+                off = 0
+                for t, r in zip(trio, rows):
+                    add(t.weight, pw[off:off + r])
+                    add(t.bias, pb[off:off + r])
+                    off += r
+                shadows[("packed",) + tuple(id(t.weight) for t in trio)] = (pw, pb, [t.weight for t in trio])
+        for m in self.model.modules():
+            if isinstance(m, nn.Linear) and m.weight.is_cuda and m.weight.dtype == torch.float32:
+                for p in (m.weight, m.bias):
+                    if p is not None and id(p) not in seen:
+                        add(p, torch.empty_like(p, dtype=torch.bfloat16))
+        self._shadows, self._shadow_src, self._shadow_dst = shadows, src, dst
 
     def _step(self, labels, args, kwargs):
+        from . import ops
+        if self._shadow_src:
+            torch._foreach_copy_(self._shadow_dst, self._shadow_src)
+        if self._arena is not None:
+            self._arena.zero_()
+        ops.set_weight_shadows(self._shadows)
+        ops.set_zero_arena(self._arena)
+        try:
+            return self._step_body(labels, args, kwargs)
+        finally:
+            ops.set_weight_shadows(None)
+            ops.set_zero_arena(None)
+
+    def _step_body(self, labels, args, kwargs):
         self.reducer.zero_grad()
         device_type = "cuda" if self.params[0].is_cuda else "cpu"
         with torch.autocast(device_type, dtype=torch.bfloat16, enabled=self.bf16 and device_type == "cuda"):

@@ -15,9 +15,7 @@ def _packed_qkv(mod, x):
     """One N=3*dim projection.  The reference cross-wires the projections (keys come from the
     `v` Linear, values from the `k` Linear: meant/xPosAttention.py:37-38), so the packed weight
     is (q | v | k).  Parameters stay three separate nn.Linear modules (state_dict contract)."""
-    w = torch.cat((mod.q.weight, mod.v.weight, mod.k.weight), dim=0)
-    b = torch.cat((mod.q.bias, mod.v.bias, mod.k.bias), dim=0)
-    return ops.linear(x, w, b)
+    return ops.linear3(x, mod.q, mod.v, mod.k)
 
 
 class xPosAttention(nn.Module):

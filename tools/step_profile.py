@@ -28,8 +28,9 @@ def main():
     torch.manual_seed(0)
     model = mb.meant_tweet(bench.DIM, 4, bench.LAG, bench.CLASSES, nn.Embedding(bench.VOCAB, bench.DIM),
                            num_encoders=a.encoders).to(dev).train()
-    step = TrainStep(model, bf16=True)
-    ops.use_fused_linear(bool(a.fused_linear))
+    # graph=True installs everything the captured step uses (Linear wrapper, weight shadows, zero arena);
+    # a huge graph_warmup keeps the steps eager so that the profiler sees individual kernels
+    step = TrainStep(model, bf16=True, graph=bool(a.fused_linear), graph_warmup=1 << 30)
     tweets, mask, labels = bench.synth_batch(a.batch, 0)
     tweets, mask, labels = tweets.to(dev), mask.to(dev), labels.to(dev)
     for _ in range(3):
