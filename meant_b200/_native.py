@@ -57,8 +57,11 @@ SIGNATURES = {
 _lib = None
 
 
+ABI_VERSION = 3   # include/meant_b200.h: meant_version()
+
+
 def lib():
-    """Load the shared library (once).  Raises if it has not been built."""
+    """Load the shared library (once).  Raises if it has not been built or is stale."""
     global _lib
     if _lib is None:
         if not os.path.exists(_LIB_PATH):
@@ -69,6 +72,9 @@ def lib():
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
+        if handle.meant_version() != ABI_VERSION:
+            raise RuntimeError(f"{_LIB_PATH} has ABI version {handle.meant_version()}, this package expects "
+                               f"{ABI_VERSION}: rebuild with `python -m meant_b200.build`")
         _lib = handle
     return _lib
 

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/meant_b200.h but not exported"
     assert set(names) == set(nv.SIGNATURES), set(names) ^ set(nv.SIGNATURES)
-    assert lib.meant_version() == 3
+    assert lib.meant_version() == nv.ABI_VERSION == 3
 
 
 def test_argument_errors_are_codes_not_crashes():
