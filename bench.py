@@ -301,7 +301,8 @@ def gpu_run(args):
                         "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in (h_tweets, h_mask, h_labels)),
                         "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": main, "roofline_extra": extra,
-                "final_loss": loss_host, "native_library": os.path.relpath(nv.lib_path(), ROOT)}
+                "final_loss": loss_host, "native_library": os.path.relpath(nv.lib_path(), ROOT),
+                "attn_tma_fallbacks": int(nv.lib().meant_attn_tma_fallbacks())}
         if n == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"], _ = cpu_reference_run(args, steps=2, warmup=1)
         print(json.dumps(line), flush=True)

@@ -102,6 +102,9 @@ int meant_attn_fwd(const meant_attn_args* args, int dtype, int impl, meant_strea
 int meant_attn_bwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);
 /* 1 if the tcgen05 kernel takes this problem (bf16, Dh in {64, 96}, ...), else 0            */
 int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int backward);
+/* diagnostics: single-tile (Sq, Sk <= 128) calls whose views the TMA tensor maps could not describe and that
+ * therefore ran on the multi-tile kernels (0 on every path the models use)                   */
+int64_t meant_attn_tma_fallbacks(void);
 
 /* ---- mean over the token axis: meant/meant.py:231, meant/meant_tweet.py:157 ------------- */
 int meant_meanpool_fwd(const void* x, void* y, int64_t N, int S, int D, int dtype, meant_stream_t stream);

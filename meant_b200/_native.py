@@ -45,6 +45,7 @@ SIGNATURES = {
     "meant_attn_fwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),
     "meant_attn_bwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),
     "meant_attn_tcgen05_supported": (i32, [C.POINTER(AttnArgs), i32, i32]),
+    "meant_attn_tma_fallbacks": (i64, []),
     "meant_meanpool_fwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_meanpool_bwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_geglu_fwd": (i32, [vp, vp, i64, i32, i32, vp]),

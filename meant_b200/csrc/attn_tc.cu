@@ -16,6 +16,7 @@
 #include "attn_common.cuh"
 #include "tc_utils.cuh"
 #include <math_constants.h>
+#include <atomic>
 
 namespace meant {
 
@@ -393,10 +394,13 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
   return 0;
 }
 
+static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels
+
 int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
   if (attn_tc2_supported(a, 0)) {
     const int r2 = attn_tc2_fwd(a, st);
     if (r2 != MEANT_EUNSUPPORTED) return r2;     // views TMA cannot describe fall through to the multi-tile kernel
+    ++g_tma_fallbacks;
   }
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st);
@@ -407,10 +411,13 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
   if (attn_tc2_supported(a, 1)) {
     const int r2 = attn_tc2_bwd(a, st);
     if (r2 != MEANT_EUNSUPPORTED) return r2;
+    ++g_tma_fallbacks;
   }
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);
 }
+
+long long attn_tma_fallbacks() { return g_tma_fallbacks.load(); }
 
 }  // namespace meant

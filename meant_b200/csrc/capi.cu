@@ -15,6 +15,9 @@ static std::atomic<int64_t> g_launches{0};
 extern "C" void meant_count_launch_(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 extern "C" int64_t meant_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 extern "C" void meant_reset_launch_count(void) { g_launches.store(0, std::memory_order_relaxed); }
+namespace meant { long long attn_tma_fallbacks(); }
+extern "C" int64_t meant_attn_tma_fallbacks(void) { return meant::attn_tma_fallbacks(); }
+
 extern "C" int meant_version(void) { return 3; }
 
 extern "C" int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int backward) {

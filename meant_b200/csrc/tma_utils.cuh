@@ -4,6 +4,8 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include "attn_common.cuh"
 
 namespace meant {
@@ -46,9 +48,22 @@ inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count,
   const cuuint32_t estr[5] = {1u, 1u, 1u, 1u, 1u};
   const CUtensorMapSwizzle sw = box_cols * 2 == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                               : box_cols * 2 == 64  ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE;
-  const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v.p), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v.p), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // a thread that has only used the runtime lazily (e.g. an autograd worker before its first launch) has no
+    // current driver context yet: bind the device's primary context and encode again
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess)
+      r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v.p), dims, strides, box, estr,
+              CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (r != CUDA_SUCCESS && getenv("MEANT_DEBUG"))
+    fprintf(stderr, "meant_b200: cuTensorMapEncodeTiled failed (%d): p=%p dims=(%llu,%llu,%llu,%llu,%llu) strides=(%llu,%llu,%llu,%llu) box=%d\n",
+            (int)r, v.p, (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)dims[2],
+            (unsigned long long)dims[3], (unsigned long long)dims[4], (unsigned long long)strides[0],
+            (unsigned long long)strides[1], (unsigned long long)strides[2], (unsigned long long)strides[3], box_cols);
   return r == CUDA_SUCCESS ? 0 : MEANT_EUNSUPPORTED;
 }
 
