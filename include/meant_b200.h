@@ -134,6 +134,12 @@ int meant_embedding_fwd(const int64_t* ids, const float* W, void* out, int64_t t
 int meant_embedding_bwd(const int64_t* ids, const void* dy, float* dW, int64_t tokens, int D, int64_t vocab,
                         int dtype, meant_stream_t stream);
 
+/* ---- nn.Linear forward as a hand-written tcgen05 GEMM (meant/meant.py:61-66, meant/xPosAttention.py:24-28):
+ *      C[M, N] (bf16) = A[M, K] (bf16) * W[N, K]^T (bf16, nn.Linear's weight layout) + bias[N] (fp32, optional).
+ *      lda / ldw / ldc: row pitches in elements.  N and K multiples of 8; pointers 16-byte aligned. ---------- */
+int meant_gemm_bf16_tn(const void* A, const void* W, const float* bias, void* C, int64_t M, int N, int K,
+                       int64_t lda, int64_t ldw, int64_t ldc, meant_stream_t stream);
+
 /* ---- tcgen05 self-test: D[128,N] (fp32) = op(A) op(B)^T for one bf16 tile; a_mn / b_mn select
  *      MN-major operands (A given as [K,128], B as [K,N]) instead of K-major ([128,K], [N,K]).
  *      Exists so the tests can pin the descriptor conventions the attention kernels rely on. */

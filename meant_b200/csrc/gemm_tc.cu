@@ -1,0 +1,196 @@
+// Hand-written tcgen05 GEMM for the Linear layers of the encoder blocks:
+//     C[M, N] (bf16) = A[M, K] (bf16, row-major) * W[N, K]^T (bf16, row-major: nn.Linear's weight) + bias[N] (fp32)
+// the forward of meant/meant.py:61-66 / meant/xPosAttention.py:24-28 (M = tokens, N, K in {768, 2304}).
+//
+// Persistent, one CTA per SM, 192 threads, three roles:
+//   warp 0  producer: one thread streams 128 x 64 A boxes and 256 x 64 W boxes (SWIZZLE_128B, K-major) through a
+//           3-stage ring with TMA; partial tiles are zero-filled / clipped by the tensor maps, so M, N, K only need
+//           to be multiples of 8.
+//   warp 1  MMA: one thread issues 4 tcgen05.mma (128 x 256 x 16) per stage into one of TWO 256-column TMEM
+//           accumulators, frees the stage with tcgen05.commit, and commits the accumulator after the last K stage --
+//           the epilogue of tile i runs under the main loop of tile i+1.
+//   warps 2-5  epilogue: TMEM -> registers (+ bias) -> bf16 -> swizzled staging tile -> four TMA stores.
+// Tiles are walked n-fastest, so the CTAs that share an A row block run at the same time and W stays in L2.
+#include "common.cuh"
+#include "tc_utils.cuh"
+#include "tma_utils.cuh"
+#include <string.h>
+
+namespace meant {
+namespace g1 {
+
+constexpr int BM = 128, BN = 256, BK = 64, NSTAGE = 3;
+constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE = A_BYTES + B_BYTES;
+constexpr uint32_t OUT_BOX = BM * 128;                       // one 128 x 64 column box of the output tile, SWIZZLE_128B
+constexpr uint32_t OFF_OUT = NSTAGE * STAGE, OFF_BARS = OFF_OUT + 4 * OUT_BOX;
+constexpr uint32_t SMEM_TOTAL = OFF_BARS + 256 + 1024;       // + alignment slack
+constexpr int NT = 192, BAR_EPI = 1;
+static_assert(SMEM_TOTAL <= 232448, "exceeds the shared memory a CTA can opt in to");
+
+struct Maps { CUtensorMap a, w, c; };
+
+__device__ __forceinline__ void load_box2(uint32_t dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n"
+               ::"r"(dst), "l"(map), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void store_box2(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];\n"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+
+__global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ Maps maps, const float* __restrict__ bias,
+                                                        int M, int N, int K) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BARS);
+  uint64_t *full = bars, *empty = bars + NSTAGE, *acc_full = bars + 2 * NSTAGE, *acc_empty = bars + 2 * NSTAGE + 2;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < NSTAGE; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_empty[i], 128); }
+    tc::fence_mbar_init();
+  }
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot, s0 = tc::smem_u32(smem);
+  const int tiles_n = (N + BN - 1) / BN, tiles = ((M + BM - 1) / BM) * tiles_n, kt = (K + BK - 1) / BK;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma::prefetch_map(&maps.a);
+      tma::prefetch_map(&maps.w);
+      int it = 0;
+      for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+        const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE;
+          if (it >= NSTAGE) tc::mbar_wait(&empty[s], ((it / NSTAGE) - 1) & 1);
+          tma::mbar_expect_tx(&full[s], STAGE);
+          load_box2(s0 + s * STAGE, &maps.a, &full[s], k * BK, m0);
+          load_box2(s0 + s * STAGE + A_BYTES, &maps.w, &full[s], k * BK, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(BM, BN, 0, 0);
+      int it = 0, ti = 0;
+      for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+        const int acc = ti & 1;
+        if (ti >= 2) tc::mbar_wait(&acc_empty[acc], ((ti >> 1) - 1) & 1);
+        tc::fence_after_sync();
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE;
+          tc::mbar_wait(&full[s], (it / NSTAGE) & 1);
+          tc::fence_after_sync();
+          const uint32_t sa = s0 + s * STAGE, sb = sa + A_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk)
+            tc::mma_ss(tmem + acc * BN, tc::make_desc_sw(sa + kk * 32, 16, 1024, 2), tc::make_desc_sw(sb + kk * 32, 16, 1024, 2),
+                       idesc, k > 0 || kk > 0);
+          tc::mma_commit(&empty[s]);                   // the stage may be refilled once these MMAs have read it
+        }
+        tc::mma_commit(&acc_full[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;                            // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    const bool leader = warp == 2 && lane == 0;
+    int ti = 0;
+    for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
+      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN, acc = ti & 1;
+      tc::mbar_wait(&acc_full[acc], (ti >> 1) & 1);
+      tc::fence_after_sync();
+      if (leader) tma::store_wait_read<0>();           // the previous tile's stores have read the staging boxes
+      tc::bar_sync(BAR_EPI, 128);
+#pragma unroll
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tc::tmem_ld32(lane_base + acc * BN + c * 32, v);
+        tc::tmem_ld_wait();
+        uint8_t* box = smem + OFF_OUT + (c >> 1) * OUT_BOX;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          float b[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          const int col = n0 + c * 32 + g * 8;
+          if (bias && col < N) {                       // N is a multiple of 8: a chunk is in or out as a whole
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(bias + col) + 1);
+            b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+          }
+          uint4 pk;
+          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(v[g * 8 + 2 * i] + b[2 * i], v[g * 8 + 2 * i + 1] + b[2 * i + 1]);
+          *reinterpret_cast<uint4*>(box + tc::sw128_off(row, (c & 1) * 4 + g)) = pk;
+        }
+      }
+      tc::fence_before_sync();
+      tc::mbar_arrive(&acc_empty[acc]);                // the accumulator may be overwritten by tile ti + 2
+      tc::fence_async_smem();
+      tc::bar_sync(BAR_EPI, 128);
+      if (leader) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (n0 + b * 64 < N) store_box2(&maps.c, s0 + OFF_OUT + b * OUT_BOX, n0 + b * 64, m0);
+        tma::store_commit();
+      }
+    }
+    if (leader) tma::store_wait_all();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 1) tc::tmem_dealloc(tmem, 512);
+}
+
+// 2-D bf16 tensor map: `cols` contiguous elements per row, row pitch ld elements, box = box_cols x box_rows, SWIZZLE_128B
+static int make_map2(CUtensorMap* m, const void* p, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows) {
+  tma::EncodeTiledFn enc = tma::encode_fn();
+  if (!enc || (reinterpret_cast<uintptr_t>(p) & 15) || (ld * 2) % 16 || cols <= 0 || rows <= 0) return MEANT_EUNSUPPORTED;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)(ld * 2)};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = CUDA_ERROR_INVALID_CONTEXT;
+  for (int attempt = 0; attempt < 2 && r == CUDA_ERROR_INVALID_CONTEXT; ++attempt) {
+    if (attempt) {                                     // see tma_utils.cuh: threads without a current driver context
+      int dev = 0;
+      if (cudaGetDevice(&dev) != cudaSuccess || cudaSetDevice(dev) != cudaSuccess) break;
+    }
+    r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(p), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  return r == CUDA_SUCCESS ? 0 : MEANT_EUNSUPPORTED;
+}
+
+}  // namespace g1
+}  // namespace meant
+
+using namespace meant;
+
+extern "C" int meant_gemm_bf16_tn(const void* A, const void* W, const float* bias, void* C, int64_t M, int N, int K,
+                                  int64_t lda, int64_t ldw, int64_t ldc, cudaStream_t st) {
+  if (!A || !W || !C || M < 0 || N <= 0 || K <= 0 || lda < K || ldw < K || ldc < N) return MEANT_EARG;
+  if (N % 8 || K % 8 || (bias && (reinterpret_cast<uintptr_t>(bias) & 15)) || M > 0x7fffffff) return MEANT_EUNSUPPORTED;
+  if (M == 0) return 0;
+  g1::Maps maps;
+  memset(&maps, 0, sizeof(maps));
+  int rc = g1::make_map2(&maps.a, A, M, K, lda, g1::BK, g1::BM);
+  if (!rc) rc = g1::make_map2(&maps.w, W, N, K, ldw, g1::BK, g1::BN);
+  if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, g1::BM);
+  if (rc) return rc;
+  cudaError_t e = cudaFuncSetAttribute(g1::gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g1::SMEM_TOTAL);
+  if (e != cudaSuccess) return (int)e;
+  int dev = 0, sms = 148;
+  if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t tiles = ((M + g1::BM - 1) / g1::BM) * ((N + g1::BN - 1) / g1::BN);
+  const int grid = (int)(tiles < sms ? tiles : sms);
+  g1::gemm_tn_kernel<<<grid, g1::NT, g1::SMEM_TOTAL, st>>>(maps, bias, (int)M, N, K);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}

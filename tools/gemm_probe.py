@@ -26,3 +26,18 @@ for n_in,n_out in ((768,768),(768,2304)):
     r["dw f32 out"]=t(lambda: torch.mm(dy.t(),x,out_dtype=torch.float32))
     r["dwT = x.t()@dy bf16"]=t(lambda: torch.mm(x.t(),dy))
     for k,v in r.items(): print(f"{n_in}->{n_out} {k:24s} {v:8.1f} us  {fl/v/1e6:7.1f} TF/s")
+
+# ---- the hand-written tcgen05 GEMM against the library on the same problem
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from meant_b200 import _native as nv
+for n_in, n_out in ((768, 768), (768, 2304)):
+    x = torch.randn(M, n_in, device="cuda").bfloat16(); w = (torch.randn(n_out, n_in, device="cuda") * 0.02).bfloat16()
+    b = torch.randn(n_out, device="cuda"); c = torch.empty(M, n_out, device="cuda").bfloat16()
+    fl = 2 * M * n_in * n_out
+    def mine():
+        rc = nv.lib().meant_gemm_bf16_tn(nv.ptr(x), nv.ptr(w), nv.ptr(b), nv.ptr(c), M, n_out, n_in, n_in, n_in, n_out, nv.stream())
+        assert rc == 0
+    v = t(mine)
+    ref = F.linear(x, w, b.bfloat16())
+    print(f"{n_in}->{n_out} meant_gemm_bf16_tn       {v:8.1f} us  {fl/v/1e6:7.1f} TF/s   max|diff| vs F.linear {float((c.float()-ref.float()).abs().max()):.3e}")
