@@ -19,13 +19,23 @@
 namespace meant {
 namespace g1 {
 
-constexpr int BM = 128, BN = 256, BK = 64, NSTAGE = 3;
-constexpr uint32_t A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE = A_BYTES + B_BYTES;
-constexpr uint32_t OUT_BOX = BM * 128;                       // one 128 x 64 column box of the output tile, SWIZZLE_128B
-constexpr uint32_t OFF_OUT = NSTAGE * STAGE, OFF_BARS = OFF_OUT + 4 * OUT_BOX;
-constexpr uint32_t SMEM_TOTAL = OFF_BARS + 256 + 1024;       // + alignment slack
+constexpr int BN = 256, BK = 64;
+constexpr uint32_t HALF_A = 128 * BK * 2, B_BYTES = BN * BK * 2;
+constexpr uint32_t OUT_BOX = 128 * 128;                      // one 128 row x 64 column box of the output tile, SWIZZLE_128B
 constexpr int NT = 192, BAR_EPI = 1;
-static_assert(SMEM_TOTAL <= 232448, "exceeds the shared memory a CTA can opt in to");
+
+// MH = 1: 128 x 256 tiles, two TMEM accumulators (epilogue under the next main loop), 4 stages, 2 staging boxes.
+// MH = 2: 256 x 256 tiles (two M = 128 MMAs share every W box: a third less L2 -> SM traffic per FLOP, which is what
+//         bounds the 128 x 256 kernel), all 512 TMEM columns in one tile, 2 staging boxes refilled 4 times.
+template <int MH>
+struct Cfg {
+  static constexpr int BM = 128 * MH, NACC = MH == 1 ? 2 : 1, SB = 2, ROUNDS = MH * 4 / SB;
+  static constexpr int NSTAGE = MH == 1 ? 4 : 3;
+  static constexpr uint32_t A_BYTES = MH * HALF_A, STAGE = A_BYTES + B_BYTES;
+  static constexpr uint32_t OFF_OUT = NSTAGE * STAGE, OFF_BARS = OFF_OUT + SB * OUT_BOX;
+  static constexpr uint32_t SMEM_TOTAL = OFF_BARS + 256 + 1024;       // + alignment slack
+  static_assert(SMEM_TOTAL <= 232448, "exceeds the shared memory a CTA can opt in to");
+};
 
 struct Maps { CUtensorMap a, w, c; };
 
@@ -38,12 +48,16 @@ __device__ __forceinline__ void store_box2(const CUtensorMap* map, uint32_t src,
                ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
 }
 
+template <int MH>
 __global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ Maps maps, const float* __restrict__ bias,
                                                         int M, int N, int K) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
+  using C = Cfg<MH>;
+  constexpr int BM = C::BM, NACC = C::NACC, NSTAGE = C::NSTAGE;
+  constexpr uint32_t STAGE = C::STAGE, A_BYTES = C::A_BYTES, OFF_OUT = C::OFF_OUT;
   uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BARS);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BARS);
   uint64_t *full = bars, *empty = bars + NSTAGE, *acc_full = bars + 2 * NSTAGE, *acc_empty = bars + 2 * NSTAGE + 2;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
@@ -69,18 +83,19 @@ __global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ 
           const int s = it % NSTAGE;
           if (it >= NSTAGE) tc::mbar_wait(&empty[s], ((it / NSTAGE) - 1) & 1);
           tma::mbar_expect_tx(&full[s], STAGE);
-          load_box2(s0 + s * STAGE, &maps.a, &full[s], k * BK, m0);
+#pragma unroll
+          for (int h = 0; h < MH; ++h) load_box2(s0 + s * STAGE + h * HALF_A, &maps.a, &full[s], k * BK, m0 + h * 128);
           load_box2(s0 + s * STAGE + A_BYTES, &maps.w, &full[s], k * BK, n0);
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::make_idesc(BM, BN, 0, 0);
+      constexpr uint32_t idesc = tc::make_idesc(128, BN, 0, 0);
       int it = 0, ti = 0;
       for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
-        const int acc = ti & 1;
-        if (ti >= 2) tc::mbar_wait(&acc_empty[acc], ((ti >> 1) - 1) & 1);
+        const int acc = ti % NACC, use = ti / NACC;
+        if (use >= 1) tc::mbar_wait(&acc_empty[acc], (use - 1) & 1);
         tc::fence_after_sync();
         for (int k = 0; k < kt; ++k, ++it) {
           const int s = it % NSTAGE;
@@ -88,9 +103,13 @@ __global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ 
           tc::fence_after_sync();
           const uint32_t sa = s0 + s * STAGE, sb = sa + A_BYTES;
 #pragma unroll
-          for (int kk = 0; kk < BK / 16; ++kk)
-            tc::mma_ss(tmem + acc * BN, tc::make_desc_sw(sa + kk * 32, 16, 1024, 2), tc::make_desc_sw(sb + kk * 32, 16, 1024, 2),
-                       idesc, k > 0 || kk > 0);
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t bd = tc::make_desc_sw(sb + kk * 32, 16, 1024, 2);
+#pragma unroll
+            for (int h = 0; h < MH; ++h)
+              tc::mma_ss(tmem + (acc * MH + h) * BN, tc::make_desc_sw(sa + h * HALF_A + kk * 32, 16, 1024, 2), bd, idesc,
+                         k > 0 || kk > 0);
+          }
           tc::mma_commit(&empty[s]);                   // the stage may be refilled once these MMAs have read it
         }
         tc::mma_commit(&acc_full[acc]);
@@ -103,41 +122,52 @@ __global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ 
     const bool leader = warp == 2 && lane == 0;
     int ti = 0;
     for (int t = blockIdx.x; t < tiles; t += gridDim.x, ++ti) {
-      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN, acc = ti & 1;
-      tc::mbar_wait(&acc_full[acc], (ti >> 1) & 1);
+      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN, acc = ti % NACC, use = ti / NACC;
+      tc::mbar_wait(&acc_full[acc], use & 1);
       tc::fence_after_sync();
-      if (leader) tma::store_wait_read<0>();           // the previous tile's stores have read the staging boxes
-      tc::bar_sync(BAR_EPI, 128);
+#pragma unroll 1
+      for (int r = 0; r < C::ROUNDS; ++r) {
+        if (leader) tma::store_wait_read<0>();         // the previous stores have read the staging boxes
+        tc::bar_sync(BAR_EPI, 128);
 #pragma unroll
-      for (int c = 0; c < BN / 32; ++c) {
-        float v[32];
-        tc::tmem_ld32(lane_base + acc * BN + c * 32, v);
-        tc::tmem_ld_wait();
-        uint8_t* box = smem + OFF_OUT + (c >> 1) * OUT_BOX;
+        for (int bi = 0; bi < C::SB; ++bi) {
+          const int g = r * C::SB + bi, h = g >> 2, cb = g & 3;      // row half, 64-column box of the tile
+          uint8_t* box = smem + OFF_OUT + bi * OUT_BOX;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          float b[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-          const int col = n0 + c * 32 + g * 8;
-          if (bias && col < N) {                       // N is a multiple of 8: a chunk is in or out as a whole
-            const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(bias + col) + 1);
-            b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+          for (int c = 0; c < 2; ++c) {
+            float v[32];
+            tc::tmem_ld32(lane_base + (acc * MH + h) * BN + cb * 64 + c * 32, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int gq = 0; gq < 4; ++gq) {
+              float b[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              const int col = n0 + cb * 64 + c * 32 + gq * 8;
+              if (bias && col < N) {                   // N is a multiple of 8: a chunk is in or out as a whole
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(bias + col) + 1);
+                b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+              }
+              uint4 pk;
+              __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(v[gq * 8 + 2 * i] + b[2 * i], v[gq * 8 + 2 * i + 1] + b[2 * i + 1]);
+              *reinterpret_cast<uint4*>(box + tc::sw128_off(row, c * 4 + gq)) = pk;
+            }
           }
-          uint4 pk;
-          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(v[g * 8 + 2 * i] + b[2 * i], v[g * 8 + 2 * i + 1] + b[2 * i + 1]);
-          *reinterpret_cast<uint4*>(box + tc::sw128_off(row, (c & 1) * 4 + g)) = pk;
         }
-      }
-      tc::fence_before_sync();
-      tc::mbar_arrive(&acc_empty[acc]);                // the accumulator may be overwritten by tile ti + 2
-      tc::fence_async_smem();
-      tc::bar_sync(BAR_EPI, 128);
-      if (leader) {
+        if (r == C::ROUNDS - 1) {
+          tc::fence_before_sync();
+          tc::mbar_arrive(&acc_empty[acc]);            // the accumulator may be overwritten
+        }
+        tc::fence_async_smem();
+        tc::bar_sync(BAR_EPI, 128);
+        if (leader) {
 #pragma unroll
-        for (int b = 0; b < 4; ++b)
-          if (n0 + b * 64 < N) store_box2(&maps.c, s0 + OFF_OUT + b * OUT_BOX, n0 + b * 64, m0);
-        tma::store_commit();
+          for (int bi = 0; bi < C::SB; ++bi) {
+            const int g = r * C::SB + bi, h = g >> 2, cb = g & 3;
+            if (n0 + cb * 64 < N && m0 + h * 128 < M) store_box2(&maps.c, s0 + OFF_OUT + bi * OUT_BOX, n0 + cb * 64, m0 + h * 128);
+          }
+          tma::store_commit();
+        }
       }
     }
     if (leader) tma::store_wait_all();
@@ -180,17 +210,23 @@ extern "C" int meant_gemm_bf16_tn(const void* A, const void* W, const float* bia
   if (M == 0) return 0;
   g1::Maps maps;
   memset(&maps, 0, sizeof(maps));
-  int rc = g1::make_map2(&maps.a, A, M, K, lda, g1::BK, g1::BM);
+  int rc = g1::make_map2(&maps.a, A, M, K, lda, g1::BK, 128);
   if (!rc) rc = g1::make_map2(&maps.w, W, N, K, ldw, g1::BK, g1::BN);
-  if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, g1::BM);
+  if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, 128);
   if (rc) return rc;
-  cudaError_t e = cudaFuncSetAttribute(g1::gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g1::SMEM_TOTAL);
-  if (e != cudaSuccess) return (int)e;
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int64_t tiles = ((M + g1::BM - 1) / g1::BM) * ((N + g1::BN - 1) / g1::BN);
+  const int64_t tiles_n = (N + g1::BN - 1) / g1::BN;
+  // 256-row tiles measured slower on the bench shapes (exposed epilogue, coarser waves): opt-in for experiments
+  const bool big = getenv("MEANT_GEMM_TILE256") != nullptr && ((M + 255) / 256) * tiles_n >= 4 * (int64_t)sms;
+  const int bm = big ? 256 : 128;
+  const size_t smem = big ? g1::Cfg<2>::SMEM_TOTAL : g1::Cfg<1>::SMEM_TOTAL;
+  auto kern = big ? g1::gemm_tn_kernel<2> : g1::gemm_tn_kernel<1>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  const int64_t tiles = ((M + bm - 1) / bm) * tiles_n;
   const int grid = (int)(tiles < sms ? tiles : sms);
-  g1::gemm_tn_kernel<<<grid, g1::NT, g1::SMEM_TOTAL, st>>>(maps, bias, (int)M, N, K);
+  kern<<<grid, g1::NT, smem, st>>>(maps, bias, (int)M, N, K);
   MEANT_LAUNCH_CHECK();
   return 0;
 }
