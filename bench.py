@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--attn-impl", default="auto", choices=["auto", "exact", "tcgen05"])
     ap.add_argument("--graph", type=int, default=1, help="capture the step into a CUDA graph")
+    ap.add_argument("--gemm", default="library", choices=["library", "native"],
+                    help="forward GEMM of the Linear layers: cuBLASLt (default) or the hand-written tcgen05 kernel")
     return ap.parse_args()
 
 
@@ -49,6 +51,7 @@ def workload_config(args, n):
             "num_encoders": args.encoders, "batch_per_gpu": args.batch, "global_batch": args.batch * n,
             "parallelism": f"dp{n}", "optimizer": "AdamW(fused) + clip_grad_norm 1.0", "mode": "train (dropout on)",
             "launch": "whole step (incl. the NCCL gradient all-reduces) replayed from one CUDA graph" if args.graph else "eager launches",
+            "linear_forward_gemm": getattr(args, "gemm", "library"),
             "l2": "no flush needed: each step streams >10 GB of activations/weights, far above the 126 MB L2"}
 
 
@@ -203,6 +206,45 @@ def rooflines(args, stats, steps):
     return main, extra
 
 
+def gemm_probe(args, dev):
+    """The hand-written tcgen05 GEMM on the block's two Linear shapes, timed with CUDA events next
+    to the library GEMM on the same operands (151 MB of activations per call: no L2 reuse between iterations)."""
+    import torch.nn.functional as F
+    from meant_b200 import _native as nv
+    _, _, tf_sus, src = peaks()
+    rows, out = args.batch * LAG * SEQ, []
+    for n_out in (DIM, 3 * DIM):
+        x = torch.randn(rows, DIM, device=dev).bfloat16()
+        w = (torch.randn(n_out, DIM, device=dev) * 0.02).bfloat16()
+        b = torch.randn(n_out, device=dev)
+        bh = b.bfloat16()
+        y = torch.empty(rows, n_out, device=dev, dtype=torch.bfloat16)
+
+        def native():
+            nv.check(nv.lib().meant_gemm_bf16_tn(nv.ptr(x), nv.ptr(w), nv.ptr(b), nv.ptr(y), rows, n_out, DIM, DIM, DIM, n_out,
+                                                 nv.stream()), "meant_gemm_bf16_tn")
+
+        times = {}
+        for name, fn in (("native", native), ("library", lambda: F.linear(x, w, bh))):
+            for _ in range(3):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            times[name] = e0.elapsed_time(e1) / 10
+        fl = 2.0 * rows * DIM * n_out
+        ach = fl / (times["native"] * 1e-3) / 1e12
+        out.append({"kernel": f"gemm_bf16_tn/m{rows}/n{n_out}/k{DIM} (hand-written tcgen05; opt-in: --gemm native)",
+                    "bound": "tensor", "achieved": round(ach, 1), "peak": tf_sus, "unit": "TFLOP/s",
+                    "frac": round(ach / tf_sus, 4), "traffic": None, "avg_ms": round(times["native"], 4),
+                    "library_same_problem_tflops": round(fl / (times["library"] * 1e-3) / 1e12, 1),
+                    "peak_source": src + ", sustained"})
+    return out
+
+
 def gpu_run(args):
     import torch.distributed as dist
     from torch import nn
@@ -221,6 +263,9 @@ def gpu_run(args):
     if args.attn_impl != "auto":
         import meant_b200.ops as ops
         ops.DEFAULT_ATTN_IMPL = {"exact": nv.IMPL_EXACT, "tcgen05": nv.IMPL_TCGEN05}[args.attn_impl]
+    if args.gemm == "native":
+        import meant_b200.ops as ops_
+        ops_.use_native_gemm(True)
     torch.manual_seed(0)
     model = mb.meant_tweet(DIM, 4, LAG, CLASSES, nn.Embedding(VOCAB, DIM), num_encoders=args.encoders).to(dev)
     model.train()
@@ -288,10 +333,12 @@ def gpu_run(args):
         torch.cuda.synchronize()
         stats = kernel_stats(nv.timers())
         nv.enable_timers(False)
+    gemm_rows = gemm_probe(args, dev) if rank == 0 else []
     if rank == 0:
         n = world
         total = args.batch * n * args.steps
         main, extra = rooflines(args, stats, timer_steps)
+        extra += gemm_rows
         line = {"metric": METRIC, "value": round(total / (ms * 1e-3), 2), "unit": UNIT, "n_gpus": n,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3),
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",

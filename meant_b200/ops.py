@@ -163,6 +163,30 @@ def _mm_f32(a, b):
         return torch.mm(a, b).float()
 
 
+_native_gemm = False
+
+
+def use_native_gemm(on=True):
+    """Forward GEMM of the Linear wrappers through the hand-written tcgen05 kernel (meant_gemm_bf16_tn) instead of
+    cuBLASLt.  Off by default: the library GEMM is still 7-10 % faster on the bench shapes."""
+    global _native_gemm
+    _native_gemm = bool(on)
+
+
+def _gemm_fwd(xc, wc, bc, bias_f32):
+    """y = xc @ wc^T + bias for bf16 operands: the tcgen05 kernel when selected and applicable, else F.linear."""
+    n_out, n_in = wc.shape
+    if _native_gemm and xc.dtype == torch.bfloat16 and n_out % 8 == 0 and n_in % 8 == 0 and xc.is_contiguous() \
+            and wc.stride(1) == 1 and wc.stride(0) % 8 == 0 and (bias_f32 is None or bias_f32.dtype == torch.float32):
+        x2 = xc.reshape(-1, n_in)
+        y = torch.empty(x2.shape[0], n_out, dtype=xc.dtype, device=xc.device)
+        nv.check(nv.timed(f"gemm_tn/m{x2.shape[0]}/n{n_out}/k{n_in}", nv.lib().meant_gemm_bf16_tn, nv.ptr(x2), nv.ptr(wc),
+                          nv.ptr(bias_f32), nv.ptr(y), x2.shape[0], n_out, n_in, n_in, wc.stride(0), n_out, nv.stream()),
+                 "meant_gemm_bf16_tn")
+        return y.view(*xc.shape[:-1], n_out)
+    return torch.nn.functional.linear(xc, wc, bc)
+
+
 class _LinearFn(torch.autograd.Function):
     """nn.Linear (meant/xPosAttention.py:24-28, meant/meant.py:61-66).  The GEMMs are plain library GEMMs
     (cuBLASLt through torch: SURVEY 8f); what is ours is the backward's bias gradient -- one streaming
@@ -179,7 +203,7 @@ class _LinearFn(torch.autograd.Function):
             wc = weight.to(dtype) if wc is None else wc
             bc = _shadow_of(bias, dtype)
             bc = (bias.to(dtype) if bias is not None else None) if bc is None else bc
-            y = torch.nn.functional.linear(xc, wc, bc)
+            y = _gemm_fwd(xc, wc, bc, bias.detach() if bias is not None else None)
         ctx.save_for_backward(xc, wc)
         ctx.cfg = (x.dtype, weight.dtype, bias.dtype if bias is not None else None)
         return y

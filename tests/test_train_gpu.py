@@ -217,3 +217,32 @@ def test_clip_folded_into_adamw_matches_clip_grad_norm():
     for a, b in zip(ref.parameters(), mine.parameters()):
         assert torch.allclose(a, b, atol=1e-6, rtol=1e-5)
         assert torch.allclose(a.grad, b.grad, atol=1e-7, rtol=1e-4)       # the clipped gradient is written back
+
+
+def test_native_gemm_in_the_linear_wrapper():
+    """ops.use_native_gemm routes the Linear forward through meant_gemm_bf16_tn: same outputs and gradients (the
+    native kernel adds the fp32 bias before rounding, the library path adds a bf16 bias: <= 1 bf16 ulp apart)."""
+    from meant_b200 import ops
+    torch.manual_seed(0)
+    lin = nn.Linear(768, 2304).cuda()
+    x = torch.randn(8, 128, 768, device="cuda", requires_grad=True)
+    dy = torch.randn(8, 128, 2304, device="cuda").bfloat16()
+    res = {}
+    try:
+        ops.use_fused_linear(True)
+        for native in (False, True):
+            ops.use_native_gemm(native)
+            for t in (x, lin.weight, lin.bias):
+                t.grad = None
+            nv = _lib()
+            nv.reset_launch_count()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                y = ops.linear(x, lin.weight, lin.bias)
+            y.backward(dy)
+            res[native] = (y.detach().float(), x.grad.clone(), lin.weight.grad.clone(), nv.launch_count())
+    finally:
+        ops.use_native_gemm(False)
+        ops.use_fused_linear(False)
+    assert res[True][3] == res[False][3] + 1                 # one more native launch: the GEMM
+    for a, b in zip(res[True][:3], res[False][:3]):
+        assert float((a - b).abs().max()) <= 2e-2 * max(1.0, float(b.abs().max()))
