@@ -11,6 +11,12 @@
 //           the epilogue of tile i runs under the main loop of tile i+1.
 //   warps 2-5  epilogue: TMEM -> registers (+ bias) -> bf16 -> swizzled staging tile -> four TMA stores.
 // Tiles are walked n-fastest, so the CTAs that share an A row block run at the same time and W stays in L2.
+//
+// Measured (B200, M = 98304, K = 768, tools/gemm_probe.py): N = 768 103 us = 1.12 PFLOP/s (cuBLASLt 95 us), N = 2304
+// 275 us = 1.26 PFLOP/s (cuBLASLt 255 us).  Per stage the MMAs read 96 B/clk of shared memory and TMA writes another
+// 96 B/clk, above the SM's 128 B/clk: the remaining gap to the library is its cta_group::2 kernel, which halves the
+// W-operand reads per CTA.  Two variants that cut L2 traffic instead (256 x 256 tiles, multicast CTA pairs) are kept
+// opt-in because they measured slower.
 #include "common.cuh"
 #include "tc_utils.cuh"
 #include "tma_utils.cuh"
@@ -46,6 +52,18 @@ __device__ __forceinline__ void load_box2(uint32_t dst, const CUtensorMap* map, 
 __device__ __forceinline__ void store_box2(const CUtensorMap* map, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];\n"
                ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+
+__device__ __forceinline__ void load_box2_mc(uint32_t dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;\n"
+               ::"r"(dst), "l"(map), "r"(tc::smem_u32(bar)), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void mma_commit_mc(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+               ::"r"(tc::smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
 
 template <int MH>
@@ -177,6 +195,144 @@ __global__ void __launch_bounds__(NT, 1) gemm_tn_kernel(const __grid_constant__ 
   if (warp == 1) tc::tmem_dealloc(tmem, 512);
 }
 
+// The same kernel for a cluster of two CTAs that work on vertically adjacent 128 x 256 tiles: both need the same W box
+// every stage, so each CTA fetches half of it (128 rows) and TMA multicasts it into both CTAs' rings -- a third less
+// L2 -> SM traffic, which is what bounds the single-CTA kernel.  A stage is refilled once BOTH CTAs' MMAs have read
+// it (tcgen05.commit multicast to the two `empty` barriers).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) gemm_tn_mc_kernel(const __grid_constant__ Maps maps, const float* __restrict__ bias,
+                                                        int M, int N, int K) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  constexpr int MH = 1;
+  using C = Cfg<MH>;
+  constexpr int BM = C::BM, NACC = C::NACC, NSTAGE = C::NSTAGE;
+  constexpr uint32_t STAGE = C::STAGE, A_BYTES = C::A_BYTES, OFF_OUT = C::OFF_OUT;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::OFF_BARS);
+  uint64_t *full = bars, *empty = bars + NSTAGE, *acc_full = bars + 2 * NSTAGE, *acc_empty = bars + 2 * NSTAGE + 2;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < NSTAGE; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 2); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_empty[i], 128); }
+    tc::fence_mbar_init();
+  }
+  if (warp == 1) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  cluster_sync();                                      // both CTAs' barriers exist before anything is multicast
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot, s0 = tc::smem_u32(smem);
+  uint32_t rank;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+  const int tiles_n = (N + BN - 1) / BN, tiles_m = (M + BM - 1) / BM, kt = (K + BK - 1) / BK;
+  const int pairs = ((tiles_m + 1) / 2) * tiles_n, cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma::prefetch_map(&maps.a);
+      tma::prefetch_map(&maps.w);
+      int it = 0;
+      for (int p = cluster; p < pairs; p += n_clusters) {
+        const int m0 = (2 * (p / tiles_n) + (int)rank) * BM, n0 = (p % tiles_n) * BN;
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE;
+          if (it >= NSTAGE) tc::mbar_wait(&empty[s], ((it / NSTAGE) - 1) & 1);
+          tma::mbar_expect_tx(&full[s], STAGE);
+#pragma unroll
+          for (int h = 0; h < MH; ++h) load_box2(s0 + s * STAGE + h * HALF_A, &maps.a, &full[s], k * BK, m0 + h * 128);
+          load_box2_mc(s0 + s * STAGE + A_BYTES + rank * (B_BYTES / 2), &maps.w, &full[s], k * BK, n0 + (int)rank * 128, 3);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(128, BN, 0, 0);
+      int it = 0, ti = 0;
+      for (int p = cluster; p < pairs; p += n_clusters, ++ti) {
+        const int acc = ti % NACC, use = ti / NACC;
+        if (use >= 1) tc::mbar_wait(&acc_empty[acc], (use - 1) & 1);
+        tc::fence_after_sync();
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE;
+          tc::mbar_wait(&full[s], (it / NSTAGE) & 1);
+          tc::fence_after_sync();
+          const uint32_t sa = s0 + s * STAGE, sb = sa + A_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t bd = tc::make_desc_sw(sb + kk * 32, 16, 1024, 2);
+#pragma unroll
+            for (int h = 0; h < MH; ++h)
+              tc::mma_ss(tmem + (acc * MH + h) * BN, tc::make_desc_sw(sa + h * HALF_A + kk * 32, 16, 1024, 2), bd, idesc,
+                         k > 0 || kk > 0);
+          }
+          mma_commit_mc(&empty[s], 3);                 // both CTAs' rings: a stage is refilled once both have read it
+        }
+        tc::mma_commit(&acc_full[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;                            // TMEM lane quarter this warp may read
+    const int row = q * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    const bool leader = warp == 2 && lane == 0;
+    int ti = 0;
+    for (int p = cluster; p < pairs; p += n_clusters, ++ti) {
+      const int m0 = (2 * (p / tiles_n) + (int)rank) * BM, n0 = (p % tiles_n) * BN, acc = ti % NACC, use = ti / NACC;
+      tc::mbar_wait(&acc_full[acc], use & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int r = 0; r < C::ROUNDS; ++r) {
+        if (leader) tma::store_wait_read<0>();         // the previous stores have read the staging boxes
+        tc::bar_sync(BAR_EPI, 128);
+#pragma unroll
+        for (int bi = 0; bi < C::SB; ++bi) {
+          const int g = r * C::SB + bi, h = g >> 2, cb = g & 3;      // row half, 64-column box of the tile
+          uint8_t* box = smem + OFF_OUT + bi * OUT_BOX;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float v[32];
+            tc::tmem_ld32(lane_base + (acc * MH + h) * BN + cb * 64 + c * 32, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int gq = 0; gq < 4; ++gq) {
+              float b[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              const int col = n0 + cb * 64 + c * 32 + gq * 8;
+              if (bias && col < N) {                   // N is a multiple of 8: a chunk is in or out as a whole
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(bias + col) + 1);
+                b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+              }
+              uint4 pk;
+              __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(v[gq * 8 + 2 * i] + b[2 * i], v[gq * 8 + 2 * i + 1] + b[2 * i + 1]);
+              *reinterpret_cast<uint4*>(box + tc::sw128_off(row, c * 4 + gq)) = pk;
+            }
+          }
+        }
+        if (r == C::ROUNDS - 1) {
+          tc::fence_before_sync();
+          tc::mbar_arrive(&acc_empty[acc]);            // the accumulator may be overwritten
+        }
+        tc::fence_async_smem();
+        tc::bar_sync(BAR_EPI, 128);
+        if (leader) {
+#pragma unroll
+          for (int bi = 0; bi < C::SB; ++bi) {
+            const int g = r * C::SB + bi, h = g >> 2, cb = g & 3;
+            if (n0 + cb * 64 < N && m0 + h * 128 < M) store_box2(&maps.c, s0 + OFF_OUT + bi * OUT_BOX, n0 + cb * 64, m0 + h * 128);
+          }
+          tma::store_commit();
+        }
+      }
+    }
+    if (leader) tma::store_wait_all();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  cluster_sync();                                      // nobody leaves while its peer may still multicast into it
+  if (warp == 1) tc::tmem_dealloc(tmem, 512);
+}
+
 // 2-D bf16 tensor map: `cols` contiguous elements per row, row pitch ld elements, box = box_cols x box_rows, SWIZZLE_128B
 static int make_map2(CUtensorMap* m, const void* p, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows) {
   tma::EncodeTiledFn enc = tma::encode_fn();
@@ -211,12 +367,22 @@ extern "C" int meant_gemm_bf16_tn(const void* A, const void* W, const float* bia
   g1::Maps maps;
   memset(&maps, 0, sizeof(maps));
   int rc = g1::make_map2(&maps.a, A, M, K, lda, g1::BK, 128);
-  if (!rc) rc = g1::make_map2(&maps.w, W, N, K, ldw, g1::BK, g1::BN);
-  if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, 128);
-  if (rc) return rc;
   int dev = 0, sms = 148;
   if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int64_t tiles_n = (N + g1::BN - 1) / g1::BN;
+  // CTA pairs with a multicast W box: correct but measured 2-15 % SLOWER than the single-CTA kernel on the bench shapes
+  // (the pair runs in lock step; L2 -> SM traffic was not the limiter), so it is opt-in: MEANT_GEMM_MC=1
+  const bool mc = sms % 2 == 0 && ((M + 255) / 256) * tiles_n >= 2 * (int64_t)sms && getenv("MEANT_GEMM_MC") != nullptr;
+  if (!rc) rc = g1::make_map2(&maps.w, W, N, K, ldw, g1::BK, mc ? 128 : g1::BN);
+  if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, 128);
+  if (rc) return rc;
+  if (mc) {
+    cudaError_t e = cudaFuncSetAttribute(g1::gemm_tn_mc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g1::Cfg<1>::SMEM_TOTAL);
+    if (e != cudaSuccess) return (int)e;
+    g1::gemm_tn_mc_kernel<<<sms, g1::NT, g1::Cfg<1>::SMEM_TOTAL, st>>>(maps, bias, (int)M, N, K);
+    MEANT_LAUNCH_CHECK();
+    return 0;
+  }
   // 256-row tiles measured slower on the bench shapes (exposed epilogue, coarser waves): opt-in for experiments
   const bool big = getenv("MEANT_GEMM_TILE256") != nullptr && ((M + 255) / 256) * tiles_n >= 4 * (int64_t)sms;
   const int bm = big ? 256 : 128;
