@@ -12,6 +12,14 @@
 //   S = Q K^T, dP = dO V^T -> P, dS (bf16, shared) -> dV = P^T dO, dK = dS^T Q, dQ = dS K,
 //   every transposed operand read MN-major from the buffer that was staged once; dQ/dK are
 //   un-rotated (transpose rotation) in the epilogue.
+// Backward, multi-tile (Sq or Sk > 128: the 196-patch vision path, S = 512 text), two launches of one kernel,
+// 256 threads (threads t and t+128 share query row / TMEM lane t and split the key columns):
+//   MODE 0  one CTA per (sequence, head, 128-key tile): K, V staged once, loop over query tiles,
+//           dV += P^T dO and dK += dS^T Q accumulate in TMEM across the loop
+//   MODE 1  one CTA per (sequence, head, 128-query tile): Q, dO staged once, loop over key tiles,
+//           dQ += dS K accumulates in TMEM
+//   S and dP are recomputed in both (8 MMA chains per tile pair instead of 5): no atomics, no fp32
+//   workspace, bit-reproducible gradients.  Causal problems skip the tile pairs above the diagonal.
 // Work per sequence and the roofline that bounds it: DESIGN.md.
 #include "attn_common.cuh"
 #include "tc_utils.cuh"
@@ -29,12 +37,12 @@ constexpr float LN2 = 0.6931471805599453f;
 // Stage rows [s0, s0+128) of a head view into chunk layout, optionally rotating pairs with the
 // per-element tables (cos/sin already carry the xPos scale).  Lanes walk 16-byte chunks of a
 // row first, so global reads are contiguous DH*2-byte segments.
-template <int DH>
+template <int DH, int NT = 128>
 __device__ __forceinline__ void stage_rows(uint8_t* smem, const HeadView& v, int n, int n2c, int h, int s0, int S,
                                            const float* __restrict__ cs, const float* __restrict__ sn, int rot_dim,
                                            int pos_is_head) {
   constexpr int CPR = DH / 8;
-  for (int idx = threadIdx.x; idx < 128 * CPR; idx += 128) {
+  for (int idx = threadIdx.x; idx < 128 * CPR; idx += NT) {
     const int r = idx / CPR, ch = idx - r * CPR;
     const int srow = s0 + r;
     uint4 raw = make_uint4(0u, 0u, 0u, 0u);
@@ -360,6 +368,194 @@ __global__ void __launch_bounds__(128, 1) attn_tc_bwd_kernel(AttnArgs a) {
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
+// ---------------------------------------------------------------------- backward, multi-tile
+template <int DH, int MODE>
+__global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ uint64_t bar1, bar2;
+  __shared__ uint32_t tmem_slot;
+  using L = BwdSmem<DH>;
+  constexpr int NT = 256;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_A = 256, T_B = 384;   // MODE 0: A = dV, B = dK; MODE 1: A = dQ
+  const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, half = tid >> 7;
+  const int tile = blockIdx.x, h = blockIdx.y, n = blockIdx.z;
+  if (tid == 0) {
+    tc::mbar_init(&bar1, 1);
+    tc::mbar_init(&bar2, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  const int nq = (a.Sq + TQ - 1) / TQ, nk = (a.Sk + TK - 1) / TK;
+  const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+  const uint32_t sq = tc::smem_u32(smem + L::Q), sk = tc::smem_u32(smem + L::K), sv = tc::smem_u32(smem + L::V),
+                 sdo = tc::smem_u32(smem + L::DO), sp = tc::smem_u32(smem + L::P), sds = tc::smem_u32(smem + L::DS);
+
+  float delta = 0.f, lse2 = 0.f;
+  // Q (rotated) and dO rows [q0, q0+128) -> shared; delta = <dO, O> and the LSE of query row q0 + t
+  auto stage_queries = [&](int q0) {
+    stage_rows<DH, NT>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+    stage_rows<DH, NT>(smem + L::DO, a.o, n, a.n2_count, h, q0, a.Sq, nullptr, nullptr, 0, 0);
+    delta = 0.f;
+    lse2 = 0.f;
+    const int qi = q0 + t;
+    if (qi < a.Sq) {
+      const __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h);
+      const __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
+#pragma unroll
+      for (int c0 = 0; c0 < DH; c0 += 8) {
+        const uint4 ov = *reinterpret_cast<const uint4*>(op + c0), gv = *reinterpret_cast<const uint4*>(gp + c0);
+        const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
+        const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 x = __bfloat1622float2(o2[i]), y = __bfloat1622float2(g2[i]);
+          delta += x.x * y.x + x.y * y.y;
+        }
+      }
+      const int64_t li = ((int64_t)n * a.H + h) * a.Sq + qi;
+      lse2 = a.lse[li] * LOG2E;
+      if (MODE == 1 && half == 0) a.delta[li] = delta;
+    }
+  };
+  auto stage_keys = [&](int k0) {
+    stage_rows<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    stage_rows<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0, a.Sk, nullptr, nullptr, 0, 0);
+  };
+
+  int j0, j1;   // loop over the other axis' tiles
+  if (MODE == 0) {
+    stage_keys(tile * TK);
+    j0 = a.causal ? tile : 0;
+    j1 = nq;
+  } else {
+    stage_queries(tile * TQ);
+    j0 = 0;
+    j1 = a.causal ? min(nk, tile + 1) : nk;
+  }
+  uint32_t phase = 0;
+  bool first = true;
+  uint32_t tmem = 0;
+#pragma unroll 1
+  for (int j = j0; j < j1; ++j) {
+    const int q0 = (MODE == 0 ? j : tile) * TQ, k0 = (MODE == 0 ? tile : j) * TK;
+    if (MODE == 0) stage_queries(q0); else stage_keys(k0);
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    tmem = tmem_slot;
+    if (tid == 0) {
+      constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
+#pragma unroll
+      for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
+#pragma unroll
+      for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_kmajor(sdo, ks), desc_kmajor(sv, ks), idesc, ks > 0);
+      tc::mma_commit(&bar1);
+    }
+    tc::mbar_wait(&bar1, phase);
+    tc::fence_after_sync();
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const int qi = q0 + t;
+#pragma unroll 1
+    for (int c0 = half * (TK / 2); c0 < (half + 1) * (TK / 2); c0 += 16) {
+      float s[16], dp[16];
+      tc::tmem_ld16(lane_base + T_S + c0, s);
+      tc::tmem_ld16(lane_base + T_DP + c0, dp);
+      tc::tmem_ld_wait();
+      uint4 pk[2], dk[2];
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
+      __nv_bfloat162* dh = reinterpret_cast<__nv_bfloat162*>(dk);
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) {
+        float p[2], ds[2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const int kj = k0 + c0 + i + jj;
+          const bool valid = qi < a.Sq && kj < a.Sk && (!a.causal || kj <= qi);
+          p[jj] = valid ? exp2f(masked_score(s[i + jj], a.scale, mrow, kj, true) - lse2) : 0.f;
+          ds[jj] = p[jj] * (dp[i + jj] - delta) * a.scale;
+        }
+        ph[i >> 1] = __floats2bfloat162_rn(p[0], p[1]);
+        dh[i >> 1] = __floats2bfloat162_rn(ds[0], ds[1]);
+      }
+      if (MODE == 0) {
+        *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk[0];
+        *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
+      }
+      *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8) * CS128 + t * 16) = dk[0];
+      *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8 + 1) * CS128 + t * 16) = dk[1];
+    }
+    tc::fence_async_smem();
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    if (tid == 0) {
+      constexpr uint32_t id_t = tc::make_idesc(TK, DH, 1, 1);   // A^T (MN-major) x B (MN-major)
+      constexpr uint32_t id_n = tc::make_idesc(TQ, DH, 0, 1);   // A (K-major)    x B (MN-major)
+      const uint32_t acc = first ? 0u : 1u;
+      if (MODE == 0) {
+#pragma unroll
+        for (int ks = 0; ks < TQ / 16; ++ks)      // dV += P^T dO   (K = queries)
+          tc::mma_ss(tmem + T_A, desc_mnmajor(sp, ks), desc_mnmajor(sdo, ks), id_t, acc | (ks > 0));
+#pragma unroll
+        for (int ks = 0; ks < TQ / 16; ++ks)      // dK += dS^T Q
+          tc::mma_ss(tmem + T_B, desc_mnmajor(sds, ks), desc_mnmajor(sq, ks), id_t, acc | (ks > 0));
+      } else {
+#pragma unroll
+        for (int ks = 0; ks < TK / 16; ++ks)      // dQ += dS K     (K = keys)
+          tc::mma_ss(tmem + T_A, desc_kmajor(sds, ks), desc_mnmajor(sk, ks), id_n, acc | (ks > 0));
+      }
+      tc::mma_commit(&bar2);
+    }
+    tc::mbar_wait(&bar2, phase);   // operands are overwritten by the next iteration's staging
+    tc::fence_after_sync();
+    first = false;
+    phase ^= 1;
+  }
+  if (first) {   // no tile pair at all (causal with Sk > Sq): the gradients of this tile are zero
+    __syncthreads();
+    tmem = tmem_slot;
+  }
+  const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+  const bool zero = first;
+  auto store_row = [&](uint32_t tcol, __nv_bfloat16* dst, const float* cs, const float* sn, int pos) {
+#pragma unroll
+    for (int c0 = half * (DH / 2); c0 < (half + 1) * (DH / 2); c0 += 16) {
+      float g[16];
+      if (!zero) {
+        tc::tmem_ld16(lane_base + tcol + c0, g);
+        tc::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) g[i] = 0.f;
+      }
+      if (cs != nullptr) unrot16(g, cs, sn, pos, a.rot_dim, c0);
+      uint4 pk[2];
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
+#pragma unroll
+      for (int i = 0; i < 16; i += 2) ph[i >> 1] = __floats2bfloat162_rn(g[i], g[i + 1]);
+      if (dst != nullptr) {
+        *reinterpret_cast<uint4*>(dst + c0) = pk[0];
+        *reinterpret_cast<uint4*>(dst + c0 + 8) = pk[1];
+      }
+    }
+  };
+  const int row = tile * 128 + t;
+  if (MODE == 0) {
+    const bool ok = row < a.Sk;
+    store_row(T_A, ok ? view_ptr<__nv_bfloat16>(a.dv, n, a.n2_count, row, h) : nullptr, nullptr, nullptr, 0);
+    store_row(T_B, ok ? view_ptr<__nv_bfloat16>(a.dk, n, a.n2_count, row, h) : nullptr, a.kcos, a.ksin,
+              a.pos_is_head ? h : min(row, a.Sk - 1));
+  } else {
+    const bool ok = row < a.Sq;
+    store_row(T_A, ok ? view_ptr<__nv_bfloat16>(a.dq, n, a.n2_count, row, h) : nullptr, a.qcos, a.qsin,
+              a.pos_is_head ? h : min(row, a.Sq - 1));
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
 // ------------------------------------------------------------------------------------ host side
 // attn_tc2.cu: persistent warp-specialised kernels for single-tile problems (Sq, Sk <= 128)
 int attn_tc2_supported(const AttnArgs& a, int backward);
@@ -379,19 +575,26 @@ int attn_tc_supported(const AttnArgs& a, int dtype, int backward) {
   if (a.qcos && (!a.qsin || !a.kcos || !a.ksin)) return 0;
   if (!view_ok(a.q) || !view_ok(a.k) || !view_ok(a.v) || !view_ok(a.o)) return 0;
   if (backward) {
-    if (a.Sq > TQ || a.Sk > TK) return 0;   // multi-tile backward: exact path for now
     if (!view_ok(a.dq) || !view_ok(a.dk) || !view_ok(a.dv) || !view_ok(a.out_saved) || !a.lse || !a.delta) return 0;
   }
   return 1;
 }
 
 template <typename Kern>
-static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaStream_t st) {
+static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaStream_t st, int threads = 128) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  kern<<<grid, 128, smem, st>>>(a);
+  kern<<<grid, threads, smem, st>>>(a);
   MEANT_LAUNCH_CHECK();
   return 0;
+}
+
+template <int DH>
+static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
+  const dim3 gk((a.Sk + TK - 1) / TK, a.H, a.N), gq((a.Sq + TQ - 1) / TQ, a.H, a.N);
+  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, BwdSmem<DH>::TOTAL, gk, a, st, 256);
+  if (r != 0) return r;
+  return launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, BwdSmem<DH>::TOTAL, gq, a, st, 256);
 }
 
 static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels
@@ -413,6 +616,7 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
     if (r2 != MEANT_EUNSUPPORTED) return r2;
     ++g_tma_fallbacks;
   }
+  if (a.Sq > TQ || a.Sk > TK) return a.Dh == 96 ? launch_bwd_mt<96>(a, st) : launch_bwd_mt<64>(a, st);
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);

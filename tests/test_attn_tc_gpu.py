@@ -1,6 +1,6 @@
 """tcgen05 attention kernels against the CUDA-core exact kernels (same C ABI, same inputs) and a
-torch fp32 reference of the same op: forward for every tile configuration, backward where the
-tensor-core backward applies (Sq, Sk <= 128)."""
+torch fp32 reference of the same op: forward and backward for every tile configuration (single-tile
+Sq, Sk <= 128: the persistent TMA kernels; larger: the multi-tile kernels of attn_tc.cu)."""
 import math
 
 import pytest
@@ -41,10 +41,13 @@ CASES = [  # n, s, heads, dh, causal, xpos, masked, backward
     (2, 128, 8, 96, False, False, False, True),
     (2, 77, 8, 96, True, True, True, True),
     (1, 1, 8, 96, True, True, False, True),
-    (2, 196, 8, 96, False, True, False, False),
-    (1, 512, 8, 96, True, True, True, False),
+    (2, 196, 8, 96, False, True, False, True),
+    (1, 512, 8, 96, True, True, True, True),
     (5, 13, 8, 64, False, False, False, True),
-    (2, 197, 8, 64, False, False, False, False),
+    (2, 197, 8, 64, False, False, False, True),
+    (2, 300, 8, 96, True, True, True, True),      # three ragged tiles, causal diagonal skipping
+    (1, 129, 8, 64, True, False, False, True),    # one row in the second tile
+    (2, 256, 8, 96, False, False, True, True),
 ]
 
 
@@ -90,3 +93,34 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
                     continue
                 c = torch.nn.functional.cosine_similarity(g[..., sl].flatten(), want, dim=0)
                 assert float(c) > 0.998, (name, part, float(c))
+
+
+def test_multitile_backward_is_reproducible_and_cross_shaped():
+    """Multi-tile backward: bit-identical gradients run to run (no atomics), and Sq != Sk (q | kv inputs)."""
+    torch.manual_seed(5)
+    heads, dh = 8, 96
+    dim = heads * dh
+    n, sq, sk = 2, 200, 333
+    q0 = torch.randn(n, sq, dim, device="cuda").bfloat16()
+    kv0 = torch.randn(n, sk, 2 * dim, device="cuda").bfloat16()
+    probe = torch.randn(n, sq, dim, device="cuda")
+    scale = dh ** -0.5
+    got = []
+    for impl in (nv.IMPL_TCGEN05, nv.IMPL_TCGEN05, nv.IMPL_EXACT):
+        q, kv = q0.clone().requires_grad_(True), kv0.clone().requires_grad_(True)
+        o = ops.attention(q=q, kv=kv, heads=heads, scale=scale, impl=impl)
+        (o.float() * probe).sum().backward()
+        got.append((o.float(), q.grad.float(), kv.grad.float()))
+    torch.cuda.synchronize()
+    for a, b in zip(got[0], got[1]):
+        assert torch.equal(a, b)
+    qf, kvf = q0.float().requires_grad_(True), kv0.float().requires_grad_(True)
+    k, v = kvf.split(dim, dim=-1)
+    qh, kh, vh = (t.view(n, -1, heads, dh).transpose(1, 2) for t in (qf, k, v))
+    ref = ((qh @ kh.transpose(-1, -2) * scale).softmax(-1) @ vh).transpose(1, 2).reshape(n, sq, dim)
+    (ref * probe).sum().backward()
+    assert float((got[0][0] - ref).abs().max()) < 2e-2
+    for name, g, want in (("dq", got[0][1], qf.grad), ("dkv", got[0][2], kvf.grad)):
+        c = torch.nn.functional.cosine_similarity(g.flatten(), want.flatten(), dim=0)
+        assert float(c) > 0.999, (name, float(c))
+        assert float((g - want).abs().max()) < 0.05 * float(want.abs().max()) + 1e-3, name
