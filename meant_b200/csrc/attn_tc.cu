@@ -14,10 +14,12 @@
 //   un-rotated (transpose rotation) in the epilogue.
 // Backward, multi-tile (Sq or Sk > 128: the 196-patch vision path, S = 512 text), two launches of one kernel,
 // 256 threads (threads t and t+128 share query row / TMEM lane t and split the key columns):
+//   MODE 1  one CTA per (sequence, head, 128-query tile): Q, dO staged once, loop over key tiles,
+//           dQ += dS K accumulates in TMEM; also writes delta = rowsum(dO * O)           (runs first)
 //   MODE 0  one CTA per (sequence, head, 128-key tile): K, V staged once, loop over query tiles,
 //           dV += P^T dO and dK += dS^T Q accumulate in TMEM across the loop
-//   MODE 1  one CTA per (sequence, head, 128-query tile): Q, dO staged once, loop over key tiles,
-//           dQ += dS K accumulates in TMEM
+//   Operands are staged with cp.async (all 16-byte copies of a tile in flight at once, the streamed pair
+//   double-buffered so tile j+1 loads under tile j's MMAs and softmax recompute) and rotated in place.
 //   S and dP are recomputed in both (8 MMA chains per tile pair instead of 5): no atomics, no fp32
 //   workspace, bit-reproducible gradients.  Causal problems skip the tile pairs above the diagonal.
 // Work per sequence and the roofline that bounds it: DESIGN.md.
@@ -88,12 +90,66 @@ struct FwdSmem {
   static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, P = 3 * OPER, TOTAL = 3 * OPER + PBUF;
 };
 
+// Asynchronous staging (multi-tile kernels): rows [s0, s0+128) of a head view go to the chunk layout as
+// 16-byte cp.async copies (rows past S zero-filled), all in flight at once; the caller commits / waits the
+// group.  rotate_staged then rotates the SAME chunks this thread copied (identical idx walk), in place.
+template <int DH, int NT>
+__device__ __forceinline__ void stage_async(uint8_t* smem, const HeadView& v, int n, int n2c, int h, int s0, int S) {
+  constexpr int CPR = DH / 8;
+  const __nv_bfloat16* base = view_ptr<__nv_bfloat16>(v, n, n2c, 0, h);
+  const uint32_t dst0 = tc::smem_u32(smem);
+  static_assert((128 * CPR) % NT == 0, "whole rounds");
+#pragma unroll
+  for (int it = 0; it < 128 * CPR / NT; ++it) {
+    const int idx = threadIdx.x + it * NT;
+    const int r = idx / CPR, ch = idx - r * CPR;
+    const bool ok = s0 + r < S;
+    tc::cp_async16(dst0 + ch * CS128 + r * 16, base + (int64_t)(ok ? s0 + r : 0) * v.ss + ch * 8, ok ? 16u : 0u);
+  }
+}
+
+template <int DH, int NT>
+__device__ __forceinline__ void rotate_staged(uint8_t* smem, int h, int s0, int S, const float* __restrict__ cs,
+                                              const float* __restrict__ sn, int rot_dim, int pos_is_head) {
+  constexpr int CPR = DH / 8;
+  if (cs == nullptr) return;
+  static_assert((128 * CPR) % NT == 0, "whole rounds");
+#pragma unroll
+  for (int it = 0; it < 128 * CPR / NT; ++it) {
+    const int idx = threadIdx.x + it * NT;
+    const int r = idx / CPR, ch = idx - r * CPR;
+    if (ch * 8 >= rot_dim || s0 + r >= S) continue;
+    uint4* slot = reinterpret_cast<uint4*>(smem + ch * CS128 + r * 16);
+    uint4 raw = *slot;
+    const int pos = pos_is_head ? h : s0 + r;
+    const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + ch * 8);
+    const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + ch * 8);
+    const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+    __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+    float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+    float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+    h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+    h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+    h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+    h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+    *slot = raw;
+  }
+}
+
+// additive score term of key kj in the log2 domain: (1 - m) * -1e9 * log2(e), -inf past the last key
+__device__ __forceinline__ float key_term(const float* mrow, int kj, int Sk) {
+  if (kj >= Sk) return -CUDART_INF_F;
+  return mrow != nullptr ? (1.0f - __ldg(mrow + kj)) * (-1e9f * LOG2E) : 0.f;
+}
+
 template <int DH>
 __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar_s, bar_o;
   __shared__ uint32_t tmem_slot;
+  __shared__ float kterm[TK];
   using L = FwdSmem<DH>;
+  constexpr int NT = 128;
   const int t = threadIdx.x, warp = t >> 5;
   const int q0 = blockIdx.x * TQ, h = blockIdx.y, n = blockIdx.z;
   if (t == 0) {
@@ -102,24 +158,34 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
-  stage_rows<DH>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+  // cp.async groups, oldest first: [Q + K(0)] [V(0)] then per tile [K(kt+1)] [V(kt+1)] (empty past the end)
+  stage_async<DH, NT>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq);
+  stage_async<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, 0, a.Sk);
+  tc::cp_async_commit();
+  stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk);
+  tc::cp_async_commit();
 
   const int qi = q0 + t;
   const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+  const float sc2 = a.scale * LOG2E;
   float m_run = -CUDART_INF_F, l_run = 0.f;
   float o_acc[DH];
 #pragma unroll
   for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
   const int last_q = min(q0 + TQ, a.Sq) - 1;
-  const int n_tiles = (a.Sk + TK - 1) / TK;
+  int n_tiles = (a.Sk + TK - 1) / TK;
+  if (a.causal) n_tiles = min(n_tiles, last_q / TK + 1);
   uint32_t phase = 0, tmem = 0;
   const uint32_t sq = tc::smem_u32(smem + L::Q), sk = tc::smem_u32(smem + L::K), sv = tc::smem_u32(smem + L::V),
                  sp = tc::smem_u32(smem + L::P);
+#pragma unroll 1
   for (int kt = 0; kt < n_tiles; ++kt) {
     const int k0 = kt * TK;
-    if (a.causal && k0 > last_q) break;
-    stage_rows<DH>(smem + L::K, a.k, n, a.n2_count, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
-    stage_rows<DH>(smem + L::V, a.v, n, a.n2_count, h, k0, a.Sk, nullptr, nullptr, 0, 0);
+    const bool more = kt + 1 < n_tiles;
+    tc::cp_async_wait<1>();            // K(kt) (and Q) landed; V(kt) may still be in flight
+    if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+    rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    kterm[t] = key_term(mrow, k0 + t, a.Sk);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -133,50 +199,52 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar_s, phase);
     tc::fence_after_sync();
+    if (more) stage_async<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, k0 + TK, a.Sk);   // K is free: next tile
+    tc::cp_async_commit();
     const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+    const bool diag = a.causal && k0 + TK - 1 > q0;   // some (row, key) of this tile pair is above the diagonal
     // pass 1: row max
     float m_tile = -CUDART_INF_F;
 #pragma unroll 1
-    for (int c0 = 0; c0 < TK; c0 += 16) {
-      float s[16];
-      tc::tmem_ld16(lane_base + c0, s);
+    for (int c0 = 0; c0 < TK; c0 += 32) {
+      float s[32];
+      tc::tmem_ld32(lane_base + c0, s);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int kj = k0 + c0 + i;
-        const bool valid = kj < a.Sk && (!a.causal || kj <= qi);
-        m_tile = fmaxf(m_tile, masked_score(s[i], a.scale, mrow, kj, valid));
+      for (int i = 0; i < 32; ++i) {
+        float x = fmaf(s[i], sc2, kterm[c0 + i]);
+        if (diag && k0 + c0 + i > qi) x = -CUDART_INF_F;
+        m_tile = fmaxf(m_tile, x);
       }
     }
     const float m_new = fmaxf(m_run, m_tile);
     const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
-    const float corr = exp2f(m_run - m_use);   // m_run = -inf -> 0
+    const float corr = tc::ex2(m_run - m_use);   // m_run = -inf -> 0
     // pass 2: P = exp2(x - m), bf16 -> shared (row t, 16-byte chunks), row sum
     float l_tile = 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < TK; c0 += 16) {
-      float s[16];
-      tc::tmem_ld16(lane_base + c0, s);
+    for (int c0 = 0; c0 < TK; c0 += 32) {
+      float s[32];
+      tc::tmem_ld32(lane_base + c0, s);
       tc::tmem_ld_wait();
-      uint4 pk[2];
+      uint4 pk[4];
       __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
 #pragma unroll
-      for (int i = 0; i < 16; i += 2) {
-        const int kj = k0 + c0 + i;
-        const bool v0 = kj < a.Sk && (!a.causal || kj <= qi);
-        const bool v1 = kj + 1 < a.Sk && (!a.causal || kj + 1 <= qi);
-        const float p0 = exp2f(masked_score(s[i], a.scale, mrow, kj, v0) - m_use);
-        const float p1 = exp2f(masked_score(s[i + 1], a.scale, mrow, kj + 1, v1) - m_use);
-        const __nv_bfloat162 pb = __floats2bfloat162_rn(p0, p1);
+      for (int i = 0; i < 32; i += 2) {
+        float x0 = fmaf(s[i], sc2, kterm[c0 + i]), x1 = fmaf(s[i + 1], sc2, kterm[c0 + i + 1]);
+        if (diag && k0 + c0 + i > qi) x0 = -CUDART_INF_F;
+        if (diag && k0 + c0 + i + 1 > qi) x1 = -CUDART_INF_F;
+        const __nv_bfloat162 pb = __floats2bfloat162_rn(tc::ex2(x0 - m_use), tc::ex2(x1 - m_use));
         ph[i >> 1] = pb;
         const float2 back = __bfloat1622float2(pb);   // sum what the tensor core will see
         l_tile += back.x + back.y;
       }
-      *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk[0];
-      *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + j) * CS128 + t * 16) = pk[j];
     }
     l_run = l_run * corr + l_tile;
     m_run = m_new;
+    tc::cp_async_wait<1>();            // V(kt) landed (K(kt+1) may still be in flight)
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -190,16 +258,19 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar_o, phase);
     tc::fence_after_sync();
+    if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, a.Sk);   // V is free: next tile
+    tc::cp_async_commit();
 #pragma unroll
-    for (int c0 = 0; c0 < DH; c0 += 16) {
-      float pv[16];
-      tc::tmem_ld16(lane_base + 128 + c0, pv);
+    for (int c0 = 0; c0 < DH; c0 += 32) {
+      float pv[32];
+      tc::tmem_ld32(lane_base + 128 + c0, pv);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 16; ++i) o_acc[c0 + i] = o_acc[c0 + i] * corr + pv[i];
+      for (int i = 0; i < 32; ++i) o_acc[c0 + i] = o_acc[c0 + i] * corr + pv[i];
     }
     phase ^= 1;
   }
+  tc::cp_async_wait<0>();
   if (qi < a.Sq) {
     const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
     __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
@@ -369,12 +440,22 @@ __global__ void __launch_bounds__(128, 1) attn_tc_bwd_kernel(AttnArgs a) {
 }
 
 // ---------------------------------------------------------------------- backward, multi-tile
+// Shared memory: the fixed pair (MODE 0: K|V, MODE 1: Q|dO), the streamed pair double-buffered, P, dS.
+template <int DH>
+struct MtSmem {
+  static constexpr uint32_t OPER = (DH / 8) * CS128;
+  static constexpr uint32_t PBUF = (TK / 8) * CS128;
+  static constexpr uint32_t FIX0 = 0, FIX1 = OPER, STR = 2 * OPER /* [2][2] */, P = 6 * OPER, DS = 6 * OPER + PBUF,
+                            TOTAL = 6 * OPER + 2 * PBUF;
+};
+
 template <int DH, int MODE>
 __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar1, bar2;
   __shared__ uint32_t tmem_slot;
-  using L = BwdSmem<DH>;
+  __shared__ float kterm[TK];
+  using L = MtSmem<DH>;
   constexpr int NT = 256;
   constexpr uint32_t T_S = 0, T_DP = 128, T_A = 256, T_B = 384;   // MODE 0: A = dV, B = dK; MODE 1: A = dQ
   const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, half = tid >> 7;
@@ -387,58 +468,86 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
   const int nq = (a.Sq + TQ - 1) / TQ, nk = (a.Sk + TK - 1) / TK;
   const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
-  const uint32_t sq = tc::smem_u32(smem + L::Q), sk = tc::smem_u32(smem + L::K), sv = tc::smem_u32(smem + L::V),
-                 sdo = tc::smem_u32(smem + L::DO), sp = tc::smem_u32(smem + L::P), sds = tc::smem_u32(smem + L::DS);
+  const float sc2 = a.scale * LOG2E;
 
-  float delta = 0.f, lse2 = 0.f;
-  // Q (rotated) and dO rows [q0, q0+128) -> shared; delta = <dO, O> and the LSE of query row q0 + t
-  auto stage_queries = [&](int q0) {
-    stage_rows<DH, NT>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
-    stage_rows<DH, NT>(smem + L::DO, a.o, n, a.n2_count, h, q0, a.Sq, nullptr, nullptr, 0, 0);
-    delta = 0.f;
-    lse2 = 0.f;
-    const int qi = q0 + t;
-    if (qi < a.Sq) {
-      const __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h);
-      const __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
-#pragma unroll
-      for (int c0 = 0; c0 < DH; c0 += 8) {
-        const uint4 ov = *reinterpret_cast<const uint4*>(op + c0), gv = *reinterpret_cast<const uint4*>(gp + c0);
-        const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
-        const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 x = __bfloat1622float2(o2[i]), y = __bfloat1622float2(g2[i]);
-          delta += x.x * y.x + x.y * y.y;
-        }
-      }
-      const int64_t li = ((int64_t)n * a.H + h) * a.Sq + qi;
-      lse2 = a.lse[li] * LOG2E;
-      if (MODE == 1 && half == 0) a.delta[li] = delta;
+  // streamed tile j -> buffer pair b:  MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
+  auto stream = [&](int j, int b) {
+    uint8_t* x = smem + L::STR + (uint32_t)b * 2 * L::OPER;
+    if (MODE == 0) {
+      stage_async<DH, NT>(x, a.q, n, a.n2_count, h, j * TQ, a.Sq);
+      stage_async<DH, NT>(x + L::OPER, a.o, n, a.n2_count, h, j * TQ, a.Sq);
+    } else {
+      stage_async<DH, NT>(x, a.k, n, a.n2_count, h, j * TK, a.Sk);
+      stage_async<DH, NT>(x + L::OPER, a.v, n, a.n2_count, h, j * TK, a.Sk);
     }
   };
-  auto stage_keys = [&](int k0) {
-    stage_rows<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
-    stage_rows<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0, a.Sk, nullptr, nullptr, 0, 0);
+  // delta = <dO, O> (computed once per query tile by the dQ pass, which runs first) and the LSE of query row qi
+  float delta = 0.f, lse2 = 0.f;
+  auto row_stats = [&](int qi) {
+    delta = 0.f;
+    lse2 = 0.f;
+    if (qi >= a.Sq) return;
+    const int64_t li = ((int64_t)n * a.H + h) * a.Sq + qi;
+    lse2 = a.lse[li] * LOG2E;
+    if (MODE == 0) {
+      delta = a.delta[li];
+      return;
+    }
+    const __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h);
+    const __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
+#pragma unroll
+    for (int c0 = 0; c0 < DH; c0 += 8) {
+      const uint4 ov = *reinterpret_cast<const uint4*>(op + c0), gv = *reinterpret_cast<const uint4*>(gp + c0);
+      const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 x = __bfloat1622float2(o2[i]), y = __bfloat1622float2(g2[i]);
+        delta += x.x * y.x + x.y * y.y;
+      }
+    }
+    if (half == 0) a.delta[li] = delta;
   };
 
-  int j0, j1;   // loop over the other axis' tiles
+  int j0, j1;   // tiles of the other axis; causal problems skip the pairs above the diagonal
   if (MODE == 0) {
-    stage_keys(tile * TK);
     j0 = a.causal ? tile : 0;
     j1 = nq;
+    stage_async<DH, NT>(smem + L::FIX0, a.k, n, a.n2_count, h, tile * TK, a.Sk);
+    stage_async<DH, NT>(smem + L::FIX1, a.v, n, a.n2_count, h, tile * TK, a.Sk);
   } else {
-    stage_queries(tile * TQ);
     j0 = 0;
     j1 = a.causal ? min(nk, tile + 1) : nk;
+    stage_async<DH, NT>(smem + L::FIX0, a.q, n, a.n2_count, h, tile * TQ, a.Sq);
+    stage_async<DH, NT>(smem + L::FIX1, a.o, n, a.n2_count, h, tile * TQ, a.Sq);
   }
-  uint32_t phase = 0;
+  if (j0 < j1) stream(j0, 0);
+  tc::cp_async_commit();
+  if (MODE == 1) row_stats(tile * TQ + t);
+  if (MODE == 0 && tid < TK) kterm[tid] = key_term(mrow, tile * TK + tid, a.Sk);
+
+  uint32_t phase = 0, tmem = 0;
   bool first = true;
-  uint32_t tmem = 0;
 #pragma unroll 1
   for (int j = j0; j < j1; ++j) {
+    const int b = (j - j0) & 1;
     const int q0 = (MODE == 0 ? j : tile) * TQ, k0 = (MODE == 0 ? tile : j) * TK;
-    if (MODE == 0) stage_queries(q0); else stage_keys(k0);
+    if (j + 1 < j1) stream(j + 1, b ^ 1);      // the other pair was released by the previous iteration's bar2
+    tc::cp_async_commit();
+    tc::cp_async_wait<1>();                     // tile j (and the fixed pair) landed
+    uint8_t* xs = smem + L::STR + (uint32_t)b * 2 * L::OPER;
+    if (MODE == 0) {
+      row_stats(q0 + t);
+      rotate_staged<DH, NT>(xs, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    } else {
+      rotate_staged<DH, NT>(xs, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+      if (tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
+    }
+    const uint32_t sq = tc::smem_u32(MODE == 0 ? xs : smem + L::FIX0), sdo = sq + L::OPER;
+    const uint32_t sk = tc::smem_u32(MODE == 0 ? smem + L::FIX0 : xs), sv = sk + L::OPER;
+    const uint32_t sp = tc::smem_u32(smem + L::P), sds = tc::smem_u32(smem + L::DS);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -456,6 +565,8 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     tc::fence_after_sync();
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int qi = q0 + t;
+    const bool diag = a.causal && k0 + TK - 1 > q0;
+    const bool qok = qi < a.Sq;
 #pragma unroll 1
     for (int c0 = half * (TK / 2); c0 < (half + 1) * (TK / 2); c0 += 16) {
       float s[16], dp[16];
@@ -470,9 +581,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
         float p[2], ds[2];
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
-          const int kj = k0 + c0 + i + jj;
-          const bool valid = qi < a.Sq && kj < a.Sk && (!a.causal || kj <= qi);
-          p[jj] = valid ? exp2f(masked_score(s[i + jj], a.scale, mrow, kj, true) - lse2) : 0.f;
+          const int c = c0 + i + jj;
+          float x = fmaf(s[i + jj], sc2, kterm[c]) - lse2;       // -inf past the last key
+          if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+          p[jj] = tc::ex2(x);
           ds[jj] = p[jj] * (dp[i + jj] - delta) * a.scale;
         }
         ph[i >> 1] = __floats2bfloat162_rn(p[0], p[1]);
@@ -507,11 +619,12 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
       }
       tc::mma_commit(&bar2);
     }
-    tc::mbar_wait(&bar2, phase);   // operands are overwritten by the next iteration's staging
+    tc::mbar_wait(&bar2, phase);   // releases this tile's buffers, P and dS
     tc::fence_after_sync();
     first = false;
     phase ^= 1;
   }
+  tc::cp_async_wait<0>();
   if (first) {   // no tile pair at all (causal with Sk > Sq): the gradients of this tile are zero
     __syncthreads();
     tmem = tmem_slot;
@@ -592,9 +705,10 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
 template <int DH>
 static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
   const dim3 gk((a.Sk + TK - 1) / TK, a.H, a.N), gq((a.Sq + TQ - 1) / TQ, a.H, a.N);
-  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, BwdSmem<DH>::TOTAL, gk, a, st, 256);
+  // the dQ pass goes first: it also writes delta = rowsum(dO * O), which the dK|dV pass reads
+  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, MtSmem<DH>::TOTAL, gq, a, st, 256);
   if (r != 0) return r;
-  return launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, BwdSmem<DH>::TOTAL, gq, a, st, 256);
+  return launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, MtSmem<DH>::TOTAL, gk, a, st, 256);
 }
 
 static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels
