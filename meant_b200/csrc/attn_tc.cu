@@ -36,6 +36,17 @@ constexpr uint32_t CS128 = 128 * 16 + 16;     // chunk stride of a 128-row chunk
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
+// Optional phase timing of the multi-tile forward (build with MEANT_PROF=1): thread 0 of CTA (0,0,0) adds
+// clock64 deltas per phase; read with meant_debug_prof_mt().  Never compiled into product builds.
+#ifdef MEANT_PROF
+__device__ unsigned long long g_prof_mt[32];
+#define MT_PROF_INIT() const bool prof_on = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0; long long prof_t = clock64()
+#define MT_PROF(slot) do { if (prof_on) { const long long now_ = clock64(); atomicAdd(&g_prof_mt[slot], (unsigned long long)(now_ - prof_t)); prof_t = now_; } } while (0)
+#else
+#define MT_PROF_INIT() do {} while (0)
+#define MT_PROF(slot) do {} while (0)
+#endif
+
 // Stage rows [s0, s0+128) of a head view into chunk layout, optionally rotating pairs with the
 // per-element tables (cos/sin already carry the xPos scale).  Lanes walk 16-byte chunks of a
 // row first, so global reads are contiguous DH*2-byte segments.
@@ -90,49 +101,82 @@ struct FwdSmem {
   static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, P = 3 * OPER, TOTAL = 3 * OPER + PBUF;
 };
 
-// Asynchronous staging (multi-tile kernels): rows [s0, s0+128) of a head view go to the chunk layout as
-// 16-byte cp.async copies (rows past S zero-filled), all in flight at once; the caller commits / waits the
-// group.  rotate_staged then rotates the SAME chunks this thread copied (identical idx walk), in place.
+// Asynchronous staging (multi-tile kernels, 256 threads): rows [s0, s0+128) of a head view go to the chunk layout
+// as 16-byte cp.async copies (rows past S zero-filled), all in flight at once; the caller commits / waits the
+// group.  Thread -> (row tid/2, chunk 2*round + tid%2): a lane pair reads one whole 32-byte sector, and the chunk
+// index is warp-uniform up to its parity, so "is this chunk rotated" never diverges (rot_dim % 16 == 0).
+// rotate_staged then rotates the SAME chunks this thread copied (identical walk), in place, with all table
+// loads of a tile issued before the first use.
 template <int DH, int NT>
 __device__ __forceinline__ void stage_async(uint8_t* smem, const HeadView& v, int n, int n2c, int h, int s0, int S) {
+  static_assert(NT == 256, "thread -> (row, chunk parity) mapping");
   constexpr int CPR = DH / 8;
-  const __nv_bfloat16* base = view_ptr<__nv_bfloat16>(v, n, n2c, 0, h);
-  const uint32_t dst0 = tc::smem_u32(smem);
-  static_assert((128 * CPR) % NT == 0, "whole rounds");
+  const int r = threadIdx.x >> 1, par = threadIdx.x & 1;
+  const bool ok = s0 + r < S;
+  const __nv_bfloat16* src = view_ptr<__nv_bfloat16>(v, n, n2c, ok ? s0 + r : 0, h) + par * 8;
+  const uint32_t dst = tc::smem_u32(smem) + par * CS128 + r * 16;
+  const uint32_t bytes = ok ? 16u : 0u;
 #pragma unroll
-  for (int it = 0; it < 128 * CPR / NT; ++it) {
-    const int idx = threadIdx.x + it * NT;
-    const int r = idx / CPR, ch = idx - r * CPR;
-    const bool ok = s0 + r < S;
-    tc::cp_async16(dst0 + ch * CS128 + r * 16, base + (int64_t)(ok ? s0 + r : 0) * v.ss + ch * 8, ok ? 16u : 0u);
+  for (int it = 0; it < CPR / 2; ++it) tc::cp_async16(dst + it * 2 * CS128, src + it * 16, bytes);
+}
+
+// RR = rotated rounds (rot_dim / 16)
+template <int DH, int RR>
+__device__ __forceinline__ void rotate_rounds(uint8_t* smem, int pos, const float* __restrict__ cs,
+                                              const float* __restrict__ sn, int rot_dim) {
+  const int r = threadIdx.x >> 1, par = threadIdx.x & 1;
+  const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + par * 8);
+  const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + par * 8);
+  float4 ca[RR], cb[RR], sa[RR], sb[RR];
+#pragma unroll
+  for (int it = 0; it < RR; ++it) {
+    ca[it] = __ldg(c4 + it * 4);
+    cb[it] = __ldg(c4 + it * 4 + 1);
+    sa[it] = __ldg(s4 + it * 4);
+    sb[it] = __ldg(s4 + it * 4 + 1);
+  }
+  uint8_t* slot0 = smem + par * CS128 + r * 16;
+#pragma unroll
+  for (int it = 0; it < RR; ++it) {
+    uint4* slot = reinterpret_cast<uint4*>(slot0 + it * 2 * CS128);
+    uint4 raw = *slot;
+    __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+    const float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+    const float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+    h2[0] = __floats2bfloat162_rn(p0.x * ca[it].x - p0.y * sa[it].x, p0.y * ca[it].y + p0.x * sa[it].y);
+    h2[1] = __floats2bfloat162_rn(p1.x * ca[it].z - p1.y * sa[it].z, p1.y * ca[it].w + p1.x * sa[it].w);
+    h2[2] = __floats2bfloat162_rn(p2.x * cb[it].x - p2.y * sb[it].x, p2.y * cb[it].y + p2.x * sb[it].y);
+    h2[3] = __floats2bfloat162_rn(p3.x * cb[it].z - p3.y * sb[it].z, p3.y * cb[it].w + p3.x * sb[it].w);
+    *slot = raw;
   }
 }
 
 template <int DH, int NT>
 __device__ __forceinline__ void rotate_staged(uint8_t* smem, int h, int s0, int S, const float* __restrict__ cs,
                                               const float* __restrict__ sn, int rot_dim, int pos_is_head) {
-  constexpr int CPR = DH / 8;
+  static_assert(NT == 256, "same walk as stage_async");
   if (cs == nullptr) return;
-  static_assert((128 * CPR) % NT == 0, "whole rounds");
-#pragma unroll
-  for (int it = 0; it < 128 * CPR / NT; ++it) {
-    const int idx = threadIdx.x + it * NT;
-    const int r = idx / CPR, ch = idx - r * CPR;
-    if (ch * 8 >= rot_dim || s0 + r >= S) continue;
-    uint4* slot = reinterpret_cast<uint4*>(smem + ch * CS128 + r * 16);
-    uint4 raw = *slot;
-    const int pos = pos_is_head ? h : s0 + r;
-    const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + ch * 8);
-    const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + ch * 8);
-    const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
-    __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
-    float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
-    float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
-    h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
-    h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
-    h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
-    h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
-    *slot = raw;
+  // rows past S were zero-filled and rotate to zero: no row predicate, the table row is clamped instead
+  const int pos = pos_is_head ? h : min(s0 + (int)(threadIdx.x >> 1), S - 1);
+  if (rot_dim == 48 && DH >= 48) rotate_rounds<DH, 3>(smem, pos, cs, sn, rot_dim);
+  else if (rot_dim == 64 && DH >= 64) rotate_rounds<DH, 4>(smem, pos, cs, sn, rot_dim);
+  else {                                    // any rot_dim % 8 == 0: per-chunk predicate
+    const int r = threadIdx.x >> 1, par = threadIdx.x & 1;
+    for (int ch = par; ch * 8 < rot_dim; ch += 2) {
+      uint4* slot = reinterpret_cast<uint4*>(smem + ch * CS128 + r * 16);
+      uint4 raw = *slot;
+      const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + ch * 8);
+      const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + ch * 8);
+      const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+      __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+      const float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+      const float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+      h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+      h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+      h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+      h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+      *slot = raw;
+    }
   }
 }
 
@@ -143,16 +187,17 @@ __device__ __forceinline__ float key_term(const float* mrow, int kj, int Sk) {
 }
 
 template <int DH>
-__global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   __shared__ uint64_t bar_s, bar_o;
   __shared__ uint32_t tmem_slot;
   __shared__ float kterm[TK];
+  __shared__ float xch[2][TQ];          // row max / row sum exchange between the two column halves
   using L = FwdSmem<DH>;
-  constexpr int NT = 128;
-  const int t = threadIdx.x, warp = t >> 5;
+  constexpr int NT = 256, HC = DH / 2, HK = TK / 2;   // O columns / key columns per thread
+  const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, hf = tid >> 7;
   const int q0 = blockIdx.x * TQ, h = blockIdx.y, n = blockIdx.z;
-  if (t == 0) {
+  if (tid == 0) {
     tc::mbar_init(&bar_s, 1);
     tc::mbar_init(&bar_o, 1);
     tc::fence_mbar_init();
@@ -168,10 +213,11 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
   const int qi = q0 + t;
   const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
   const float sc2 = a.scale * LOG2E;
-  float m_run = -CUDART_INF_F, l_run = 0.f;
-  float o_acc[DH];
+  MT_PROF_INIT();
+  float m_run = -CUDART_INF_F, l_run = 0.f;    // l_run: this half's columns only, combined at the end
+  float o_acc[HC];
 #pragma unroll
-  for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
+  for (int i = 0; i < HC; ++i) o_acc[i] = 0.f;
   const int last_q = min(q0 + TQ, a.Sq) - 1;
   int n_tiles = (a.Sk + TK - 1) / TK;
   if (a.causal) n_tiles = min(n_tiles, last_q / TK + 1);
@@ -182,16 +228,22 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
   for (int kt = 0; kt < n_tiles; ++kt) {
     const int k0 = kt * TK;
     const bool more = kt + 1 < n_tiles;
+    const bool diag = a.causal && k0 + TK - 1 > q0;       // some (row, key) of this tile pair is above the diagonal
+    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk;   // no additive term, no masking at all
+    MT_PROF(10);
     tc::cp_async_wait<1>();            // K(kt) (and Q) landed; V(kt) may still be in flight
+    MT_PROF(0);
     if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
     rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
-    kterm[t] = key_term(mrow, k0 + t, a.Sk);
+    if (!plain && tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
+    MT_PROF(1);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
     tmem = tmem_slot;
-    if (t == 0) {
+    MT_PROF(2);
+    if (tid == 0) {
       constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
 #pragma unroll
       for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
@@ -199,31 +251,42 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar_s, phase);
     tc::fence_after_sync();
+    MT_PROF(3);
     if (more) stage_async<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, k0 + TK, a.Sk);   // K is free: next tile
     tc::cp_async_commit();
-    const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-    const bool diag = a.causal && k0 + TK - 1 > q0;   // some (row, key) of this tile pair is above the diagonal
-    // pass 1: row max
+    MT_PROF(4);
+    const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    const int cb = hf * HK;            // this thread's key columns: [cb, cb + HK)
+    // pass 1: row max over my columns, then across the two halves
     float m_tile = -CUDART_INF_F;
 #pragma unroll 1
-    for (int c0 = 0; c0 < TK; c0 += 32) {
+    for (int c0 = cb; c0 < cb + HK; c0 += 32) {
       float s[32];
       tc::tmem_ld32(lane_base + c0, s);
       tc::tmem_ld_wait();
+      if (plain) {
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        float x = fmaf(s[i], sc2, kterm[c0 + i]);
-        if (diag && k0 + c0 + i > qi) x = -CUDART_INF_F;
-        m_tile = fmaxf(m_tile, x);
+        for (int i = 0; i < 32; ++i) m_tile = fmaxf(m_tile, s[i] * sc2);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          float x = fmaf(s[i], sc2, kterm[c0 + i]);
+          if (diag && k0 + c0 + i > qi) x = -CUDART_INF_F;
+          m_tile = fmaxf(m_tile, x);
+        }
       }
     }
+    xch[hf][t] = m_tile;
+    __syncthreads();
+    m_tile = fmaxf(m_tile, xch[hf ^ 1][t]);
+    MT_PROF(5);
     const float m_new = fmaxf(m_run, m_tile);
     const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
     const float corr = tc::ex2(m_run - m_use);   // m_run = -inf -> 0
     // pass 2: P = exp2(x - m), bf16 -> shared (row t, 16-byte chunks), row sum
     float l_tile = 0.f;
 #pragma unroll 1
-    for (int c0 = 0; c0 < TK; c0 += 32) {
+    for (int c0 = cb; c0 < cb + HK; c0 += 32) {
       float s[32];
       tc::tmem_ld32(lane_base + c0, s);
       tc::tmem_ld_wait();
@@ -231,10 +294,17 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
       __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
-        float x0 = fmaf(s[i], sc2, kterm[c0 + i]), x1 = fmaf(s[i + 1], sc2, kterm[c0 + i + 1]);
-        if (diag && k0 + c0 + i > qi) x0 = -CUDART_INF_F;
-        if (diag && k0 + c0 + i + 1 > qi) x1 = -CUDART_INF_F;
-        const __nv_bfloat162 pb = __floats2bfloat162_rn(tc::ex2(x0 - m_use), tc::ex2(x1 - m_use));
+        float x0, x1;
+        if (plain) {
+          x0 = fmaf(s[i], sc2, -m_use);
+          x1 = fmaf(s[i + 1], sc2, -m_use);
+        } else {
+          x0 = fmaf(s[i], sc2, kterm[c0 + i]) - m_use;
+          x1 = fmaf(s[i + 1], sc2, kterm[c0 + i + 1]) - m_use;
+          if (diag && k0 + c0 + i > qi) x0 = -CUDART_INF_F;
+          if (diag && k0 + c0 + i + 1 > qi) x1 = -CUDART_INF_F;
+        }
+        const __nv_bfloat162 pb = __floats2bfloat162_rn(tc::ex2(x0), tc::ex2(x1));
         ph[i >> 1] = pb;
         const float2 back = __bfloat1622float2(pb);   // sum what the tensor core will see
         l_tile += back.x + back.y;
@@ -244,12 +314,14 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     }
     l_run = l_run * corr + l_tile;
     m_run = m_new;
+    MT_PROF(6);
     tc::cp_async_wait<1>();            // V(kt) landed (K(kt+1) may still be in flight)
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    if (t == 0) {
+    MT_PROF(7);
+    if (tid == 0) {
       constexpr uint32_t idesc = tc::make_idesc(TQ, DH, 0, 1);
 #pragma unroll
       for (int ks = 0; ks < TK / 16; ++ks)
@@ -258,35 +330,41 @@ __global__ void __launch_bounds__(128, 2) attn_tc_fwd_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar_o, phase);
     tc::fence_after_sync();
+    MT_PROF(8);
     if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, a.Sk);   // V is free: next tile
     tc::cp_async_commit();
+    {
+      float pv[HC];
 #pragma unroll
-    for (int c0 = 0; c0 < DH; c0 += 32) {
-      float pv[32];
-      tc::tmem_ld32(lane_base + 128 + c0, pv);
+      for (int c0 = 0; c0 < HC; c0 += 16) tc::tmem_ld16(lane_base + 128 + hf * HC + c0, pv + c0);
       tc::tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) o_acc[c0 + i] = o_acc[c0 + i] * corr + pv[i];
+      for (int i = 0; i < HC; ++i) o_acc[i] = fmaf(o_acc[i], corr, pv[i]);
     }
     phase ^= 1;
+    MT_PROF(9);
   }
   tc::cp_async_wait<0>();
+  xch[hf][t] = l_run;
+  __syncthreads();
+  l_run += xch[hf ^ 1][t];
   if (qi < a.Sq) {
     const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
-    __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
+    __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h) + hf * HC;
 #pragma unroll
-    for (int c0 = 0; c0 < DH; c0 += 8) {
+    for (int c0 = 0; c0 < HC; c0 += 8) {
       uint4 pk;
       __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
       for (int i = 0; i < 8; i += 2) ph[i >> 1] = __floats2bfloat162_rn(o_acc[c0 + i] * inv, o_acc[c0 + i + 1] * inv);
       *reinterpret_cast<uint4*>(op + c0) = pk;
     }
-    if (a.lse) a.lse[((int64_t)n * a.H + h) * a.Sq + qi] = m_run * LN2 + logf(l_run);
+    if (a.lse && hf == 0) a.lse[((int64_t)n * a.H + h) * a.Sq + qi] = m_run * LN2 + logf(l_run);
   }
   tc::fence_before_sync();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc(tmem_slot, 256);
+  MT_PROF(11);
 }
 
 // ------------------------------------------------------------------------------------ backward
@@ -300,6 +378,21 @@ struct BwdSmem {
 
 // un-rotate (transpose rotation) 16 consecutive features [c0, c0+16) of a gradient row in place
 __device__ __forceinline__ void unrot16(float* g, const float* cs, const float* sn, int pos, int rot_dim, int c0) {
+  if (c0 >= rot_dim) return;
+  if (c0 + 16 <= rot_dim) {   // whole 16-feature block rotated: 128-bit table loads
+    const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim + c0);
+    const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim + c0);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float4 c = __ldg(c4 + q), s = __ldg(s4 + q);
+      const float a0 = g[4 * q], a1 = g[4 * q + 1], b0 = g[4 * q + 2], b1 = g[4 * q + 3];
+      g[4 * q] = a0 * c.x + a1 * s.y;
+      g[4 * q + 1] = a1 * c.y - a0 * s.x;
+      g[4 * q + 2] = b0 * c.z + b1 * s.w;
+      g[4 * q + 3] = b1 * c.w - b0 * s.z;
+    }
+    return;
+  }
 #pragma unroll
   for (int i = 0; i < 16; i += 2)
     if (c0 + i < rot_dim) unrot_pair(g[i], g[i + 1], cs, sn, pos, rot_dim, c0 + i);
@@ -567,6 +660,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     const int qi = q0 + t;
     const bool diag = a.causal && k0 + TK - 1 > q0;
     const bool qok = qi < a.Sq;
+    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk && q0 + TQ <= a.Sq;   // tile pair without any masking
 #pragma unroll 1
     for (int c0 = half * (TK / 2); c0 < (half + 1) * (TK / 2); c0 += 16) {
       float s[16], dp[16];
@@ -582,8 +676,13 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
 #pragma unroll
         for (int jj = 0; jj < 2; ++jj) {
           const int c = c0 + i + jj;
-          float x = fmaf(s[i + jj], sc2, kterm[c]) - lse2;       // -inf past the last key
-          if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+          float x;
+          if (plain) {
+            x = fmaf(s[i + jj], sc2, -lse2);
+          } else {
+            x = fmaf(s[i + jj], sc2, kterm[c]) - lse2;           // -inf past the last key
+            if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+          }
           p[jj] = tc::ex2(x);
           ds[jj] = p[jj] * (dp[i + jj] - delta) * a.scale;
         }
@@ -720,8 +819,8 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     ++g_tma_fallbacks;
   }
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
-  if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st);
-  return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st);
+  if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st, 256);
+  return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st, 256);
 }
 
 int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
@@ -739,3 +838,18 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
 long long attn_tma_fallbacks() { return g_tma_fallbacks.load(); }
 
 }  // namespace meant
+
+extern "C" int meant_debug_prof_mt(unsigned long long* out32, int reset) {
+#ifdef MEANT_PROF
+  cudaDeviceSynchronize();
+  if (out32 && cudaMemcpyFromSymbol(out32, meant::g_prof_mt, sizeof(unsigned long long) * 32) != cudaSuccess) return -1;
+  if (reset) {
+    unsigned long long z[32] = {0};
+    cudaMemcpyToSymbol(meant::g_prof_mt, z, sizeof(z));
+  }
+  return 1;
+#else
+  (void)out32; (void)reset;
+  return 0;
+#endif
+}

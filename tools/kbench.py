@@ -47,6 +47,12 @@ def prof(tag, items, launches):
         return
     per = launches * ((items + 147) // 148)
     print(f"  prof {tag}: compute", [round(buf[i] / per) for i in range(16)], "loader", [round(buf[16 + i] / per) for i in range(16)])
+    fn2 = getattr(nv.lib(), "meant_debug_prof_mt", None)   # multi-tile forward: cycles per phase, CTA (0,0,0), per launch
+    if fn2 is not None:
+        b2 = (ctypes.c_ulonglong * 32)()
+        fn2.restype = ctypes.c_int
+        if fn2(b2, 1) == 1 and any(b2):
+            print(f"  prof_mt {tag}: cycles/launch", [round(b2[i] / launches) for i in range(12)])
 
 
 def attn(args):
