@@ -32,7 +32,7 @@ enum { MEANT_F32 = 0, MEANT_BF16 = 1 };
 enum { MEANT_IMPL_AUTO = 0, MEANT_IMPL_EXACT = 1, MEANT_IMPL_TCGEN05 = 2 };
 
 /* ---- library ------------------------------------------------------------------------- */
-int meant_version(void);                 /* ABI version (3), bumped on any signature change */
+int meant_version(void);                 /* ABI version (4), bumped on any signature change */
 int64_t meant_launch_count(void);        /* kernels launched by this library so far       */
 void meant_reset_launch_count(void);
 
@@ -96,7 +96,15 @@ typedef struct {
   int pos_is_head;              /* rotary position = head index (reference flash variants) */
   int causal;
   float scale;                  /* softmax scale applied to q k^T                          */
+  meant_head_view q_rot, k_rot; /* optional (p != NULL): Rq q and Rk k written by meant_attn_prerotate; the
+                                 * multi-tile kernels (Sq or Sk > 128) then read these instead of rotating every
+                                 * tile on the way in (a K tile is needed by every query tile)              */
 } meant_attn_args;
+
+/* Rotates q -> q_rot and k -> k_rot (caller-owned buffers, any head-view strides) with the qcos.. tables of `args`:
+ * the per-position pair rotation of meant/rotary_embedding_torch.py:37-44,96-110 applied once per element.
+ * bf16 only.  Optional: without it (q_rot.p == NULL) the attention kernels rotate in flight.              */
+int meant_attn_prerotate(const meant_attn_args* args, int dtype, meant_stream_t stream);
 
 int meant_attn_fwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);
 int meant_attn_bwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);

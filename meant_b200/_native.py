@@ -27,7 +27,8 @@ class AttnArgs(C.Structure):
                 ("lse", vp), ("delta", vp), ("qcos", vp), ("qsin", vp), ("kcos", vp), ("ksin", vp),
                 ("key_mask", vp),
                 ("N", i32), ("n2_count", i32), ("H", i32), ("Sq", i32), ("Sk", i32), ("Dh", i32),
-                ("rot_dim", i32), ("pos_is_head", i32), ("causal", i32), ("scale", f32)]
+                ("rot_dim", i32), ("pos_is_head", i32), ("causal", i32), ("scale", f32),
+                ("q_rot", HeadView), ("k_rot", HeadView)]
 
 
 # name -> (restype, argtypes); mirrors include/meant_b200.h one to one
@@ -46,6 +47,7 @@ SIGNATURES = {
     "meant_attn_fwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),
     "meant_attn_bwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),
     "meant_attn_tcgen05_supported": (i32, [C.POINTER(AttnArgs), i32, i32]),
+    "meant_attn_prerotate": (i32, [C.POINTER(AttnArgs), i32, vp]),
     "meant_attn_tma_fallbacks": (i64, []),
     "meant_meanpool_fwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_meanpool_bwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
@@ -59,7 +61,7 @@ SIGNATURES = {
 _lib = None
 
 
-ABI_VERSION = 3   # include/meant_b200.h: meant_version()
+ABI_VERSION = 4   # include/meant_b200.h: meant_version()
 
 
 def lib():

@@ -204,8 +204,13 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
   // cp.async groups, oldest first: [Q + K(0)] [V(0)] then per tile [K(kt+1)] [V(kt+1)] (empty past the end)
-  stage_async<DH, NT>(smem + L::Q, a.q, n, a.n2_count, h, q0, a.Sq);
-  stage_async<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, 0, a.Sk);
+  const bool pre = a.q_rot.p != nullptr;          // Q, K already rotated by meant_attn_prerotate
+  const HeadView& qv = pre ? a.q_rot : a.q;
+  const HeadView& kv = pre ? a.k_rot : a.k;
+  const float* qcos = pre ? nullptr : a.qcos;
+  const float* kcos = pre ? nullptr : a.kcos;
+  stage_async<DH, NT>(smem + L::Q, qv, n, a.n2_count, h, q0, a.Sq);
+  stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, 0, a.Sk);
   tc::cp_async_commit();
   stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk);
   tc::cp_async_commit();
@@ -229,12 +234,12 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     const int k0 = kt * TK;
     const bool more = kt + 1 < n_tiles;
     const bool diag = a.causal && k0 + TK - 1 > q0;       // some (row, key) of this tile pair is above the diagonal
-    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk;   // no additive term, no masking at all
+    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk && sc2 > 0.f;   // no additive term, no masking
     MT_PROF(10);
     tc::cp_async_wait<1>();            // K(kt) (and Q) landed; V(kt) may still be in flight
     MT_PROF(0);
-    if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
-    rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
+    rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
     if (!plain && tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
     MT_PROF(1);
     tc::fence_async_smem();
@@ -252,21 +257,21 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     tc::mbar_wait(&bar_s, phase);
     tc::fence_after_sync();
     MT_PROF(3);
-    if (more) stage_async<DH, NT>(smem + L::K, a.k, n, a.n2_count, h, k0 + TK, a.Sk);   // K is free: next tile
+    if (more) stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, k0 + TK, a.Sk);   // K is free: next tile
     tc::cp_async_commit();
     MT_PROF(4);
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int cb = hf * HK;            // this thread's key columns: [cb, cb + HK)
     // pass 1: row max over my columns, then across the two halves
-    float m_tile = -CUDART_INF_F;
+    float m_tile = -CUDART_INF_F, m_raw = -CUDART_INF_F;
 #pragma unroll 1
     for (int c0 = cb; c0 < cb + HK; c0 += 32) {
       float s[32];
       tc::tmem_ld32(lane_base + c0, s);
       tc::tmem_ld_wait();
-      if (plain) {
+      if (plain) {              // sc2 > 0: the max of the raw scores, scaled once below
 #pragma unroll
-        for (int i = 0; i < 32; ++i) m_tile = fmaxf(m_tile, s[i] * sc2);
+        for (int i = 0; i < 32; ++i) m_raw = fmaxf(m_raw, s[i]);
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
@@ -276,6 +281,7 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
         }
       }
     }
+    if (plain) m_tile = m_raw * sc2;
     xch[hf][t] = m_tile;
     __syncthreads();
     m_tile = fmaxf(m_tile, xch[hf ^ 1][t]);
@@ -304,10 +310,9 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
           if (diag && k0 + c0 + i > qi) x0 = -CUDART_INF_F;
           if (diag && k0 + c0 + i + 1 > qi) x1 = -CUDART_INF_F;
         }
-        const __nv_bfloat162 pb = __floats2bfloat162_rn(tc::ex2(x0), tc::ex2(x1));
-        ph[i >> 1] = pb;
-        const float2 back = __bfloat1622float2(pb);   // sum what the tensor core will see
-        l_tile += back.x + back.y;
+        const float e0 = tc::ex2(x0), e1 = tc::ex2(x1);
+        ph[i >> 1] = __floats2bfloat162_rn(e0, e1);
+        l_tile += e0 + e1;
       }
 #pragma unroll
       for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + j) * CS128 + t * 16) = pk[j];
@@ -563,14 +568,19 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
   const float sc2 = a.scale * LOG2E;
 
+  const bool pre = a.q_rot.p != nullptr;          // Q, K already rotated by meant_attn_prerotate
+  const HeadView& qv = pre ? a.q_rot : a.q;
+  const HeadView& kv = pre ? a.k_rot : a.k;
+  const float* qcos = pre ? nullptr : a.qcos;
+  const float* kcos = pre ? nullptr : a.kcos;
   // streamed tile j -> buffer pair b:  MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
   auto stream = [&](int j, int b) {
     uint8_t* x = smem + L::STR + (uint32_t)b * 2 * L::OPER;
     if (MODE == 0) {
-      stage_async<DH, NT>(x, a.q, n, a.n2_count, h, j * TQ, a.Sq);
+      stage_async<DH, NT>(x, qv, n, a.n2_count, h, j * TQ, a.Sq);
       stage_async<DH, NT>(x + L::OPER, a.o, n, a.n2_count, h, j * TQ, a.Sq);
     } else {
-      stage_async<DH, NT>(x, a.k, n, a.n2_count, h, j * TK, a.Sk);
+      stage_async<DH, NT>(x, kv, n, a.n2_count, h, j * TK, a.Sk);
       stage_async<DH, NT>(x + L::OPER, a.v, n, a.n2_count, h, j * TK, a.Sk);
     }
   };
@@ -606,12 +616,12 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   if (MODE == 0) {
     j0 = a.causal ? tile : 0;
     j1 = nq;
-    stage_async<DH, NT>(smem + L::FIX0, a.k, n, a.n2_count, h, tile * TK, a.Sk);
+    stage_async<DH, NT>(smem + L::FIX0, kv, n, a.n2_count, h, tile * TK, a.Sk);
     stage_async<DH, NT>(smem + L::FIX1, a.v, n, a.n2_count, h, tile * TK, a.Sk);
   } else {
     j0 = 0;
     j1 = a.causal ? min(nk, tile + 1) : nk;
-    stage_async<DH, NT>(smem + L::FIX0, a.q, n, a.n2_count, h, tile * TQ, a.Sq);
+    stage_async<DH, NT>(smem + L::FIX0, qv, n, a.n2_count, h, tile * TQ, a.Sq);
     stage_async<DH, NT>(smem + L::FIX1, a.o, n, a.n2_count, h, tile * TQ, a.Sq);
   }
   if (j0 < j1) stream(j0, 0);
@@ -631,11 +641,11 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     uint8_t* xs = smem + L::STR + (uint32_t)b * 2 * L::OPER;
     if (MODE == 0) {
       row_stats(q0 + t);
-      rotate_staged<DH, NT>(xs, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
-      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
+      rotate_staged<DH, NT>(xs, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
+      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
     } else {
-      rotate_staged<DH, NT>(xs, h, k0, a.Sk, a.kcos, a.ksin, a.rot_dim, a.pos_is_head);
-      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, q0, a.Sq, a.qcos, a.qsin, a.rot_dim, a.pos_is_head);
+      rotate_staged<DH, NT>(xs, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
+      if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
       if (tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
     }
     const uint32_t sq = tc::smem_u32(MODE == 0 ? xs : smem + L::FIX0), sdo = sq + L::OPER;
@@ -768,6 +778,41 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
+// ------------------------------------------------------------------------------------ pre-rotation
+// q -> q_rot (blockIdx.y = 0) and k -> k_rot (blockIdx.y = 1): one thread per 16-byte chunk, chunks of a packed
+// row contiguous across the warp.  HBM-bound: reads and writes Q and K once.
+__global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
+  const bool isk = blockIdx.y != 0;
+  const HeadView& src = isk ? a.k : a.q;
+  const HeadView& dst = isk ? a.k_rot : a.q_rot;
+  const float* __restrict__ cs = isk ? a.kcos : a.qcos;
+  const float* __restrict__ sn = isk ? a.ksin : a.qsin;
+  const int S = isk ? a.Sk : a.Sq, cpr = a.Dh >> 3;
+  const int64_t total = (int64_t)a.N * S * a.H * cpr;
+  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(idx % cpr);
+    int64_t rest = idx / cpr;
+    const int h = (int)(rest % a.H);
+    rest /= a.H;
+    const int sr = (int)(rest % S), n = (int)(rest / S);
+    uint4 raw = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(src, n, a.n2_count, sr, h) + ch * 8);
+    if (ch * 8 < a.rot_dim) {
+      const int pos = a.pos_is_head ? h : sr;
+      const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * a.rot_dim + ch * 8);
+      const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * a.rot_dim + ch * 8);
+      const float4 ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+      __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+      const float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+      const float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+      h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+      h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+      h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+      h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+    }
+    *reinterpret_cast<uint4*>(view_ptr<__nv_bfloat16>(dst, n, a.n2_count, sr, h) + ch * 8) = raw;
+  }
+}
+
 // ------------------------------------------------------------------------------------ host side
 // attn_tc2.cu: persistent warp-specialised kernels for single-tile problems (Sq, Sk <= 128)
 int attn_tc2_supported(const AttnArgs& a, int backward);
@@ -786,6 +831,7 @@ int attn_tc_supported(const AttnArgs& a, int dtype, int backward) {
   if (a.rot_dim % 8 != 0 || a.rot_dim > a.Dh) return 0;
   if (a.qcos && (!a.qsin || !a.kcos || !a.ksin)) return 0;
   if (!view_ok(a.q) || !view_ok(a.k) || !view_ok(a.v) || !view_ok(a.o)) return 0;
+  if (a.q_rot.p != nullptr && (!view_ok(a.q_rot) || !view_ok(a.k_rot))) return 0;
   if (backward) {
     if (!view_ok(a.dq) || !view_ok(a.dk) || !view_ok(a.dv) || !view_ok(a.out_saved) || !a.lse || !a.delta) return 0;
   }
@@ -836,6 +882,20 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
 }
 
 long long attn_tma_fallbacks() { return g_tma_fallbacks.load(); }
+
+int attn_prerotate(const AttnArgs& a, int dtype, cudaStream_t st) {
+  if (dtype != MEANT_DT_BF16 || !a.qcos || !a.qsin || !a.kcos || !a.ksin) return MEANT_EARG;
+  if (!view_ok(a.q) || !view_ok(a.k) || !view_ok(a.q_rot) || !view_ok(a.k_rot)) return MEANT_EUNSUPPORTED;
+  if (a.N <= 0 || a.H <= 0 || a.Sq <= 0 || a.Sk <= 0 || a.n2_count <= 0 || a.Dh % 8 != 0 || a.rot_dim % 8 != 0 ||
+      a.rot_dim > a.Dh)
+    return MEANT_EARG;
+  const int64_t total = (int64_t)a.N * (a.Sq > a.Sk ? a.Sq : a.Sk) * a.H * (a.Dh / 8);
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  attn_prerotate_kernel<<<dim3((unsigned)blocks, 2), 256, 0, st>>>(a);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
 
 }  // namespace meant
 

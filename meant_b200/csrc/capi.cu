@@ -8,6 +8,7 @@ int attn_exact_bwd(const AttnArgs& a, int dtype, cudaStream_t st);
 int attn_tc_supported(const AttnArgs& a, int dtype, int backward);
 int attn_tc_fwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc_bwd(const AttnArgs& a, cudaStream_t st);
+int attn_prerotate(const AttnArgs& a, int dtype, cudaStream_t st);
 }  // namespace meant
 
 static std::atomic<int64_t> g_launches{0};
@@ -18,7 +19,7 @@ extern "C" void meant_reset_launch_count(void) { g_launches.store(0, std::memory
 namespace meant { long long attn_tma_fallbacks(); }
 extern "C" int64_t meant_attn_tma_fallbacks(void) { return meant::attn_tma_fallbacks(); }
 
-extern "C" int meant_version(void) { return 3; }
+extern "C" int meant_version(void) { return 4; }
 
 extern "C" int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int backward) {
   return args ? meant::attn_tc_supported(*args, dtype, backward) : 0;
@@ -40,4 +41,9 @@ extern "C" int meant_attn_bwd(const meant_attn_args* args, int dtype, int impl, 
   if (impl == MEANT_IMPL_TCGEN05 && !tc_ok) return MEANT_EUNSUPPORTED;
   if (impl == MEANT_IMPL_TCGEN05 || (impl == MEANT_IMPL_AUTO && tc_ok)) return meant::attn_tc_bwd(*args, st);
   return meant::attn_exact_bwd(*args, dtype, st);
+}
+
+extern "C" int meant_attn_prerotate(const meant_attn_args* args, int dtype, meant_stream_t stream) {
+  if (!args) return MEANT_EARG;
+  return meant::attn_prerotate(*args, dtype, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -433,15 +433,25 @@ class _AttnFn(torch.autograd.Function):
             a.key_mask = nv.ptr(km)
         a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
         a.pos_is_head, a.causal, a.scale = int(pos_is_head), int(causal), float(scale)
+        # Multi-tile problems on the tensor-core path: rotate Q and K ONCE into scratch (every query tile needs every
+        # key tile; the kernels then stage plain tiles), kept for the backward pass.
+        qrot = krot = None
+        if (PREROTATE and tabs is not None and (sq > 128 or sk > 128) and impl != nv.IMPL_EXACT
+                and nv.lib().meant_attn_tcgen05_supported(a, nv.dt(t0), 0)):
+            qrot = torch.empty(n, sq, dim, dtype=dtype, device=t0.device)
+            krot = torch.empty(n, sk, dim, dtype=dtype, device=t0.device)
+            a.q_rot, a.k_rot = _view(qrot, 0, heads, dh), _view(krot, 0, heads, dh)
+            nv.check(nv.timed(f"attn_prerotate/S{sq}x{sk}/Dh{dh}", nv.lib().meant_attn_prerotate, a, nv.dt(t0), nv.stream()),
+                     "meant_attn_prerotate")
         nv.check(nv.timed(f"attn_fwd/S{sq}x{sk}/Dh{dh}/c{int(causal)}", nv.lib().meant_attn_fwd, a, nv.dt(t0), impl, nv.stream()),
                  "meant_attn_fwd")
-        ctx.save_for_backward(t0, t1, t2, out, lse, km, *(tabs or ()))
+        ctx.save_for_backward(t0, t1, t2, out, lse, km, qrot, krot, *(tabs or ()))
         ctx.cfg = (mode, heads, float(scale), int(causal), int(pos_is_head), impl, rot is not None)
         return out
 
     @staticmethod
     def backward(ctx, dout):
-        t0, t1, t2, out, lse, km, *tabs = ctx.saved_tensors
+        t0, t1, t2, out, lse, km, qrot, krot, *tabs = ctx.saved_tensors
         mode, heads, scale, causal, pos_is_head, impl, has_rot = ctx.cfg
         dout = dout.to(out.dtype).contiguous()
         g0 = torch.empty_like(t0)
@@ -473,6 +483,8 @@ class _AttnFn(torch.autograd.Function):
             a.rot_dim = tabs[0].shape[-1]
         if km is not None:
             a.key_mask = nv.ptr(km)
+        if qrot is not None:
+            a.q_rot, a.k_rot = _view(qrot, 0, heads, dh), _view(krot, 0, heads, dh)
         a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = n, 1, heads, sq, sk, dh
         a.pos_is_head, a.causal, a.scale = pos_is_head, causal, scale
         nv.check(nv.timed(f"attn_bwd/S{sq}x{sk}/Dh{dh}/c{causal}", nv.lib().meant_attn_bwd, a, nv.dt(t0), impl, nv.stream()),
@@ -481,6 +493,7 @@ class _AttnFn(torch.autograd.Function):
 
 
 DEFAULT_ATTN_IMPL = nv.IMPL_AUTO   # bench/tests may force IMPL_EXACT or IMPL_TCGEN05
+PREROTATE = True                   # multi-tile tensor-core attention: rotate Q, K once (meant_attn_prerotate)
 
 
 def attention(qkv=None, q=None, kv=None, k=None, v=None, *, heads, scale, causal=False, rot=None,

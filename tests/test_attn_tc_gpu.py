@@ -124,3 +124,29 @@ def test_multitile_backward_is_reproducible_and_cross_shaped():
         c = torch.nn.functional.cosine_similarity(g.flatten(), want.flatten(), dim=0)
         assert float(c) > 0.999, (name, float(c))
         assert float((g - want).abs().max()) < 0.05 * float(want.abs().max()) + 1e-3, name
+
+
+@pytest.mark.parametrize("s,causal", [(196, False), (300, True)])
+def test_prerotated_and_in_flight_rotation_agree(s, causal):
+    """Multi-tile kernels: Q, K rotated once by meant_attn_prerotate (default) vs rotated per tile in the kernel."""
+    torch.manual_seed(s)
+    heads, dh, n = 8, 96, 2
+    dim = heads * dh
+    base = torch.randn(n, s, 3 * dim, device="cuda").bfloat16()
+    rot = RotaryEmbedding(dim=48, use_xpos=True).tables(s, "cuda")
+    probe = torch.randn(n, s, dim, device="cuda")
+    got = []
+    try:
+        for pre in (True, False):
+            ops.PREROTATE = pre
+            x = base.clone().requires_grad_(True)
+            o = ops.attention(x, heads=heads, scale=dim ** -0.5, causal=causal, rot=rot, impl=nv.IMPL_TCGEN05)
+            (o.float() * probe).sum().backward()
+            got.append((o.float(), x.grad.float()))
+    finally:
+        ops.PREROTATE = True
+    torch.cuda.synchronize()
+    # same bf16 rotation arithmetic either way: outputs agree to rounding of the accumulation order
+    assert float((got[0][0] - got[1][0]).abs().max()) < 1e-2
+    c = torch.nn.functional.cosine_similarity(got[0][1].flatten(), got[1][1].flatten(), dim=0)
+    assert float(c) > 0.9999, float(c)
