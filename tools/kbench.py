@@ -4,6 +4,7 @@ than L2 or an L2 flush between iterations).  Used for the ncu captures under pro
 
     python tools/kbench.py attn  [--n 768] [--s 128] [--dh 96] [--iters 20]
     python tools/kbench.py norm  [--rows 98304] [--d 768]
+    python tools/kbench.py gemm  [--rows 98304] [--d 768] [--nout 2304]   # hand-written tcgen05 GEMM vs the library
 """
 import argparse
 import math
@@ -114,19 +115,42 @@ def norm(args):
               f"bwd(autograd) {b_med*1e3:.1f} us {tb*byts/b_med/1e6:.0f} GB/s")
 
 
+def gemm(args):
+    import torch.nn.functional as F
+    m, k, n = args.rows, args.d, args.nout
+    x = torch.randn(m, k, device="cuda").bfloat16()
+    w = (torch.randn(n, k, device="cuda") * 0.02).bfloat16()
+    b = torch.randn(n, device="cuda")
+    c = torch.empty(m, n, device="cuda", dtype=torch.bfloat16)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def native():
+        rc = nv.lib().meant_gemm_bf16_tn(nv.ptr(x), nv.ptr(w), nv.ptr(b), nv.ptr(c), m, n, k, k, k, n, nv.stream())
+        assert rc == 0, rc
+
+    bb = b.bfloat16()
+    t_nat, _ = timeit(native, args.iters, flush)
+    t_lib, _ = timeit(lambda: F.linear(x, w, bb), args.iters, flush)
+    err = (c.float() - F.linear(x, w, bb).float()).abs().max().item()
+    fl = 2.0 * m * n * k
+    print(f"gemm M={m} N={n} K={k} bf16: tcgen05 {t_nat*1e3:.1f} us {fl/t_nat/1e9:.0f} TFLOP/s | library {t_lib*1e3:.1f} us "
+          f"{fl/t_lib/1e9:.0f} TFLOP/s | max|diff| {err:.3g}")
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["attn", "norm"])
+    ap.add_argument("what", choices=["attn", "norm", "gemm"])
     ap.add_argument("--n", type=int, default=768)
     ap.add_argument("--s", type=int, default=128)
     ap.add_argument("--dh", type=int, default=96)
     ap.add_argument("--heads", type=int, default=8)
     ap.add_argument("--rows", type=int, default=98304)
     ap.add_argument("--d", type=int, default=768)
+    ap.add_argument("--nout", type=int, default=2304)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--causal", type=int, default=1)
     ap.add_argument("--norot", action="store_true")
     ap.add_argument("--impl", default="auto")
     a = ap.parse_args()
     a.causal = bool(a.causal)
-    {"attn": attn, "norm": norm}[a.what](a)
+    {"attn": attn, "norm": norm, "gemm": gemm}[a.what](a)
