@@ -23,6 +23,7 @@
 //   S and dP are recomputed in both (8 MMA chains per tile pair instead of 5): no atomics, no fp32
 //   workspace, bit-reproducible gradients.  Causal problems skip the tile pairs above the diagonal.
 // Work per sequence and the roofline that bounds it: DESIGN.md.
+#include <type_traits>
 #include "attn_common.cuh"
 #include "tc_utils.cuh"
 #include <math_constants.h>
@@ -553,11 +554,15 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   __shared__ uint64_t bar1, bar2;
   __shared__ uint32_t tmem_slot;
   __shared__ float kterm[TK];
+  __shared__ float sdelta[TQ];
   using L = MtSmem<DH>;
+  static_assert(DH / 8 <= 16, "delta walk: one 16-lane group per row");
   constexpr int NT = 256;
   constexpr uint32_t T_S = 0, T_DP = 128, T_A = 256, T_B = 384;   // MODE 0: A = dV, B = dK; MODE 1: A = dQ
   const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, half = tid >> 7;
   const int tile = blockIdx.x, h = blockIdx.y, n = blockIdx.z;
+  MT_PROF_INIT();
+  constexpr int PB = 12 + MODE * 10;   // phase-timer slots of this pass
   if (tid == 0) {
     tc::mbar_init(&bar1, 1);
     tc::mbar_init(&bar2, 1);
@@ -584,32 +589,54 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
       stage_async<DH, NT>(x + L::OPER, a.v, n, a.n2_count, h, j * TK, a.Sk);
     }
   };
-  // delta = <dO, O> (computed once per query tile by the dQ pass, which runs first) and the LSE of query row qi
+  // delta = <dO, O>: computed once per query tile by the dQ pass (which runs first) and kept in a.delta for the
+  // dK|dV pass.  Coalesced: a 16-lane group reads one row of O and dO (DH*2 contiguous bytes each), two rows per
+  // warp instruction, all loads of the warp's 16 rows in flight before the first use.
   float delta = 0.f, lse2 = 0.f;
-  auto row_stats = [&](int qi) {
+  auto row_stats = [&](int qi) {               // per-thread statistics of query row qi (coalesced fp32 reads)
     delta = 0.f;
     lse2 = 0.f;
     if (qi >= a.Sq) return;
     const int64_t li = ((int64_t)n * a.H + h) * a.Sq + qi;
     lse2 = a.lse[li] * LOG2E;
-    if (MODE == 0) {
-      delta = a.delta[li];
-      return;
-    }
-    const __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h);
-    const __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h);
+    if (MODE == 0) delta = a.delta[li];
+  };
+  auto tile_delta = [&](int q0) {
+    const int lane = tid & 31, sub = lane >> 4, c = lane & 15;
+    float d[8];
+    uint4 ov[8], gv[8];
 #pragma unroll
-    for (int c0 = 0; c0 < DH; c0 += 8) {
-      const uint4 ov = *reinterpret_cast<const uint4*>(op + c0), gv = *reinterpret_cast<const uint4*>(gp + c0);
-      const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov);
-      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv);
+    for (int it = 0; it < 8; ++it) {
+      const int qi = q0 + warp * 16 + it * 2 + sub;
+      ov[it] = make_uint4(0u, 0u, 0u, 0u);
+      gv[it] = ov[it];
+      if (qi < a.Sq && c < DH / 8) {
+        ov[it] = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h) + c * 8);
+        gv[it] = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h) + c * 8);
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov[it]);
+      const __nv_bfloat162* g2 = reinterpret_cast<const __nv_bfloat162*>(&gv[it]);
+      float acc = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const float2 x = __bfloat1622float2(o2[i]), y = __bfloat1622float2(g2[i]);
-        delta += x.x * y.x + x.y * y.y;
+        acc += x.x * y.x + x.y * y.y;
+      }
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      d[it] = acc;
+    }
+    if (c == 0) {
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int r = warp * 16 + it * 2 + sub, qi = q0 + r;
+        sdelta[r] = d[it];
+        if (qi < a.Sq) a.delta[((int64_t)n * a.H + h) * a.Sq + qi] = d[it];
       }
     }
-    if (half == 0) a.delta[li] = delta;
   };
 
   int j0, j1;   // tiles of the other axis; causal problems skip the pairs above the diagonal
@@ -626,7 +653,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   }
   if (j0 < j1) stream(j0, 0);
   tc::cp_async_commit();
-  if (MODE == 1) row_stats(tile * TQ + t);
+  if (MODE == 1) {
+    row_stats(tile * TQ + t);
+    tile_delta(tile * TQ);                  // visible to the softmax below after the loop's first __syncthreads
+  }
   if (MODE == 0 && tid < TK) kterm[tid] = key_term(mrow, tile * TK + tid, a.Sk);
 
   uint32_t phase = 0, tmem = 0;
@@ -637,10 +667,12 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     const int q0 = (MODE == 0 ? j : tile) * TQ, k0 = (MODE == 0 ? tile : j) * TK;
     if (j + 1 < j1) stream(j + 1, b ^ 1);      // the other pair was released by the previous iteration's bar2
     tc::cp_async_commit();
+    MT_PROF(PB + 0);
+    if (MODE == 0) row_stats(q0 + t);           // latency hidden behind the wait
     tc::cp_async_wait<1>();                     // tile j (and the fixed pair) landed
+    MT_PROF(PB + 1);
     uint8_t* xs = smem + L::STR + (uint32_t)b * 2 * L::OPER;
     if (MODE == 0) {
-      row_stats(q0 + t);
       rotate_staged<DH, NT>(xs, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
       if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
     } else {
@@ -651,11 +683,14 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     const uint32_t sq = tc::smem_u32(MODE == 0 ? xs : smem + L::FIX0), sdo = sq + L::OPER;
     const uint32_t sk = tc::smem_u32(MODE == 0 ? smem + L::FIX0 : xs), sv = sk + L::OPER;
     const uint32_t sp = tc::smem_u32(smem + L::P), sds = tc::smem_u32(smem + L::DS);
+    MT_PROF(PB + 2);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
+    MT_PROF(PB + 3);
     tmem = tmem_slot;
+    if (MODE == 1 && first) delta = sdelta[t];
     if (tid == 0) {
       constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
 #pragma unroll
@@ -666,50 +701,65 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar1, phase);
     tc::fence_after_sync();
+    MT_PROF(PB + 4);
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int qi = q0 + t;
     const bool diag = a.causal && k0 + TK - 1 > q0;
     const bool qok = qi < a.Sq;
     const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk && q0 + TQ <= a.Sq;   // tile pair without any masking
-#pragma unroll 1
-    for (int c0 = half * (TK / 2); c0 < (half + 1) * (TK / 2); c0 += 16) {
-      float s[16], dp[16];
-      tc::tmem_ld16(lane_base + T_S + c0, s);
-      tc::tmem_ld16(lane_base + T_DP + c0, dp);
+    // This thread's 64 key columns: all four TMEM loads in flight, then 64 independent element chains.
+    {
+      const int cb = half * (TK / 2);
+      float s[2][32], dp[2][32];
+      tc::tmem_ld32(lane_base + T_S + cb, s[0]);
+      tc::tmem_ld32(lane_base + T_DP + cb, dp[0]);
+      tc::tmem_ld32(lane_base + T_S + cb + 32, s[1]);
+      tc::tmem_ld32(lane_base + T_DP + cb + 32, dp[1]);
       tc::tmem_ld_wait();
-      uint4 pk[2], dk[2];
-      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
-      __nv_bfloat162* dh = reinterpret_cast<__nv_bfloat162*>(dk);
+      const float dsc = a.scale;
+      auto emit = [&](auto plain_tag) {
+        constexpr bool PLAIN = decltype(plain_tag)::value;
 #pragma unroll
-      for (int i = 0; i < 16; i += 2) {
-        float p[2], ds[2];
+        for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll
-        for (int jj = 0; jj < 2; ++jj) {
-          const int c = c0 + i + jj;
-          float x;
-          if (plain) {
-            x = fmaf(s[i + jj], sc2, -lse2);
-          } else {
-            x = fmaf(s[i + jj], sc2, kterm[c]) - lse2;           // -inf past the last key
-            if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+          for (int i0 = 0; i0 < 32; i0 += 8) {
+            const int c0 = cb + blk * 32 + i0;
+            uint4 pk, dk;
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+            __nv_bfloat162* dh = reinterpret_cast<__nv_bfloat162*>(&dk);
+#pragma unroll
+            for (int i = 0; i < 8; i += 2) {
+              float p[2], ds[2];
+#pragma unroll
+              for (int jj = 0; jj < 2; ++jj) {
+                const int c = c0 + i + jj;
+                float x;
+                if (PLAIN) {
+                  x = fmaf(s[blk][i0 + i + jj], sc2, -lse2);
+                } else {
+                  x = fmaf(s[blk][i0 + i + jj], sc2, kterm[c]) - lse2;           // -inf past the last key
+                  if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+                }
+                p[jj] = tc::ex2(x);
+                ds[jj] = p[jj] * (dp[blk][i0 + i + jj] - delta) * dsc;
+              }
+              ph[i >> 1] = __floats2bfloat162_rn(p[0], p[1]);
+              dh[i >> 1] = __floats2bfloat162_rn(ds[0], ds[1]);
+            }
+            if (MODE == 0) *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk;
+            *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8) * CS128 + t * 16) = dk;
           }
-          p[jj] = tc::ex2(x);
-          ds[jj] = p[jj] * (dp[i + jj] - delta) * a.scale;
         }
-        ph[i >> 1] = __floats2bfloat162_rn(p[0], p[1]);
-        dh[i >> 1] = __floats2bfloat162_rn(ds[0], ds[1]);
-      }
-      if (MODE == 0) {
-        *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8) * CS128 + t * 16) = pk[0];
-        *reinterpret_cast<uint4*>(smem + L::P + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
-      }
-      *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8) * CS128 + t * 16) = dk[0];
-      *reinterpret_cast<uint4*>(smem + L::DS + (c0 / 8 + 1) * CS128 + t * 16) = dk[1];
+      };
+      if (plain) emit(std::true_type{});
+      else emit(std::false_type{});
     }
+    MT_PROF(PB + 5);
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
+    MT_PROF(PB + 6);
     if (tid == 0) {
       constexpr uint32_t id_t = tc::make_idesc(TK, DH, 1, 1);   // A^T (MN-major) x B (MN-major)
       constexpr uint32_t id_n = tc::make_idesc(TQ, DH, 0, 1);   // A (K-major)    x B (MN-major)
@@ -730,6 +780,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     }
     tc::mbar_wait(&bar2, phase);   // releases this tile's buffers, P and dS
     tc::fence_after_sync();
+    MT_PROF(PB + 7);
     first = false;
     phase ^= 1;
   }
@@ -740,7 +791,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   }
   const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   const bool zero = first;
-  auto store_row = [&](uint32_t tcol, __nv_bfloat16* dst, const float* cs, const float* sn, int pos) {
+  // Accumulators leave through the (now free) P / dS buffers: thread (row t, column half) un-rotates and packs its
+  // row into the chunk layout, then lane pairs write whole 32-byte sectors of the head view (stage_async's walk).
+  auto stage_out = [&](uint32_t tcol, uint8_t* buf, const float* cs, const float* sn, int pos) {
 #pragma unroll
     for (int c0 = half * (DH / 2); c0 < (half + 1) * (DH / 2); c0 += 16) {
       float g[16];
@@ -756,25 +809,34 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
       __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
 #pragma unroll
       for (int i = 0; i < 16; i += 2) ph[i >> 1] = __floats2bfloat162_rn(g[i], g[i + 1]);
-      if (dst != nullptr) {
-        *reinterpret_cast<uint4*>(dst + c0) = pk[0];
-        *reinterpret_cast<uint4*>(dst + c0 + 8) = pk[1];
-      }
+      *reinterpret_cast<uint4*>(buf + (c0 / 8) * CS128 + t * 16) = pk[0];
+      *reinterpret_cast<uint4*>(buf + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
     }
+  };
+  auto flush_out = [&](const uint8_t* buf, const HeadView& dst, int S) {
+    const int r = tid >> 1, par = tid & 1, srow = tile * 128 + r;
+    if (srow >= S) return;
+    __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(dst, n, a.n2_count, srow, h) + par * 8;
+    const uint8_t* sp = buf + par * CS128 + r * 16;
+#pragma unroll
+    for (int it = 0; it < DH / 16; ++it)
+      *reinterpret_cast<uint4*>(gp + it * 16) = *reinterpret_cast<const uint4*>(sp + it * 2 * CS128);
   };
   const int row = tile * 128 + t;
   if (MODE == 0) {
-    const bool ok = row < a.Sk;
-    store_row(T_A, ok ? view_ptr<__nv_bfloat16>(a.dv, n, a.n2_count, row, h) : nullptr, nullptr, nullptr, 0);
-    store_row(T_B, ok ? view_ptr<__nv_bfloat16>(a.dk, n, a.n2_count, row, h) : nullptr, a.kcos, a.ksin,
-              a.pos_is_head ? h : min(row, a.Sk - 1));
+    stage_out(T_A, smem + L::P, nullptr, nullptr, 0);
+    stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? h : min(row, a.Sk - 1));
+    __syncthreads();
+    flush_out(smem + L::P, a.dv, a.Sk);
+    flush_out(smem + L::DS, a.dk, a.Sk);
   } else {
-    const bool ok = row < a.Sq;
-    store_row(T_A, ok ? view_ptr<__nv_bfloat16>(a.dq, n, a.n2_count, row, h) : nullptr, a.qcos, a.qsin,
-              a.pos_is_head ? h : min(row, a.Sq - 1));
+    stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? h : min(row, a.Sq - 1));
+    __syncthreads();
+    flush_out(smem + L::DS, a.dq, a.Sq);
   }
   tc::fence_before_sync();
   __syncthreads();
+  MT_PROF(PB + 8);
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
