@@ -560,7 +560,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   constexpr int NT = 256;
   constexpr uint32_t T_S = 0, T_DP = 128, T_A = 256, T_B = 384;   // MODE 0: A = dV, B = dK; MODE 1: A = dQ
   const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, half = tid >> 7;
-  const int tile = blockIdx.x, h = blockIdx.y, n = blockIdx.z;
+  // Persistent: CTA c walks work items (tile, head, sequence) k * G + (c + k) % G, so that its consecutive items
+  // have different tile indices (causal tiles differ in length) and neighbouring CTAs share one head's operands in
+  // L2.  The next item's operand loads are issued before the current item's gradients are staged out.
+  int tile = 0, h = 0, n = 0;
   MT_PROF_INIT();
   constexpr int PB = 12 + MODE * 10;   // phase-timer slots of this pass
   if (tid == 0) {
@@ -570,7 +573,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
   const int nq = (a.Sq + TQ - 1) / TQ, nk = (a.Sk + TK - 1) / TK;
-  const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+  const int nt = MODE == 0 ? nk : nq;
+  const int64_t n_items = (int64_t)nt * a.H * a.N;
+  const float* mrow = nullptr;
   const float sc2 = a.scale * LOG2E;
 
   const bool pre = a.q_rot.p != nullptr;          // Q, K already rotated by meant_attn_prerotate
@@ -578,33 +583,37 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   const HeadView& kv = pre ? a.k_rot : a.k;
   const float* qcos = pre ? nullptr : a.qcos;
   const float* kcos = pre ? nullptr : a.kcos;
+  // (measured slower and not kept: a line-friendly walk with consecutive lanes on consecutive chunks of a row; an L2
+  // bulk prefetch of the next item; un-rotation tables fetched ahead of the next item's copies)
+  auto stage_qk = [&](uint8_t* dst, const HeadView& v, int s0, int S) { stage_async<DH, NT>(dst, v, n, a.n2_count, h, s0, S); };
+  auto stage_plain = stage_qk;
   // streamed tile j -> buffer pair b:  MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
   auto stream = [&](int j, int b) {
     uint8_t* x = smem + L::STR + (uint32_t)b * 2 * L::OPER;
     if (MODE == 0) {
-      stage_async<DH, NT>(x, qv, n, a.n2_count, h, j * TQ, a.Sq);
-      stage_async<DH, NT>(x + L::OPER, a.o, n, a.n2_count, h, j * TQ, a.Sq);
+      stage_qk(x, qv, j * TQ, a.Sq);
+      stage_plain(x + L::OPER, a.o, j * TQ, a.Sq);
     } else {
-      stage_async<DH, NT>(x, kv, n, a.n2_count, h, j * TK, a.Sk);
-      stage_async<DH, NT>(x + L::OPER, a.v, n, a.n2_count, h, j * TK, a.Sk);
+      stage_qk(x, kv, j * TK, a.Sk);
+      stage_plain(x + L::OPER, a.v, j * TK, a.Sk);
     }
   };
   // delta = <dO, O>: computed once per query tile by the dQ pass (which runs first) and kept in a.delta for the
   // dK|dV pass.  Coalesced: a 16-lane group reads one row of O and dO (DH*2 contiguous bytes each), two rows per
   // warp instruction, all loads of the warp's 16 rows in flight before the first use.
-  float delta = 0.f, lse2 = 0.f;
-  auto row_stats = [&](int qi) {               // per-thread statistics of query row qi (coalesced fp32 reads)
-    delta = 0.f;
-    lse2 = 0.f;
+  // Rows past Sq keep lse = delta = 0: their Q and dO rows are zero-filled, so P is finite and dS, P^T dO vanish.
+  float delta = 0.f, lse_raw = 0.f;
+  auto row_stats = [&](int qi) {               // per-thread statistics of query row qi (coalesced fp32 reads);
+    delta = 0.f;                               // nothing consumes the loads here: the latency hides behind what follows
+    lse_raw = 0.f;
     if (qi >= a.Sq) return;
     const int64_t li = ((int64_t)n * a.H + h) * a.Sq + qi;
-    lse2 = a.lse[li] * LOG2E;
+    lse_raw = __ldg(a.lse + li);
     if (MODE == 0) delta = a.delta[li];
   };
-  auto tile_delta = [&](int q0) {
+  uint4 ov[MODE == 1 ? 8 : 1], gv[MODE == 1 ? 8 : 1];
+  auto tile_delta_issue = [&](int q0) {
     const int lane = tid & 31, sub = lane >> 4, c = lane & 15;
-    float d[8];
-    uint4 ov[8], gv[8];
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int qi = q0 + warp * 16 + it * 2 + sub;
@@ -615,6 +624,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
         gv[it] = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h) + c * 8);
       }
     }
+  };
+  auto tile_delta_reduce = [&](int q0) {       // same item as the matching tile_delta_issue (n, h unchanged)
+    const int lane = tid & 31, sub = lane >> 4, c = lane & 15;
+    float d[8];
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const __nv_bfloat162* o2 = reinterpret_cast<const __nv_bfloat162*>(&ov[it]);
@@ -639,28 +652,42 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     }
   };
 
-  int j0, j1;   // tiles of the other axis; causal problems skip the pairs above the diagonal
-  if (MODE == 0) {
-    j0 = a.causal ? tile : 0;
-    j1 = nq;
-    stage_async<DH, NT>(smem + L::FIX0, kv, n, a.n2_count, h, tile * TK, a.Sk);
-    stage_async<DH, NT>(smem + L::FIX1, a.v, n, a.n2_count, h, tile * TK, a.Sk);
-  } else {
-    j0 = 0;
-    j1 = a.causal ? min(nk, tile + 1) : nk;
-    stage_async<DH, NT>(smem + L::FIX0, qv, n, a.n2_count, h, tile * TQ, a.Sq);
-    stage_async<DH, NT>(smem + L::FIX1, a.o, n, a.n2_count, h, tile * TQ, a.Sq);
-  }
-  if (j0 < j1) stream(j0, 0);
-  tc::cp_async_commit();
-  if (MODE == 1) {
-    row_stats(tile * TQ + t);
-    tile_delta(tile * TQ);                  // visible to the softmax below after the loop's first __syncthreads
-  }
-  if (MODE == 0 && tid < TK) kterm[tid] = key_term(mrow, tile * TK + tid, a.Sk);
+  int j0 = 0, j1 = 0;   // tiles of the other axis; causal problems skip the pairs above the diagonal
+  auto begin_item = [&](int64_t kth) -> bool {
+    const int64_t G = gridDim.x, idx = kth * G + (blockIdx.x + kth) % G;
+    if (idx >= n_items) return false;
+    tile = (int)(idx % nt);
+    h = (int)((idx / nt) % a.H);
+    n = (int)(idx / ((int64_t)nt * a.H));
+    mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+    if (MODE == 0) {
+      j0 = a.causal ? tile : 0;
+      j1 = nq;
+      stage_qk(smem + L::FIX0, kv, tile * TK, a.Sk);
+      stage_plain(smem + L::FIX1, a.v, tile * TK, a.Sk);
+    } else {
+      j0 = 0;
+      j1 = a.causal ? min(nk, tile + 1) : nk;
+      stage_qk(smem + L::FIX0, qv, tile * TQ, a.Sq);
+      stage_plain(smem + L::FIX1, a.o, tile * TQ, a.Sq);
+    }
+    if (j0 < j1) stream(j0, 0);
+    tc::cp_async_commit();
+    if (MODE == 1) {
+      row_stats(tile * TQ + t);
+      tile_delta_issue(tile * TQ);            // reduced after the previous item's gradients are staged out
+    }
+    if (MODE == 0 && tid < TK) kterm[tid] = key_term(mrow, tile * TK + tid, a.Sk);
+    return true;
+  };
+  begin_item(0);
+  if (MODE == 1) tile_delta_reduce(tile * TQ);   // visible to the softmax after the loop's first __syncthreads
 
   uint32_t phase = 0, tmem = 0;
   bool first = true;
+  int64_t kth = 0;
+#pragma unroll 1
+  for (;;) {
 #pragma unroll 1
   for (int j = j0; j < j1; ++j) {
     const int b = (j - j0) & 1;
@@ -705,8 +732,8 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int qi = q0 + t;
     const bool diag = a.causal && k0 + TK - 1 > q0;
-    const bool qok = qi < a.Sq;
-    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk && q0 + TQ <= a.Sq;   // tile pair without any masking
+    const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk;   // no additive key term, nothing above the diagonal
+    const float lse2 = lse_raw * LOG2E;
     // This thread's 64 key columns: all four TMEM loads in flight, then 64 independent element chains.
     {
       const int cb = half * (TK / 2);
@@ -717,8 +744,8 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
       tc::tmem_ld32(lane_base + T_DP + cb + 32, dp[1]);
       tc::tmem_ld_wait();
       const float dsc = a.scale;
-      auto emit = [&](auto plain_tag) {
-        constexpr bool PLAIN = decltype(plain_tag)::value;
+      auto emit = [&](auto variant) {            // 0: bare scores, 1: + key term (padding, keys past Sk), 2: + causal diagonal
+        constexpr int VAR = decltype(variant)::value;
 #pragma unroll
         for (int blk = 0; blk < 2; ++blk) {
 #pragma unroll
@@ -734,11 +761,11 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
               for (int jj = 0; jj < 2; ++jj) {
                 const int c = c0 + i + jj;
                 float x;
-                if (PLAIN) {
+                if (VAR == 0) {
                   x = fmaf(s[blk][i0 + i + jj], sc2, -lse2);
                 } else {
                   x = fmaf(s[blk][i0 + i + jj], sc2, kterm[c]) - lse2;           // -inf past the last key
-                  if (!qok || (diag && k0 + c > qi)) x = -CUDART_INF_F;
+                  if (VAR == 2 && k0 + c > qi) x = -CUDART_INF_F;
                 }
                 p[jj] = tc::ex2(x);
                 ds[jj] = p[jj] * (dp[blk][i0 + i + jj] - delta) * dsc;
@@ -751,8 +778,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
           }
         }
       };
-      if (plain) emit(std::true_type{});
-      else emit(std::false_type{});
+      if (plain) emit(std::integral_constant<int, 0>{});
+      else if (!diag) emit(std::integral_constant<int, 1>{});
+      else emit(std::integral_constant<int, 2>{});
     }
     MT_PROF(PB + 5);
     tc::fence_async_smem();
@@ -784,59 +812,75 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     first = false;
     phase ^= 1;
   }
-  tc::cp_async_wait<0>();
+  const int etile = tile, eh = h, en = n;   // the finished item: its gradients are staged out below
+  const bool zero = first;
   if (first) {   // no tile pair at all (causal with Sk > Sq): the gradients of this tile are zero
+    tc::cp_async_wait<0>();
     __syncthreads();
     tmem = tmem_slot;
   }
+  const bool more = begin_item(++kth);      // every buffer the loads target was released by the last bar2
+  MT_PROF(PB + 8);
   const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-  const bool zero = first;
   // Accumulators leave through the (now free) P / dS buffers: thread (row t, column half) un-rotates and packs its
   // row into the chunk layout, then lane pairs write whole 32-byte sectors of the head view (stage_async's walk).
   auto stage_out = [&](uint32_t tcol, uint8_t* buf, const float* cs, const float* sn, int pos) {
+    constexpr int NB = DH / 32;                // 16-column blocks per thread
+    float g[NB][16];
+    if (!zero) {
 #pragma unroll
-    for (int c0 = half * (DH / 2); c0 < (half + 1) * (DH / 2); c0 += 16) {
-      float g[16];
-      if (!zero) {
-        tc::tmem_ld16(lane_base + tcol + c0, g);
-        tc::tmem_ld_wait();
-      } else {
+      for (int bi = 0; bi < NB; ++bi) tc::tmem_ld16(lane_base + tcol + half * (DH / 2) + bi * 16, g[bi]);
+      tc::tmem_ld_wait();
+    } else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) g[i] = 0.f;
-      }
-      if (cs != nullptr) unrot16(g, cs, sn, pos, a.rot_dim, c0);
+      for (int bi = 0; bi < NB; ++bi)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) g[bi][i] = 0.f;
+    }
+    if (cs != nullptr) {
+#pragma unroll
+      for (int bi = 0; bi < NB; ++bi) unrot16(g[bi], cs, sn, pos, a.rot_dim, half * (DH / 2) + bi * 16);
+    }
+#pragma unroll
+    for (int bi = 0; bi < NB; ++bi) {
+      const int c0 = half * (DH / 2) + bi * 16;
       uint4 pk[2];
       __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(pk);
 #pragma unroll
-      for (int i = 0; i < 16; i += 2) ph[i >> 1] = __floats2bfloat162_rn(g[i], g[i + 1]);
+      for (int i = 0; i < 16; i += 2) ph[i >> 1] = __floats2bfloat162_rn(g[bi][i], g[bi][i + 1]);
       *reinterpret_cast<uint4*>(buf + (c0 / 8) * CS128 + t * 16) = pk[0];
       *reinterpret_cast<uint4*>(buf + (c0 / 8 + 1) * CS128 + t * 16) = pk[1];
     }
   };
   auto flush_out = [&](const uint8_t* buf, const HeadView& dst, int S) {
-    const int r = tid >> 1, par = tid & 1, srow = tile * 128 + r;
+    const int r = tid >> 1, par = tid & 1, srow = etile * 128 + r;
     if (srow >= S) return;
-    __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(dst, n, a.n2_count, srow, h) + par * 8;
+    __nv_bfloat16* gp = view_ptr<__nv_bfloat16>(dst, en, a.n2_count, srow, eh) + par * 8;
     const uint8_t* sp = buf + par * CS128 + r * 16;
 #pragma unroll
     for (int it = 0; it < DH / 16; ++it)
       *reinterpret_cast<uint4*>(gp + it * 16) = *reinterpret_cast<const uint4*>(sp + it * 2 * CS128);
   };
-  const int row = tile * 128 + t;
+  const int row = etile * 128 + t;
   if (MODE == 0) {
     stage_out(T_A, smem + L::P, nullptr, nullptr, 0);
-    stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? h : min(row, a.Sk - 1));
+    stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? eh : min(row, a.Sk - 1));
     __syncthreads();
     flush_out(smem + L::P, a.dv, a.Sk);
     flush_out(smem + L::DS, a.dk, a.Sk);
   } else {
-    stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? h : min(row, a.Sq - 1));
+    stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? eh : min(row, a.Sq - 1));
     __syncthreads();
     flush_out(smem + L::DS, a.dq, a.Sq);
+    if (more) tile_delta_reduce(tile * TQ);
   }
+  MT_PROF(PB + 9);
+  if (!more) break;
+  first = true;
+  }   // items
+  tc::cp_async_wait<0>();
   tc::fence_before_sync();
   __syncthreads();
-  MT_PROF(PB + 8);
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
@@ -911,7 +955,9 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
 
 template <int DH>
 static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
-  const dim3 gk((a.Sk + TK - 1) / TK, a.H, a.N), gq((a.Sq + TQ - 1) / TQ, a.H, a.N);
+  // persistent kernels: one CTA per SM, work items (tile, head, sequence) strided inside the kernel
+  const int64_t ik = (int64_t)((a.Sk + TK - 1) / TK) * a.H * a.N, iq = (int64_t)((a.Sq + TQ - 1) / TQ) * a.H * a.N;
+  const dim3 gk((unsigned)(ik < 148 ? ik : 148)), gq((unsigned)(iq < 148 ? iq : 148));
   // the dQ pass goes first: it also writes delta = rowsum(dO * O), which the dK|dV pass reads
   const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, MtSmem<DH>::TOTAL, gq, a, st, 256);
   if (r != 0) return r;

@@ -54,8 +54,8 @@ def prof(tag, items, launches):
         fn2.restype = ctypes.c_int
         if fn2(b2, 1) == 1 and any(b2):
             print(f"  prof_mt {tag}: cycles/launch fwd", [round(b2[i] / launches) for i in range(12)],
-                  "bwd dK|dV pass", [round(b2[i] / launches) for i in range(12, 21)],
-                  "bwd dQ pass", [round(b2[i] / launches) for i in range(22, 31)])
+                  "bwd dK|dV pass", [round(b2[i] / launches) for i in range(12, 22)],
+                  "bwd dQ pass", [round(b2[i] / launches) for i in range(22, 32)])
 
 
 def attn(args):
