@@ -583,8 +583,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   const HeadView& kv = pre ? a.k_rot : a.k;
   const float* qcos = pre ? nullptr : a.qcos;
   const float* kcos = pre ? nullptr : a.kcos;
-  // (measured slower and not kept: a line-friendly walk with consecutive lanes on consecutive chunks of a row; an L2
-  // bulk prefetch of the next item; un-rotation tables fetched ahead of the next item's copies)
+  // (measured and not kept, none faster: walks with 8 or 12 consecutive lanes on one row's chunks, an L2 bulk
+  // prefetch of the next item, un-rotation tables fetched ahead of the next item's copies - the 16-byte cp.async
+  // stream itself, ~22 B/clk per SM while it is being issued, is what bounds the item)
   auto stage_qk = [&](uint8_t* dst, const HeadView& v, int s0, int S) { stage_async<DH, NT>(dst, v, n, a.n2_count, h, s0, S); };
   auto stage_plain = stage_qk;
   // streamed tile j -> buffer pair b:  MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
