@@ -48,6 +48,9 @@ CASES = [  # n, s, heads, dh, causal, xpos, masked, backward
     (2, 300, 8, 96, True, True, True, True),      # three ragged tiles, causal diagonal skipping
     (1, 129, 8, 64, True, False, False, True),    # one row in the second tile
     (2, 256, 8, 96, False, False, True, True),
+    # more work items than CTAs: the persistent multi-tile backward walks 4-5 items per CTA
+    (40, 196, 8, 96, False, True, False, True),   # 640 items per pass
+    (26, 300, 8, 96, True, True, True, True),     # 624 items, causal tiles of unequal length
 ]
 
 
@@ -86,6 +89,9 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
             assert torch.isfinite(g).all()
             cos = torch.nn.functional.cosine_similarity(g.flatten(), xr.grad.flatten(), dim=0)
             assert float(cos) > 0.999, (name, float(cos))
+            if n > 8:   # per sequence: a gradient written to the wrong work item cannot hide in the global cosine
+                per = torch.nn.functional.cosine_similarity(g.reshape(n, -1), xr.grad.reshape(n, -1), dim=1)
+                assert float(per.min()) > 0.999, (name, int(per.argmin()), float(per.min()))
             for part, sl in (("dq", slice(0, dim)), ("dk", slice(dim, 2 * dim)), ("dv", slice(2 * dim, 3 * dim))):
                 want = xr.grad[..., sl].flatten()
                 if float(want.norm()) < 1e-6 * float(xr.grad.norm()):   # e.g. one key: dq = dk = 0 exactly
