@@ -548,10 +548,30 @@ struct MtSmem {
                             TOTAL = 6 * OPER + 2 * PBUF;
 };
 
+constexpr int MT_LOADERS = 128, MT_THREADS = 256 + MT_LOADERS;   // multi-tile backward: 8 compute warps + a loader warpgroup
+
+// stage_async's walk for the 128 loader threads: lane pairs on one row's 32-byte sectors, two passes of 64 rows.
+template <int DH>
+__device__ __forceinline__ void stage_async_half(uint8_t* smem, const HeadView& v, int n, int n2c, int h, int s0, int S, int lt) {
+  constexpr int CPR = DH / 8;
+  const int par = lt & 1;
+#pragma unroll
+  for (int pass = 0; pass < 2; ++pass) {
+    const int r = (lt >> 1) + pass * 64;
+    const bool ok = s0 + r < S;
+    const __nv_bfloat16* src = view_ptr<__nv_bfloat16>(v, n, n2c, ok ? s0 + r : 0, h) + par * 8;
+    const uint32_t dst = tc::smem_u32(smem) + par * CS128 + r * 16;
+    const uint32_t bytes = ok ? 16u : 0u;
+#pragma unroll
+    for (int it = 0; it < CPR / 2; ++it) tc::cp_async16(dst + it * 2 * CS128, src + it * 16, bytes);
+  }
+}
+
 template <int DH, int MODE>
-__global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bar1, bar2;
+  // bar1 / bar2: MMA chains done.  full_* / empty_*: operand buffers between the loader warpgroup and the compute warps.
+  __shared__ uint64_t bar1, bar2, full_fix, empty_fix, full_str[2], empty_str[2];
   __shared__ uint32_t tmem_slot;
   __shared__ float kterm[TK];
   __shared__ float sdelta[TQ];
@@ -562,16 +582,27 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, half = tid >> 7;
   // Persistent: CTA c walks work items (tile, head, sequence) k * G + (c + k) % G, so that its consecutive items
   // have different tile indices (causal tiles differ in length) and neighbouring CTAs share one head's operands in
-  // L2.  The next item's operand loads are issued before the current item's gradients are staged out.
+  // L2.  Warps 0-7 compute; warps 8-11 (one warpgroup, registers handed to the compute warps) only issue the 16-byte
+  // cp.async copies - their issue blocks on the memory pipeline - and run ahead as far as the buffers allow, so the
+  // next item's operands land while the finished item's gradients are staged out.
   int tile = 0, h = 0, n = 0;
   MT_PROF_INIT();
   constexpr int PB = 12 + MODE * 10;   // phase-timer slots of this pass
   if (tid == 0) {
     tc::mbar_init(&bar1, 1);
     tc::mbar_init(&bar2, 1);
+    tc::mbar_init(&full_fix, MT_LOADERS);      // one pre-counted cp.async arrival per loader thread
+    tc::mbar_init(&full_str[0], MT_LOADERS);
+    tc::mbar_init(&full_str[1], MT_LOADERS);
+    tc::mbar_init(&empty_fix, 1);              // tcgen05.commit of the last MMA chain that read the buffer
+    tc::mbar_init(&empty_str[0], 1);
+    tc::mbar_init(&empty_str[1], 1);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();                             // all 384 threads: barriers initialised, TMEM address published
+  tc::fence_after_sync();
   const int nq = (a.Sq + TQ - 1) / TQ, nk = (a.Sk + TK - 1) / TK;
   const int nt = MODE == 0 ? nk : nq;
   const int64_t n_items = (int64_t)nt * a.H * a.N;
@@ -586,19 +617,71 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   // (measured and not kept, none faster: walks with 8 or 12 consecutive lanes on one row's chunks, an L2 bulk
   // prefetch of the next item, un-rotation tables fetched ahead of the next item's copies - the 16-byte cp.async
   // stream itself, ~22 B/clk per SM while it is being issued, is what bounds the item)
-  auto stage_qk = [&](uint8_t* dst, const HeadView& v, int s0, int S) { stage_async<DH, NT>(dst, v, n, a.n2_count, h, s0, S); };
-  auto stage_plain = stage_qk;
-  // streamed tile j -> buffer pair b:  MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
-  auto stream = [&](int j, int b) {
-    uint8_t* x = smem + L::STR + (uint32_t)b * 2 * L::OPER;
+  // work item kth of this CTA -> (tile, h, n, j0, j1); false past the end.  Both roles walk the same sequence.
+  int j0 = 0, j1 = 0;   // tiles of the other axis; causal problems skip the pairs above the diagonal
+  auto decode_item = [&](int64_t kth) -> bool {
+    const int64_t G = gridDim.x, idx = kth * G + (blockIdx.x + kth) % G;
+    if (idx >= n_items) return false;
+    tile = (int)(idx % nt);
+    h = (int)((idx / nt) % a.H);
+    n = (int)(idx / ((int64_t)nt * a.H));
     if (MODE == 0) {
-      stage_qk(x, qv, j * TQ, a.Sq);
-      stage_plain(x + L::OPER, a.o, j * TQ, a.Sq);
+      j0 = a.causal ? tile : 0;
+      j1 = nq;
     } else {
-      stage_qk(x, kv, j * TK, a.Sk);
-      stage_plain(x + L::OPER, a.v, j * TK, a.Sk);
+      j0 = 0;
+      j1 = a.causal ? min(nk, tile + 1) : nk;
     }
+    return true;
   };
+
+  if (tid >= NT) {   // ------------------------------------------------------------------ loader warpgroup
+    tc::reg_dec<40>();
+    const int lt = tid - NT;
+    auto stage = [&](uint8_t* dst, const HeadView& v, int s0, int S) {
+      stage_async_half<DH>(dst, v, n, a.n2_count, h, s0, S, lt);
+    };
+    uint32_t pe_fix = 1, pe_str0 = 1, pe_str1 = 1;   // a fresh barrier's "previous phase" counts as complete
+#pragma unroll 1
+    for (int64_t kth = 0; decode_item(kth); ++kth) {
+      if (j0 >= j1) continue;                  // empty item: nothing is loaded, nothing is waited for
+      tc::mbar_wait(&empty_fix, pe_fix);
+      pe_fix ^= 1;
+      if (MODE == 0) {
+        stage(smem + L::FIX0, kv, tile * TK, a.Sk);
+        stage(smem + L::FIX1, a.v, tile * TK, a.Sk);
+      } else {
+        stage(smem + L::FIX0, qv, tile * TQ, a.Sq);
+        stage(smem + L::FIX1, a.o, tile * TQ, a.Sq);
+      }
+      tc::cp_async_arrive(&full_fix);
+#pragma unroll 1
+      for (int j = j0; j < j1; ++j) {
+        const int b = (j - j0) & 1;
+        if (b == 0) {
+          tc::mbar_wait(&empty_str[0], pe_str0);
+          pe_str0 ^= 1;
+        } else {
+          tc::mbar_wait(&empty_str[1], pe_str1);
+          pe_str1 ^= 1;
+        }
+        uint8_t* x = smem + L::STR + (uint32_t)b * 2 * L::OPER;   // MODE 0: Q(j) | dO(j),  MODE 1: K(j) | V(j)
+        if (MODE == 0) {
+          stage(x, qv, j * TQ, a.Sq);
+          stage(x + L::OPER, a.o, j * TQ, a.Sq);
+        } else {
+          stage(x, kv, j * TK, a.Sk);
+          stage(x + L::OPER, a.v, j * TK, a.Sk);
+        }
+        tc::cp_async_arrive(&full_str[b]);
+      }
+    }
+    tc::cp_async_commit();
+    tc::cp_async_wait<0>();
+    return;
+  }
+  // ------------------------------------------------------------------------------------- compute warps
+  tc::reg_inc<232>();
   // delta = <dO, O>: computed once per query tile by the dQ pass (which runs first) and kept in a.delta for the
   // dK|dV pass.  Coalesced: a 16-lane group reads one row of O and dO (DH*2 contiguous bytes each), two rows per
   // warp instruction, all loads of the warp's 16 rows in flight before the first use.
@@ -653,27 +736,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     }
   };
 
-  int j0 = 0, j1 = 0;   // tiles of the other axis; causal problems skip the pairs above the diagonal
-  auto begin_item = [&](int64_t kth) -> bool {
-    const int64_t G = gridDim.x, idx = kth * G + (blockIdx.x + kth) % G;
-    if (idx >= n_items) return false;
-    tile = (int)(idx % nt);
-    h = (int)((idx / nt) % a.H);
-    n = (int)(idx / ((int64_t)nt * a.H));
+  auto begin_item = [&](int64_t kth) -> bool {   // the compute side of an item: its statistics
+    if (!decode_item(kth)) return false;
     mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
-    if (MODE == 0) {
-      j0 = a.causal ? tile : 0;
-      j1 = nq;
-      stage_qk(smem + L::FIX0, kv, tile * TK, a.Sk);
-      stage_plain(smem + L::FIX1, a.v, tile * TK, a.Sk);
-    } else {
-      j0 = 0;
-      j1 = a.causal ? min(nk, tile + 1) : nk;
-      stage_qk(smem + L::FIX0, qv, tile * TQ, a.Sq);
-      stage_plain(smem + L::FIX1, a.o, tile * TQ, a.Sq);
-    }
-    if (j0 < j1) stream(j0, 0);
-    tc::cp_async_commit();
     if (MODE == 1) {
       row_stats(tile * TQ + t);
       tile_delta_issue(tile * TQ);            // reduced after the previous item's gradients are staged out
@@ -682,9 +747,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     return true;
   };
   begin_item(0);
-  if (MODE == 1) tile_delta_reduce(tile * TQ);   // visible to the softmax after the loop's first __syncthreads
+  if (MODE == 1) tile_delta_reduce(tile * TQ);   // visible to the softmax after the loop's first barrier
 
-  uint32_t phase = 0, tmem = 0;
+  uint32_t phase = 0, pf_fix = 0, pf_str0 = 0, pf_str1 = 0;
+  const uint32_t tmem = tmem_slot;
   bool first = true;
   int64_t kth = 0;
 #pragma unroll 1
@@ -693,11 +759,19 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   for (int j = j0; j < j1; ++j) {
     const int b = (j - j0) & 1;
     const int q0 = (MODE == 0 ? j : tile) * TQ, k0 = (MODE == 0 ? tile : j) * TK;
-    if (j + 1 < j1) stream(j + 1, b ^ 1);      // the other pair was released by the previous iteration's bar2
-    tc::cp_async_commit();
     MT_PROF(PB + 0);
     if (MODE == 0) row_stats(q0 + t);           // latency hidden behind the wait
-    tc::cp_async_wait<1>();                     // tile j (and the fixed pair) landed
+    if (first) {
+      tc::mbar_wait(&full_fix, pf_fix);         // the fixed pair landed
+      pf_fix ^= 1;
+    }
+    if (b == 0) {                               // streamed pair j landed
+      tc::mbar_wait(&full_str[0], pf_str0);
+      pf_str0 ^= 1;
+    } else {
+      tc::mbar_wait(&full_str[1], pf_str1);
+      pf_str1 ^= 1;
+    }
     MT_PROF(PB + 1);
     uint8_t* xs = smem + L::STR + (uint32_t)b * 2 * L::OPER;
     if (MODE == 0) {
@@ -714,10 +788,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     MT_PROF(PB + 2);
     tc::fence_async_smem();
     tc::fence_before_sync();
-    __syncthreads();
+    tc::bar_sync(1, NT);
     tc::fence_after_sync();
     MT_PROF(PB + 3);
-    tmem = tmem_slot;
     if (MODE == 1 && first) delta = sdelta[t];
     if (tid == 0) {
       constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
@@ -786,7 +859,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
     MT_PROF(PB + 5);
     tc::fence_async_smem();
     tc::fence_before_sync();
-    __syncthreads();
+    tc::bar_sync(1, NT);
     tc::fence_after_sync();
     MT_PROF(PB + 6);
     if (tid == 0) {
@@ -806,8 +879,10 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
           tc::mma_ss(tmem + T_A, desc_kmajor(sds, ks), desc_mnmajor(sk, ks), id_n, acc | (ks > 0));
       }
       tc::mma_commit(&bar2);
+      tc::mma_commit(&empty_str[b]);            // the loader may refill this streamed pair ...
+      if (j + 1 == j1) tc::mma_commit(&empty_fix);   // ... and, after the item's last chain, the fixed pair
     }
-    tc::mbar_wait(&bar2, phase);   // releases this tile's buffers, P and dS
+    tc::mbar_wait(&bar2, phase);   // P and dS may be rewritten
     tc::fence_after_sync();
     MT_PROF(PB + 7);
     first = false;
@@ -815,11 +890,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   }
   const int etile = tile, eh = h, en = n;   // the finished item: its gradients are staged out below
   const bool zero = first;
-  if (first) {   // no tile pair at all (causal with Sk > Sq): the gradients of this tile are zero
-    tc::cp_async_wait<0>();
-    __syncthreads();
-    tmem = tmem_slot;
-  }
+  // (zero: no tile pair at all - causal with Sk > Sq - the gradients of this tile are zero)
   const bool more = begin_item(++kth);      // every buffer the loads target was released by the last bar2
   MT_PROF(PB + 8);
   const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
@@ -866,12 +937,12 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   if (MODE == 0) {
     stage_out(T_A, smem + L::P, nullptr, nullptr, 0);
     stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? eh : min(row, a.Sk - 1));
-    __syncthreads();
+    tc::bar_sync(1, NT);
     flush_out(smem + L::P, a.dv, a.Sk);
     flush_out(smem + L::DS, a.dk, a.Sk);
   } else {
     stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? eh : min(row, a.Sq - 1));
-    __syncthreads();
+    tc::bar_sync(1, NT);
     flush_out(smem + L::DS, a.dq, a.Sq);
     if (more) tile_delta_reduce(tile * TQ);
   }
@@ -879,9 +950,8 @@ __global__ void __launch_bounds__(256, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
   if (!more) break;
   first = true;
   }   // items
-  tc::cp_async_wait<0>();
   tc::fence_before_sync();
-  __syncthreads();
+  tc::bar_sync(1, NT);
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
@@ -960,9 +1030,9 @@ static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
   const int64_t ik = (int64_t)((a.Sk + TK - 1) / TK) * a.H * a.N, iq = (int64_t)((a.Sq + TQ - 1) / TQ) * a.H * a.N;
   const dim3 gk((unsigned)(ik < 148 ? ik : 148)), gq((unsigned)(iq < 148 ? iq : 148));
   // the dQ pass goes first: it also writes delta = rowsum(dO * O), which the dK|dV pass reads
-  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, MtSmem<DH>::TOTAL, gq, a, st, 256);
+  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, MtSmem<DH>::TOTAL, gq, a, st, MT_THREADS);
   if (r != 0) return r;
-  return launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, MtSmem<DH>::TOTAL, gk, a, st, 256);
+  return launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, MtSmem<DH>::TOTAL, gk, a, st, MT_THREADS);
 }
 
 static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels
