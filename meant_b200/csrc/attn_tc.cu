@@ -26,14 +26,17 @@
 #include <type_traits>
 #include "attn_common.cuh"
 #include "tc_utils.cuh"
+#include "tma_utils.cuh"
 #include <math_constants.h>
 #include <atomic>
+#include <string.h>
+#include <stdlib.h>
 
 namespace meant {
 
 constexpr int TQ = 128;                       // query rows per CTA == TMEM lanes
 constexpr int TK = 128;                       // keys per tile
-constexpr uint32_t CS128 = 128 * 16 + 16;     // chunk stride of a 128-row chunk-layout buffer
+constexpr uint32_t CS128 = 128 * 16;          // chunk stride of a 128-row chunk-layout buffer (unpadded: a TMA box lands in it)
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
@@ -567,8 +570,16 @@ __device__ __forceinline__ void stage_async_half(uint8_t* smem, const HeadView& 
   }
 }
 
+// Tensor maps of the multi-tile backward (chunk-layout boxes, tma_utils.cuh::make_chunk_map); use_tma = 0 keeps the
+// cp.async loader warpgroup and the sector-wise stores (views TMA cannot describe).
+enum { MT_Q = 0, MT_K, MT_V, MT_DO, MT_DQ, MT_DK, MT_DV, MT_NMAPS };
+struct MtMaps {
+  CUtensorMap m[MT_NMAPS];
+  int use_tma;
+};
+
 template <int DH, int MODE>
-__global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs a, const __grid_constant__ MtMaps maps) {
   extern __shared__ __align__(128) uint8_t smem[];
   // bar1 / bar2: MMA chains done.  full_* / empty_*: operand buffers between the loader warpgroup and the compute warps.
   __shared__ uint64_t bar1, bar2, full_fix, empty_fix, full_str[2], empty_str[2];
@@ -591,9 +602,10 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   if (tid == 0) {
     tc::mbar_init(&bar1, 1);
     tc::mbar_init(&bar2, 1);
-    tc::mbar_init(&full_fix, MT_LOADERS);      // one pre-counted cp.async arrival per loader thread
-    tc::mbar_init(&full_str[0], MT_LOADERS);
-    tc::mbar_init(&full_str[1], MT_LOADERS);
+    const uint32_t producers = maps.use_tma ? 1u : (uint32_t)MT_LOADERS;   // one expect_tx arrival, or one pre-counted
+    tc::mbar_init(&full_fix, producers);                                     // cp.async arrival per loader thread
+    tc::mbar_init(&full_str[0], producers);
+    tc::mbar_init(&full_str[1], producers);
     tc::mbar_init(&empty_fix, 1);              // tcgen05.commit of the last MMA chain that read the buffer
     tc::mbar_init(&empty_str[0], 1);
     tc::mbar_init(&empty_str[1], 1);
@@ -638,6 +650,47 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   if (tid >= NT) {   // ------------------------------------------------------------------ loader warpgroup
     tc::reg_dec<40>();
     const int lt = tid - NT;
+    if (maps.use_tma) {   // one thread drives TMA: one box per operand tile, straight into the chunk layout
+      if (lt != 0) return;
+      const CUtensorMap* mq = &maps.m[MT_Q];
+      const CUtensorMap* mk = &maps.m[MT_K];
+      const CUtensorMap* mv = &maps.m[MT_V];
+      const CUtensorMap* mo = &maps.m[MT_DO];
+      tma::prefetch_map(mq);
+      tma::prefetch_map(mk);
+      tma::prefetch_map(mv);
+      tma::prefetch_map(mo);
+      const CUtensorMap* fa = MODE == 0 ? mk : mq;   // fixed pair
+      const CUtensorMap* fb = MODE == 0 ? mv : mo;
+      const CUtensorMap* sa = MODE == 0 ? mq : mk;   // streamed pair
+      const CUtensorMap* sb = MODE == 0 ? mo : mv;
+      uint32_t pe_fix = 1, pe_str0 = 1, pe_str1 = 1;
+#pragma unroll 1
+      for (int64_t kth = 0; decode_item(kth); ++kth) {
+        if (j0 >= j1) continue;
+        tc::mbar_wait(&empty_fix, pe_fix);
+        pe_fix ^= 1;
+        tma::mbar_expect_tx(&full_fix, 2 * L::OPER);
+        tma::load_box(tc::smem_u32(smem + L::FIX0), fa, &full_fix, 0, tile * 128, 0, h, n);
+        tma::load_box(tc::smem_u32(smem + L::FIX1), fb, &full_fix, 0, tile * 128, 0, h, n);
+#pragma unroll 1
+        for (int j = j0; j < j1; ++j) {
+          const int b = (j - j0) & 1;
+          if (b == 0) {
+            tc::mbar_wait(&empty_str[0], pe_str0);
+            pe_str0 ^= 1;
+          } else {
+            tc::mbar_wait(&empty_str[1], pe_str1);
+            pe_str1 ^= 1;
+          }
+          const uint32_t x = tc::smem_u32(smem + L::STR + (uint32_t)b * 2 * L::OPER);
+          tma::mbar_expect_tx(&full_str[b], 2 * L::OPER);
+          tma::load_box(x, sa, &full_str[b], 0, j * 128, 0, h, n);
+          tma::load_box(x + L::OPER, sb, &full_str[b], 0, j * 128, 0, h, n);
+        }
+      }
+      return;
+    }
     auto stage = [&](uint8_t* dst, const HeadView& v, int s0, int S) {
       stage_async_half<DH>(dst, v, n, a.n2_count, h, s0, S, lt);
     };
@@ -793,6 +846,7 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
     MT_PROF(PB + 3);
     if (MODE == 1 && first) delta = sdelta[t];
     if (tid == 0) {
+      if (first && maps.use_tma) tma::store_wait_read<0>();   // the previous item's gradient boxes have left P / dS
       constexpr uint32_t idesc = tc::make_idesc(TQ, TK, 0, 0);
 #pragma unroll
       for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_kmajor(sq, ks), desc_kmajor(sk, ks), idesc, ks > 0);
@@ -937,19 +991,37 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   if (MODE == 0) {
     stage_out(T_A, smem + L::P, nullptr, nullptr, 0);
     stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? eh : min(row, a.Sk - 1));
+    tc::fence_async_smem();
     tc::bar_sync(1, NT);
-    flush_out(smem + L::P, a.dv, a.Sk);
-    flush_out(smem + L::DS, a.dk, a.Sk);
+    if (maps.use_tma) {
+      if (tid == 0) {
+        tma::store_box(&maps.m[MT_DV], tc::smem_u32(smem + L::P), 0, etile * 128, 0, eh, en);
+        tma::store_box(&maps.m[MT_DK], tc::smem_u32(smem + L::DS), 0, etile * 128, 0, eh, en);
+        tma::store_commit();
+      }
+    } else {
+      flush_out(smem + L::P, a.dv, a.Sk);
+      flush_out(smem + L::DS, a.dk, a.Sk);
+    }
   } else {
     stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? eh : min(row, a.Sq - 1));
+    tc::fence_async_smem();
     tc::bar_sync(1, NT);
-    flush_out(smem + L::DS, a.dq, a.Sq);
+    if (maps.use_tma) {
+      if (tid == 0) {
+        tma::store_box(&maps.m[MT_DQ], tc::smem_u32(smem + L::DS), 0, etile * 128, 0, eh, en);
+        tma::store_commit();
+      }
+    } else {
+      flush_out(smem + L::DS, a.dq, a.Sq);
+    }
     if (more) tile_delta_reduce(tile * TQ);
   }
   MT_PROF(PB + 9);
   if (!more) break;
   first = true;
   }   // items
+  if (tid == 0 && maps.use_tma) tma::store_wait_all();
   tc::fence_before_sync();
   tc::bar_sync(1, NT);
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
@@ -1030,9 +1102,26 @@ static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
   const int64_t ik = (int64_t)((a.Sk + TK - 1) / TK) * a.H * a.N, iq = (int64_t)((a.Sq + TQ - 1) / TQ) * a.H * a.N;
   const dim3 gk((unsigned)(ik < 148 ? ik : 148)), gq((unsigned)(iq < 148 ? iq : 148));
   // the dQ pass goes first: it also writes delta = rowsum(dO * O), which the dK|dV pass reads
-  const int r = launch_tc(attn_tc_bwd_mt_kernel<DH, 1>, MtSmem<DH>::TOTAL, gq, a, st, MT_THREADS);
+  MtMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  {
+    const bool pre = a.q_rot.p != nullptr;
+    const HeadView* vs[MT_NMAPS] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o, &a.dq, &a.dk, &a.dv};
+    const int seq[MT_NMAPS] = {a.Sq, a.Sk, a.Sk, a.Sq, a.Sq, a.Sk, a.Sk};
+    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
+    for (int i = 0; i < MT_NMAPS && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH) == 0;
+    maps.use_tma = ok;
+  }
+  auto launch = [&](auto kern, dim3 grid) -> int {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)MtSmem<DH>::TOTAL);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, MT_THREADS, MtSmem<DH>::TOTAL, st>>>(a, maps);
+    MEANT_LAUNCH_CHECK();
+    return 0;
+  };
+  const int r = launch(attn_tc_bwd_mt_kernel<DH, 1>, gq);
   if (r != 0) return r;
-  return launch_tc(attn_tc_bwd_mt_kernel<DH, 0>, MtSmem<DH>::TOTAL, gk, a, st, MT_THREADS);
+  return launch(attn_tc_bwd_mt_kernel<DH, 0>, gk);
 }
 
 static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels

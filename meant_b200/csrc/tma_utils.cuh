@@ -67,6 +67,40 @@ inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count,
   return r == CUDA_SUCCESS ? 0 : MEANT_EUNSUPPORTED;
 }
 
+// Tensor map that lands a head tile in the unswizzled CHUNK layout of attn_tc.cu ([chunk][row][16 B], chunk stride
+// 128 * 16 B): dimensions, fastest first, (8 elements of a chunk, row s, chunk, h, n); box = 8 x 128 x Dh/8 x 1 x 1.
+// One copy per operand tile; rows >= S zero-filled on load, dropped on store.  Views with a split sequence index
+// (n2_count > 1) would need a sixth dimension: MEANT_EUNSUPPORTED.
+inline int make_chunk_map(CUtensorMap* m, const HeadView& v, int N, int n2_count, int H, int S, int Dh) {
+  EncodeTiledFn enc = encode_fn();
+  if (!enc || n2_count != 1 || Dh % 8) return MEANT_EUNSUPPORTED;
+  if (reinterpret_cast<uintptr_t>(v.p) & 15) return MEANT_EUNSUPPORTED;
+  const cuuint64_t dims[5] = {8u, (cuuint64_t)S, (cuuint64_t)(Dh / 8), (cuuint64_t)H, (cuuint64_t)N};
+  int64_t st[4] = {v.ss * 2, 16, v.sh * 2, v.sn1 * 2};                  // bytes, dims 1..4
+  cuuint64_t strides[4];
+  for (int i = 0; i < 4; ++i) {
+    if (dims[i + 1] == 1 && st[i] <= 0) st[i] = 16;
+    if (st[i] <= 0 || st[i] % 16 || st[i] >= ((int64_t)1 << 40)) return MEANT_EUNSUPPORTED;
+    strides[i] = (cuuint64_t)st[i];
+  }
+  const cuuint32_t box[5] = {8u, 128u, (cuuint32_t)(Dh / 8), 1u, 1u};
+  const cuuint32_t estr[5] = {1u, 1u, 1u, 1u, 1u};
+  CUresult r = CUDA_ERROR_UNKNOWN;
+  for (int attempt = 0; attempt < 2 && r != CUDA_SUCCESS; ++attempt) {
+    if (attempt == 1) {   // no current driver context on this thread yet (see make_head_map)
+      int dev = 0;
+      if (r != CUDA_ERROR_INVALID_CONTEXT || cudaGetDevice(&dev) != cudaSuccess || cudaSetDevice(dev) != cudaSuccess) break;
+    }
+    r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(v.p), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  if (r != CUDA_SUCCESS && getenv("MEANT_DEBUG"))
+    fprintf(stderr, "meant_b200: chunk map encode failed (%d): p=%p S=%d Dh=%d strides=(%lld,%lld,%lld,%lld)\n", (int)r, v.p, S,
+            Dh, (long long)st[0], (long long)st[1], (long long)st[2], (long long)st[3]);
+  return r == CUDA_SUCCESS ? 0 : MEANT_EUNSUPPORTED;
+}
+
 #ifdef __CUDACC__
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
