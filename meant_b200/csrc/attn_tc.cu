@@ -190,10 +190,16 @@ __device__ __forceinline__ float key_term(const float* mrow, int kj, int Sk) {
   return mrow != nullptr ? (1.0f - __ldg(mrow + kj)) * (-1e9f * LOG2E) : 0.f;
 }
 
+// Tensor maps of the multi-tile forward: q (rotated copy when there is one), k, v as chunk-layout boxes.
+struct FwdMtMaps {
+  CUtensorMap m[3];
+  int use_tma;
+};
+
 template <int DH>
-__global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
+__global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const __grid_constant__ FwdMtMaps maps) {
   extern __shared__ __align__(128) uint8_t smem[];
-  __shared__ uint64_t bar_s, bar_o;
+  __shared__ uint64_t bar_s, bar_o, bar_k, bar_v;   // MMA chains done; TMA: Q|K and V tiles landed
   __shared__ uint32_t tmem_slot;
   __shared__ float kterm[TK];
   __shared__ float xch[2][TQ];          // row max / row sum exchange between the two column halves
@@ -204,6 +210,8 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
   if (tid == 0) {
     tc::mbar_init(&bar_s, 1);
     tc::mbar_init(&bar_o, 1);
+    tc::mbar_init(&bar_k, 1);
+    tc::mbar_init(&bar_v, 1);
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
@@ -213,11 +221,26 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
   const HeadView& kv = pre ? a.k_rot : a.k;
   const float* qcos = pre ? nullptr : a.qcos;
   const float* kcos = pre ? nullptr : a.kcos;
-  stage_async<DH, NT>(smem + L::Q, qv, n, a.n2_count, h, q0, a.Sq);
-  stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, 0, a.Sk);
-  tc::cp_async_commit();
-  stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk);
-  tc::cp_async_commit();
+  // Operand tiles: one TMA box each, straight into the chunk layout (make_chunk_map), issued by thread 0 and counted
+  // in bytes on bar_k (Q with K(0), then K(kt+1)) / bar_v; views TMA cannot describe keep the cp.async groups.
+  const bool use_tma = maps.use_tma != 0;
+  uint32_t par_k = 0, par_v = 0;
+  if (use_tma) {
+    __syncthreads();                    // the barriers exist before anybody polls them
+    if (tid == 0) {
+      tma::mbar_expect_tx(&bar_k, 2 * L::OPER);
+      tma::load_box(tc::smem_u32(smem + L::Q), &maps.m[0], &bar_k, 0, q0, 0, h, n);
+      tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, 0, 0, h, n);
+      tma::mbar_expect_tx(&bar_v, L::OPER);
+      tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, 0, 0, h, n);
+    }
+  } else {
+    stage_async<DH, NT>(smem + L::Q, qv, n, a.n2_count, h, q0, a.Sq);
+    stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, 0, a.Sk);
+    tc::cp_async_commit();
+    stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk);
+    tc::cp_async_commit();
+  }
 
   const int qi = q0 + t;
   const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
@@ -240,7 +263,12 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     const bool diag = a.causal && k0 + TK - 1 > q0;       // some (row, key) of this tile pair is above the diagonal
     const bool plain = !diag && mrow == nullptr && k0 + TK <= a.Sk && sc2 > 0.f;   // no additive term, no masking
     MT_PROF(10);
-    tc::cp_async_wait<1>();            // K(kt) (and Q) landed; V(kt) may still be in flight
+    if (use_tma) {
+      tc::mbar_wait(&bar_k, par_k);
+      par_k ^= 1;
+    } else {
+      tc::cp_async_wait<1>();          // K(kt) (and Q) landed; V(kt) may still be in flight
+    }
     MT_PROF(0);
     if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
     rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
@@ -261,8 +289,15 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     tc::mbar_wait(&bar_s, phase);
     tc::fence_after_sync();
     MT_PROF(3);
-    if (more) stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, k0 + TK, a.Sk);   // K is free: next tile
-    tc::cp_async_commit();
+    if (use_tma) {                                                                      // K is free: next tile
+      if (more && tid == 0) {
+        tma::mbar_expect_tx(&bar_k, L::OPER);
+        tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, k0 + TK, 0, h, n);
+      }
+    } else {
+      if (more) stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, k0 + TK, a.Sk);
+      tc::cp_async_commit();
+    }
     MT_PROF(4);
     const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
     const int cb = hf * HK;            // this thread's key columns: [cb, cb + HK)
@@ -324,7 +359,12 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     l_run = l_run * corr + l_tile;
     m_run = m_new;
     MT_PROF(6);
-    tc::cp_async_wait<1>();            // V(kt) landed (K(kt+1) may still be in flight)
+    if (use_tma) {
+      tc::mbar_wait(&bar_v, par_v);
+      par_v ^= 1;
+    } else {
+      tc::cp_async_wait<1>();          // V(kt) landed (K(kt+1) may still be in flight)
+    }
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -340,8 +380,15 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a) {
     tc::mbar_wait(&bar_o, phase);
     tc::fence_after_sync();
     MT_PROF(8);
-    if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, a.Sk);   // V is free: next tile
-    tc::cp_async_commit();
+    if (use_tma) {                                                                      // V is free: next tile
+      if (more && tid == 0) {
+        tma::mbar_expect_tx(&bar_v, L::OPER);
+        tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, k0 + TK, 0, h, n);
+      }
+    } else {
+      if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, a.Sk);
+      tc::cp_async_commit();
+    }
     {
       float pv[HC];
 #pragma unroll
@@ -1161,8 +1208,25 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     ++g_tma_fallbacks;
   }
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
-  if (a.Dh == 96) return launch_tc(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL, grid, a, st, 256);
-  return launch_tc(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL, grid, a, st, 256);
+  FwdMtMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  {
+    const bool pre = a.q_rot.p != nullptr;
+    const HeadView* vs[3] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v};
+    const int seq[3] = {a.Sq, a.Sk, a.Sk};
+    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
+    for (int i = 0; i < 3 && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], a.Dh) == 0;
+    maps.use_tma = ok;
+  }
+  auto launch = [&](auto kern, size_t smem) -> int {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    kern<<<grid, 256, smem, st>>>(a, maps);
+    MEANT_LAUNCH_CHECK();
+    return 0;
+  };
+  if (a.Dh == 96) return launch(attn_tc_fwd_kernel<96>, FwdSmem<96>::TOTAL);
+  return launch(attn_tc_fwd_kernel<64>, FwdSmem<64>::TOTAL);
 }
 
 int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
