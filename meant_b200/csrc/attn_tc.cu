@@ -1214,7 +1214,7 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     const bool pre = a.q_rot.p != nullptr;
     const HeadView* vs[3] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v};
     const int seq[3] = {a.Sq, a.Sk, a.Sk};
-    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
+    int ok = getenv("MEANT_MT_NO_TMA") == nullptr && getenv("MEANT_MT_FWD_TMA") != nullptr;   // opt-in until measured
     for (int i = 0; i < 3 && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], a.Dh) == 0;
     maps.use_tma = ok;
   }
