@@ -803,14 +803,17 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   uint4 ov[MODE == 1 ? 8 : 1], gv[MODE == 1 ? 8 : 1];
   auto tile_delta_issue = [&](int q0) {
     const int lane = tid & 31, sub = lane >> 4, c = lane & 15;
+    const __nv_bfloat16* ob = view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, 0, h) + c * 8;   // row 0 of this head
+    const __nv_bfloat16* gb = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, 0, h) + c * 8;
+    const int64_t oss = a.out_saved.ss, gss = a.o.ss;
 #pragma unroll
     for (int it = 0; it < 8; ++it) {
       const int qi = q0 + warp * 16 + it * 2 + sub;
       ov[it] = make_uint4(0u, 0u, 0u, 0u);
       gv[it] = ov[it];
       if (qi < a.Sq && c < DH / 8) {
-        ov[it] = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, qi, h) + c * 8);
-        gv[it] = *reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h) + c * 8);
+        ov[it] = *reinterpret_cast<const uint4*>(ob + qi * oss);
+        gv[it] = *reinterpret_cast<const uint4*>(gb + qi * gss);
       }
     }
   };
@@ -1214,7 +1217,7 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     const bool pre = a.q_rot.p != nullptr;
     const HeadView* vs[3] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v};
     const int seq[3] = {a.Sq, a.Sk, a.Sk};
-    int ok = getenv("MEANT_MT_NO_TMA") == nullptr && getenv("MEANT_MT_FWD_TMA") != nullptr;   // opt-in until measured
+    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
     for (int i = 0; i < 3 && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], a.Dh) == 0;
     maps.use_tma = ok;
   }
