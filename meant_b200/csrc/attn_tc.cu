@@ -102,7 +102,7 @@ template <int DH>
 struct FwdSmem {
   static constexpr uint32_t OPER = (DH / 8) * CS128;       // Q, K or V tile
   static constexpr uint32_t PBUF = (TK / 8) * CS128;       // P tile
-  static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, P = 3 * OPER, TOTAL = 3 * OPER + PBUF;
+  static constexpr uint32_t Q = 0, K = OPER, V = 2 * OPER, P = 3 * OPER, TOTAL = 3 * OPER + PBUF + 1024;   // + alignment slack
 };
 
 // Asynchronous staging (multi-tile kernels, 256 threads): rows [s0, s0+128) of a head view go to the chunk layout
@@ -193,12 +193,14 @@ __device__ __forceinline__ float key_term(const float* mrow, int kj, int Sk) {
 // Tensor maps of the multi-tile forward: q (rotated copy when there is one), k, v as chunk-layout boxes.
 struct FwdMtMaps {
   CUtensorMap m[3];
+  CUtensorMap o[2];     // output as head-view boxes (64 columns SWIZZLE_128B [+ 32 columns SWIZZLE_64B])
   int use_tma;
 };
 
 template <int DH>
 __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const __grid_constant__ FwdMtMaps maps) {
-  extern __shared__ __align__(128) uint8_t smem[];
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzled output boxes: 1024-byte atoms
   __shared__ uint64_t bar_s, bar_o, bar_k, bar_v;   // MMA chains done; TMA: Q|K and V tiles landed
   __shared__ uint32_t tmem_slot;
   __shared__ float kterm[TK];
@@ -404,7 +406,29 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
   xch[hf][t] = l_run;
   __syncthreads();
   l_run += xch[hf ^ 1][t];
-  if (qi < a.Sq) {
+  if (use_tma) {
+    // O leaves through the free P buffer as swizzled sub-tiles and one or two TMA boxes (rows past Sq clipped)
+    const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
+#pragma unroll
+    for (int c0 = 0; c0 < HC; c0 += 8) {
+      uint4 pk;
+      __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+      for (int i = 0; i < 8; i += 2) ph[i >> 1] = __floats2bfloat162_rn(o_acc[c0 + i] * inv, o_acc[c0 + i + 1] * inv);
+      const int ch = (hf * HC + c0) / 8;
+      const uint32_t off = ch < 8 ? tc::sw128_off(t, ch) : 128u * 128u + tc::sw64_off(t, ch - 8);
+      *reinterpret_cast<uint4*>(smem + L::P + off) = pk;
+    }
+    if (qi < a.Sq && a.lse && hf == 0) a.lse[((int64_t)n * a.H + h) * a.Sq + qi] = m_run * LN2 + logf(l_run);
+    tc::fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      tma::store_box(&maps.o[0], tc::smem_u32(smem + L::P), 0, h, q0, 0, n);
+      if (DH > 64) tma::store_box(&maps.o[1], tc::smem_u32(smem + L::P) + 128u * 128u, 64, h, q0, 0, n);
+      tma::store_commit();
+      tma::store_wait_read<0>();
+    }
+  } else if (qi < a.Sq) {
     const float inv = l_run > 0.f ? 1.0f / l_run : 0.f;
     __nv_bfloat16* op = view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, qi, h) + hf * HC;
 #pragma unroll
@@ -1219,6 +1243,8 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     const int seq[3] = {a.Sq, a.Sk, a.Sk};
     int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
     for (int i = 0; i < 3 && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], a.Dh) == 0;
+    if (ok) ok = tma::make_head_map(&maps.o[0], a.o, a.N, a.n2_count, a.H, a.Sq, a.Dh, 64) == 0;
+    if (ok && a.Dh > 64) ok = tma::make_head_map(&maps.o[1], a.o, a.N, a.n2_count, a.H, a.Sq, a.Dh, 32) == 0;
     maps.use_tma = ok;
   }
   auto launch = [&](auto kern, size_t smem) -> int {
