@@ -1124,8 +1124,8 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
 }
 
 // ------------------------------------------------------------------------------------ pre-rotation
-// q -> q_rot (blockIdx.y = 0) and k -> k_rot (blockIdx.y = 1): one thread per 16-byte chunk, chunks of a packed
-// row contiguous across the warp.  HBM-bound: reads and writes Q and K once.
+// q -> q_rot (blockIdx.y = 0) and k -> k_rot (blockIdx.y = 1) in 16-byte chunks, chunks of a head's row contiguous
+// across the warp.  HBM-bound: reads and writes Q and K once.
 __global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
   const bool isk = blockIdx.y != 0;
   const HeadView& src = isk ? a.k : a.q;
@@ -1133,6 +1133,40 @@ __global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
   const float* __restrict__ cs = isk ? a.kcos : a.qcos;
   const float* __restrict__ sn = isk ? a.ksin : a.qsin;
   const int S = isk ? a.Sk : a.Sq, cpr = a.Dh >> 3;
+  if (!a.pos_is_head) {
+    // Token-position tables do not depend on the head: a thread owns (row, chunk), fetches its 64 bytes of table
+    // values ONCE and walks the heads (table traffic through L1 was 4x the payload with a thread per head chunk).
+    const int64_t total = (int64_t)a.N * S * cpr;
+    for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+      const int ch = (int)(idx % cpr);
+      const int64_t row = idx / cpr;
+      const int sr = (int)(row % S), n = (int)(row / S);
+      const __nv_bfloat16* sp = view_ptr<__nv_bfloat16>(src, n, a.n2_count, sr, 0) + ch * 8;
+      __nv_bfloat16* dp = view_ptr<__nv_bfloat16>(dst, n, a.n2_count, sr, 0) + ch * 8;
+      const bool rot = ch * 8 < a.rot_dim;
+      float4 ca, cb, sa, sb;
+      if (rot) {
+        const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)sr * a.rot_dim + ch * 8);
+        const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)sr * a.rot_dim + ch * 8);
+        ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
+      }
+#pragma unroll 4
+      for (int h = 0; h < a.H; ++h) {
+        uint4 raw = *reinterpret_cast<const uint4*>(sp + (int64_t)h * src.sh);
+        if (rot) {
+          __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw);
+          const float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+          const float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+          h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+          h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+          h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+          h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+        }
+        *reinterpret_cast<uint4*>(dp + (int64_t)h * dst.sh) = raw;
+      }
+    }
+    return;
+  }
   const int64_t total = (int64_t)a.N * S * a.H * cpr;
   for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
     const int ch = (int)(idx % cpr);
