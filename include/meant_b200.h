@@ -40,7 +40,8 @@ void meant_reset_launch_count(void);
  * Fused neighbours (all optional):
  *   res/sum_out : s = x + res is normalised and also written to sum_out
  *                 (meant/meant.py:116,120 residual adds feeding encode2[0] / the next block)
- *   pre_gelu    : s = gelu(x), exact erf form (meant/meant.py:107 GELU -> RMSNorm)
+ *   pre_gelu    : s = gelu(x), exact erf form (meant/meant.py:107 GELU -> RMSNorm); not together with
+ *                 res (MEANT_EARG): the backward keeps one tensor and could not split the two gradients
  *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107);
  *                 seed_dev (optional, device memory) is added to seed when the kernel runs, so a
  *                 captured CUDA graph draws a fresh mask on every replay

@@ -418,6 +418,8 @@ extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* ga
                                  float* rinv, int64_t rows, int d, float eps, int pre_gelu, float drop_p,
                                  uint64_t seed, const uint64_t* seed_dev, int dtype, cudaStream_t stream) {
   if (!x || !gain || !y || !rinv || rows < 0 || d <= 0 || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
+  // gelu(x) + res: the backward keeps only the sum and could not separate the two gradients (no caller needs it)
+  if (pre_gelu && res) return MEANT_EARG;
   if (rows == 0) return 0;
   NormArgs a{x, res, gain, nullptr, y, sum_out, rinv, nullptr, rows, d, eps, pre_gelu,
              drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
@@ -432,6 +434,7 @@ extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* g
                                  int pre_gelu, float drop_p, uint64_t seed, const uint64_t* seed_dev, float* dxsum,
                                  int dtype, cudaStream_t stream) {
   if (!dy || !src || !gain || !rinv || !dx || !dgain || rows < 0 || d <= 0) return MEANT_EARG;
+  if (pre_gelu && dsum_in) return MEANT_EARG;   // see meant_rmsnorm_fwd
   if (rows == 0) return 0;
   NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, dxsum, rows, d, eps, pre_gelu,
                 drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,

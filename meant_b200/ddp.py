@@ -41,6 +41,7 @@ class BucketedGradAllReduce:
         if cur:
             self._seal(cur, grad_dtype)
         self._pending = [len(ps) for _, ps in self.buckets]
+        self._next = 0             # first bucket not yet handed to the communicator this step
         self._hooks = [p.register_post_accumulate_grad_hook(self._on_grad) for p in self.params]
 
     def _seal(self, ps, grad_dtype):
@@ -62,10 +63,14 @@ class BucketedGradAllReduce:
             p.grad = None
         self._pending = [len(ps) for _, ps in self.buckets]
         self._handles = []
+        self._next = 0
 
     def _reduce(self, b):
-        """Pack bucket b (parameters without a gradient this step contribute zeros and keep .grad = None
-        only if no rank produced one -- every rank must see the same set), then all-reduce it."""
+        """Pack bucket b and all-reduce it.  A parameter without a local gradient this step contributes zeros
+        -- the correct term of the average when another rank did produce one -- and EVERY parameter of the
+        bucket ends up with .grad = its reduced slice, so all ranks hand the optimizer the same gradients and the
+        replicas cannot drift apart (a parameter no rank used gets an all-zero gradient, as under
+        torch's DistributedDataParallel)."""
         flat, ps = self.buckets[b]
         views = self._views[b]
         have = [(v, p) for v, p in zip(views, ps) if p.grad is not None]
@@ -73,7 +78,7 @@ class BucketedGradAllReduce:
             flat.zero_()
         if have:
             torch._foreach_copy_([v for v, _ in have], [p.grad for _, p in have])
-        for v, p in have:
+        for v, p in zip(views, ps):
             p.grad = v
         if flat.is_cuda:
             self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
@@ -84,17 +89,27 @@ class BucketedGradAllReduce:
     def _on_grad(self, p):
         b = self._bucket_of[p]
         self._pending[b] -= 1
+        if self._pending[b] < 0:
+            # a second backward() before zero_grad(): the bucket was already reduced, the new micro-batch would
+            # accumulate locally and never be exchanged
+            raise RuntimeError("BucketedGradAllReduce: a parameter received a second gradient before zero_grad(); "
+                               "gradient accumulation over several backward passes is not supported -- call "
+                               "zero_grad() between them")
         if self._pending[b] == 0 and self.world > 1:
-            self._reduce(b)
+            # collectives are issued in bucket order on every rank (a bucket that completes early waits for its
+            # predecessors), so a rank on which some parameter got no gradient cannot reorder them
+            while self._next < len(self.buckets) and self._pending[self._next] == 0:
+                self._reduce(self._next)
+                self._next += 1
 
     def finish(self):
         """Wait for every bucket; buckets some of whose parameters got no gradient this step are reduced
         here so that all ranks issue the same collectives."""
         if self.world > 1:
-            for b, left in enumerate(self._pending):
-                if left > 0:
-                    self._reduce(b)
-                    self._pending[b] = 0
+            while self._next < len(self.buckets):
+                self._reduce(self._next)
+                self._pending[self._next] = 0
+                self._next += 1
         for h in self._handles:
             h.wait()
         self._handles = []

@@ -148,6 +148,9 @@ def rms_norm(x, gain, eps=1e-8, residual=None, pre_gelu=False, drop_p=0.0):
     """y = gain * s / (rms(s) + eps), s = gelu?(x) (+ residual); returns y, or (y, s) when a
     residual is given.  drop_p > 0 applies inverted dropout to y (training only: the caller
     passes 0 in eval mode)."""
+    if pre_gelu and residual is not None:
+        raise ValueError("rms_norm: pre_gelu together with a residual is not supported (the backward keeps only the "
+                         "sum, so the gradients of x and of the residual could not be separated)")
     seed = _seed() if drop_p > 0.0 else 0
     return _RMSNormFn.apply(x, residual, gain, float(eps), bool(pre_gelu), float(drop_p), seed)
 
@@ -334,6 +337,9 @@ def embed(mod, ids):
     if type(mod) is torch.nn.Embedding and mod.padding_idx is None and mod.max_norm is None and not mod.sparse \
             and not mod.scale_grad_by_freq and w.is_cuda and w.dtype == torch.float32 and w.shape[1] % 8 == 0 \
             and w.is_contiguous() and ids.dtype == torch.int64:
+        if ids.device != w.device:
+            # nn.Embedding raises for this too; a host pointer must never reach the gather kernel
+            raise RuntimeError(f"embed: token ids are on {ids.device} but the embedding table is on {w.device}")
         return _EmbeddingFn.apply(ids, w, compute_dtype(w))
     return mod(ids)
 

@@ -26,9 +26,18 @@ CASES = [
     ("temporal_768_l24", "temporal", dict(b=2, lag=24, dim=768, heads=8)),
     ("temporal_src_768_l5", "temporal_src", dict(b=3, lag=5, dim=768, heads=8)),
     ("temporal_src_772_l5", "temporal_src", dict(b=2, lag=5, dim=772, heads=8)),
+    # ---- flash variants (meant/xPosAttention_flash.py, meant/flash_attention.py): head-index rotary.  Goldens come from
+    #      the unmodified reference MODULES with the third-party flash_attn_func replaced by its published definition
+    #      (oracle/gen_golden.py:flash_attn stub): the kernel of flash-attn 2.5.2 itself stays parity-unpinned.
+    ("xpos_flash_s128", "xpos_flash", dict(b=2, s=128, dim=768, heads=8)),
+    ("xpos_flash_s200", "xpos_flash", dict(b=1, s=200, dim=768, heads=8)),
+    ("pixel_flash_n196", "pixel_flash", dict(b=2, s=196, dim=768, heads=8)),
+    ("pixel_flash_n50", "pixel_flash", dict(b=1, s=50, dim=768, heads=8)),
     # ---- encoder blocks (meant/meant.py:35-145)
     ("lang_enc_s128", "lang_enc", dict(b=2, s=128, dim=768, heads=8, mask=True)),
     ("vis_enc_n196", "vis_enc", dict(b=1, s=196, dim=768, heads=8)),
+    ("lang_enc_flash_s128", "lang_enc", dict(b=2, s=128, dim=768, heads=8, mask=False, flash=True)),
+    ("vis_enc_flash_n196", "vis_enc", dict(b=1, s=196, dim=768, heads=8, flash=True)),
     ("temp_enc_1536_l5", "temp_enc", dict(b=3, lag=5, dim=1536, heads=8, normed=True)),
     ("temp_enc_768_l12", "temp_enc", dict(b=2, lag=12, dim=768, heads=8, normed=False)),
     # ---- model assemblies
@@ -38,10 +47,15 @@ CASES = [
     ("meant_vision_l12", "meant_vision", dict(b=1, lag=12, c=4, hw=224, enc=1)),
     ("meant_vqa_s40", "meant_vqa", dict(b=2, s=40, c=4, hw=224, enc=1, mask=True)),
     ("lang_pretrainer_s512", "lang_pretrainer", dict(b=1, s=512, enc=2, mask=True)),
+    # ---- the depth and sizes the bench runs (BASELINE.json configs[1..4]) at b=1
+    ("meant_tweet_l12_12enc", "meant_tweet", dict(b=1, lag=12, s=128, enc=12)),
+    ("meant_l24", "meant", dict(b=1, lag=24, s=128, c=4, hw=224, enc=1, mask=True)),
+    ("lang_pretrainer_s512_12enc", "lang_pretrainer", dict(b=1, s=512, enc=12, mask=True)),
     # ---- TimeSformer divided space-time path (src/meant/timesformer_pytorch.py)
     ("timesformer_f5", "timesformer", dict(b=1, f=5, hw=224, depth=1, shift=False)),
     ("timesformer_f12_small", "timesformer", dict(b=1, f=12, hw=64, depth=1, shift=False)),
     ("timesformer_shift_small", "timesformer", dict(b=2, f=3, hw=32, depth=2, shift=True)),
+    ("timesformer_f12_224", "timesformer", dict(b=1, f=12, hw=224, depth=1, shift=False)),
 ]
 
 CASE_BY_NAME = {c[0]: c for c in CASES}
@@ -57,7 +71,7 @@ def make_inputs(name, kind, cfg):
         if cfg["mask"]:
             d["attention_mask"] = detfill.padding_mask(cfg["b"], cfg["s"], name + "/mask")
         return d
-    if kind in ("pixel", "vis_enc"):
+    if kind in ("pixel", "vis_enc", "xpos_flash", "pixel_flash"):
         return dict(x=u((cfg["b"], cfg["s"], cfg["dim"]), name + "/x", 1.0))
     if kind in ("temporal", "temporal_src", "temp_enc"):
         return dict(x=u((cfg["b"], cfg["lag"], cfg["dim"]), name + "/x", 1.0))

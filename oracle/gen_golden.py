@@ -12,7 +12,16 @@ Shims (nothing under /root/reference is edited):
     (utils/__init__.py imports torchmetrics, which is missing);
   * stub torchmetrics / seaborn / matplotlib for the `src` tree;
   * meant_tweet's languageEncoder is replaced by meant.meant.languageEncoder
-    (meant/meant_tweet.py:81 returns the undefined `final_resi`).
+    (meant/meant_tweet.py:81 returns the undefined `final_resi`);
+  * `flash_attn` (third party, CUDA only: flash-attn==2.5.2) is replaced by a stub whose
+    flash_attn_func is the published definition of that call (softmax(scale q k^T [+ causal]) v on
+    `b s h d` tensors, scale default d^-1/2, fp32 accumulation).  The reference MODULES that call it
+    (meant/xPosAttention_flash.py, meant/flash_attention.py) run unmodified, so their projections,
+    head-index rotary quirk and scale choices are pinned; the flash-attn kernel itself is not.
+    The stub returns fp32 even for the fp16 inputs meant/flash_attention.py:42 hands it, because the
+    fp32 `multi_mad` that follows only accepts fp16 under CUDA autocast;
+  * `meant.meant.ampere = True` while a flash=True encoder is constructed (meant/meant.py:22-25 gates the
+    flash classes on the CUDA device name; there is no device here).
 """
 import importlib.util
 import json
@@ -26,7 +35,27 @@ import torch
 REF = "/root/reference"
 
 
+def _flash_attn_func(q, k, v, dropout_p=0.0, softmax_scale=None, causal=False, window_size=(-1, -1),
+                     alibi_slopes=None, deterministic=False, **kw):
+    """flash_attn.flash_attn_func as published (flash_attn_interface.py docstring): q, k, v are
+    (batch, seqlen, nheads, headdim); softmax_scale defaults to headdim^-1/2; causal masks key j > query i
+    (equal lengths); accumulation in fp32."""
+    assert dropout_p == 0.0 and tuple(window_size) == (-1, -1) and alibi_slopes is None
+    qf, kf, vf = (t.float().transpose(1, 2) for t in (q, k, v))
+    scale = qf.shape[-1] ** -0.5 if softmax_scale is None else softmax_scale
+    scores = torch.matmul(qf, kf.transpose(-1, -2)) * scale
+    if causal:
+        sq, sk = scores.shape[-2:]
+        scores = scores.masked_fill(~torch.ones(sq, sk, dtype=torch.bool).tril(), float("-inf"))
+    return torch.matmul(torch.softmax(scores, dim=-1), vf).transpose(1, 2)
+
+
 def install_shims():
+    fa = types.ModuleType("flash_attn")
+    fa.__path__ = []
+    fa.flash_attn_func = _flash_attn_func
+    fa.flash_attn_qkvpacked_func = None
+    sys.modules["flash_attn"] = fa
     for m in ("torchmetrics", "seaborn", "matplotlib", "matplotlib.pyplot"):
         if m not in sys.modules:
             stub = types.ModuleType(m)
@@ -60,16 +89,30 @@ def build_reference(kind, cfg, RMSNorm):
     if kind == "pixel":
         pe = RotaryEmbedding(dim=cfg["dim"] // cfg["heads"] // 2, freqs_for="pixel")
         return ref.attention(cfg["heads"], cfg["dim"], pe), lambda m, i: m(i["x"])
+    if kind == "xpos_flash":
+        m = ref.xPosAttention_flash(cfg["heads"], cfg["dim"], RotaryEmbedding(dim=48, use_xpos=True))
+        return m, lambda m, i: m(i["x"])
+    if kind == "pixel_flash":
+        pe = RotaryEmbedding(dim=cfg["dim"] // cfg["heads"] // 2, freqs_for="pixel")
+        return ref.flash_attention(cfg["heads"], cfg["dim"], pe), lambda m, i: m(i["x"])
     if kind == "temporal":
         return ref.temporal(cfg["heads"], cfg["dim"]), lambda m, i: m(i["x"])
     if kind == "temporal_src":
         from src.meant.temporal import temporal as t_src
         return t_src(cfg["heads"], cfg["dim"]), lambda m, i: m(i["x"])
-    if kind == "lang_enc":
-        return ref.languageEncoder(cfg["dim"], cfg["heads"]), \
-            lambda m, i: m(i["x"], i.get("attention_mask"))
-    if kind == "vis_enc":
-        return ref.visionEncoder(cfg["dim"], cfg["heads"]), lambda m, i: m(i["x"])
+    if kind in ("lang_enc", "vis_enc"):
+        flash = bool(cfg.get("flash"))
+        sys.modules["meant.meant"].ampere = flash       # device-name gate of meant/meant.py:22-25
+        try:
+            if kind == "lang_enc":
+                m = ref.languageEncoder(cfg["dim"], cfg["heads"], flash=flash)
+                assert type(m.encode[2]).__name__ == ("xPosAttention_flash" if flash else "xPosAttention")
+                return m, lambda m, i: m(i["x"], i.get("attention_mask"))
+            m = ref.visionEncoder(cfg["dim"], cfg["heads"], flash=flash)
+            assert type(m.encode[2]).__name__ == ("flash_attention" if flash else "attention")
+            return m, lambda m, i: m(i["x"])
+        finally:
+            sys.modules["meant.meant"].ampere = False
     if kind == "temp_enc":
         mm, mv = sys.modules["meant.meant"], sys.modules["meant.meant_vision"]
         cls = mm.temporalEncoder if cfg["normed"] else mv.temporalEncoder

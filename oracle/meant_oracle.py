@@ -121,9 +121,10 @@ def pixel_attention(p, prefix, x, heads):
 
 
 def xpos_attention_flash(p, prefix, x, heads, causal=True):
-    """meant/xPosAttention_flash.py:35-45 -- PARITY UNPINNED (flash-attn 2.5.2 is CUDA
-    only).  Tensors are `b s h d`, so the rotary position is the head index; the softmax
-    scale is Dh^-1/2 (softmax_scale=None); no padding mask."""
+    """meant/xPosAttention_flash.py:35-45.  Tensors are `b s h d`, so the rotary position is the
+    head index; the softmax scale is Dh^-1/2 (softmax_scale=None); no padding mask.  Pinned to the
+    unmodified reference module with flash_attn_func replaced by its published definition
+    (oracle/gen_golden.py); the flash-attn 2.5.2 CUDA kernel itself stays PARITY UNPINNED."""
     b, s, dim = x.shape
     dh = dim // heads
     q = lin(p, prefix + ".q", x).view(b, s, heads, dh)
@@ -135,14 +136,16 @@ def xpos_attention_flash(p, prefix, x, heads, causal=True):
     return lin(p, prefix + ".multi_mad", merge_heads(o))
 
 
-def flash_attention(p, prefix, x, heads):
-    """meant/flash_attention.py:35-47 -- PARITY UNPINNED.  Head-index pixel rotary,
-    scale 1/dim, non-causal (the .half() casts are not restated: fp32 oracle)."""
+def flash_attention(p, prefix, x, heads, half_inputs=True):
+    """meant/flash_attention.py:35-47.  Head-index pixel rotary, scale 1/dim, non-causal; q, k, v are
+    rounded to fp16 before the attention core (`.half()`, :42) when half_inputs is set (the pinned
+    form; the flash-attn kernel itself stays PARITY UNPINNED, see xpos_attention_flash)."""
     b, s, dim = x.shape
     dh = dim // heads
-    q = plain_rotate(p, prefix + ".pos_emb", lin(p, prefix + ".q", x).view(b, s, heads, dh))
-    k = plain_rotate(p, prefix + ".pos_emb", lin(p, prefix + ".v", x).view(b, s, heads, dh))
-    v = lin(p, prefix + ".k", x).view(b, s, heads, dh)
+    rnd = (lambda t: t.half().float()) if half_inputs else (lambda t: t)
+    q = rnd(plain_rotate(p, prefix + ".pos_emb", lin(p, prefix + ".q", x).view(b, s, heads, dh)))
+    k = rnd(plain_rotate(p, prefix + ".pos_emb", lin(p, prefix + ".v", x).view(b, s, heads, dh)))
+    v = rnd(lin(p, prefix + ".k", x).view(b, s, heads, dh))
     o = softmax_attention(q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2), 1.0 / dim)
     return lin(p, prefix + ".multi_mad", merge_heads(o))
 

@@ -38,14 +38,18 @@ def oracle_forward(kind, cfg, p, inp):
         return mo.xpos_attention(p, "", inp["x"], h, inp.get("attention_mask"))
     if kind == "pixel":
         return mo.pixel_attention(p, "", inp["x"], h)
+    if kind == "xpos_flash":
+        return mo.xpos_attention_flash(p, "", inp["x"], h)
+    if kind == "pixel_flash":
+        return mo.flash_attention(p, "", inp["x"], h, half_inputs=cfg.get("half_inputs", True))
     if kind == "temporal":
         return mo.temporal_attention(p, "", inp["x"], h)
     if kind == "temporal_src":
         return to.temporal_attention_src(p, "", inp["x"], h)
     if kind == "lang_enc":
-        return mm.language_encoder(p, "", inp["x"], h, inp.get("attention_mask"))
+        return mm.language_encoder(p, "", inp["x"], h, inp.get("attention_mask"), flash=bool(cfg.get("flash")))
     if kind == "vis_enc":
-        return mm.vision_encoder(p, "", inp["x"], h)
+        return mm.vision_encoder(p, "", inp["x"], h, flash=bool(cfg.get("flash")))
     if kind == "temp_enc":
         return mm.temporal_encoder(p, "", inp["x"], h, cfg["normed"])
     if kind == "meant":
@@ -69,11 +73,13 @@ def _strip(p):
     return {"." + k: v for k, v in p.items()} | dict(p)
 
 
-def run_case(name, manifest=None, data=None, want_grads=True):
+def run_case(name, manifest=None, data=None, want_grads=True, cfg_override=None):
     """-> (out, {param key: grad}, {input name: grad}, state dict, inputs)."""
     if manifest is None:
         manifest, data = load_golden()
     _, kind, cfg = cases.CASE_BY_NAME[name]
+    if cfg_override:
+        cfg = dict(cfg, **cfg_override)
     sd = state_from_manifest(name, manifest, data)
     inp = cases.make_inputs(name, kind, cfg)
     leaves = {}

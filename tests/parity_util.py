@@ -17,14 +17,21 @@ def build_module(kind, cfg):
     if kind == "pixel":
         pe = mb.RotaryEmbedding(dim=cfg["dim"] // cfg["heads"] // 2, freqs_for="pixel")
         return mb.attention(cfg["heads"], cfg["dim"], pe), lambda m, i: m(i["x"])
+    if kind == "xpos_flash":
+        m = mb.xPosAttention_flash(cfg["heads"], cfg["dim"], mb.RotaryEmbedding(dim=48, use_xpos=True))
+        return m, lambda m, i: m(i["x"])
+    if kind == "pixel_flash":
+        pe = mb.RotaryEmbedding(dim=cfg["dim"] // cfg["heads"] // 2, freqs_for="pixel")
+        return mb.flash_attention(cfg["heads"], cfg["dim"], pe), lambda m, i: m(i["x"])
     if kind == "temporal":
         return mb.temporal(cfg["heads"], cfg["dim"]), lambda m, i: m(i["x"])
     if kind == "temporal_src":
         return mb.temporal_src(cfg["heads"], cfg["dim"]), lambda m, i: m(i["x"])
     if kind == "lang_enc":
-        return mb.languageEncoder(cfg["dim"], cfg["heads"]), lambda m, i: m(i["x"], i.get("attention_mask"))
+        return mb.languageEncoder(cfg["dim"], cfg["heads"], flash=bool(cfg.get("flash"))), \
+            lambda m, i: m(i["x"], i.get("attention_mask"))
     if kind == "vis_enc":
-        return mb.visionEncoder(cfg["dim"], cfg["heads"]), lambda m, i: m(i["x"])
+        return mb.visionEncoder(cfg["dim"], cfg["heads"], flash=bool(cfg.get("flash"))), lambda m, i: m(i["x"])
     if kind == "temp_enc":
         if cfg["normed"]:
             return mb.temporalEncoder(cfg["dim"], cfg["heads"], cfg["lag"]), lambda m, i: m(i["x"])
@@ -87,10 +94,12 @@ def cosine(a, b):
     return float(torch.dot(a, b) / (na * nb).clamp_min(1e-300))
 
 
-def compare_grads(mine, ref, min_cos=0.999, what=""):
-    """Per-tensor gradient check.  Tensors whose true gradient is (numerically) zero -- e.g. the
-    key bias of single-query softmax attention, which shifts every score equally -- are noise
-    in both implementations: for those only the magnitude is bounded."""
+def compare_grads(mine, ref, min_cos=0.999, what="", norm_tol=None):
+    """Per-tensor gradient check: cosine >= min_cos AND (norm_tol given) | |mine| / |ref| - 1 | <= norm_tol, so a
+    uniform scale error (a wrong dropout keep-scale, a missing 1/world, a mis-folded softmax scale) cannot pass.
+    Tensors whose true gradient is (numerically) zero -- e.g. the key bias of single-query softmax attention,
+    which shifts every score equally -- are noise in both implementations: for those only the magnitude is
+    bounded."""
     top = max(float(g.norm()) for g in ref.values()) if ref else 0.0
     worst = 1.0
     for k, g in ref.items():
@@ -102,4 +111,7 @@ def compare_grads(mine, ref, min_cos=0.999, what=""):
         c = cosine(mine[k], g)
         worst = min(worst, c)
         assert c >= min_cos, f"{what}: grad cosine {k}: {c}"
+        if norm_tol is not None:
+            ratio = float(mine[k].double().norm()) / gn
+            assert abs(ratio - 1.0) <= norm_tol, f"{what}: grad norm ratio {k}: {ratio}"
     return worst

@@ -56,7 +56,8 @@ def _worker(rank, world, port, steps, out):
         n = x.shape[0] // world
         xs, ys = x[rank * n:(rank + 1) * n], y[rank * n:(rank + 1) * n]
         losses = [float(step(ys, xs)) for _ in range(steps)]
-        assert model.unused.weight.grad is None
+        # a parameter no rank used still gets the (all-zero) reduced slice: every rank hands the optimizer the same set
+        assert model.unused.weight.grad is not None and float(model.unused.weight.grad.abs().max()) == 0.0
         out[rank] = ([p.detach().clone() for p in model.parameters()], losses)
     finally:
         dist.destroy_process_group()
@@ -81,6 +82,63 @@ def test_two_ranks_match_single_process():
         assert torch.allclose(a, r, atol=1e-6, rtol=1e-5)          # and follow the single-process trajectory
     for k in range(steps):
         assert abs(0.5 * (l0[k] + l1[k]) - ref_losses[k]) < 1e-5
+
+
+class BranchNet(nn.Module):
+    """`extra` is used by rank 0 only (data-dependent control flow): its gradient exists on one rank."""
+
+    def __init__(self):
+        super().__init__()
+        self.a = nn.Linear(12, 16)
+        self.extra = nn.Linear(12, 16)
+        self.head = nn.Linear(16, 3)
+
+    def forward(self, x, use_extra):
+        h = torch.tanh(self.a(x))
+        if use_extra:
+            h = h + torch.tanh(self.extra(x))
+        return self.head(h)
+
+
+def _branch_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        model = BranchNet()
+        red = BucketedGradAllReduce(list(model.parameters()), bucket_mb=0.0005)
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.0)
+        x, y = _data()
+        n = x.shape[0] // world
+        for _ in range(2):
+            red.zero_grad()
+            nn.functional.cross_entropy(model(x[rank * n:(rank + 1) * n], rank == 0), y[rank * n:(rank + 1) * n]).backward()
+            red.finish()
+            assert model.extra.weight.grad is not None            # also on the rank that never ran `extra`
+            opt.step()
+        # a second backward without zero_grad must not silently skip the exchange
+        raised = False
+        try:
+            nn.functional.cross_entropy(model(x[:2], True), y[:2]).backward()
+        except RuntimeError as e:
+            raised = "zero_grad" in str(e)
+        out[rank] = ([p.detach().clone() for p in model.parameters()], raised)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_parameter_used_on_one_rank_only_stays_in_sync():
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_branch_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    (p0, r0), (p1, r1) = out[0], out[1]
+    assert r0 and r1
+    torch.manual_seed(0)
+    init = [p.detach().clone() for p in BranchNet().parameters()]
+    for a, b in zip(p0, p1):
+        assert torch.equal(a, b)                                   # replicas identical although one rank skipped `extra`
+    assert not torch.equal(p0[2], init[2])                         # and `extra.weight` did move on both
 
 
 def test_single_rank_keeps_autograd_gradients():
