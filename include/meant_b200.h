@@ -32,7 +32,7 @@ enum { MEANT_F32 = 0, MEANT_BF16 = 1 };
 enum { MEANT_IMPL_AUTO = 0, MEANT_IMPL_EXACT = 1, MEANT_IMPL_TCGEN05 = 2 };
 
 /* ---- library ------------------------------------------------------------------------- */
-int meant_version(void);                 /* ABI version (4), bumped on any signature change */
+int meant_version(void);                 /* ABI version (5), bumped on any signature change */
 int64_t meant_launch_count(void);        /* kernels launched by this library so far       */
 void meant_reset_launch_count(void);
 
@@ -75,8 +75,9 @@ int meant_layernorm_bwd(const void* dy, const void* x, const float* gain, const 
  *
  * A head view addresses element (n, s, h, d) at  p + n1*sn1 + n2*sn2 + s*ss + h*sh + d  with
  * n = n1*n2_count + n2 and strides in ELEMENTS, so `b s (h d)` projections, a fused
- * [tokens, 3*dim] QKV buffer and the TimeSformer '(b n) f d' / '(b f) n d' groups are all
- * read in place -- no rearranged copy is ever made.                                        */
+ * [tokens, 3*dim] QKV buffer and the TimeSformer '(b n) f d' / '(b f) n d' groups
+ * (src/meant/timesformer_pytorch.py:122: n1 = b, n2 = patch or frame) are all read and written in
+ * place: meant_b200/timesformer_pytorch.py passes such views, no rearranged copy is made.   */
 typedef struct {
   void* p;
   int64_t sn1, sn2, ss, sh;
@@ -100,6 +101,16 @@ typedef struct {
   meant_head_view q_rot, k_rot; /* optional (p != NULL): Rq q and Rk k written by meant_attn_prerotate; the
                                  * multi-tile kernels (Sq or Sk > 128) then read these instead of rotating every
                                  * tile on the way in (a K tile is needed by every query tile)              */
+  /* Shared extra key/value row -- the TimeSformer cls token, which every time / space group attends to
+   * un-rotated (src/meant/timesformer_pytorch.py:125-133; the reference `repeat`s and `cat`s it).  With
+   * kx.p != NULL the LAST key (index Sk-1) of every sequence n = n1*n2_count + n2 is the row kx / vx (n1, h, :)
+   * at p + n1*sn1 + h*sh (sn2, ss ignored) and k / v hold the other Sk-1 rows; the rotary tables still have Sk
+   * rows (row Sk-1 is not applied).  Backward: the gradient of that row, summed over the n2_count sequences
+   * sharing it, is ACCUMULATED atomically into dkx / dvx: fp32 [N / n2_count, H, Dh], zero on entry.
+   * Not combined with causal, key_mask, pos_is_head or q_rot / k_rot.                                       */
+  meant_head_view kx, vx;
+  float* dkx;
+  float* dvx;
 } meant_attn_args;
 
 /* Rotates q -> q_rot and k -> k_rot (caller-owned buffers, any head-view strides) with the qcos.. tables of `args`:
@@ -114,6 +125,16 @@ int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int bac
 /* diagnostics: single-tile (Sq, Sk <= 128) calls whose views the TMA tensor maps could not describe and that
  * therefore ran on the multi-tile kernels (0 on every path the models use)                   */
 int64_t meant_attn_tma_fallbacks(void);
+
+/* ---- single-query attention (Sq = 1): temporal.forward (meant/temporal.py:43-58: the target day over the lag
+ *      window) and the TimeSformer cls query, which sees every token (src/meant/timesformer_pytorch.py:116-119).
+ *      No rotation, no masks.  The keys are split into chunks of 64 across CTAs: `partial` is caller-owned scratch,
+ *      fp32 [N, H, ceil(Sk/64), Dh + 2]; forward = partial pass + merge (2 launches), writes o (1 row) and lse.
+ *      Backward reads q, k, v, dO (args->o), out_saved, lse; writes dq (1 row; via `partial`, fp32 [N, H, Dh], zero
+ *      on entry) and dk, dv for every key -- ADDED to what dk / dv already hold when accumulate != 0 (the keys
+ *      also receive gradients from the group attention of the same module).                                   */
+int meant_attn_q1_fwd(const meant_attn_args* args, float* partial, int dtype, meant_stream_t stream);
+int meant_attn_q1_bwd(const meant_attn_args* args, float* partial, int accumulate, int dtype, meant_stream_t stream);
 
 /* ---- mean over the token axis: meant/meant.py:231, meant/meant_tweet.py:157 ------------- */
 int meant_meanpool_fwd(const void* x, void* y, int64_t N, int S, int D, int dtype, meant_stream_t stream);

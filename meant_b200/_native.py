@@ -28,7 +28,8 @@ class AttnArgs(C.Structure):
                 ("key_mask", vp),
                 ("N", i32), ("n2_count", i32), ("H", i32), ("Sq", i32), ("Sk", i32), ("Dh", i32),
                 ("rot_dim", i32), ("pos_is_head", i32), ("causal", i32), ("scale", f32),
-                ("q_rot", HeadView), ("k_rot", HeadView)]
+                ("q_rot", HeadView), ("k_rot", HeadView),
+                ("kx", HeadView), ("vx", HeadView), ("dkx", vp), ("dvx", vp)]
 
 
 # name -> (restype, argtypes); mirrors include/meant_b200.h one to one
@@ -49,6 +50,8 @@ SIGNATURES = {
     "meant_attn_tcgen05_supported": (i32, [C.POINTER(AttnArgs), i32, i32]),
     "meant_attn_prerotate": (i32, [C.POINTER(AttnArgs), i32, vp]),
     "meant_attn_tma_fallbacks": (i64, []),
+    "meant_attn_q1_fwd": (i32, [C.POINTER(AttnArgs), vp, i32, vp]),
+    "meant_attn_q1_bwd": (i32, [C.POINTER(AttnArgs), vp, i32, i32, vp]),
     "meant_meanpool_fwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_meanpool_bwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_geglu_fwd": (i32, [vp, vp, i64, i32, i32, vp]),
@@ -61,7 +64,7 @@ SIGNATURES = {
 _lib = None
 
 
-ABI_VERSION = 4   # include/meant_b200.h: meant_version()
+ABI_VERSION = 5   # include/meant_b200.h: meant_version()
 
 
 def lib():

@@ -13,16 +13,27 @@ constexpr int QT = 16;   // query rows per CTA (2 per warp, 8 warps)
 constexpr int BK = 32;   // keys per shared-memory tile (one per lane)
 constexpr int MAXDL = 8; // Dh <= 256
 
+// xv (optional, p != NULL): the shared extra row (meant_attn_args.kx / vx) that stands for row S-1, un-rotated
+template <typename T>
+__device__ __forceinline__ const T* xrow_ptr(const HeadView& xv, int n, int n2c, int h) {
+  return static_cast<const T*>(xv.p) + (int64_t)(n / n2c) * xv.sn1 + (int64_t)h * xv.sh;
+}
+
 template <typename T>
 __device__ __forceinline__ void load_tile(float* dst, int DhP, const HeadView& v, int n, int n2c, int h, int s0,
                                           int R, int S, int Dh, const float* c, const float* s, int rot_dim,
-                                          int pos_is_head, float mul) {
+                                          int pos_is_head, float mul, const HeadView* xv = nullptr) {
   const int half = Dh >> 1;
+  const bool has_x = xv != nullptr && xv->p != nullptr;
   for (int idx = threadIdx.x; idx < R * half; idx += blockDim.x) {
     const int r = idx / half, d0 = (idx - r * half) * 2;
     const int srow = s0 + r;
     float x0 = 0.f, x1 = 0.f;
-    if (srow < S) {
+    if (has_x && srow == S - 1) {
+      const T* p = xrow_ptr<T>(*xv, n, n2c, h) + d0;
+      x0 = to_f(p[0]) * mul;
+      x1 = to_f(p[1]) * mul;
+    } else if (srow < S) {
       const T* p = view_ptr<T>(v, n, n2c, srow, h) + d0;
       x0 = to_f(p[0]);
       x1 = to_f(p[1]);
@@ -64,8 +75,8 @@ __global__ void __launch_bounds__(256) attn_exact_fwd_kernel(AttnArgs a) {
   for (int kt = 0; kt < n_tiles; ++kt) {
     if (a.causal && kt * BK > last_q) break;
     __syncthreads();
-    load_tile<T>(Ks, DhP, a.k, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f);
-    load_tile<T>(Vs, DhP, a.v, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f);
+    load_tile<T>(Ks, DhP, a.k, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f, &a.kx);
+    load_tile<T>(Vs, DhP, a.v, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f, &a.vx);
     __syncthreads();
 #pragma unroll
     for (int rr = 0; rr < 2; ++rr) {
@@ -152,8 +163,8 @@ __global__ void __launch_bounds__(256) attn_exact_dq_kernel(AttnArgs a) {
   for (int kt = 0; kt < n_tiles; ++kt) {
     if (a.causal && kt * BK > last_q) break;
     __syncthreads();
-    load_tile<T>(Ks, DhP, a.k, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f);
-    load_tile<T>(Vs, DhP, a.v, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f);
+    load_tile<T>(Ks, DhP, a.k, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f, &a.kx);
+    load_tile<T>(Vs, DhP, a.v, n, a.n2_count, h, kt * BK, BK, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f, &a.vx);
     __syncthreads();
 #pragma unroll
     for (int rr = 0; rr < 2; ++rr) {
@@ -218,8 +229,8 @@ __global__ void __launch_bounds__(256) attn_exact_dkv_kernel(AttnArgs a) {
   float* delta_s = lse_s + BK;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int k0 = blockIdx.x * QT, h = blockIdx.y, n = blockIdx.z;
-  load_tile<T>(Kr, DhP, a.k, n, a.n2_count, h, k0, QT, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f);
-  load_tile<T>(Vr, DhP, a.v, n, a.n2_count, h, k0, QT, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f);
+  load_tile<T>(Kr, DhP, a.k, n, a.n2_count, h, k0, QT, a.Sk, Dh, a.kcos, a.ksin, a.rot_dim, a.pos_is_head, 1.f, &a.kx);
+  load_tile<T>(Vr, DhP, a.v, n, a.n2_count, h, k0, QT, a.Sk, Dh, nullptr, nullptr, 0, 0, 1.f, &a.vx);
   float dk[2][MAXDL], dv[2][MAXDL];
 #pragma unroll
   for (int rr = 0; rr < 2; ++rr)
@@ -271,6 +282,20 @@ __global__ void __launch_bounds__(256) attn_exact_dkv_kernel(AttnArgs a) {
   for (int rr = 0; rr < 2; ++rr) {
     const int r = warp * 2 + rr, kj = k0 + r;
     if (kj >= a.Sk) continue;
+    if (a.kx.p != nullptr && kj == a.Sk - 1) {
+      // the shared extra row: its gradient sums over the n2_count sequences that read it (fp32 atomics, no rotation)
+      float* xk = a.dkx + ((int64_t)(n / a.n2_count) * a.H + h) * Dh;
+      float* xv = a.dvx + ((int64_t)(n / a.n2_count) * a.H + h) * Dh;
+#pragma unroll
+      for (int i = 0; i < MAXDL; ++i) {
+        const int d = lane + 32 * i;
+        if (d < Dh) {
+          atomicAdd(xk + d, dk[rr][i]);
+          atomicAdd(xv + d, dv[rr][i]);
+        }
+      }
+      continue;
+    }
     T* gk = view_ptr<T>(a.dk, n, a.n2_count, kj, h);
     T* gv = view_ptr<T>(a.dv, n, a.n2_count, kj, h);
     const int pos = a.pos_is_head ? h : kj;
@@ -293,6 +318,7 @@ __global__ void __launch_bounds__(256) attn_exact_dkv_kernel(AttnArgs a) {
 }
 
 static bool args_ok(const AttnArgs& a) {
+  if (a.kx.p != nullptr && (a.vx.p == nullptr || a.causal || a.key_mask || a.pos_is_head || a.Sk < 1)) return false;
   return a.N > 0 && a.H > 0 && a.Sq > 0 && a.Sk > 0 && a.Dh > 0 && (a.Dh % 2 == 0) && a.Dh <= 32 * MAXDL &&
          a.n2_count > 0 && (a.rot_dim % 2 == 0) && a.rot_dim <= a.Dh && a.H <= 65535 && a.N <= 65535;
 }
@@ -340,7 +366,7 @@ int attn_exact_fwd(const AttnArgs& a, int dtype, cudaStream_t st) {
 
 int attn_exact_bwd(const AttnArgs& a, int dtype, cudaStream_t st) {
   if (!args_ok(a) || !a.q.p || !a.k.p || !a.v.p || !a.o.p || !a.out_saved.p || !a.dq.p || !a.dk.p || !a.dv.p ||
-      !a.lse || !a.delta)
+      !a.lse || !a.delta || (a.kx.p != nullptr && (!a.dkx || !a.dvx)))
     return MEANT_EARG;
   if (dtype == MEANT_DT_F32) return run_bwd<float>(a, st);
   if (dtype == MEANT_DT_BF16) return run_bwd<__nv_bfloat16>(a, st);

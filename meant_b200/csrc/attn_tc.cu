@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
   constexpr int NT = 256, HC = DH / 2, HK = TK / 2;   // O columns / key columns per thread
   const int tid = threadIdx.x, warp = tid >> 5, t = tid & 127, hf = tid >> 7;
   const int q0 = blockIdx.x * TQ, h = blockIdx.y, n = blockIdx.z;
+  const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count, hc = h * (DH / 8);   // chunk-map coordinates of this head
   if (tid == 0) {
     tc::mbar_init(&bar_s, 1);
     tc::mbar_init(&bar_o, 1);
@@ -217,6 +218,16 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     tc::fence_mbar_init();
   }
   if (warp == 0) tc::tmem_alloc(&tmem_slot, 256);
+  // Shared extra key / value row (meant_attn_args.kx / vx): k and v hold Skb = Sk - 1 rows, the tile that contains key
+  // Sk - 1 gets that row written in after it has landed (threads [0, CPR): K's 16-byte chunks, [CPR, 2 CPR): V's).
+  const bool has_x = a.kx.p != nullptr;
+  const int Skb = a.Sk - (has_x ? 1 : 0);
+  uint4 xreg = make_uint4(0u, 0u, 0u, 0u);
+  if (has_x && tid < 2 * (DH / 8)) {
+    const HeadView& xv = tid < DH / 8 ? a.kx : a.vx;
+    xreg = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(xv.p) + (int64_t)n1 * xv.sn1 + (int64_t)h * xv.sh +
+                                           (tid % (DH / 8)) * 8);
+  }
   // cp.async groups, oldest first: [Q + K(0)] [V(0)] then per tile [K(kt+1)] [V(kt+1)] (empty past the end)
   const bool pre = a.q_rot.p != nullptr;          // Q, K already rotated by meant_attn_prerotate
   const HeadView& qv = pre ? a.q_rot : a.q;
@@ -231,16 +242,16 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     __syncthreads();                    // the barriers exist before anybody polls them
     if (tid == 0) {
       tma::mbar_expect_tx(&bar_k, 2 * L::OPER);
-      tma::load_box(tc::smem_u32(smem + L::Q), &maps.m[0], &bar_k, 0, q0, 0, h, n);
-      tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, 0, 0, h, n);
+      tma::load_box(tc::smem_u32(smem + L::Q), &maps.m[0], &bar_k, 0, q0, hc, n2, n1);
+      tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, 0, hc, n2, n1);
       tma::mbar_expect_tx(&bar_v, L::OPER);
-      tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, 0, 0, h, n);
+      tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, 0, hc, n2, n1);
     }
   } else {
     stage_async<DH, NT>(smem + L::Q, qv, n, a.n2_count, h, q0, a.Sq);
-    stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, 0, a.Sk);
+    stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, 0, Skb);
     tc::cp_async_commit();
-    stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, a.Sk);
+    stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, 0, Skb);
     tc::cp_async_commit();
   }
 
@@ -274,6 +285,11 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     MT_PROF(0);
     if (kt == 0) rotate_staged<DH, NT>(smem + L::Q, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
     rotate_staged<DH, NT>(smem + L::K, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
+    const int xr = Skb - k0;                                  // tile row of the extra key, if it is in this tile
+    if (has_x && xr >= 0 && xr < TK) {
+      __syncthreads();                                        // row xr was zero-filled and "rotated" by another thread
+      if (tid < DH / 8) *reinterpret_cast<uint4*>(smem + L::K + tid * CS128 + xr * 16) = xreg;
+    }
     if (!plain && tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
     MT_PROF(1);
     tc::fence_async_smem();
@@ -294,10 +310,10 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     if (use_tma) {                                                                      // K is free: next tile
       if (more && tid == 0) {
         tma::mbar_expect_tx(&bar_k, L::OPER);
-        tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, k0 + TK, 0, h, n);
+        tma::load_box(tc::smem_u32(smem + L::K), &maps.m[1], &bar_k, 0, k0 + TK, hc, n2, n1);
       }
     } else {
-      if (more) stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, k0 + TK, a.Sk);
+      if (more) stage_async<DH, NT>(smem + L::K, kv, n, a.n2_count, h, k0 + TK, Skb);
       tc::cp_async_commit();
     }
     MT_PROF(4);
@@ -367,6 +383,10 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     } else {
       tc::cp_async_wait<1>();          // V(kt) landed (K(kt+1) may still be in flight)
     }
+    if (has_x && xr >= 0 && xr < TK) {
+      if (!use_tma) __syncthreads();   // cp.async: the zero fill of row xr belongs to other threads' groups
+      if (tid >= DH / 8 && tid < 2 * (DH / 8)) *reinterpret_cast<uint4*>(smem + L::V + (tid - DH / 8) * CS128 + xr * 16) = xreg;
+    }
     tc::fence_async_smem();
     tc::fence_before_sync();
     __syncthreads();
@@ -385,10 +405,10 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     if (use_tma) {                                                                      // V is free: next tile
       if (more && tid == 0) {
         tma::mbar_expect_tx(&bar_v, L::OPER);
-        tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, k0 + TK, 0, h, n);
+        tma::load_box(tc::smem_u32(smem + L::V), &maps.m[2], &bar_v, 0, k0 + TK, hc, n2, n1);
       }
     } else {
-      if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, a.Sk);
+      if (more) stage_async<DH, NT>(smem + L::V, a.v, n, a.n2_count, h, k0 + TK, Skb);
       tc::cp_async_commit();
     }
     {
@@ -423,8 +443,8 @@ __global__ void __launch_bounds__(256, 2) attn_tc_fwd_kernel(AttnArgs a, const _
     tc::fence_async_smem();
     __syncthreads();
     if (tid == 0) {
-      tma::store_box(&maps.o[0], tc::smem_u32(smem + L::P), 0, h, q0, 0, n);
-      if (DH > 64) tma::store_box(&maps.o[1], tc::smem_u32(smem + L::P) + 128u * 128u, 64, h, q0, 0, n);
+      tma::store_box(&maps.o[0], tc::smem_u32(smem + L::P), 0, h, q0, n2, n1);
+      if (DH > 64) tma::store_box(&maps.o[1], tc::smem_u32(smem + L::P) + 128u * 128u, 64, h, q0, n2, n1);
       tma::store_commit();
       tma::store_wait_read<0>();
     }
@@ -672,9 +692,12 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   // L2.  Warps 0-7 compute; warps 8-11 (one warpgroup, registers handed to the compute warps) only issue the 16-byte
   // cp.async copies - their issue blocks on the memory pipeline - and run ahead as far as the buffers allow, so the
   // next item's operands land while the finished item's gradients are staged out.
-  int tile = 0, h = 0, n = 0;
+  int tile = 0, h = 0, n = 0, n1 = 0, n2 = 0, hc = 0;   // (n1, n2, hc): chunk-map coordinates of (n, h)
   MT_PROF_INIT();
   constexpr int PB = 12 + MODE * 10;   // phase-timer slots of this pass
+  // shared extra key / value row (meant_attn_args.kx / vx): see the forward kernel
+  const bool has_x = a.kx.p != nullptr;
+  const int Skb = a.Sk - (has_x ? 1 : 0);
   if (tid == 0) {
     tc::mbar_init(&bar1, 1);
     tc::mbar_init(&bar2, 1);
@@ -713,6 +736,9 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
     tile = (int)(idx % nt);
     h = (int)((idx / nt) % a.H);
     n = (int)(idx / ((int64_t)nt * a.H));
+    n1 = n / a.n2_count;
+    n2 = n - n1 * a.n2_count;
+    hc = h * (DH / 8);
     if (MODE == 0) {
       j0 = a.causal ? tile : 0;
       j1 = nq;
@@ -747,8 +773,8 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
         tc::mbar_wait(&empty_fix, pe_fix);
         pe_fix ^= 1;
         tma::mbar_expect_tx(&full_fix, 2 * L::OPER);
-        tma::load_box(tc::smem_u32(smem + L::FIX0), fa, &full_fix, 0, tile * 128, 0, h, n);
-        tma::load_box(tc::smem_u32(smem + L::FIX1), fb, &full_fix, 0, tile * 128, 0, h, n);
+        tma::load_box(tc::smem_u32(smem + L::FIX0), fa, &full_fix, 0, tile * 128, hc, n2, n1);
+        tma::load_box(tc::smem_u32(smem + L::FIX1), fb, &full_fix, 0, tile * 128, hc, n2, n1);
 #pragma unroll 1
         for (int j = j0; j < j1; ++j) {
           const int b = (j - j0) & 1;
@@ -761,8 +787,8 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
           }
           const uint32_t x = tc::smem_u32(smem + L::STR + (uint32_t)b * 2 * L::OPER);
           tma::mbar_expect_tx(&full_str[b], 2 * L::OPER);
-          tma::load_box(x, sa, &full_str[b], 0, j * 128, 0, h, n);
-          tma::load_box(x + L::OPER, sb, &full_str[b], 0, j * 128, 0, h, n);
+          tma::load_box(x, sa, &full_str[b], 0, j * 128, hc, n2, n1);
+          tma::load_box(x + L::OPER, sb, &full_str[b], 0, j * 128, hc, n2, n1);
         }
       }
       return;
@@ -777,8 +803,8 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
       tc::mbar_wait(&empty_fix, pe_fix);
       pe_fix ^= 1;
       if (MODE == 0) {
-        stage(smem + L::FIX0, kv, tile * TK, a.Sk);
-        stage(smem + L::FIX1, a.v, tile * TK, a.Sk);
+        stage(smem + L::FIX0, kv, tile * TK, Skb);
+        stage(smem + L::FIX1, a.v, tile * TK, Skb);
       } else {
         stage(smem + L::FIX0, qv, tile * TQ, a.Sq);
         stage(smem + L::FIX1, a.o, tile * TQ, a.Sq);
@@ -799,8 +825,8 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
           stage(x, qv, j * TQ, a.Sq);
           stage(x + L::OPER, a.o, j * TQ, a.Sq);
         } else {
-          stage(x, kv, j * TK, a.Sk);
-          stage(x + L::OPER, a.v, j * TK, a.Sk);
+          stage(x, kv, j * TK, Skb);
+          stage(x + L::OPER, a.v, j * TK, Skb);
         }
         tc::cp_async_arrive(&full_str[b]);
       }
@@ -868,9 +894,15 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
     }
   };
 
+  uint4 xreg = make_uint4(0u, 0u, 0u, 0u);      // threads [0, CPR): K's chunks of the extra row, [CPR, 2 CPR): V's
   auto begin_item = [&](int64_t kth) -> bool {   // the compute side of an item: its statistics
     if (!decode_item(kth)) return false;
     mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+    if (has_x && tid < 2 * (DH / 8)) {
+      const HeadView& xv = tid < DH / 8 ? a.kx : a.vx;
+      xreg = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(xv.p) + (int64_t)n1 * xv.sn1 + (int64_t)h * xv.sh +
+                                             (tid % (DH / 8)) * 8);
+    }
     if (MODE == 1) {
       row_stats(tile * TQ + t);
       tile_delta_issue(tile * TQ);            // reduced after the previous item's gradients are staged out
@@ -913,6 +945,15 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
       rotate_staged<DH, NT>(xs, h, k0, a.Sk, kcos, a.ksin, a.rot_dim, a.pos_is_head);
       if (first) rotate_staged<DH, NT>(smem + L::FIX0, h, q0, a.Sq, qcos, a.qsin, a.rot_dim, a.pos_is_head);
       if (tid < TK) kterm[tid] = key_term(mrow, k0 + tid, a.Sk);
+    }
+    {   // the extra key / value row goes into the K | V pair (MODE 0: fixed, once per item; MODE 1: streamed tile j)
+      const int xr = Skb - k0;
+      if (has_x && xr >= 0 && xr < TK && (MODE == 1 || first)) {
+        tc::bar_sync(1, NT);                     // row xr was zero-filled (and "rotated") by other threads
+        uint8_t* kd = MODE == 0 ? smem + L::FIX0 : xs;
+        if (tid < DH / 8) *reinterpret_cast<uint4*>(kd + tid * CS128 + xr * 16) = xreg;
+        else if (tid < 2 * (DH / 8)) *reinterpret_cast<uint4*>(kd + L::OPER + (tid - DH / 8) * CS128 + xr * 16) = xreg;
+      }
     }
     const uint32_t sq = tc::smem_u32(MODE == 0 ? xs : smem + L::FIX0), sdo = sq + L::OPER;
     const uint32_t sk = tc::smem_u32(MODE == 0 ? smem + L::FIX0 : xs), sv = sk + L::OPER;
@@ -1032,7 +1073,7 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   const uint32_t lane_base = tmem + ((uint32_t)((warp & 3) * 32) << 16);
   // Accumulators leave through the (now free) P / dS buffers: thread (row t, column half) un-rotates and packs its
   // row into the chunk layout, then lane pairs write whole 32-byte sectors of the head view (stage_async's walk).
-  auto stage_out = [&](uint32_t tcol, uint8_t* buf, const float* cs, const float* sn, int pos) {
+  auto stage_out = [&](uint32_t tcol, uint8_t* buf, const float* cs, const float* sn, int pos, float* xdst) {
     constexpr int NB = DH / 32;                // 16-column blocks per thread
     float g[NB][16];
     if (!zero) {
@@ -1044,6 +1085,12 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
       for (int bi = 0; bi < NB; ++bi)
 #pragma unroll
         for (int i = 0; i < 16; ++i) g[bi][i] = 0.f;
+    }
+    if (xdst != nullptr) {   // this row is the shared extra key: its gradient sums over the sequences that read it
+#pragma unroll
+      for (int bi = 0; bi < NB; ++bi)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) atomicAdd(xdst + half * (DH / 2) + bi * 16 + i, g[bi][i]);
     }
     if (cs != nullptr) {
 #pragma unroll
@@ -1071,8 +1118,9 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   };
   auto store_out = [&](int which, const uint8_t* buf) {   // one thread: the staged tile as one or two TMA boxes
     const uint32_t src = tc::smem_u32(buf);
-    tma::store_box(&maps.o[which][0], src, 0, eh, etile * 128, 0, en);
-    if (DH > 64) tma::store_box(&maps.o[which][1], src + 128u * 128u, 64, eh, etile * 128, 0, en);
+    const int en1 = en / a.n2_count, en2 = en - en1 * a.n2_count;
+    tma::store_box(&maps.o[which][0], src, 0, eh, etile * 128, en2, en1);
+    if (DH > 64) tma::store_box(&maps.o[which][1], src + 128u * 128u, 64, eh, etile * 128, en2, en1);
   };
   auto flush_out = [&](const uint8_t* buf, const HeadView& dst, int S) {
     const int r = tid >> 1, par = tid & 1, srow = etile * 128 + r;
@@ -1085,8 +1133,10 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
   };
   const int row = etile * 128 + t;
   if (MODE == 0) {
-    stage_out(T_A, smem + L::P, nullptr, nullptr, 0);
-    stage_out(T_B, smem + L::DS, a.kcos, a.ksin, a.pos_is_head ? eh : min(row, a.Sk - 1));
+    const bool xrow = has_x && row == Skb && !zero;
+    const int64_t xoff = ((int64_t)(en / a.n2_count) * a.H + eh) * DH;
+    stage_out(T_A, smem + L::P, nullptr, nullptr, 0, xrow ? a.dvx + xoff : nullptr);
+    stage_out(T_B, smem + L::DS, xrow ? nullptr : a.kcos, a.ksin, a.pos_is_head ? eh : min(row, a.Sk - 1), xrow ? a.dkx + xoff : nullptr);
     tc::fence_async_smem();
     tc::bar_sync(1, NT);
     if (maps.use_tma) {
@@ -1096,11 +1146,11 @@ __global__ void __launch_bounds__(MT_THREADS, 1) attn_tc_bwd_mt_kernel(AttnArgs 
         tma::store_commit();
       }
     } else {
-      flush_out(smem + L::P, a.dv, a.Sk);
-      flush_out(smem + L::DS, a.dk, a.Sk);
+      flush_out(smem + L::P, a.dv, Skb);
+      flush_out(smem + L::DS, a.dk, Skb);
     }
   } else {
-    stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? eh : min(row, a.Sq - 1));
+    stage_out(T_A, smem + L::DS, a.qcos, a.qsin, a.pos_is_head ? eh : min(row, a.Sq - 1), nullptr);
     tc::fence_async_smem();
     tc::bar_sync(1, NT);
     if (maps.use_tma) {
@@ -1203,8 +1253,16 @@ static bool view_ok(const HeadView& v) {
          v.ss % 8 == 0 && v.sh % 8 == 0;
 }
 
+static bool xview_ok(const HeadView& v) {
+  return v.p != nullptr && (reinterpret_cast<uintptr_t>(v.p) % 16 == 0) && v.sn1 % 8 == 0 && v.sh % 8 == 0;
+}
+
 int attn_tc_supported(const AttnArgs& a, int dtype, int backward) {
   if (dtype != MEANT_DT_BF16) return 0;
+  if (a.kx.p != nullptr) {   // shared extra key: plain non-causal attention only, Sk counts it
+    if (!xview_ok(a.kx) || !xview_ok(a.vx) || a.causal || a.key_mask || a.pos_is_head || a.q_rot.p || a.Sk < 2) return 0;
+    if (backward && (!a.dkx || !a.dvx)) return 0;
+  }
   if (a.Dh != 64 && a.Dh != 96) return 0;
   if (a.N <= 0 || a.H <= 0 || a.Sq <= 0 || a.Sk <= 0 || a.n2_count <= 0 || a.N > 65535 || a.H > 65535) return 0;
   if (a.rot_dim % 8 != 0 || a.rot_dim > a.Dh) return 0;
@@ -1226,6 +1284,12 @@ static int launch_tc(Kern kern, size_t smem, dim3 grid, const AttnArgs& a, cudaS
   return 0;
 }
 
+// MEANT_MT_NO_TMA=1 keeps the multi-tile kernels on their cp.async loaders (the GPU suite runs both); read once
+static bool mt_no_tma() {
+  static const bool v = getenv("MEANT_MT_NO_TMA") != nullptr;
+  return v;
+}
+
 template <int DH>
 static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
   // persistent kernels: one CTA per SM, work items (tile, head, sequence) strided inside the kernel
@@ -1236,12 +1300,13 @@ static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
   memset(&maps, 0, sizeof(maps));
   {
     const bool pre = a.q_rot.p != nullptr;
+    const int skb = a.Sk - (a.kx.p != nullptr ? 1 : 0);   // rows k / v / dk / dv really hold (meant_attn_args.kx)
     const HeadView* vs[MT_NMAPS] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o};
-    const int seq[MT_NMAPS] = {a.Sq, a.Sk, a.Sk, a.Sq};
-    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
+    const int seq[MT_NMAPS] = {a.Sq, skb, skb, a.Sq};
+    int ok = !mt_no_tma();
     for (int i = 0; i < MT_NMAPS && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH) == 0;
     const HeadView* os[3] = {&a.dq, &a.dk, &a.dv};
-    const int oseq[3] = {a.Sq, a.Sk, a.Sk};
+    const int oseq[3] = {a.Sq, skb, skb};
     for (int i = 0; i < 3 && ok; ++i) {
       ok = tma::make_head_map(&maps.o[i][0], *os[i], a.N, a.n2_count, a.H, oseq[i], DH, 64) == 0;
       if (ok && DH > 64) ok = tma::make_head_map(&maps.o[i][1], *os[i], a.N, a.n2_count, a.H, oseq[i], DH, 32) == 0;
@@ -1273,9 +1338,10 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
   memset(&maps, 0, sizeof(maps));
   {
     const bool pre = a.q_rot.p != nullptr;
+    const int skb = a.Sk - (a.kx.p != nullptr ? 1 : 0);
     const HeadView* vs[3] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v};
-    const int seq[3] = {a.Sq, a.Sk, a.Sk};
-    int ok = getenv("MEANT_MT_NO_TMA") == nullptr;
+    const int seq[3] = {a.Sq, skb, skb};
+    int ok = !mt_no_tma();
     for (int i = 0; i < 3 && ok; ++i) ok = tma::make_chunk_map(&maps.m[i], *vs[i], a.N, a.n2_count, a.H, seq[i], a.Dh) == 0;
     if (ok) ok = tma::make_head_map(&maps.o[0], a.o, a.N, a.n2_count, a.H, a.Sq, a.Dh, 64) == 0;
     if (ok && a.Dh > 64) ok = tma::make_head_map(&maps.o[1], a.o, a.N, a.n2_count, a.H, a.Sq, a.Dh, 32) == 0;
@@ -1298,7 +1364,7 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
     if (r2 != MEANT_EUNSUPPORTED) return r2;
     ++g_tma_fallbacks;
   }
-  if (a.Sq > TQ || a.Sk > TK) return a.Dh == 96 ? launch_bwd_mt<96>(a, st) : launch_bwd_mt<64>(a, st);
+  if (a.Sq > TQ || a.Sk > TK || a.kx.p != nullptr) return a.Dh == 96 ? launch_bwd_mt<96>(a, st) : launch_bwd_mt<64>(a, st);
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);

@@ -163,6 +163,44 @@ __device__ __forceinline__ float key_bias2(float mval, int k, int Sk) {
   return k < Sk ? (1.0f - mval) * -1e9f * LOG2E : -CUDART_INF_F;
 }
 
+// Packed groups (GRP kernels): the TimeSformer '(b n) f d' / '(b f) n d' groups (src/meant/timesformer_pytorch.py:122)
+// are much shorter than a 128-row tile (a time group is f <= 24 rows), so G consecutive groups n2 = blk*G .. of one
+// n1 share a tile behind a block-diagonal mask: tile row r = g * gl + s.  One TMA box (columns, 1 head, gl rows,
+// G groups) over the in-place head view lands / leaves exactly those rows, so nothing is rearranged in memory.
+// The optional shared extra key (meant_attn_args.kx / vx: the cls token) is tile row xr = G * gl, written by the
+// producer warp; every query row sees its own group's gl keys and that row.
+struct Grp {
+  int gl;      // rows per group (Sq == Sk - has_x)
+  int G;       // groups per tile
+  int nb;      // tiles per n1: ceil(n2_count / G)
+  int xr;      // G * gl: query rows / body key rows per tile; the tile row of the extra key
+  int has_x;
+};
+
+// work item -> (n1, first group n2, head); heads fastest, as in the un-grouped kernels
+__device__ __forceinline__ void grp_coords(int item, int H, const Grp& g, int& n1, int& n2, int& h) {
+  h = item % H;
+  const int rest = item / H;
+  n2 = (rest % g.nb) * g.G;
+  n1 = rest / g.nb;
+}
+
+// 32-column blocks that hold a visible key for any of the rows [t0, t0 + 32): bit b <-> columns [32 b, 32 b + 32)
+__device__ __forceinline__ uint32_t grp_block_mask(int t0, const Grp& g) {
+  const int lo = min(t0, g.xr - 1) / g.gl * g.gl, hi = min((min(t0 + 31, g.xr - 1) / g.gl + 1) * g.gl, g.xr);
+  uint32_t m = 0;
+  for (int b = lo >> 5; b <= (hi - 1) >> 5; ++b) m |= 1u << b;
+  if (g.has_x) m |= 1u << (g.xr >> 5);
+  return m;
+}
+
+// zero row r of an operand tile (rows a packed-group box does not cover)
+template <int CPR>
+__device__ __forceinline__ void zero_row(uint8_t* tile, int r) {
+#pragma unroll
+  for (int ch = 0; ch < CPR; ++ch) *reinterpret_cast<uint4*>(tile + oper_off(r, ch)) = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // ============================================================================== forward
 template <int DH>
 struct FwdL {
@@ -211,8 +249,9 @@ __device__ __forceinline__ void stage_acc_sw(uint32_t taddr, uint8_t* tile, int 
   }
 }
 
-template <int DH, int RC>
-__global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_items, const __grid_constant__ FwdMaps maps) {
+template <int DH, int RC, bool GRP>
+__global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_items, const __grid_constant__ FwdMaps maps,
+                                                            const Grp grp) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
   uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
@@ -225,6 +264,12 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
   uint64_t *landed = bars, *s_full = bars + NST, *o_full = bars + 2 * NST, *o_staged = bars + 3 * NST,
            *aux_ready = bars + 4 * NST, *rot_done = bars + 5 * NST, *p_ready = bars + 6 * NST;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (GRP) {
+    // a packed-group box covers grp.xr < 128 rows: the rows below it are never written by TMA, so every operand
+    // row starts out as zero (V rows stay zero for good; Q / K rows are re-zeroed by their compute threads)
+    for (uint32_t i = tid * 16; i < L::AUX; i += F_NT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0u, 0u, 0u, 0u);
+    tc::fence_async_smem();
+  }
   if (tid == 0) {
     for (int i = 0; i < NST; ++i) {
       tc::mbar_init(&landed[i], 1);
@@ -245,7 +290,10 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
   const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const int rc = a.qcos ? a.rot_dim / 8 : 0;
   const uint32_t s0 = tc::smem_u32(smem);
-  const int n_s = (a.Sk + 15) & ~15;                            // PV K extent (keys, rounded to one MMA K step)
+  // per-tile extents: query rows, keys (packed groups: G groups of gl rows, plus the shared extra key)
+  const int Tq = GRP ? grp.xr : a.Sq, Tk = GRP ? grp.xr + grp.has_x : a.Sk;
+  const int n_s = (Tk + 15) & ~15;                              // PV K extent (keys, rounded to one MMA K step)
+  const uint32_t tile_bytes = GRP ? (uint32_t)grp.xr * DH * 2u : G::OPER;   // what one operand's boxes deliver
 
   if (warp == F_PROD) {
     // ------------------------------------------------------------------ producer warp
@@ -256,16 +304,42 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
       for (int i = 0; i < 8; ++i)
         if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
     }
+    auto coords = [&](int item, int& n, int& h, int& n2, int& n1) {
+      if (GRP) {
+        grp_coords(item, a.H, grp, n1, n2, h);
+        n = n1 * a.n2_count + n2;
+      } else {
+        n = item / a.H;
+        h = item - n * a.H;
+        n1 = n / a.n2_count;
+        n2 = n - n1 * a.n2_count;
+      }
+    };
     auto store_out = [&](int item, int st) {                      // staged O of `item` -> global (lane 0)
-      const int n = item / a.H, h = item - n * a.H, n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      int n, h, n2, n1;
+      coords(item, n, h, n2, n1);
       const uint32_t sb = s0 + st * L::STAGE;
       tma::store_box(&maps.m[6], sb, 0, h, 0, n2, n1);
       if (G::TAIL) tma::store_box(&maps.m[7], sb + SUB_A, 64, h, 0, n2, n1);
       tma::store_commit();
     };
+    // the shared extra key / value row of an item: lanes [0, CPR) fetch K's 16-byte chunks, [CPR, 2 CPR) V's
+    auto load_x = [&](int item) -> uint4 {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (GRP && grp.has_x && lane < 2 * G::CPR) {
+        int n, h, n2, n1;
+        coords(item, n, h, n2, n1);
+        const HeadView& xv = lane < G::CPR ? a.kx : a.vx;
+        v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(xv.p) + (int64_t)n1 * xv.sn1 + (int64_t)h * xv.sh +
+                                            (lane % G::CPR) * 8);
+      }
+      return v;
+    };
+    uint4 xnext = n_my > 0 ? load_x(blockIdx.x) : make_uint4(0u, 0u, 0u, 0u);
     for (int j = 0; j < n_my; ++j) {
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
-      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      const int item = blockIdx.x + j * gridDim.x, st = j % NST;
+      int n, h, n2, n1;
+      coords(item, n, h, n2, n1);
       pf.tick(0);
       if (j >= NST) {   // the stage still holds item j - NST: its staged output goes out first
         tc::mbar_wait(&o_staged[st], ((j - NST) / NST) & 1);
@@ -276,19 +350,28 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
         }
         pf.tick(2);
       }
+      if (GRP && grp.has_x) {
+        __syncwarp();                                             // lane 0's store has read the stage out
+        const uint32_t sb = st * L::STAGE;
+        if (lane < 2 * G::CPR)
+          *reinterpret_cast<uint4*>(smem + sb + (lane < G::CPR ? 1 : 2) * G::OPER + oper_off(grp.xr, lane % G::CPR)) = xnext;
+        tc::fence_async_smem();
+        __syncwarp();                                             // ordered before lane 0's expect_tx arrive (release)
+      }
       if (lane == 0) {
         const uint32_t sb = s0 + st * L::STAGE;
-        tma::mbar_expect_tx(&landed[st], 3 * G::OPER);
+        tma::mbar_expect_tx(&landed[st], 3 * tile_bytes);
 #pragma unroll
         for (int v = 0; v < 3; ++v) {
           tma::load_box(sb + v * G::OPER, &maps.m[2 * v], &landed[st], 0, h, 0, n2, n1);
           if (G::TAIL) tma::load_box(sb + v * G::OPER + SUB_A, &maps.m[2 * v + 1], &landed[st], 64, h, 0, n2, n1);
         }
       }
+      if (j + 1 < n_my) xnext = load_x(item + (int)gridDim.x);    // in flight while this item's boxes are issued
       pf.tick(3);
       float4 mv = make_float4(1.f, 1.f, 1.f, 1.f);
       const int k0 = lane * 4;
-      if (a.key_mask) {
+      if (!GRP && a.key_mask) {
         const float* mrow = a.key_mask + (int64_t)n * a.Sk;
         if (k0 + 3 < a.Sk && (a.Sk & 3) == 0) mv = __ldg(reinterpret_cast<const float4*>(mrow + k0));
         else {
@@ -299,8 +382,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
         }
       }
       reinterpret_cast<float4*>(smem + L::AUX + st * 512)[lane] =
-          make_float4(key_bias2(mv.x, k0, a.Sk), key_bias2(mv.y, k0 + 1, a.Sk), key_bias2(mv.z, k0 + 2, a.Sk),
-                      key_bias2(mv.w, k0 + 3, a.Sk));
+          make_float4(key_bias2(mv.x, k0, Tk), key_bias2(mv.y, k0 + 1, Tk), key_bias2(mv.z, k0 + 2, Tk),
+                      key_bias2(mv.w, k0 + 3, Tk));
       tc::mbar_arrive(&aux_ready[st]);
       pf.tick(4);
     }
@@ -344,13 +427,17 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
     const float scale2 = a.scale * LOG2E;
     float* red_max = reinterpret_cast<float*>(smem + L::RED);     // [2][128]
     float* red_sum = red_max + 256;                               // [2][128]
-    int nblk = (a.Sk + 31) >> 5;                                  // 32-key blocks with any unmasked key for this warp's rows
+    int nblk = (Tk + 31) >> 5;                                    // 32-key blocks with any unmasked key for this warp's rows
     if (a.causal) nblk = min(nblk, rg + 1);
+    // packed groups: this row's visible keys are [glo, ghi) and the extra key gx; bmask = blocks its warp touches
+    const int glo = GRP ? min(t, grp.xr - 1) / grp.gl * grp.gl : 0, ghi = GRP ? glo + grp.gl : 0;
+    const int gx = GRP && grp.has_x ? grp.xr : -1;
+    const uint32_t bmask = GRP ? grp_block_mask(rg * 32, grp) : 0xffffffffu;
     RotTab<RC> tab;                                               // half 0: q tables, half 1: k tables
     const float* tcs = half ? a.kcos : a.qcos;
     const float* tsn = half ? a.ksin : a.qsin;
     int cur_h = -1;
-    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
+    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, GRP ? min(t, grp.xr - 1) % grp.gl : min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
     Prof pf;
     pf.init(blockIdx.x == 0 && tid == 96, 0);
     // rotate item j's Q / K rows in place and hand the stage to the MMA warp
@@ -359,12 +446,15 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
       pf.tick(8);
       tc::mbar_wait(&landed[st], (j / NST) & 1);
       pf.tick(9);
-      if (rc) {
+      uint8_t* mine = smem + st * L::STAGE + half * G::OPER;
+      if (GRP && t >= grp.xr) {           // rows the boxes do not cover hold the previous item's P / O staging
+        if (half == 0 || t > grp.xr || !grp.has_x) zero_row<G::CPR>(mine, t);   // (the extra key row is the producer's)
+      } else if (rc) {
         if (a.pos_is_head) {
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
           if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + st * L::STAGE + half * G::OPER, t, rc, tab);
+        rot_row<RC, false>(mine, t, rc, tab);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
@@ -373,7 +463,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
     };
     if (n_my > 0) prepare(0);
     for (int j = 0; j < n_my; ++j) {
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H, h = item - n * a.H, st = j % NST;
+      const int item = blockIdx.x + j * gridDim.x, st = j % NST;
       const uint32_t par = (j / NST) & 1;
       pf.tick(0);
       tc::mbar_wait(&aux_ready[st], par);
@@ -387,7 +477,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
-        if (blk < nblk) {                                           // warp-uniform
+        if (blk < nblk && ((bmask >> blk) & 1u)) {                  // warp-uniform
           float sv[32];
           tc::tmem_ld32(ts + blk * 32, sv);
           tc::tmem_ld_wait();
@@ -399,7 +489,13 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 #pragma unroll
             for (int u = 0; u < 4; ++u) sv[e + u] = fmaf(sv[e + u], scale2, bb[u]);
           }
-          if (diag) {                                               // warp-uniform
+          if (GRP) {                                                // block-diagonal mask: own group + the extra key
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const int c = blk * 32 + e;
+              m = fmaxf(m, ((c >= glo && c < ghi) || c == gx) ? sv[e] : -CUDART_INF_F);
+            }
+          } else if (diag) {                                        // warp-uniform
 #pragma unroll
             for (int e = 0; e < 32; ++e) m = fmaxf(m, e > lane ? -CUDART_INF_F : sv[e]);
           } else {
@@ -419,7 +515,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
-        if (blk < nblk) {
+        if (blk < nblk && ((bmask >> blk) & 1u)) {
           float sv[32];
           tc::tmem_ld32(ts + blk * 32, sv);
           tc::tmem_ld_wait();
@@ -434,7 +530,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
             for (int u = 0; u < 4; ++u) {
               const int e = q * 8 + 2 * u;
               float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - m_use)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - m_use));
-              if (diag) {                                           // warp-uniform: off-diagonal blocks skip the masking
+              if (GRP) {
+                const int c = blk * 32 + e;
+                if (!((c >= glo && c < ghi) || c == gx)) p0 = 0.f;
+                if (!((c + 1 >= glo && c + 1 < ghi) || c + 1 == gx)) p1 = 0.f;
+              } else if (diag) {                                    // warp-uniform: off-diagonal blocks skip the masking
                 if (e > lane) p0 = 0.f;
                 if (e + 1 > lane) p1 = 0.f;
               }
@@ -463,7 +563,18 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
       tc::fence_after_sync();
       pf.tick(6);
       stage_acc_sw<G::CPR / 2>(ts + half * HALF, smem + st * L::STAGE, t, half * (G::CPR / 2), l > 0.f ? 1.0f / l : 0.f);
-      if (half == 0 && t < a.Sq && a.lse) a.lse[((int64_t)n * a.H + h) * a.Sq + t] = m_use * LN2 + logf(l);
+      if (half == 0 && a.lse) {
+        if (GRP) {
+          int n1, n2, h;
+          grp_coords(item, a.H, grp, n1, n2, h);
+          const int g = t / grp.gl;
+          if (t < grp.xr && n2 + g < a.n2_count)
+            a.lse[((int64_t)(n1 * a.n2_count + n2 + g) * a.H + h) * grp.gl + (t - g * grp.gl)] = m_use * LN2 + logf(l);
+        } else if (t < a.Sq) {
+          const int n = item / a.H, h = item - n * a.H;
+          a.lse[((int64_t)n * a.H + h) * a.Sq + t] = m_use * LN2 + logf(l);
+        }
+      }
       tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(&o_staged[st]);
@@ -529,8 +640,24 @@ __device__ __forceinline__ void stage_acc_unrot_sw(uint32_t taddr, uint8_t* tile
   }
 }
 
-template <int DH, int RC>
-__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMaps maps) {
+// fp32 accumulator row `row` (TMEM lanes of this warp, columns [taddr, taddr + ncols)) added atomically to dst[0..ncols):
+// the gradient of the shared extra key / value row, which sums over every tile that reads it.  Whole warp calls
+// (tcgen05.ld is warp-collective); only the lane that owns the row adds.
+__device__ __forceinline__ void x_row_atomic(uint32_t taddr, int ncols, bool mine, float* dst) {
+  for (int c0 = 0; c0 < ncols; c0 += 16) {
+    float g[16];
+    tc::tmem_ld16(taddr + c0, g);
+    tc::tmem_ld_wait();
+    if (mine) {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) atomicAdd(dst + c0 + i, g[i]);
+    }
+  }
+}
+
+template <int DH, int RC, bool GRP>
+__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMaps maps,
+                                                            const Grp grp) {
   extern __shared__ __align__(128) uint8_t smem_raw[];
   __shared__ uint32_t tmem_slot;
   uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);   // swizzle atoms are 1024-byte aligned
@@ -543,6 +670,10 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
            *sdp_full = bars + 8, *pds_ready = bars + 9, *grads_full = bars + 10, *staged = bars + 11, *stg_free = bars + 12,
            *dq_full = bars + 13, *dq_staged = bars + 14, *p_ready = bars + 15, *dv_done = bars + 16;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (GRP) {   // rows a packed-group box does not cover start out as zero (see the forward kernel)
+    for (uint32_t i = tid * 16; i < L::AUX; i += F_NT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0u, 0u, 0u, 0u);
+    tc::fence_async_smem();
+  }
   if (tid == 0) {
     for (int i = 0; i < 2; ++i) {
       tc::mbar_init(&landed_qk[i], 1);
@@ -571,6 +702,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
   const int rc = a.qcos ? a.rot_dim / 8 : 0;
   const uint32_t s0 = tc::smem_u32(smem);
   const uint32_t svd = s0 + L::VD, sp = s0 + L::P, sds = s0 + L::DS;
+  const int Tq = GRP ? grp.xr : a.Sq, Tk = GRP ? grp.xr + grp.has_x : a.Sk;   // per-tile query rows / keys
+  const uint32_t tile_bytes = GRP ? (uint32_t)grp.xr * DH * 2u : G::OPER;
 
   if (warp == F_PROD) {
     // ------------------------------------------------------------------ producer warp
@@ -582,10 +715,15 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
     }
     auto coords = [&](int j, int& h, int& n2, int& n1) {
-      const int item = blockIdx.x + j * gridDim.x, n = item / a.H;
-      h = item - n * a.H;
-      n1 = n / a.n2_count;
-      n2 = n - n1 * a.n2_count;
+      const int item = blockIdx.x + j * gridDim.x;
+      if (GRP) {
+        grp_coords(item, a.H, grp, n1, n2, h);
+      } else {
+        const int n = item / a.H;
+        h = item - n * a.H;
+        n1 = n / a.n2_count;
+        n2 = n - n1 * a.n2_count;
+      }
     };
     auto load_tile = [&](int view, uint32_t dst, uint64_t* bar, int h, int n2, int n1) {
       tma::load_box(dst, &maps.m[2 * view], bar, 0, h, 0, n2, n1);
@@ -605,47 +743,81 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       store_tile(5, sq, h, n2, n1);                               // dk (over this item's Q)
       tma::store_commit();
     };
+    // shared extra key / value row of item j: lanes [0, CPR) hold K's 16-byte chunks, [CPR, 2 CPR) V's
+    auto load_x = [&](int j) -> uint4 {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (GRP && grp.has_x && lane < 2 * G::CPR) {
+        int h, n2, n1;
+        coords(j, h, n2, n1);
+        const HeadView& xv = lane < G::CPR ? a.kx : a.vx;
+        v = *reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(xv.p) + (int64_t)n1 * xv.sn1 + (int64_t)h * xv.sh +
+                                            (lane % G::CPR) * 8);
+      }
+      return v;
+    };
+    uint4 xnext = n_my > 0 ? load_x(0) : make_uint4(0u, 0u, 0u, 0u);
     for (int j = 0; j < n_my; ++j) {
       const int b = j & 1;
       int h, n2, n1;
       coords(j, h, n2, n1);
       const int n = n1 * a.n2_count + n2;
+      const uint4 xcur = xnext;
       pf.tick(0);
-      if (lane == 0) {       // Q | K pair b still holds item j-2's dQ / dK staging until those stores have read it
-        if (j >= 2) tma::store_wait_read<0>();
+      if (lane == 0 && j >= 2) tma::store_wait_read<0>();   // Q | K pair b still holds item j-2's dQ / dK staging until read
+      if (GRP && grp.has_x) {
+        __syncwarp();
+        if (lane < G::CPR)                                        // K's extra row, ahead of the boxes of this pair
+          *reinterpret_cast<uint4*>(smem + L::QK + (b * 2 + 1) * G::OPER + oper_off(grp.xr, lane)) = xcur;
+        tc::fence_async_smem();
+        __syncwarp();
+      }
+      if (lane == 0) {
         const uint32_t sq = s0 + L::QK + b * 2 * G::OPER;
-        tma::mbar_expect_tx(&landed_qk[b], 2 * G::OPER);
+        tma::mbar_expect_tx(&landed_qk[b], 2 * tile_bytes);
         load_tile(0, sq, &landed_qk[b], h, n2, n1);
         load_tile(1, sq + G::OPER, &landed_qk[b], h, n2, n1);
       }
+      if (j + 1 < n_my) xnext = load_x(j + 1);
       pf.tick(1);
       if (j > 0) tc::mbar_wait(sdp_full, (j - 1) & 1);            // V(j-1)'s slot is free once dP of that item has run
       pf.tick(2);
       if (lane == 0) {
-        tma::mbar_expect_tx(landed_do, G::OPER);
+        tma::mbar_expect_tx(landed_do, tile_bytes);
         load_tile(3, svd + (b ^ 1) * G::OPER, landed_do, h, n2, n1);
       }
       {
         const int k0 = lane * 4;
         float mv[4] = {1.f, 1.f, 1.f, 1.f}, ls[4] = {0.f, 0.f, 0.f, 0.f};
-        const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
-        const float* lrow = a.lse + ((int64_t)n * a.H + h) * a.Sq;
+        const float* mrow = !GRP && a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          if (mrow && k0 + u < a.Sk) mv[u] = __ldg(mrow + k0 + u);
-          if (k0 + u < a.Sq) ls[u] = __ldg(lrow + k0 + u);
+          const int r = k0 + u;
+          if (mrow && r < a.Sk) mv[u] = __ldg(mrow + r);
+          if (GRP) {                                              // tile row r = group g, row r - g gl of that group
+            const int g = r / grp.gl;
+            if (r < grp.xr && n2 + g < a.n2_count)
+              ls[u] = __ldg(a.lse + ((int64_t)(n + g) * a.H + h) * grp.gl + (r - g * grp.gl));
+          } else if (r < a.Sq) {
+            ls[u] = __ldg(a.lse + ((int64_t)n * a.H + h) * a.Sq + r);
+          }
         }
         float* aux = reinterpret_cast<float*>(smem + L::AUX + b * 1024);
-        reinterpret_cast<float4*>(aux)[lane] = make_float4(key_bias2(mv[0], k0, a.Sk), key_bias2(mv[1], k0 + 1, a.Sk),
-                                                           key_bias2(mv[2], k0 + 2, a.Sk), key_bias2(mv[3], k0 + 3, a.Sk));
+        reinterpret_cast<float4*>(aux)[lane] = make_float4(key_bias2(mv[0], k0, Tk), key_bias2(mv[1], k0 + 1, Tk),
+                                                           key_bias2(mv[2], k0 + 2, Tk), key_bias2(mv[3], k0 + 3, Tk));
         reinterpret_cast<float4*>(aux + 128)[lane] = make_float4(ls[0] * LOG2E, ls[1] * LOG2E, ls[2] * LOG2E, ls[3] * LOG2E);
         tc::mbar_arrive(&aux_ready[b]);
       }
       pf.tick(3);
       if (j > 0) tc::mbar_wait(dv_done, (j - 1) & 1);             // dO(j-1)'s slot is free once dV of that item has run
       pf.tick(4);
+      if (GRP && grp.has_x) {
+        if (lane >= G::CPR && lane < 2 * G::CPR)                  // V's extra row, ahead of V's boxes
+          *reinterpret_cast<uint4*>(smem + L::VD + b * G::OPER + oper_off(grp.xr, lane - G::CPR)) = xcur;
+        tc::fence_async_smem();
+        __syncwarp();
+      }
       if (lane == 0) {
-        tma::mbar_expect_tx(landed_v, G::OPER);
+        tma::mbar_expect_tx(landed_v, tile_bytes);
         load_tile(2, svd + b * G::OPER, landed_v, h, n2, n1);
       }
       if (j > 0) {
@@ -684,7 +856,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
         for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
         tc::mma_commit(sdp_full);
-        const int kq = (a.Sq + 15) >> 4, kk = (a.Sk + 15) >> 4;
+        const int kq = (Tq + 15) >> 4, kk = (Tk + 15) >> 4;
         tc::mbar_wait(p_ready, j & 1);                            // P is complete after pass 1: dV runs under pass 2
         tc::fence_after_sync();
 #pragma unroll
@@ -710,14 +882,17 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
     const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
     const float scale = a.scale, scale2 = a.scale * LOG2E;
     float* red_delta = reinterpret_cast<float*>(smem + L::RED);
-    const bool qrow = t < a.Sq;
-    int nblk = (a.Sk + 31) >> 5;
+    const bool qrow = t < Tq;
+    int nblk = (Tk + 31) >> 5;
     if (a.causal) nblk = min(nblk, rg + 1);
+    const int glo = GRP ? min(t, grp.xr - 1) / grp.gl * grp.gl : 0, ghi = GRP ? glo + grp.gl : 0;
+    const int gx = GRP && grp.has_x ? grp.xr : -1;
+    const uint32_t bmask = GRP ? grp_block_mask(rg * 32, grp) : 0xffffffffu;
     RotTab<RC> tab;                                               // half 0: q tables (Q, dQ), half 1: k tables (K, dK)
     const float* tcs = half ? a.kcos : a.qcos;
     const float* tsn = half ? a.ksin : a.qsin;
     int cur_h = -1;
-    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
+    if (rc && !a.pos_is_head) load_tab<RC>(tab, tcs, tsn, GRP ? min(t, grp.xr - 1) % grp.gl : min(t, (half ? a.Sk : a.Sq) - 1), a.rot_dim);
     Prof pc;
     pc.init(blockIdx.x == 0 && tid == 96, 0);
     // rotate item j's Q / K rows in place (buffer j & 1) and hand the pair to the MMA warp
@@ -726,12 +901,15 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       pc.tick(8);
       tc::mbar_wait(&landed_qk[b], (j >> 1) & 1);
       pc.tick(9);
-      if (rc) {
+      uint8_t* mine = smem + L::QK + (b * 2 + half) * G::OPER;
+      if (GRP && t >= grp.xr) {           // rows the boxes do not cover hold an older item's dQ / dK staging
+        if (half == 0 || t > grp.xr || !grp.has_x) zero_row<G::CPR>(mine, t);   // (the extra key row is the producer's)
+      } else if (rc) {
         if (a.pos_is_head) {
           const int h = (blockIdx.x + j * gridDim.x) % a.H;
           if (h != cur_h) { load_tab<RC>(tab, tcs, tsn, h, a.rot_dim); cur_h = h; }
         }
-        rot_row<RC, false>(smem + L::QK + (b * 2 + half) * G::OPER, t, rc, tab);
+        rot_row<RC, false>(mine, t, rc, tab);
       }
       tc::fence_async_smem();
       tc::fence_before_sync();
@@ -755,9 +933,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
-        if (blk < nblk) {
+        if (blk < nblk && ((bmask >> blk) & 1u)) {
           const int lim = !qrow ? -1 : ((a.causal && blk == rg) ? lane : 31);
-          const bool masked = (a.causal && blk == rg) || rg * 32 + 31 >= a.Sq;   // warp-uniform: most blocks skip the test
+          const bool masked = (a.causal && blk == rg) || rg * 32 + 31 >= Tq;   // warp-uniform: most blocks skip the test
 #pragma unroll
           for (int hb = 0; hb < 2; ++hb) {                          // 16 columns at a time keeps the live set small
             float sv16[16], dp[16];
@@ -772,7 +950,10 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
               for (int u = 0; u < 4; ++u) {
                 p[u] = tc::ex2(fmaf(sv16[e + u], scale2, bb[u]) - lse2);
-                if (masked && hb * 16 + e + u > lim) p[u] = 0.f;
+                if (GRP) {                                          // block-diagonal mask: own group + the extra key
+                  const int c = blk * 32 + hb * 16 + e + u;
+                  if (!qrow || !((c >= glo && c < ghi) || c == gx)) p[u] = 0.f;
+                } else if (masked && hb * 16 + e + u > lim) p[u] = 0.f;
                 delta = fmaf(p[u], dp[e + u], delta);
               }
               const __nv_bfloat162 p01 = __floats2bfloat162_rn(p[0], p[1]), p23 = __floats2bfloat162_rn(p[2], p[3]);
@@ -804,7 +985,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
 #pragma unroll
         for (int hb = 0; hb < 2; ++hb) {
           uint32_t dsk[8];
-          if (blk < nblk) {
+          if (blk < nblk && ((bmask >> blk) & 1u)) {
             float dp[16];
             tc::tmem_ld16(lane_base + T_DP + blk * 32 + hb * 16, dp);
             tc::tmem_ld_wait();
@@ -833,6 +1014,13 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
       pc.tick(6);
       // half 0 owns the dQ row, half 1 the dK row (each un-rotates with its own table); dV is split by columns
       uint8_t* pair = smem + L::QK + b * 2 * G::OPER;
+      // the shared extra key's gradients (tile row grp.xr) are summed over tiles in fp32 instead of being stored
+      const bool xwarp = GRP && grp.has_x && rg == (grp.xr >> 5);   // warp-uniform
+      int xn1 = 0, xh = 0;
+      if (xwarp) {
+        int n2;
+        grp_coords(blockIdx.x + j * gridDim.x, a.H, grp, xn1, n2, xh);
+      }
       if (half == 0) {
         tc::mbar_wait(dq_full, j & 1);
         tc::fence_after_sync();
@@ -847,8 +1035,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_kernel(AttnArgs a, int n_it
         tc::fence_after_sync();
         pc.tick(7);
         stage_acc_unrot_sw<DH, RC>(lane_base + T_DK, pair, t, rc, tab);                 // over Q
+        if (xwarp) x_row_atomic(lane_base + T_DK, DH, lane == (grp.xr & 31), a.dkx + ((int64_t)xn1 * a.H + xh) * DH);
       }
       stage_acc_sw<G::CPR / 2>(lane_base + T_DV + half * HALF, smem + L::DS, t, half * (G::CPR / 2), 1.0f);
+      if (xwarp) x_row_atomic(lane_base + T_DV + half * HALF, HALF, lane == (grp.xr & 31),
+                              a.dvx + ((int64_t)xn1 * a.H + xh) * DH + half * HALF);
       tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(staged);
@@ -874,9 +1065,29 @@ static int num_sms() {
   return n;
 }
 
+// Packed-group geometry of a problem (t2::Grp; G = 0: not a packed-group problem).  Taken when the problem is plain
+// self-attention inside short groups -- Sq == Sk (- the shared extra key), no causal / padding mask, token-position
+// tables -- and either carries the extra key (any group count) or at least two groups of one n1 fit a tile.
+static t2::Grp grp_of(const AttnArgs& a) {
+  t2::Grp g = {0, 0, 0, 0, 0};
+  const int has_x = a.kx.p != nullptr ? 1 : 0;
+  const int gl = a.Sk - has_x;
+  if (gl <= 0 || a.Sq != gl || gl + has_x > 128 || a.causal || a.key_mask || a.pos_is_head) return g;
+  int G = (128 - has_x) / gl;
+  if (G > a.n2_count) G = a.n2_count;
+  if (G < 1 || (!has_x && G < 2)) return g;
+  g.gl = gl;
+  g.G = G;
+  g.nb = (a.n2_count + G - 1) / G;
+  g.xr = G * gl;
+  g.has_x = has_x;
+  return g;
+}
+
 // single-tile problems the persistent kernels take (the caller has already checked dtype, views, Dh)
 int attn_tc2_supported(const AttnArgs& a, int backward) {
   if (a.Sq > 128 || a.Sk > 128) return 0;
+  if (a.kx.p != nullptr && grp_of(a).G == 0) return 0;      // the extra key exists in the packed-group kernels only
   if (a.qcos) {
     const int rc_max = a.Dh == 96 ? 6 : 8;
     if (a.rot_dim / 8 > rc_max) return 0;
@@ -891,24 +1102,28 @@ int attn_tc2_supported(const AttnArgs& a, int backward) {
   return 1;
 }
 
-// tensor maps for `count` head views (a 64-column SWIZZLE_128B map and, for Dh = 96, a 32-column SWIZZLE_64B map each)
+// tensor maps for `count` head views (a 64-column SWIZZLE_128B map and, for Dh = 96, a 32-column SWIZZLE_64B map each);
+// packed groups: boxes of gl rows x G groups instead of one 128-row tile
 template <int DH>
-static int build_maps(CUtensorMap* m, const AttnArgs& a, const HeadView* const* vs, const int* seq, int count) {
+static int build_maps(CUtensorMap* m, const AttnArgs& a, const HeadView* const* vs, const int* seq, int count, const t2::Grp& g) {
+  const int rows = g.G ? g.gl : 128, ngrp = g.G ? g.G : 1;
   for (int i = 0; i < count; ++i) {
-    int rc = tma::make_head_map(&m[2 * i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 64);
-    if (rc == 0 && DH > 64) rc = tma::make_head_map(&m[2 * i + 1], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 32);
+    int rc = tma::make_head_map(&m[2 * i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 64, rows, ngrp);
+    if (rc == 0 && DH > 64) rc = tma::make_head_map(&m[2 * i + 1], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 32, rows, ngrp);
     if (rc) return rc;
   }
   return 0;
 }
 
 template <typename Kern, typename Maps>
-static int launch2(Kern kern, size_t smem, const AttnArgs& a, const Maps& maps, cudaStream_t st) {
+static int launch2(Kern kern, size_t smem, const AttnArgs& a, const Maps& maps, const t2::Grp& g, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  const int64_t items = (int64_t)a.N * a.H;
+  // work items: (sequence, head), or with packed groups (n1, tile of G groups, head)
+  const int64_t items = g.G ? (int64_t)(a.N / a.n2_count) * g.nb * a.H : (int64_t)a.N * a.H;
+  if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
   const int grid = (int)(items < num_sms() ? items : num_sms());
-  kern<<<grid, t2::F_NT, smem, st>>>(a, (int)items, maps);
+  kern<<<grid, t2::F_NT, smem, st>>>(a, (int)items, maps, g);
   MEANT_LAUNCH_CHECK();
   return 0;
 }
@@ -935,20 +1150,27 @@ template <int DH, int RC>
 static int launch_fwd(const AttnArgs& a, cudaStream_t st) {
   t2::FwdMaps maps;
   memset(&maps, 0, sizeof(maps));
+  const t2::Grp g = grp_of(a);
+  const int skb = a.Sk - g.has_x;                   // rows k / v hold (the extra key lives in kx / vx)
   const HeadView* vs[4] = {&a.q, &a.k, &a.v, &a.o};
-  const int seq[4] = {a.Sq, a.Sk, a.Sk, a.Sq};
-  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 4)) return rc;
-  return launch2(t2::attn2_fwd_kernel<DH, RC>, t2::FwdL<DH>::TOTAL, a, maps, st);
+  const int seq[4] = {a.Sq, skb, skb, a.Sq};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 4, g)) return rc;
+  if (g.G) return launch2(t2::attn2_fwd_kernel<DH, RC, true>, t2::FwdL<DH>::TOTAL, a, maps, g, st);
+  return launch2(t2::attn2_fwd_kernel<DH, RC, false>, t2::FwdL<DH>::TOTAL, a, maps, g, st);
 }
 
 template <int DH, int RC>
 static int launch_bwd(const AttnArgs& a, cudaStream_t st) {
   t2::BwdMaps maps;
   memset(&maps, 0, sizeof(maps));
+  const t2::Grp g = grp_of(a);
+  const int skb = a.Sk - g.has_x;
+  if (g.has_x && (!a.dkx || !a.dvx)) return MEANT_EARG;
   const HeadView* vs[7] = {&a.q, &a.k, &a.v, &a.o, &a.dq, &a.dk, &a.dv};
-  const int seq[7] = {a.Sq, a.Sk, a.Sk, a.Sq, a.Sq, a.Sk, a.Sk};
-  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7)) return rc;
-  return launch2(t2::attn2_bwd_kernel<DH, RC>, t2::BwdL<DH>::TOTAL, a, maps, st);
+  const int seq[7] = {a.Sq, skb, skb, a.Sq, a.Sq, skb, skb};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7, g)) return rc;
+  if (g.G) return launch2(t2::attn2_bwd_kernel<DH, RC, true>, t2::BwdL<DH>::TOTAL, a, maps, g, st);
+  return launch2(t2::attn2_bwd_kernel<DH, RC, false>, t2::BwdL<DH>::TOTAL, a, maps, g, st);
 }
 
 // MEANT_EUNSUPPORTED: a view the tensor maps cannot describe (the caller falls back to the multi-tile kernels)

@@ -19,7 +19,7 @@ extern "C" void meant_reset_launch_count(void) { g_launches.store(0, std::memory
 namespace meant { long long attn_tma_fallbacks(); }
 extern "C" int64_t meant_attn_tma_fallbacks(void) { return meant::attn_tma_fallbacks(); }
 
-extern "C" int meant_version(void) { return 4; }
+extern "C" int meant_version(void) { return 5; }
 
 extern "C" int meant_attn_tcgen05_supported(const meant_attn_args* args, int dtype, int backward) {
   return args ? meant::attn_tc_supported(*args, dtype, backward) : 0;

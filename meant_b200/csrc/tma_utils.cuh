@@ -32,7 +32,10 @@ inline EncodeTiledFn encode_fn() {
 // shared memory as 128 rows of box_cols * 2 bytes with the matching swizzle (128 B rows: SWIZZLE_128B, 64 B rows:
 // SWIZZLE_64B) -- the operand sub-tile layout of attn_tc2.cu.  Rows >= S are out of bounds: zero-filled on load,
 // dropped on store.  Returns 0, or MEANT_EUNSUPPORTED when the view cannot be described.
-inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count, int H, int S, int Dh, int box_cols) {
+// box_rows x box_n2: rows of one sequence x consecutive n2 sequences per box (default: one 128-row tile of one sequence;
+// the packed-group kernels of attn_tc2.cu take gl rows of G groups, which land as tile rows g * gl + s).
+inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count, int H, int S, int Dh, int box_cols,
+                         int box_rows = 128, int box_n2 = 1) {
   EncodeTiledFn enc = encode_fn();
   if (!enc || n2_count <= 0 || N % n2_count) return MEANT_EUNSUPPORTED;
   if (reinterpret_cast<uintptr_t>(v.p) & 15) return MEANT_EUNSUPPORTED;
@@ -44,7 +47,8 @@ inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count,
     if (st[i] <= 0 || st[i] % 16 || st[i] >= ((int64_t)1 << 40)) return MEANT_EUNSUPPORTED;
     strides[i] = (cuuint64_t)st[i];
   }
-  const cuuint32_t box[5] = {(cuuint32_t)box_cols, 1u, 128u, 1u, 1u};
+  if (box_rows <= 0 || box_rows > 256 || box_n2 <= 0 || box_n2 > 256 || box_rows * box_n2 > 128) return MEANT_EUNSUPPORTED;
+  const cuuint32_t box[5] = {(cuuint32_t)box_cols, 1u, (cuuint32_t)box_rows, (cuuint32_t)box_n2, 1u};
   const cuuint32_t estr[5] = {1u, 1u, 1u, 1u, 1u};
   const CUtensorMapSwizzle sw = box_cols * 2 == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
                               : box_cols * 2 == 64  ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE;
@@ -68,15 +72,17 @@ inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count,
 }
 
 // Tensor map that lands a head tile in the unswizzled CHUNK layout of attn_tc.cu ([chunk][row][16 B], chunk stride
-// 128 * 16 B): dimensions, fastest first, (8 elements of a chunk, row s, chunk, h, n); box = 8 x 128 x Dh/8 x 1 x 1.
-// One copy per operand tile; rows >= S zero-filled on load, dropped on store.  Views with a split sequence index
-// (n2_count > 1) would need a sixth dimension: MEANT_EUNSUPPORTED.
+// 128 * 16 B): dimensions, fastest first, (8 elements of a chunk, row s, chunk of the whole row, n2, n1); box =
+// 8 x 128 x Dh/8 x 1 x 1 at chunk coordinate h * Dh/8.  The heads of a row are contiguous (sh == Dh in every view the
+// models build), so head and chunk fold into ONE dimension of H * Dh/8 chunks 16 bytes apart, which leaves room for
+// the split sequence index n = n1 * n2_count + n2 of the TimeSformer groups.  One copy per operand tile; rows >= S
+// zero-filled on load, dropped on store.  Views whose heads are not contiguous: MEANT_EUNSUPPORTED (cp.async path).
 inline int make_chunk_map(CUtensorMap* m, const HeadView& v, int N, int n2_count, int H, int S, int Dh) {
   EncodeTiledFn enc = encode_fn();
-  if (!enc || n2_count != 1 || Dh % 8) return MEANT_EUNSUPPORTED;
+  if (!enc || n2_count <= 0 || N % n2_count || Dh % 8 || v.sh != Dh) return MEANT_EUNSUPPORTED;
   if (reinterpret_cast<uintptr_t>(v.p) & 15) return MEANT_EUNSUPPORTED;
-  const cuuint64_t dims[5] = {8u, (cuuint64_t)S, (cuuint64_t)(Dh / 8), (cuuint64_t)H, (cuuint64_t)N};
-  int64_t st[4] = {v.ss * 2, 16, v.sh * 2, v.sn1 * 2};                  // bytes, dims 1..4
+  const cuuint64_t dims[5] = {8u, (cuuint64_t)S, (cuuint64_t)(H * (Dh / 8)), (cuuint64_t)n2_count, (cuuint64_t)(N / n2_count)};
+  int64_t st[4] = {v.ss * 2, 16, v.sn2 * 2, v.sn1 * 2};                 // bytes, dims 1..4
   cuuint64_t strides[4];
   for (int i = 0; i < 4; ++i) {
     if (dims[i + 1] == 1 && st[i] <= 0) st[i] = 16;

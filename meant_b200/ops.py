@@ -514,6 +514,142 @@ def attention(qkv=None, q=None, kv=None, k=None, v=None, *, heads, scale, causal
     return _AttnFn.apply(q, k, v, "q_k_v", heads, scale, causal, rot, pos_is_head, key_mask, impl)
 
 
+# ------------------------------------------------- TimeSformer divided space-time attention
+class _DividedAttnFn(torch.autograd.Function):
+    """The attention core of src/meant/timesformer_pytorch.py:108-145 on the packed [b, 1 + f*n, 3*inner] projection
+    (q | k | v), IN PLACE: the '(b n) f d' / '(b f) n d' groups of :122 are head views over that buffer
+    (n1 = b, n2 = patch or frame), the cls key / value every group attends to (:125-133, `repeat` + `cat` in the
+    reference) is the kernels' shared extra key read from the un-replicated row 0, outputs and gradients are written
+    straight into `b (f n) (h d)` buffers, and the cls query (:116-119) runs on the single-query kernels.  No
+    rearranged, repeated or concatenated copy of q, k, v or of their gradients exists."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads, scale, f, n, time_mode, rot, impl):
+        dtype = compute_dtype(qkv)
+        nv.require_cuda(qkv)
+        qkv = qkv.to(dtype)
+        if qkv.dim() != 3 or qkv.stride(-1) != 1 or qkv.stride(1) != qkv.shape[-1] or qkv.data_ptr() % 16:
+            qkv = qkv.contiguous()
+        b, tokens, w = qkv.shape
+        inner = w // 3
+        dh = inner // heads
+        if tokens != 1 + f * n or inner * 3 != w or dh * heads != inner:
+            raise ValueError(f"divided attention: {tuple(qkv.shape)} is not [b, 1 + {f}*{n}, 3 * heads * dim_head]")
+        out = torch.empty(b, tokens, inner, dtype=dtype, device=qkv.device)
+        tabs = None
+        if rot is not None:
+            tabs = tuple(r.contiguous() for r in rot)
+        ctx.cfg = (heads, float(scale), f, n, bool(time_mode), impl)
+        lse_c = torch.empty(b, heads, dtype=torch.float32, device=qkv.device)
+        nchunk = (tokens + 63) // 64
+        partial = torch.empty(b, heads, nchunk, dh + 2, dtype=torch.float32, device=qkv.device)
+        a = _DividedAttnFn._cls_args(qkv, out, lse_c, heads, scale)
+        nv.check(nv.timed(f"attn_q1_fwd/Sk{tokens}/Dh{dh}", nv.lib().meant_attn_q1_fwd, a, nv.ptr(partial), nv.dt(qkv), nv.stream()),
+                 "meant_attn_q1_fwd")
+        g, lse_g = _DividedAttnFn._group_args(qkv, out, None, heads, scale, f, n, time_mode, tabs)
+        nv.check(nv.timed(f"attn_grp_fwd/{'time' if time_mode else 'space'}/S{g.Sq}/Dh{dh}", nv.lib().meant_attn_fwd, g,
+                          nv.dt(qkv), impl, nv.stream()), "meant_attn_fwd")
+        ctx.save_for_backward(qkv, out, lse_c, lse_g, *(tabs or ()))
+        return out
+
+    @staticmethod
+    def _cls_args(qkv, out, lse_c, heads, scale):
+        """Single-query problem: row 0 of q against every row of k, v."""
+        b, tokens, w = qkv.shape
+        inner = w // 3
+        dh = inner // heads
+        a = AttnArgs()
+        a.q, a.k, a.v = (_view(qkv, c, heads, dh) for c in (0, inner, 2 * inner))
+        a.o = _view(out, 0, heads, dh)
+        a.lse = nv.ptr(lse_c)
+        a.N, a.n2_count, a.H, a.Sq, a.Sk, a.Dh = b, 1, heads, 1, tokens, dh
+        a.scale = float(scale)
+        return a
+
+    @staticmethod
+    def _group_args(qkv, out, lse_g, heads, scale, f, n, time_mode, tabs):
+        """Grouped problem over the body tokens 1..: time groups (b, patch) of f rows, or space groups (b, frame) of
+        n rows; the cls row is the shared extra key (Sk = rows + 1)."""
+        b, tokens, w = qkv.shape
+        inner = w // 3
+        dh = inner // heads
+        es = qkv.element_size()
+        rows, n2c = (f, n) if time_mode else (n, f)
+
+        def body(t, col):        # head view of the body tokens of t[b, tokens, width] at column `col`, grouped
+            width = t.stride(1)
+            sn2, ss = (width, n * width) if time_mode else (n * width, width)
+            return HeadView(t.data_ptr() + (width + col) * es, t.stride(0), sn2, ss, dh)
+
+        def xrow(t, col):        # row 0 of every batch element
+            return HeadView(t.data_ptr() + col * es, t.stride(0), 0, 0, dh)
+
+        g = AttnArgs()
+        g.q, g.k, g.v = (body(qkv, c) for c in (0, inner, 2 * inner))
+        g.kx, g.vx = xrow(qkv, inner), xrow(qkv, 2 * inner)
+        g.o = body(out, 0)
+        if lse_g is None:
+            lse_g = torch.empty(b * n2c, heads, rows, dtype=torch.float32, device=qkv.device)
+        g.lse = nv.ptr(lse_g)
+        if tabs is not None:
+            g.qcos, g.qsin, g.kcos, g.ksin = (nv.ptr(r) for r in tabs)
+            g.rot_dim = tabs[0].shape[-1]
+            if tabs[0].shape[0] < rows or tabs[2].shape[0] < rows + 1 or g.rot_dim > dh:
+                raise ValueError("rotary tables do not cover the group length / head size")
+        g.N, g.n2_count, g.H, g.Sq, g.Sk, g.Dh = b * n2c, n2c, heads, rows, rows + 1, dh
+        g.scale = float(scale)
+        return g, lse_g
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse_c, lse_g, *tabs = ctx.saved_tensors
+        heads, scale, f, n, time_mode, impl = ctx.cfg
+        tabs = tuple(tabs) or None
+        b, tokens, w = qkv.shape
+        inner = w // 3
+        dh = inner // heads
+        dout = dout.to(out.dtype).contiguous()
+        dqkv = torch.empty_like(qkv)
+        acc = _zeros(3 * b * inner, qkv.device).view(3, b, inner)          # dkx | dvx | dq of the cls row, fp32
+        # groups: dq, dk, dv of the body rows (written), gradient of the shared cls key / value (accumulated)
+        g, _ = _DividedAttnFn._group_args(qkv, out, lse_g, heads, scale, f, n, time_mode, tabs)
+        es = qkv.element_size()
+        rows, n2c = (f, n) if time_mode else (n, f)
+
+        def body(t, col):
+            width = t.stride(1)
+            sn2, ss = (width, n * width) if time_mode else (n * width, width)
+            return HeadView(t.data_ptr() + (width + col) * es, t.stride(0), sn2, ss, dh)
+
+        g.dq, g.dk, g.dv = (body(dqkv, c) for c in (0, inner, 2 * inner))
+        g.o = body(dout, 0)
+        g.out_saved = body(out, 0)
+        delta = torch.empty_like(lse_g)
+        g.delta = nv.ptr(delta)
+        g.dkx, g.dvx = nv.ptr(acc[0]), nv.ptr(acc[1])
+        nv.check(nv.timed(f"attn_grp_bwd/{'time' if time_mode else 'space'}/S{rows}/Dh{dh}", nv.lib().meant_attn_bwd, g,
+                          nv.dt(qkv), impl, nv.stream()), "meant_attn_bwd")
+        dqkv[:, 0, inner:2 * inner].copy_(acc[0])
+        dqkv[:, 0, 2 * inner:].copy_(acc[1])
+        # cls query: dq of row 0; its dk, dv are ADDED to what the groups left in every row
+        a = _DividedAttnFn._cls_args(qkv, dout, lse_c, heads, scale)      # a.o = dO
+        a.out_saved = _view(out, 0, heads, dh)
+        a.dk, a.dv = _view(dqkv, inner, heads, dh), _view(dqkv, 2 * inner, heads, dh)
+        nv.check(nv.timed(f"attn_q1_bwd/Sk{tokens}/Dh{dh}", nv.lib().meant_attn_q1_bwd, a, nv.ptr(acc[2]), 1, nv.dt(qkv),
+                          nv.stream()), "meant_attn_q1_bwd")
+        dqkv[:, 0, :inner].copy_(acc[2])
+        return dqkv, None, None, None, None, None, None, None
+
+
+def divided_attention(qkv, *, heads, scale, frames, patches, time_mode, rot=None, impl=None):
+    """TimeSformer time ('(b n) f d' groups) or space ('(b f) n d' groups) attention plus the cls query, on the packed
+    q | k | v projection [b, 1 + frames*patches, 3*heads*dim_head]; returns [b, 1 + frames*patches, heads*dim_head].
+    rot = (qcos, qsin, kcos, ksin): query tables with one row per group position, key tables with one more row (the
+    cls key, not rotated)."""
+    impl = DEFAULT_ATTN_IMPL if impl is None else impl
+    return _DividedAttnFn.apply(qkv, heads, scale, frames, patches, time_mode, rot, impl)
+
+
 # ------------------------------------------------------------------- pooling, GEGLU, shift
 class _MeanPoolFn(torch.autograd.Function):
     @staticmethod

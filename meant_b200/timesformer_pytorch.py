@@ -43,10 +43,11 @@ class _AxialRotary(nn.Module):
 
 
 def _with_cls_row(cos, sin):
-    """Key-side tables for [cls, tokens...]: row 0 is the identity rotation (the cls key is
-    concatenated un-rotated, src/meant/timesformer_pytorch.py:125-133)."""
+    """Key-side tables for [tokens..., cls]: the last row is the identity rotation (the cls key joins every group
+    un-rotated, src/meant/timesformer_pytorch.py:125-133; softmax attention does not depend on the key order, and the
+    kernels take the shared cls row as the LAST key)."""
     one = torch.ones_like(cos[:1])
-    return torch.cat((one, cos), 0).contiguous(), torch.cat((torch.zeros_like(sin[:1]), sin), 0).contiguous()
+    return torch.cat((cos, one), 0).contiguous(), torch.cat((sin, torch.zeros_like(sin[:1])), 0).contiguous()
 
 
 class PreNorm(nn.Module):
@@ -101,9 +102,7 @@ class Attention(nn.Module):
     def forward(self, x, einops_from=None, einops_to=None, mask=None, cls_mask=None, rot_emb=None, **dims):
         if mask is not None or cls_mask is not None:
             raise NotImplementedError("frame masks are not used on the MEANT path (meant_forward passes none)")
-        b, ntok, _ = x.shape
-        h, dh = self.heads, self.dim_head
-        inner = h * dh
+        ntok = x.shape[1]
         time_mode = einops_to.replace(" ", "").startswith("(bn)")
         if time_mode:
             n = dims['n']
@@ -111,29 +110,15 @@ class Attention(nn.Module):
         else:
             f = dims['f']
             n = (ntok - 1) // f
-        qkv = self.to_qkv(x)                                     # [b, 1+f*n, 3*inner], packed q|k|v
-        q, k, v = qkv[..., :inner], qkv[..., inner:2 * inner], qkv[..., 2 * inner:]
-        # the cls query sees every key (:119)
-        cls_out = ops.attention(q=q[:, :1], k=k, v=v, heads=h, scale=self.scale)
-
-        def groups(t):                                           # body tokens -> [groups, len, inner]
-            t = t[:, 1:].reshape(b, f, n, inner)
-            return t.transpose(1, 2).reshape(b * n, f, inner) if time_mode else t.reshape(b * f, n, inner)
-
-        g = b * n if time_mode else b * f
-        rep = g // b
-        qg = groups(q)
-        kg = torch.cat((k[:, :1].repeat_interleave(rep, dim=0), groups(k)), dim=1)
-        vg = torch.cat((v[:, :1].repeat_interleave(rep, dim=0), groups(v)), dim=1)
+        qkv = self.to_qkv(x)                                     # [b, 1 + f*n, 3*inner], packed q | k | v
         rot = None
         if rot_emb is not None:
             cos, sin = rot_emb
             kc, ks = _with_cls_row(cos, sin)
             rot = (cos, sin, kc, ks)
-        og = ops.attention(q=qg, k=kg, v=vg, heads=h, scale=self.scale, rot=rot)
-        if time_mode:
-            og = og.reshape(b, n, f, inner).transpose(1, 2)
-        out = torch.cat((cls_out, og.reshape(b, f * n, inner)), dim=1)
+        # cls query over every key (:119) + the grouped attention (:122-139), read and written in place
+        out = ops.divided_attention(qkv, heads=self.heads, scale=self.scale, frames=f, patches=n, time_mode=time_mode,
+                                    rot=rot)
         return self.to_out(out)
 
 

@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/meant_b200.h but not exported"
     assert set(names) == set(nv.SIGNATURES), set(names) ^ set(nv.SIGNATURES)
-    assert lib.meant_version() == nv.ABI_VERSION == 4
+    assert lib.meant_version() == nv.ABI_VERSION == 5
 
 
 def test_argument_errors_are_codes_not_crashes():
@@ -47,7 +47,7 @@ def test_argument_errors_are_codes_not_crashes():
 def test_attn_args_struct_layout_matches_header():
     # 8 head views of 40 bytes, 7 pointers, 9 ints, 1 float (+ tail padding to 8)
     assert ctypes.sizeof(nv.HeadView) == 40
-    assert ctypes.sizeof(nv.AttnArgs) == 8 * 40 + 7 * 8 + 10 * 4 + 2 * 40
+    assert ctypes.sizeof(nv.AttnArgs) == 8 * 40 + 7 * 8 + 10 * 4 + 2 * 40 + 2 * 40 + 2 * 8
 
 
 @pytest.mark.parametrize("name", [c[0] for c in cases.CASES])
