@@ -21,6 +21,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 import torch  # noqa: E402
 
@@ -42,6 +43,10 @@ def parse():
     ap.add_argument("--graph", type=int, default=1, help="capture the step into a CUDA graph")
     ap.add_argument("--gemm", default="library", choices=["library", "native"],
                     help="forward GEMM of the Linear layers: cuBLASLt (default) or the hand-written tcgen05 kernel")
+    ap.add_argument("--configs", default="auto",
+                    help="extra BASELINE configs measured in the same process and reported in the `configs` array: "
+                         "auto (N=1: vision,timesformer,full12,full,long; N>1: full), none, or a comma list")
+    ap.add_argument("--config-steps", type=int, default=5)
     return ap.parse_args()
 
 
@@ -95,8 +100,11 @@ def cpu_reference_run(args, steps, warmup):
             times.append(time.perf_counter() - t0)
     sec = sum(times) / len(times)
     return {"value": args.cpu_batch / sec, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{steps} steps of {args.cpu_batch} samples (fwd+bwd+clip+AdamW, fp32, eval-mode "
-                      f"dropout, {args.encoders} encoders), {sec:.2f} s/step"}, sec
+            "sample": f"{steps} steps of batch {args.cpu_batch} (the GPU arm steps batch {args.batch} per GPU), "
+                      f"fwd+bwd+clip+AdamW in fp32, {args.encoders} encoders, {sec:.2f} s/step.  Two things understate "
+                      f"the CPU rate slightly: the oracle runs eval-mode dropout (identity) while the GPU arm trains "
+                      f"with dropout on, and the per-step cost of clip + AdamW over all {sum(v.numel() for v in leaves) / 1e6:.0f} M "
+                      f"parameters is spread over {args.cpu_batch} samples instead of {args.batch}"}, sec
 
 
 # ------------------------------------------------------------------------------ clock sampling
@@ -150,9 +158,12 @@ def kernel_stats(timers):
     return out
 
 
-# ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch of the dominant kernels at THIS workload
-# (profiles/r1h_attn2_summary.txt; N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
+# ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch of the dominant kernels at THIS workload, read from a
+# committed `ncu --set full` capture (N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
+# It is a profile-derived constant, NOT a measurement of the run that prints it: `traffic_source` says so in the line.
 NCU_TRAFFIC = {"attn_fwd": 581.6e6, "attn_bwd": 1017.6e6}
+NCU_TRAFFIC_SOURCE = "profiles/r1n_ncu/r1n_attn128_summary.txt (ncu --set full capture of this kernel at this shape, scaled by " \
+                     "sequences/768; not re-measured by this run)"
 
 
 def rooflines(args, stats, steps):
@@ -175,7 +186,7 @@ def rooflines(args, stats, steps):
             scale_n = nseq / 768.0
             r = {"kernel": name, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
                  "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["attn_bwd" if bwd else "attn_fwd"] * scale_n,
-                 "avg_ms": round(ms, 4), "launches_per_step": count / steps, "peak_source": src,
+                 "traffic_source": NCU_TRAFFIC_SOURCE, "avg_ms": round(ms, 4), "launches_per_step": count / steps, "peak_source": src,
                  "algorithmic_bytes_per_launch": byts}
             fl = flops_fwd * (2.0 if bwd else 1.0)
             tf = fl / (ms * 1e-3) / 1e12
@@ -242,6 +253,72 @@ def gemm_probe(args, dev):
                     "frac": round(ach / tf_sus, 4), "traffic": None, "avg_ms": round(times["native"], 4),
                     "library_same_problem_tflops": round(fl / (times["library"] * 1e-3) / 1e12, 1),
                     "peak_source": src + ", sustained"})
+    return out
+
+
+def extra_configs(args, dev, rank, world, barrier, max_over_ranks):
+    """configs[2..4] of BASELINE.json (and the north star's full-modality lag-12 step) through the same TrainStep, a
+    few steps each, in this process: ms/step, samples/s, the step's kernel-time split and a tensor-core roofline object
+    for every attention kernel of the config (FLOPs per SURVEY.md 8d), the dominant one first."""
+    import gc
+    import cfg_models
+    from meant_b200 import _native as nv
+    from meant_b200.train import TrainStep
+    names = args.configs
+    if names == "auto":
+        names = "vision,timesformer,full12,full,long" if world == 1 else "full"
+    if names in ("none", ""):
+        return []
+    _, tf_burst, tf_sus, src = peaks()
+    out = []
+    for what in names.split(","):
+        batch = cfg_models.DEFAULT_BATCH[what]
+        torch.manual_seed(0)
+        model, labels, inputs, desc, shapes = cfg_models.build(what, batch, dev, encoders=args.encoders, seed=1234 + rank)
+        model = model.to(dev).train()
+        step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=2)
+        for _ in range(4 if step.graph else 3):       # eager warm-up, capture, one replay
+            step(labels, *inputs)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.config_steps):
+            step(labels, *inputs)
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1)) / args.config_steps
+        row = {"config": desc, "batch_per_gpu": batch, "n_gpus": world, "steps": args.config_steps,
+               "ms_per_step": round(ms, 3), "value": round(batch * world / (ms * 1e-3), 1), "unit": UNIT,
+               "launch": "CUDA graph replay" if step.graph else "eager"}
+        if rank == 0:
+            nv.enable_timers(True)
+            step._step(labels, inputs, {})            # one eager pass of the same step: per-kernel CUDA events
+            torch.cuda.synchronize()
+            stats = kernel_stats(nv.timers())
+            nv.enable_timers(False)
+            att = []
+            for tag, sq, sk, dh, seqs, causal in shapes:
+                for name, (kms, count) in sorted(stats.items()):
+                    if not name.startswith("attn_") or tag not in name or "q1" in name or "prerotate" in name:
+                        continue
+                    bwd = "_bwd" in name
+                    fl = cfg_models.attention_flops(sq, sk, dh, HEADS, seqs, causal, bwd)
+                    tf = fl / (kms * 1e-3) / 1e12
+                    att.append({"kernel": name, "bound": "tensor", "achieved": round(tf, 2), "peak": tf_sus, "unit": "TFLOP/s",
+                                "frac": round(tf / tf_sus, 4), "traffic": None, "avg_ms": round(kms, 4),
+                                "launches_per_step": count, "ms_per_step": round(kms * count, 3),
+                                "algorithmic_flops_per_launch": fl, "peak_source": src + ", sustained"})
+            att.sort(key=lambda r: -r["ms_per_step"])
+            row["roofline"] = att[0] if att else None
+            row["attention_kernels"] = att
+            row["aux_kernels_ms"] = {k: round(v[0] * v[1], 3) for k, v in stats.items()
+                                     if k.startswith("attn_") and ("q1" in k or "prerotate" in k)}
+            row["step_split_ms"] = cfg_models.step_split_ms(lambda: step._step(labels, inputs, {}))
+        out.append(row)
+        step.close()
+        del step, model, labels, inputs
+        gc.collect()
+        torch.cuda.empty_cache()
     return out
 
 
@@ -334,6 +411,11 @@ def gpu_run(args):
         stats = kernel_stats(nv.timers())
         nv.enable_timers(False)
     gemm_rows = gemm_probe(args, dev) if rank == 0 else []
+    split = None
+    if rank == 0:
+        import cfg_models
+        split = cfg_models.step_split_ms(lambda: step._step(d_labels, (d_tweets, d_mask), {}))
+    cfg_rows = extra_configs(args, dev, rank, world, barrier, max_over_ranks)
     if rank == 0:
         n = world
         total = args.batch * n * args.steps
@@ -348,6 +430,7 @@ def gpu_run(args):
                         "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in (h_tweets, h_mask, h_labels)),
                         "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e / args.steps, 3)},
                 "gpu_launches": int(launches), "clocks": clocks, "roofline": main, "roofline_extra": extra,
+                "step_split_ms": split, "configs": cfg_rows,
                 "final_loss": loss_host, "native_library": os.path.relpath(nv.lib_path(), ROOT),
                 "attn_tma_fallbacks": int(nv.lib().meant_attn_tma_fallbacks())}
         if n == 1 and not args.no_cpu_baseline:
@@ -369,8 +452,8 @@ def reference_run(args):
         return
     base, sec = cpu_reference_run(args, steps=args.steps, warmup=args.warmup)
     cfg = workload_config(args, args.gpus)
-    cfg["note"] = "CPU arm: same model/config, bounded batch per step (cpu_baseline.sample)"
-    print(json.dumps({"impl": "reference", "metric": METRIC, "value": round(base["value"], 4), "unit": UNIT,
+    print(json.dumps({"impl": "reference", "note": "CPU arm: same model/config, bounded batch per step (cpu_baseline.sample)",
+                      "metric": METRIC, "value": round(base["value"], 4), "unit": UNIT,
                       "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                       "ms_per_step": round(sec * 1e3, 2), "higher_is_better": True, "scaling": "weak",
                       "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,

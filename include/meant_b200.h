@@ -170,6 +170,64 @@ int meant_embedding_bwd(const int64_t* ids, const void* dy, float* dW, int64_t t
 int meant_gemm_bf16_tn(const void* A, const void* W, const float* bias, void* C, int64_t M, int N, int K,
                        int64_t lda, int64_t ldw, int64_t ldc, meant_stream_t stream);
 
+/* ---- the step after backward: src/in_loop_train.py:237-244 (CrossEntropyLoss on the sigmoid outputs, clip_grad_norm_(1.0),
+ *      AdamW: :568), as multi-tensor kernels.  A launch takes a BY-VALUE table of up to MEANT_OPT_MAX_TENSORS fp32 tensors
+ *      cut into MEANT_OPT_CHUNK-element chunks: block i of the launch works on chunk block_chunk[i] of tensor
+ *      block_tensor[i] (n_blocks <= MEANT_OPT_MAX_BLOCKS); the caller issues as many launches as the parameter list needs. */
+#define MEANT_OPT_CHUNK 65536
+#define MEANT_OPT_MAX_TENSORS 48
+#define MEANT_OPT_MAX_BLOCKS 320
+typedef struct {
+  void* p[MEANT_OPT_MAX_TENSORS];       /* parameters (fp32, updated in place); unused by meant_multi_sqnorm   */
+  void* g[MEANT_OPT_MAX_TENSORS];       /* gradients (fp32)                                                    */
+  void* m[MEANT_OPT_MAX_TENSORS];       /* exp_avg (fp32)                                                      */
+  void* v[MEANT_OPT_MAX_TENSORS];       /* exp_avg_sq (fp32)                                                   */
+  void* shadow[MEANT_OPT_MAX_TENSORS];  /* optional bf16 copy of the updated parameter (NULL: none)            */
+  int64_t numel[MEANT_OPT_MAX_TENSORS];
+  int32_t block_chunk[MEANT_OPT_MAX_BLOCKS];
+  uint8_t block_tensor[MEANT_OPT_MAX_BLOCKS];
+  int32_t n_tensors, n_blocks;
+} meant_tensor_table;
+
+/* *sumsq (device, fp32) += sum over the table's gradients of g^2: the squared total norm of clip_grad_norm_.          */
+int meant_multi_sqnorm(const meant_tensor_table* table, float* sumsq, meant_stream_t stream);
+/* torch.optim.AdamW (decoupled weight decay, bias correction) on every tensor of the table.  *step (device) is the 1-based
+ * step count t; sumsq (optional, device) is the finished squared gradient norm: gradients are used as
+ * g * min(1, max_norm / (sqrt(*sumsq) + 1e-6)), i.e. clip_grad_norm_(max_norm) without a pass that rescales them.     */
+int meant_adamw_step(const meant_tensor_table* table, const float* step, const float* sumsq, float lr, float beta1,
+                     float beta2, float eps, float weight_decay, float max_norm, meant_stream_t stream);
+/* *loss = mean_i CrossEntropy(probs[i, :], target[i]) over B rows of C values (the reference feeds the model's sigmoid
+ * outputs to nn.CrossEntropyLoss, src/in_loop_train.py:237); dprobs (optional) = grad_scale * d loss / d probs.        */
+int meant_prob_ce(const float* probs, const int64_t* target, float* loss, float* dprobs, int B, int C, float grad_scale,
+                  meant_stream_t stream);
+
+/* ---- softmax-weighted pooling head of the `src` tree (src/meant/meant_tweet.py:173,259-261 lang_prep;
+ *      src/meant/meant_timesformer.py:274-279,335-345 lang_prep / image_prep):
+ *        w = Softmax(dim=2)(Linear(d,1)(GELU(LayerNorm(h)))),  out[n, :] = sum_t w[n, t] x[n, t, :],  h = Linear(d,d)(x)
+ *      x, h: [N, S, d] (the first Linear is the caller's GEMM); prob [N, S] receives w for the backward pass.
+ *      degenerate != 0: Softmax over an axis of length one (what the reference's image_prep does on its 3-D input):
+ *      every weight is 1, out = sum_t x[n, t, :], h and the parameters are not read.
+ *      Backward: dx is the gradient through the weighted sum only (the caller adds the Linear(d,d) path);
+ *      dln_w, dln_b, dw2 [d] fp32 are accumulated atomically (zero on entry).  d = 256, 512, 768 or 1024. --------- */
+int meant_softmax_pool_fwd(const void* x, const void* h, const float* ln_w, const float* ln_b, float ln_eps,
+                           const float* w2, float b2, void* out, float* prob, int64_t N, int S, int d,
+                           int degenerate, int dtype, meant_stream_t stream);
+int meant_softmax_pool_bwd(const void* dout, const void* x, const void* h, const float* ln_w, const float* ln_b,
+                           float ln_eps, const float* w2, const float* prob, void* dx, void* dh, float* dln_w,
+                           float* dln_b, float* dw2, int64_t N, int S, int d, int degenerate, int dtype,
+                           meant_stream_t stream);
+
+/* ---- token cross entropy of the MLM head (pretrain_mlm.py:154,182: nn.CrossEntropyLoss()(out.view(-1, vocab),
+ *      target.view(-1)), ignore_index): *loss_sum += sum over counted rows of (logsumexp - logit[target]), *count +=
+ *      counted rows (both fp32 device scalars, zero on entry; loss = loss_sum / count), lse[rows] kept for the backward
+ *      pass, which writes dlogits = *dloss / *count * (softmax - onehot) (0 for ignored rows; may alias logits).
+ *      ld: row pitch in elements. ------------------------------------------------------------------------------ */
+int meant_token_ce_fwd(const void* logits, const int64_t* target, float* lse, float* loss_sum, float* count,
+                       int64_t rows, int64_t V, int64_t ld, int64_t ignore_index, int dtype, meant_stream_t stream);
+int meant_token_ce_bwd(const void* logits, const int64_t* target, const float* lse, const float* count,
+                       const float* dloss, void* dlogits, int64_t rows, int64_t V, int64_t ld, int64_t ignore_index,
+                       int dtype, meant_stream_t stream);
+
 /* ---- tcgen05 self-test: D[128,N] (fp32) = op(A) op(B)^T for one bf16 tile; a_mn / b_mn select
  *      MN-major operands (A given as [K,128], B as [K,N]) instead of K-major ([128,K], [N,K]).
  *      Exists so the tests can pin the descriptor conventions the attention kernels rely on. */

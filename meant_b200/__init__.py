@@ -15,9 +15,12 @@ from .temporal import temporal, temporal_src
 from .rms_norm import RMSNorm
 from .rotary_embedding_torch import RotaryEmbedding
 from .timesformer_pytorch import TimeSformer, dividedSpaceTimeAttention
+from .heads import make_prep, softmax_pool, token_cross_entropy, meant_vision_pretrainer
+from .optim import FusedAdamW, prob_cross_entropy
 from . import ops
 
 __all__ = ["attention", "flash_attention", "meant", "languageEncoder", "visionEncoder", "temporalEncoder",
            "meant_vision", "meant_tweet", "meant_vqa", "meant_language_pretrainer", "xPosAttention",
            "xPosAttention_flash", "temporal", "temporal_src", "RMSNorm", "RotaryEmbedding", "TimeSformer",
-           "dividedSpaceTimeAttention", "ops"]
+           "dividedSpaceTimeAttention", "make_prep", "softmax_pool", "token_cross_entropy", "meant_vision_pretrainer",
+           "FusedAdamW", "prob_cross_entropy", "ops"]

@@ -32,6 +32,16 @@ class AttnArgs(C.Structure):
                 ("kx", HeadView), ("vx", HeadView), ("dkx", vp), ("dvx", vp)]
 
 
+OPT_CHUNK, OPT_MAX_TENSORS, OPT_MAX_BLOCKS = 65536, 48, 320
+
+
+class TensorTable(C.Structure):
+    _fields_ = [("p", vp * OPT_MAX_TENSORS), ("g", vp * OPT_MAX_TENSORS), ("m", vp * OPT_MAX_TENSORS),
+                ("v", vp * OPT_MAX_TENSORS), ("shadow", vp * OPT_MAX_TENSORS), ("numel", i64 * OPT_MAX_TENSORS),
+                ("block_chunk", C.c_int32 * OPT_MAX_BLOCKS), ("block_tensor", C.c_uint8 * OPT_MAX_BLOCKS),
+                ("n_tensors", C.c_int32), ("n_blocks", C.c_int32)]
+
+
 # name -> (restype, argtypes); mirrors include/meant_b200.h one to one
 SIGNATURES = {
     "meant_version": (i32, []),
@@ -57,6 +67,13 @@ SIGNATURES = {
     "meant_geglu_fwd": (i32, [vp, vp, i64, i32, i32, vp]),
     "meant_geglu_bwd": (i32, [vp, vp, vp, i64, i32, i32, vp]),
     "meant_token_shift": (i32, [vp, vp, i32, i32, i32, i32, i32, i32, vp]),
+    "meant_multi_sqnorm": (i32, [C.POINTER(TensorTable), vp, vp]),
+    "meant_adamw_step": (i32, [C.POINTER(TensorTable), vp, vp, f32, f32, f32, f32, f32, f32, vp]),
+    "meant_prob_ce": (i32, [vp, vp, vp, vp, i32, i32, f32, vp]),
+    "meant_softmax_pool_fwd": (i32, [vp, vp, vp, vp, f32, vp, f32, vp, vp, i64, i32, i32, i32, i32, vp]),
+    "meant_softmax_pool_bwd": (i32, [vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i32, i32, vp]),
+    "meant_token_ce_fwd": (i32, [vp, vp, vp, vp, vp, i64, i64, i64, i64, i32, vp]),
+    "meant_token_ce_bwd": (i32, [vp, vp, vp, vp, vp, vp, i64, i64, i64, i64, i32, vp]),
     "meant_tc_probe": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     "meant_tc_probe_sw": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
 }

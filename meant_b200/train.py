@@ -6,6 +6,7 @@ import torch.distributed as dist
 import torch.nn.functional as F
 
 from .ddp import BucketedGradAllReduce, broadcast_parameters
+from .optim import FusedAdamW, prob_cross_entropy
 
 
 class TrainStep:
@@ -17,7 +18,7 @@ class TrainStep:
     (ops.use_fused_linear).  Input shapes and non-tensor arguments must not change between calls."""
 
     def __init__(self, model, lr=5e-5, betas=(0.9, 0.999), weight_decay=0.0, max_grad_norm=1.0,
-                 bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3):
+                 bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3, own_optimizer=True):
         self.model = model
         self.bf16 = bf16
         self.max_grad_norm = max_grad_norm
@@ -26,8 +27,6 @@ class TrainStep:
         self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group)
         fused = self._fused = self.params[0].is_cuda
         self.graph = bool(graph) and fused
-        self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused,
-                                     capturable=self.graph)
         self._graph_warmup, self._calls = int(graph_warmup), 0
         self._g = self._static = self._loss = self._seed_t = None
         self.launches_per_replay = 0            # native-library launches captured in one step
@@ -38,6 +37,22 @@ class TrainStep:
             if bf16:
                 self._build_shadows()
             self._arena = torch.zeros(1 << 20, dtype=torch.float32, device=self.params[0].device)
+        # The step after backward on the library's multi-tensor kernels (optim.py: gradient norm, clip + AdamW, the bf16
+        # weight shadows written by the update itself) -- or torch's optimizer (CPU tensors: the gloo tests)
+        self._own = bool(own_optimizer) and fused and all(p.dtype == torch.float32 and p.is_contiguous() for p in self.params)
+        if self._own:
+            self.opt = FusedAdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, max_norm=max_grad_norm or 0.0,
+                                  shadows=self._shadows)
+            self.refresh_shadows()
+        else:
+            self.opt = torch.optim.AdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, fused=fused,
+                                         capturable=self.graph)
+
+    def refresh_shadows(self):
+        """Re-derive the bf16 weight shadows from the fp32 parameters.  With the library's optimizer the update keeps
+        them current, so this runs once here -- call it again after changing parameters from outside (load_state_dict)."""
+        if self._shadow_src:
+            torch._foreach_copy_(self._shadow_dst, self._shadow_src)
 
     def _build_shadows(self):
         """bf16 copies of every nn.Linear weight / bias, refreshed by ONE multi-tensor cast per step; the q, v, k
@@ -73,7 +88,7 @@ class TrainStep:
 
     def _step(self, labels, args, kwargs):
         from . import ops
-        if self._shadow_src:
+        if self._shadow_src and not self._own:
             torch._foreach_copy_(self._shadow_dst, self._shadow_src)
         if self._arena is not None:
             self._arena.zero_()
@@ -90,9 +105,12 @@ class TrainStep:
         device_type = "cuda" if self.params[0].is_cuda else "cpu"
         with torch.autocast(device_type, dtype=torch.bfloat16, enabled=self.bf16 and device_type == "cuda"):
             out = self.model(*args, **kwargs)
-        loss = F.cross_entropy(out.float(), labels)
+        loss = prob_cross_entropy(out, labels) if self._own else F.cross_entropy(out.float(), labels)
         loss.backward()
         self.reducer.finish()
+        if self._own:
+            self.opt.step()                      # gradient norm + clip + AdamW (+ shadows): optim.py
+            return loss.detach()
         if self.max_grad_norm and self._fused:
             # clip_grad_norm_ without its own pass over the gradients: fused AdamW divides every gradient by
             # `grad_scale` (and writes it back) inside its update kernel, so the clip coefficient rides along

@@ -197,7 +197,8 @@ def test_norm_backward_supplies_linear_bias_gradient():
         assert float((x1 - x0).abs().max()) <= 2e-2 * max(1.0, float(x0.abs().max()))
 
 
-def test_clip_folded_into_adamw_matches_clip_grad_norm():
+@pytest.mark.parametrize("own", [True, False])
+def test_clip_folded_into_adamw_matches_clip_grad_norm(own):
     from meant_b200.train import TrainStep
     torch.manual_seed(0)
     ref = nn.Sequential(nn.Linear(64, 64), nn.Tanh(), nn.Linear(64, 3)).cuda()
@@ -206,7 +207,7 @@ def test_clip_folded_into_adamw_matches_clip_grad_norm():
     x = torch.randn(32, 64, device="cuda") * 30.0            # large gradients: the clip is active
     y = torch.randint(0, 3, (32,), device="cuda")
     opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.0, fused=True)
-    step = TrainStep(mine, lr=1e-2, bf16=False, max_grad_norm=1.0)
+    step = TrainStep(mine, lr=1e-2, bf16=False, max_grad_norm=1.0, own_optimizer=own)
     for _ in range(3):
         opt.zero_grad()
         F.cross_entropy(ref(x), y).backward()
@@ -216,7 +217,8 @@ def test_clip_folded_into_adamw_matches_clip_grad_norm():
     assert float(norm) > 1.0
     for a, b in zip(ref.parameters(), mine.parameters()):
         assert torch.allclose(a, b, atol=1e-6, rtol=1e-5)
-        assert torch.allclose(a.grad, b.grad, atol=1e-7, rtol=1e-4)       # the clipped gradient is written back
+        if not own:   # torch's fused AdamW writes the clipped gradient back; the library's update leaves gradients alone
+            assert torch.allclose(a.grad, b.grad, atol=1e-7, rtol=1e-4)
 
 
 def test_native_gemm_in_the_linear_wrapper():

@@ -24,68 +24,18 @@ import meant_b200 as mb  # noqa: E402
 from meant_b200 import _native as nv  # noqa: E402
 from meant_b200.train import TrainStep  # noqa: E402
 
-DIM, HEADS, VOCAB, CLASSES = 768, 8, 64001, 2
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import cfg_models  # noqa: E402
 
 
 def build(a, dev):
-    g = torch.Generator().manual_seed(1234)
-    b = a.batch
-    labels = torch.randint(0, CLASSES, (b,), generator=g).to(dev)
-    if a.what == "vision":
-        lag = 12
-        model = mb.meant_vision(DIM, 4, 224, 224, 16, lag, CLASSES, num_encoders=a.encoders)
-        images = torch.randn(b, lag, 4, 224, 224, generator=g).to(dev)
-        return model, labels, (images,), {}, f"meant_vision lag=12 224x224/16 C=4 B={b} encoders={a.encoders}"
-    if a.what == "timesformer":
-        from meant_b200.timesformer_pytorch import TimeSformer
-        frames = 12
-
-        class Wrap(nn.Module):   # meant_forward returns tokens; pool + classify so that a training step exists
-            def __init__(self):
-                super().__init__()
-                self.body = TimeSformer(dim=DIM, num_frames=frames, num_classes=CLASSES, image_size=224, patch_size=16,
-                                        depth=a.depth, heads=8, dim_head=64)
-                self.head = nn.Linear(DIM, CLASSES)
-
-            def forward(self, video):
-                return torch.sigmoid(self.head(self.body.meant_forward(video).mean(dim=1).float()))
-
-        video = torch.randn(b, frames, 3, 224, 224, generator=g).to(dev)
-        return Wrap(), labels, (video,), {}, f"TimeSformer.meant_forward 12 frames 224x224/16 B={b} depth={a.depth}"
-    if a.what == "full":
-        lag, s = 24, 128
-        model = mb.meant(DIM, DIM, 4, 224, 224, 16, lag, CLASSES, nn.Embedding(VOCAB, DIM), num_encoders=a.encoders)
-        tweets = torch.randint(0, VOCAB, (b, lag, s), generator=g).to(dev)
-        cut = torch.randint(0, s // 4 + 1, (b, lag, 1), generator=g)
-        mask = (torch.arange(s).view(1, 1, s) < (s - cut)).float().to(dev)
-        images = torch.randn(b, lag, 4, 224, 224, generator=g).to(dev)
-        return model, labels, (tweets, images, mask), {}, f"meant lag=24 S=128 + 224x224/16 C=4 B={b} encoders={a.encoders}"
-    # long: the S = 512 causal xPos language stack of meant_vqa / the MLM pre-trainer (configs[4])
-    s = 512
-
-    class Stack(nn.Module):
-        def __init__(self):
-            super().__init__()
-            self.embedding = nn.Embedding(VOCAB, DIM)
-            self.languageEncoders = nn.ModuleList([mb.languageEncoder(DIM, HEADS) for _ in range(a.encoders)])
-            self.head = nn.Linear(DIM, CLASSES)
-
-        def forward(self, ids, mask):
-            from meant_b200 import ops
-            x = ops.embed(self.embedding, ids)
-            for enc in self.languageEncoders:
-                x = enc(x, attention_mask=mask)
-            return torch.sigmoid(self.head(x.mean(dim=1).float()))
-
-    ids = torch.randint(0, VOCAB, (b, s), generator=g).to(dev)
-    cut = torch.randint(0, s // 4 + 1, (b, 1), generator=g)
-    mask = (torch.arange(s).view(1, s) < (s - cut)).float().to(dev)
-    return Stack(), labels, (ids, mask), {}, f"languageEncoder x{a.encoders} S=512 causal xPos B={b}"
+    model, labels, args, desc, _ = cfg_models.build(a.what, a.batch, dev, encoders=a.encoders, depth=a.depth)
+    return model, labels, args, {}, desc
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["vision", "timesformer", "full", "long"])
+    ap.add_argument("what", choices=["vision", "timesformer", "full", "full12", "long"])
     ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--encoders", type=int, default=12)
     ap.add_argument("--depth", type=int, default=1)
@@ -95,7 +45,7 @@ def main():
     ap.add_argument("--attn-impl", default="auto", choices=["auto", "exact", "tcgen05"])
     a = ap.parse_args()
     if a.batch is None:
-        a.batch = {"vision": 16, "timesformer": 8, "full": 16, "long": 32}[a.what]
+        a.batch = cfg_models.DEFAULT_BATCH[a.what]
     from meant_b200 import ops
     ops.DEFAULT_ATTN_IMPL = {"auto": nv.IMPL_AUTO, "exact": nv.IMPL_EXACT, "tcgen05": nv.IMPL_TCGEN05}[a.attn_impl]
     dev = torch.device("cuda", 0)

@@ -153,6 +153,8 @@ if __name__ == "__main__":
     ap.add_argument("--causal", type=int, default=1)
     ap.add_argument("--norot", action="store_true")
     ap.add_argument("--impl", default="auto")
+    ap.add_argument("--prerotate", type=int, default=1, help="multi-tile attention: rotate Q, K once into scratch (0: in the kernels)")
     a = ap.parse_args()
     a.causal = bool(a.causal)
+    ops.PREROTATE = bool(a.prerotate)
     {"attn": attn, "norm": norm, "gemm": gemm}[a.what](a)
