@@ -164,6 +164,29 @@ int meant_embedding_fwd(const int64_t* ids, const float* W, void* out, int64_t t
 int meant_embedding_bwd(const int64_t* ids, const void* dy, float* dW, int64_t tokens, int D, int64_t vocab,
                         int dtype, meant_stream_t stream);
 
+/* ---- patchify, the im2col operand of the patch-embedding GEMM: 'b c (h p1) (w p2) -> b (h w) (p1 p2 c)'
+ *      (meant/meant.py:193-195; src/meant/timesformer_pytorch.py:219-220 per frame) fused with the cast to out_dtype.
+ *      in [B, C, H, W] -> out [B, (H/P)(W/P), P*P*C]; transpose != 0: the adjoint, in = patches, out = image layout. -- */
+int meant_patchify(const void* in, void* out, int64_t B, int C, int H, int W, int P, int in_dtype, int out_dtype,
+                   int transpose, meant_stream_t stream);
+
+/* ---- the BERTweet / RoBERTa embedding block the reference hands to its text models as `embedding`
+ *      (src/in_loop_train.py:440,486-496 `embedding=bertweet.embeddings`, applied at meant/meant.py:211-212):
+ *        pos = cumsum(ids != pad) * (ids != pad) + pad;  out = Dropout(LayerNorm(word[ids] + position[pos] + type[0]))
+ *      ids [N, S]; word / pos / type tables and LayerNorm parameters fp32; out [N, S, d] in `dtype`; pos_ids, mean, rstd
+ *      [N, S] are kept for the backward pass, which scatter-adds into dword [vocab, d], dpos [max_pos, d] and accumulates
+ *      dtype_row, dln_w, dln_b [d] (all fp32, zero on entry).  d = 256, 512, 768 or 1024.  drop_p / seed / seed_dev as in
+ *      meant_rmsnorm_fwd.  Ids outside [0, vocab) produce LayerNorm(0) rows and receive no gradient. --------------- */
+int meant_embed_ln_fwd(const int64_t* ids, const float* word, const float* pos, const float* type, const float* ln_w,
+                       const float* ln_b, float eps, void* out, int* pos_ids, float* mean, float* rstd, int64_t N, int S,
+                       int d, int64_t vocab, int max_pos, int pad_idx, float drop_p, uint64_t seed,
+                       const uint64_t* seed_dev, int dtype, meant_stream_t stream);
+int meant_embed_ln_bwd(const void* dy, const int64_t* ids, const int* pos_ids, const float* mean, const float* rstd,
+                       const float* word, const float* pos, const float* type, const float* ln_w, float* dword,
+                       float* dpos, float* dtype_row, float* dln_w, float* dln_b, int64_t N, int S, int d, int64_t vocab,
+                       int max_pos, float drop_p, uint64_t seed, const uint64_t* seed_dev, int dtype,
+                       meant_stream_t stream);
+
 /* ---- nn.Linear forward as a hand-written tcgen05 GEMM (meant/meant.py:61-66, meant/xPosAttention.py:24-28):
  *      C[M, N] (bf16) = A[M, K] (bf16) * W[N, K]^T (bf16, nn.Linear's weight layout) + bias[N] (fp32, optional).
  *      lda / ldw / ldc: row pitches in elements.  N and K multiples of 8; pointers 16-byte aligned. ---------- */

@@ -53,6 +53,10 @@ SIGNATURES = {
     "meant_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i64, i32, i32, i64, i64, i64, vp]),
     "meant_embedding_fwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
     "meant_embedding_bwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
+    "meant_patchify": (i32, [vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "meant_embed_ln_fwd": (i32, [vp, vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i64, i32, i32, i64, i32, i32, f32, u64, vp, i32, vp]),
+    "meant_embed_ln_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, i64, i32, f32, u64, vp,
+                                 i32, vp]),
     "meant_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp]),
     "meant_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, i32, vp]),
     "meant_attn_fwd": (i32, [C.POINTER(AttnArgs), i32, i32, vp]),

@@ -239,9 +239,58 @@ __global__ void __launch_bounds__(256) embedding_bwd_kernel(const int64_t* __res
   }
 }
 
+// Patchify: 'b c (h p1) (w p2) -> b (h w) (p1 p2 c)' (meant/meant.py:193-195; per frame the same pattern in
+// src/meant/timesformer_pytorch.py:219-220) fused with the cast to the compute dtype: the im2col operand of the
+// patch-embedding GEMM is written once, in bf16 under autocast, instead of a permuted fp32 copy plus a cast pass.
+// A thread owns one pixel position (p1, p2) of one patch: it reads the C channel values (each read is part of a
+// 16-pixel, 64-byte run of an image row) and writes them as C consecutive outputs, so a warp writes one contiguous
+// 32 * C element run.  TRANSPOSE: the adjoint (patch gradients back to the image layout).
+template <typename TI, typename TO, bool TRANSPOSE>
+__global__ void __launch_bounds__(256) patchify_kernel(const TI* __restrict__ in, TO* __restrict__ out, int64_t B, int C,
+                                                       int H, int W, int P) {
+  const int hp = H / P, wp = W / P;
+  const int64_t total = B * hp * wp * P * P;
+  for (int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * 256) {
+    const int p2 = (int)(idx % P);
+    int64_t r = idx / P;
+    const int p1 = (int)(r % P);
+    r /= P;
+    const int w = (int)(r % wp);
+    r /= wp;
+    const int h = (int)(r % hp);
+    const int64_t b = r / hp;
+    const int64_t img = (b * C * H + (int64_t)(h * P + p1)) * W + (w * P + p2);     // channel 0; + c * H * W
+    const int64_t pat = idx * C;                                                      // (b, h, w, p1, p2, 0)
+    for (int c = 0; c < C; ++c) {
+      if (!TRANSPOSE) out[pat + c] = from_f<TO>(to_f(in[img + (int64_t)c * H * W]));
+      else out[img + (int64_t)c * H * W] = from_f<TO>(to_f(in[pat + c]));
+    }
+  }
+}
+
 }  // namespace meant
 
 using namespace meant;
+
+extern "C" int meant_patchify(const void* in, void* out, int64_t B, int C, int H, int W, int P, int in_dtype, int out_dtype,
+                              int transpose, cudaStream_t st) {
+  if (!in || !out || B <= 0 || C <= 0 || H <= 0 || W <= 0 || P <= 0 || H % P || W % P) return MEANT_EARG;
+  const int64_t total = B * (H / P) * (W / P) * P * P;
+  unsigned blocks = (unsigned)((total + 255) / 256 < 148 * 32 ? (total + 255) / 256 : 148 * 32);
+#define PATCHIFY_GO(TI, TO)                                                                                     \
+  do {                                                                                                          \
+    if (transpose) patchify_kernel<TI, TO, true><<<blocks, 256, 0, st>>>((const TI*)in, (TO*)out, B, C, H, W, P); \
+    else patchify_kernel<TI, TO, false><<<blocks, 256, 0, st>>>((const TI*)in, (TO*)out, B, C, H, W, P);        \
+  } while (0)
+  if (in_dtype == MEANT_DT_F32 && out_dtype == MEANT_DT_F32) PATCHIFY_GO(float, float);
+  else if (in_dtype == MEANT_DT_F32 && out_dtype == MEANT_DT_BF16) PATCHIFY_GO(float, __nv_bfloat16);
+  else if (in_dtype == MEANT_DT_BF16 && out_dtype == MEANT_DT_BF16) PATCHIFY_GO(__nv_bfloat16, __nv_bfloat16);
+  else if (in_dtype == MEANT_DT_BF16 && out_dtype == MEANT_DT_F32) PATCHIFY_GO(__nv_bfloat16, float);
+  else return MEANT_EUNSUPPORTED;
+#undef PATCHIFY_GO
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
 
 #define DISPATCH_T(dtype, CALL)                                   \
   if (dtype == MEANT_DT_F32) { using T = float; CALL; }           \

@@ -108,10 +108,9 @@ class temporalEncoder(nn.Module):
 
 
 def patchify(images, patch):
-    """'b c (h p1) (w p2) -> b (h w) (p1 p2 c)' (meant/meant.py:193-195), as one strided copy."""
-    b, c, hh, ww = images.shape
-    x = images.reshape(b, c, hh // patch, patch, ww // patch, patch)
-    return x.permute(0, 2, 4, 3, 5, 1).reshape(b, (hh // patch) * (ww // patch), patch * patch * c)
+    """'b c (h p1) (w p2) -> b (h w) (p1 p2 c)' (meant/meant.py:193-195): the library's patchify kernel, which also casts
+    to the compute dtype (the GEMM operand is written once)."""
+    return ops.patchify(images, patch)
 
 
 class _PatchRearrange(nn.Module):

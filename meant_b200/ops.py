@@ -329,6 +329,69 @@ class _EmbeddingFn(torch.autograd.Function):
         return None, dw, None
 
 
+class _EmbedBlockFn(torch.autograd.Function):
+    """word + position + type gather, position ids from the padding mask, LayerNorm and dropout in one kernel
+    (csrc/embed.cu); backward scatter-adds into the three tables' gradients."""
+
+    @staticmethod
+    def forward(ctx, ids, word, pos, typ, ln_w, ln_b, eps, pad, drop_p, seed, dtype, frozen_rows):
+        ids2 = ids.reshape(-1, ids.shape[-1]).contiguous()
+        n, s = ids2.shape
+        d = word.shape[1]
+        dev = word.device
+        lw, lb = _f32(ln_w), _f32(ln_b)
+        out = torch.empty(n, s, d, dtype=dtype, device=dev)
+        pos_ids = torch.empty(n, s, dtype=torch.int32, device=dev)
+        mean = torch.empty(n, s, dtype=torch.float32, device=dev)
+        rstd = torch.empty_like(mean)
+        sdev = _graph_seed if drop_p > 0.0 else None
+        nv.check(nv.timed(f"embed_ln_fwd/S{s}/d{d}", nv.lib().meant_embed_ln_fwd, nv.ptr(ids2), nv.ptr(word), nv.ptr(pos), nv.ptr(typ),
+                          nv.ptr(lw), nv.ptr(lb), float(eps), nv.ptr(out), nv.ptr(pos_ids), nv.ptr(mean), nv.ptr(rstd), n, s, d,
+                          word.shape[0], pos.shape[0], int(pad), float(drop_p), seed, nv.ptr(sdev), nv.dt(out), nv.stream()),
+                 "meant_embed_ln_fwd")
+        ctx.save_for_backward(ids2, pos_ids, mean, rstd, word, pos, typ, lw)
+        ctx.sdev = sdev
+        ctx.cfg = (float(drop_p), seed, ln_w.dtype, typ.shape, frozen_rows)
+        return out.view(*ids.shape, d)
+
+    @staticmethod
+    def backward(ctx, dy):
+        ids2, pos_ids, mean, rstd, word, pos, typ, lw = ctx.saved_tensors
+        drop_p, seed, lndt, tshape, frozen_rows = ctx.cfg
+        n, s = ids2.shape
+        d = word.shape[1]
+        dy2 = dy.reshape(n, s, d).contiguous()
+        dword = torch.zeros_like(word)
+        dpos = torch.zeros_like(pos)
+        acc = torch.zeros(3, d, dtype=torch.float32, device=word.device)
+        nv.check(nv.timed(f"embed_ln_bwd/S{s}/d{d}", nv.lib().meant_embed_ln_bwd, nv.ptr(dy2), nv.ptr(ids2), nv.ptr(pos_ids), nv.ptr(mean),
+                          nv.ptr(rstd), nv.ptr(word), nv.ptr(pos), nv.ptr(typ), nv.ptr(lw), nv.ptr(dword), nv.ptr(dpos), nv.ptr(acc[0]),
+                          nv.ptr(acc[1]), nv.ptr(acc[2]), n, s, d, word.shape[0], pos.shape[0], drop_p, seed, nv.ptr(ctx.sdev),
+                          nv.dt(dy2), nv.stream()), "meant_embed_ln_bwd")
+        dtyp = torch.zeros(tshape, dtype=torch.float32, device=word.device)
+        dtyp[0].copy_(acc[0])
+        # nn.Embedding(padding_idx=...) keeps that row's gradient at zero (Roberta: the pad row of word and position tables)
+        if frozen_rows[0] is not None:
+            dword[frozen_rows[0]].zero_()
+        if frozen_rows[1] is not None:
+            dpos[frozen_rows[1]].zero_()
+        if frozen_rows[2] is not None:
+            dtyp[frozen_rows[2]].zero_()
+        return None, dword, dpos, dtyp, acc[1].to(lndt), acc[2].to(lndt), None, None, None, None, None, None
+
+
+def _is_bert_block(mod):
+    """A Hugging Face Bert/Roberta-style embedding block (what `bertweet.embeddings` is): duck-typed, no import."""
+    names = ("word_embeddings", "position_embeddings", "token_type_embeddings", "LayerNorm", "dropout")
+    if not all(hasattr(mod, k) for k in names):
+        return False
+    we, pe, te, ln = mod.word_embeddings, mod.position_embeddings, mod.token_type_embeddings, mod.LayerNorm
+    return all(isinstance(e, torch.nn.Embedding) and e.weight.is_cuda and e.weight.dtype == torch.float32 and
+               e.weight.is_contiguous() and e.max_norm is None for e in (we, pe, te)) and \
+        isinstance(ln, torch.nn.LayerNorm) and ln.elementwise_affine and ln.bias is not None and \
+        we.weight.shape[1] in (256, 512, 768, 1024) and getattr(mod, "position_embedding_type", "absolute") == "absolute"
+
+
 def embed(mod, ids):
     """The model's `embedding` module applied to token ids (meant/meant_tweet.py:152).  A plain nn.Embedding on the
     GPU runs the gather kernel, which writes the compute dtype directly, and a scatter-add backward; any other module
@@ -341,7 +404,54 @@ def embed(mod, ids):
             # nn.Embedding raises for this too; a host pointer must never reach the gather kernel
             raise RuntimeError(f"embed: token ids are on {ids.device} but the embedding table is on {w.device}")
         return _EmbeddingFn.apply(ids, w, compute_dtype(w))
+    if ids.dtype == torch.int64 and ids.dim() >= 2 and _is_bert_block(mod):
+        we = mod.word_embeddings
+        if ids.device != we.weight.device:
+            raise RuntimeError(f"embed: token ids are on {ids.device} but the embedding tables are on {we.weight.device}")
+        # RoBERTa derives position ids from the padding mask (padding_idx on the block); BERT counts 0..S-1, which is
+        # the same formula with a pad id no token carries and an offset of -1: not built, falls through to the module
+        pad = getattr(mod, "padding_idx", None)
+        if pad is not None:
+            p = float(mod.dropout.p) if mod.training else 0.0
+            return _EmbedBlockFn.apply(ids, we.weight, mod.position_embeddings.weight, mod.token_type_embeddings.weight,
+                                       mod.LayerNorm.weight, mod.LayerNorm.bias, mod.LayerNorm.eps, int(pad), p,
+                                       _seed() if p > 0.0 else 0, compute_dtype(we.weight),
+                                       (we.padding_idx, mod.position_embeddings.padding_idx, mod.token_type_embeddings.padding_idx))
     return mod(ids)
+
+
+# ----------------------------------------------------------------------------- patchify
+class _PatchifyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, images, patch, dtype):
+        nv.require_cuda(images)
+        if images.dtype not in (torch.float32, torch.bfloat16):
+            images = images.float()
+        x = images.contiguous()
+        b, c, hh, ww = x.shape
+        if hh % patch or ww % patch:
+            raise ValueError(f"image size {hh}x{ww} is not divisible by the patch size {patch}")
+        out = torch.empty(b, (hh // patch) * (ww // patch), patch * patch * c, dtype=dtype, device=x.device)
+        nv.check(nv.timed(f"patchify/c{c}/{hh}x{ww}", nv.lib().meant_patchify, nv.ptr(x), nv.ptr(out), b, c, hh, ww, patch, nv.dt(x),
+                          nv.dt(out), 0, nv.stream()), "meant_patchify")
+        ctx.cfg = (b, c, hh, ww, patch, images.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        b, c, hh, ww, patch, idt = ctx.cfg
+        dy = dy.contiguous()
+        if dy.dtype not in (torch.float32, torch.bfloat16):
+            dy = dy.float()
+        dx = torch.empty(b, c, hh, ww, dtype=idt if idt in (torch.float32, torch.bfloat16) else torch.float32, device=dy.device)
+        nv.check(nv.lib().meant_patchify(nv.ptr(dy), nv.ptr(dx), b, c, hh, ww, patch, nv.dt(dy), nv.dt(dx), 1, nv.stream()),
+                 "meant_patchify")
+        return dx, None, None
+
+
+def patchify(images, patch):
+    """'b c (h p1) (w p2) -> b (h w) (p1 p2 c)' (meant/meant.py:193-195) written once in the compute dtype."""
+    return _PatchifyFn.apply(images, patch, compute_dtype(images))
 
 
 # ---------------------------------------------------------------------------- LayerNorm

@@ -157,7 +157,7 @@ class TimeSformer(nn.Module):
         assert hh % p == 0 and ww % p == 0, f'height {hh} and width {ww} of video must be divisible by the patch size {p}'
         hp, wp = hh // p, ww // p
         n = hp * wp
-        v = video.reshape(b, f, c, hp, p, wp, p).permute(0, 1, 3, 5, 4, 6, 2).reshape(b, f * n, p * p * c)
+        v = ops.patchify(video.reshape(b * f, c, hh, ww), p).view(b, f * n, p * p * c)
         tokens = self.to_patch_embedding(v)
         x = torch.cat((self.cls_token.to(tokens.dtype)[None].expand(b, -1, -1), tokens), dim=1)
         x = x.to(ops.compute_dtype(x))
