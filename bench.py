@@ -47,6 +47,8 @@ def parse():
                     help="extra BASELINE configs measured in the same process and reported in the `configs` array: "
                          "auto (N=1: vision,timesformer,full12,full,long; N>1: full), none, or a comma list")
     ap.add_argument("--config-steps", type=int, default=5)
+    ap.add_argument("--grad-dtype", default="auto", choices=["auto", "fp32", "bf16"],
+                    help="dtype of the data-parallel gradient buckets (auto: bf16 when more than one rank)")
     return ap.parse_args()
 
 
@@ -54,7 +56,9 @@ def workload_config(args, n):
     return {"workload": "meant_tweet lag=12 S=128 text+price-shaped synthetic batch (BASELINE configs[1])",
             "lag": LAG, "seq_len": SEQ, "dim": DIM, "heads": HEADS, "vocab": VOCAB,
             "num_encoders": args.encoders, "batch_per_gpu": args.batch, "global_batch": args.batch * n,
-            "parallelism": f"dp{n}", "optimizer": "AdamW(fused) + clip_grad_norm 1.0", "mode": "train (dropout on)",
+            "parallelism": f"dp{n}", "optimizer": "AdamW + clip_grad_norm 1.0 (meant_b200.optim multi-tensor kernels)",
+            "grad_buckets": "bf16" if args.grad_dtype == "bf16" or (args.grad_dtype == "auto" and n > 1) else "fp32",
+            "mode": "train (dropout on)",
             "launch": "whole step (incl. the NCCL gradient all-reduces) replayed from one CUDA graph" if args.graph else "eager launches",
             "linear_forward_gemm": getattr(args, "gemm", "library"),
             "l2": "no flush needed: each step streams >10 GB of activations/weights, far above the 126 MB L2"}
@@ -276,7 +280,8 @@ def extra_configs(args, dev, rank, world, barrier, max_over_ranks):
         torch.manual_seed(0)
         model, labels, inputs, desc, shapes = cfg_models.build(what, batch, dev, encoders=args.encoders, seed=1234 + rank)
         model = model.to(dev).train()
-        step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=2)
+        gdt = torch.bfloat16 if args.grad_dtype == "bf16" or (args.grad_dtype == "auto" and world > 1) else None
+        step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=2, grad_dtype=gdt)
         for _ in range(4 if step.graph else 3):       # eager warm-up, capture, one replay
             step(labels, *inputs)
         barrier()
@@ -290,12 +295,15 @@ def extra_configs(args, dev, rank, world, barrier, max_over_ranks):
         row = {"config": desc, "batch_per_gpu": batch, "n_gpus": world, "steps": args.config_steps,
                "ms_per_step": round(ms, 3), "value": round(batch * world / (ms * 1e-3), 1), "unit": UNIT,
                "launch": "CUDA graph replay" if step.graph else "eager"}
+        # one eager pass of the same step for the per-kernel CUDA events and one under torch.profiler for the split:
+        # EVERY rank runs them (the step holds collectives), rank 0 keeps the numbers
+        nv.enable_timers(rank == 0)
+        step._step(labels, inputs, {})
+        torch.cuda.synchronize()
+        stats = kernel_stats(nv.timers()) if rank == 0 else {}
+        nv.enable_timers(False)
+        split_c = cfg_models.step_split_ms(lambda: step._step(labels, inputs, {}))
         if rank == 0:
-            nv.enable_timers(True)
-            step._step(labels, inputs, {})            # one eager pass of the same step: per-kernel CUDA events
-            torch.cuda.synchronize()
-            stats = kernel_stats(nv.timers())
-            nv.enable_timers(False)
             att = []
             for tag, sq, sk, dh, seqs, causal in shapes:
                 for name, (kms, count) in sorted(stats.items()):
@@ -313,7 +321,7 @@ def extra_configs(args, dev, rank, world, barrier, max_over_ranks):
             row["attention_kernels"] = att
             row["aux_kernels_ms"] = {k: round(v[0] * v[1], 3) for k, v in stats.items()
                                      if k.startswith("attn_") and ("q1" in k or "prerotate" in k)}
-            row["step_split_ms"] = cfg_models.step_split_ms(lambda: step._step(labels, inputs, {}))
+            row["step_split_ms"] = split_c
         out.append(row)
         step.close()
         del step, model, labels, inputs
@@ -346,7 +354,8 @@ def gpu_run(args):
     torch.manual_seed(0)
     model = mb.meant_tweet(DIM, 4, LAG, CLASSES, nn.Embedding(VOCAB, DIM), num_encoders=args.encoders).to(dev)
     model.train()
-    step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=min(3, args.warmup))
+    gdt = torch.bfloat16 if args.grad_dtype == "bf16" or (args.grad_dtype == "auto" and world > 1) else None
+    step = TrainStep(model, bf16=True, graph=bool(args.graph), graph_warmup=min(3, args.warmup), grad_dtype=gdt)
     h_tweets, h_mask, h_labels = synth_batch(args.batch, rank, pin=True)
     d_tweets, d_mask, d_labels = (t.to(dev) for t in (h_tweets, h_mask, h_labels))
 
@@ -411,10 +420,8 @@ def gpu_run(args):
         stats = kernel_stats(nv.timers())
         nv.enable_timers(False)
     gemm_rows = gemm_probe(args, dev) if rank == 0 else []
-    split = None
-    if rank == 0:
-        import cfg_models
-        split = cfg_models.step_split_ms(lambda: step._step(d_labels, (d_tweets, d_mask), {}))
+    import cfg_models
+    split = cfg_models.step_split_ms(lambda: step._step(d_labels, (d_tweets, d_mask), {}))   # every rank: collectives inside
     cfg_rows = extra_configs(args, dev, rank, world, barrier, max_over_ranks)
     if rank == 0:
         n = world
@@ -440,8 +447,10 @@ def gpu_run(args):
     if world > 1:
         barrier()
         sys.stdout.flush()
-        if step.graph:
-            os._exit(0)    # communicator teardown after graph capture can block; every rank is done and in step
+        # TrainStep.close() released the captured graph AND the work handles created under capture (they never complete
+        # outside the graph and kept the communicator's teardown waiting in round 1): a plain teardown now returns
+        if os.environ.get("MEANT_BENCH_HARD_EXIT") == "1":
+            os._exit(0)
         dist.destroy_process_group()
 
 

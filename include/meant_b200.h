@@ -202,7 +202,7 @@ int meant_gemm_bf16_tn(const void* A, const void* W, const float* bias, void* C,
 #define MEANT_OPT_MAX_BLOCKS 320
 typedef struct {
   void* p[MEANT_OPT_MAX_TENSORS];       /* parameters (fp32, updated in place); unused by meant_multi_sqnorm   */
-  void* g[MEANT_OPT_MAX_TENSORS];       /* gradients (fp32)                                                    */
+  void* g[MEANT_OPT_MAX_TENSORS];       /* gradients: fp32, or bf16 when g_bf16 != 0 (bf16 data-parallel buckets) */
   void* m[MEANT_OPT_MAX_TENSORS];       /* exp_avg (fp32)                                                      */
   void* v[MEANT_OPT_MAX_TENSORS];       /* exp_avg_sq (fp32)                                                   */
   void* shadow[MEANT_OPT_MAX_TENSORS];  /* optional bf16 copy of the updated parameter (NULL: none)            */
@@ -210,6 +210,7 @@ typedef struct {
   int32_t block_chunk[MEANT_OPT_MAX_BLOCKS];
   uint8_t block_tensor[MEANT_OPT_MAX_BLOCKS];
   int32_t n_tensors, n_blocks;
+  int32_t g_bf16, reserved_;
 } meant_tensor_table;
 
 /* *sumsq (device, fp32) += sum over the table's gradients of g^2: the squared total norm of clip_grad_norm_.          */

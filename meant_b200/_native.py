@@ -39,7 +39,7 @@ class TensorTable(C.Structure):
     _fields_ = [("p", vp * OPT_MAX_TENSORS), ("g", vp * OPT_MAX_TENSORS), ("m", vp * OPT_MAX_TENSORS),
                 ("v", vp * OPT_MAX_TENSORS), ("shadow", vp * OPT_MAX_TENSORS), ("numel", i64 * OPT_MAX_TENSORS),
                 ("block_chunk", C.c_int32 * OPT_MAX_BLOCKS), ("block_tensor", C.c_uint8 * OPT_MAX_BLOCKS),
-                ("n_tensors", C.c_int32), ("n_blocks", C.c_int32)]
+                ("n_tensors", C.c_int32), ("n_blocks", C.c_int32), ("g_bf16", C.c_int32), ("reserved_", C.c_int32)]
 
 
 # name -> (restype, argtypes); mirrors include/meant_b200.h one to one

@@ -15,23 +15,33 @@ namespace meant {
 
 constexpr int OPT_CHUNK = MEANT_OPT_CHUNK;
 
+// four consecutive gradients (fp32: one 16-byte load, bf16: one 8-byte load) / one gradient, as fp32
+__device__ __forceinline__ float4 ld4(const float* g) { return __ldg(reinterpret_cast<const float4*>(g)); }
+__device__ __forceinline__ float4 ld4(const __nv_bfloat16* g) {
+  const uint2 pk = __ldg(reinterpret_cast<const uint2*>(g));
+  const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.x));
+  const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&pk.y));
+  return make_float4(lo.x, lo.y, hi.x, hi.y);
+}
+
+// TG: gradient storage type (fp32 autograd tensors, or the bf16 slices of the data-parallel reducer's buckets)
+template <typename TG>
 __global__ void __launch_bounds__(256) multi_sqnorm_kernel(const __grid_constant__ meant_tensor_table tab, float* __restrict__ out) {
   const int ti = tab.block_tensor[blockIdx.x];
   const int64_t n = tab.numel[ti], base = (int64_t)tab.block_chunk[blockIdx.x] * OPT_CHUNK;
   const int64_t end = base + OPT_CHUNK < n ? base + OPT_CHUNK : n;
-  const float* __restrict__ g = static_cast<const float*>(tab.g[ti]);
+  const TG* __restrict__ g = static_cast<const TG*>(tab.g[ti]);
   float acc = 0.f;
-  // 16-byte loads when the chunk start is aligned (chunks are multiples of 4 elements; the tensor base may not be)
-  if ((reinterpret_cast<uintptr_t>(g + base) & 15) == 0) {
+  // vector loads when the chunk start is aligned (chunks are multiples of 4 elements; the tensor base may not be)
+  if ((reinterpret_cast<uintptr_t>(g + base) & (4 * sizeof(TG) - 1)) == 0) {
     const int64_t n4 = (end - base) >> 2;
-    const float4* g4 = reinterpret_cast<const float4*>(g + base);
     for (int64_t i = threadIdx.x; i < n4; i += 256) {
-      const float4 v = __ldg(g4 + i);
+      const float4 v = ld4(g + base + (i << 2));
       acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     }
-    for (int64_t i = base + (n4 << 2) + threadIdx.x; i < end; i += 256) acc += g[i] * g[i];
+    for (int64_t i = base + (n4 << 2) + threadIdx.x; i < end; i += 256) { const float x = to_f(g[i]); acc += x * x; }
   } else {
-    for (int64_t i = base + threadIdx.x; i < end; i += 256) acc += g[i] * g[i];
+    for (int64_t i = base + threadIdx.x; i < end; i += 256) { const float x = to_f(g[i]); acc += x * x; }
   }
   __shared__ float red[8];
   acc = warp_sum(acc);
@@ -49,8 +59,8 @@ struct AdamwHyper {
   float lr, beta1, beta2, eps, wd, max_norm;
 };
 
-template <bool VEC>
-__device__ __forceinline__ void adamw_range(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+template <bool VEC, typename TG>
+__device__ __forceinline__ void adamw_range(float* __restrict__ p, const TG* __restrict__ g, float* __restrict__ m,
                                             float* __restrict__ v, __nv_bfloat16* __restrict__ sh, int64_t base, int64_t end,
                                             const AdamwHyper& hp, float coef, float bc1, float rbc2) {
   auto upd = [&](float& pp, float gg, float& mm, float& vv) {
@@ -67,7 +77,7 @@ __device__ __forceinline__ void adamw_range(float* __restrict__ p, const float* 
       const int64_t o = base + (i << 2);
       float4 pp = *reinterpret_cast<const float4*>(p + o), mm = *reinterpret_cast<const float4*>(m + o),
              vv = *reinterpret_cast<const float4*>(v + o);
-      const float4 gg = __ldg(reinterpret_cast<const float4*>(g + o));
+      const float4 gg = ld4(g + o);
       upd(pp.x, gg.x, mm.x, vv.x);
       upd(pp.y, gg.y, mm.y, vv.y);
       upd(pp.z, gg.z, mm.z, vv.z);
@@ -87,7 +97,7 @@ __device__ __forceinline__ void adamw_range(float* __restrict__ p, const float* 
   }
   for (int64_t i = base + threadIdx.x; i < end; i += 256) {
     float pp = p[i], mm = m[i], vv = v[i];
-    upd(pp, g[i], mm, vv);
+    upd(pp, to_f(g[i]), mm, vv);
     p[i] = pp;
     m[i] = mm;
     v[i] = vv;
@@ -95,13 +105,14 @@ __device__ __forceinline__ void adamw_range(float* __restrict__ p, const float* 
   }
 }
 
+template <typename TG>
 __global__ void __launch_bounds__(256) adamw_kernel(const __grid_constant__ meant_tensor_table tab, const float* __restrict__ step,
                                                     const float* __restrict__ sumsq, const AdamwHyper hp) {
   const int ti = tab.block_tensor[blockIdx.x];
   const int64_t n = tab.numel[ti], base = (int64_t)tab.block_chunk[blockIdx.x] * OPT_CHUNK;
   const int64_t end = base + OPT_CHUNK < n ? base + OPT_CHUNK : n;
   float* p = static_cast<float*>(tab.p[ti]);
-  const float* g = static_cast<const float*>(tab.g[ti]);
+  const TG* g = static_cast<const TG*>(tab.g[ti]);
   float* m = static_cast<float*>(tab.m[ti]);
   float* v = static_cast<float*>(tab.v[ti]);
   __nv_bfloat16* sh = static_cast<__nv_bfloat16*>(tab.shadow[ti]);
@@ -110,8 +121,9 @@ __global__ void __launch_bounds__(256) adamw_kernel(const __grid_constant__ mean
   // torch.nn.utils.clip_grad_norm_: coef = min(1, max_norm / (total_norm + 1e-6))
   float coef = 1.0f;
   if (sumsq != nullptr && hp.max_norm > 0.f) coef = fminf(1.0f, hp.max_norm / (sqrtf(*sumsq) + 1e-6f));
-  const uintptr_t al = reinterpret_cast<uintptr_t>(p + base) | reinterpret_cast<uintptr_t>(g + base) |
-                       reinterpret_cast<uintptr_t>(m + base) | reinterpret_cast<uintptr_t>(v + base) |
+  // every vector access of the fast path is naturally aligned: 16 bytes for fp32, 8 bytes for the bf16 streams
+  const uintptr_t al = reinterpret_cast<uintptr_t>(p + base) | reinterpret_cast<uintptr_t>(m + base) |
+                       reinterpret_cast<uintptr_t>(v + base) | (reinterpret_cast<uintptr_t>(g + base) * (16 / (4 * sizeof(TG)))) |
                        (sh ? reinterpret_cast<uintptr_t>(sh + base) << 1 : 0);
   if ((al & 15) == 0) adamw_range<true>(p, g, m, v, sh, base, end, hp, coef, bc1, rbc2);
   else adamw_range<false>(p, g, m, v, sh, base, end, hp, coef, bc1, rbc2);
@@ -163,7 +175,8 @@ extern "C" int meant_multi_sqnorm(const meant_tensor_table* table, float* sumsq,
   if (!table_ok(table) || !sumsq) return MEANT_EARG;
   for (int i = 0; i < table->n_tensors; ++i)
     if (!table->g[i] || table->numel[i] <= 0) return MEANT_EARG;
-  multi_sqnorm_kernel<<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, sumsq);
+  if (table->g_bf16) multi_sqnorm_kernel<__nv_bfloat16><<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, sumsq);
+  else multi_sqnorm_kernel<float><<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, sumsq);
   MEANT_LAUNCH_CHECK();
   return 0;
 }
@@ -175,7 +188,8 @@ extern "C" int meant_adamw_step(const meant_tensor_table* table, const float* st
   for (int i = 0; i < table->n_tensors; ++i)
     if (!table->p[i] || !table->g[i] || !table->m[i] || !table->v[i] || table->numel[i] <= 0) return MEANT_EARG;
   const AdamwHyper hp{lr, beta1, beta2, eps, weight_decay, max_norm};
-  adamw_kernel<<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, step, sumsq, hp);
+  if (table->g_bf16) adamw_kernel<__nv_bfloat16><<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, step, sumsq, hp);
+  else adamw_kernel<float><<<table->n_blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(*table, step, sumsq, hp);
   MEANT_LAUNCH_CHECK();
   return 0;
 }

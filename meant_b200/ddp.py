@@ -12,7 +12,10 @@ Design
     buffer with ONE multi-tensor copy, re-points every .grad at its slice of the buffer and
     launches all_reduce(bucket, AVG, async_op=True) -- NCCL runs it on its own stream;
   * with one rank nothing is packed at all: the optimizer reads the autograd tensors;
-  * finish() waits for the outstanding handles before the optimizer reads the gradients.
+  * finish() waits for the outstanding handles before the optimizer reads the gradients;
+  * grad_dtype=torch.bfloat16 exchanges bf16 buckets (half the bytes on the wire): gradients are cast while they are
+    packed, all-reduced in bf16, and handed to the optimizer as bf16 slices through grads() -- .grad is dropped then,
+    because torch does not allow a bf16 .grad on an fp32 parameter (meant_b200.optim.FusedAdamW reads either type).
 The same code runs on gloo (CPU tensors) for the world_size-2 tests.
 """
 import torch
@@ -24,6 +27,8 @@ class BucketedGradAllReduce:
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.params = [p for p in params if p.requires_grad]
+        self.grad_dtype = grad_dtype
+        self._reduced = {}         # compressed mode: param -> reduced bucket slice of this step
         self.buckets = []          # [(flat tensor, [params])]
         self._bucket_of = {}
         self._pending = []
@@ -64,6 +69,14 @@ class BucketedGradAllReduce:
         self._pending = [len(ps) for _, ps in self.buckets]
         self._handles = []
         self._next = 0
+        self._reduced = {}
+
+    def grads(self):
+        """{param: gradient} for the optimizer after finish(): the reduced bucket slices (bf16 in compressed mode), or
+        with one rank the autograd tensors."""
+        if self._reduced:
+            return dict(self._reduced)
+        return {p: p.grad for p in self.params if p.grad is not None}
 
     def _reduce(self, b):
         """Pack bucket b and all-reduce it.  A parameter without a local gradient this step contributes zeros
@@ -78,8 +91,13 @@ class BucketedGradAllReduce:
             flat.zero_()
         if have:
             torch._foreach_copy_([v for v, _ in have], [p.grad for _, p in have])
+        compressed = self.grad_dtype is not None and self.grad_dtype != ps[0].dtype
         for v, p in zip(views, ps):
-            p.grad = v
+            if compressed:
+                self._reduced[p] = v
+                p.grad = None
+            else:
+                p.grad = v
         if flat.is_cuda:
             self._handles.append(dist.all_reduce(flat, op=dist.ReduceOp.AVG, group=self.group, async_op=True))
         else:  # gloo has no AVG

@@ -8,7 +8,7 @@ import torch
 from . import _native as nv
 
 
-def _tables(entries):
+def _tables(entries, g_bf16=False):
     """entries: [(p, g, m, v, shadow or None)] -> list of TensorTable, each <= 48 tensors and <= 320 chunks.  A tensor
     larger than one launch's chunks (the 64001 x 768 embedding: 751 chunks) is cut across launches by offsetting its
     pointers (chunk boundaries are multiples of 65536 elements, so the 16-byte alignment of the vector path survives)."""
@@ -17,6 +17,7 @@ def _tables(entries):
     def fresh():
         t = nv.TensorTable()
         t.n_tensors = t.n_blocks = 0
+        t.g_bf16 = 1 if g_bf16 else 0
         return t
 
     for p, g, m, v, sh in entries:
@@ -30,7 +31,7 @@ def _tables(entries):
             part = min(numel - done, room * nv.OPT_CHUNK)
             i = cur.n_tensors
             cur.p[i] = p.data_ptr() + 4 * done
-            cur.g[i] = g.data_ptr() + 4 * done
+            cur.g[i] = g.data_ptr() + (2 if g_bf16 else 4) * done
             cur.m[i] = m.data_ptr() + 4 * done
             cur.v[i] = v.data_ptr() + 4 * done
             cur.shadow[i] = (sh.data_ptr() + 2 * done) if sh is not None else None
@@ -76,24 +77,29 @@ class FusedAdamW:
         self._cache_key, self._cache = None, None
         self.launches = 0
 
-    def _build(self):
-        live = [p for p in self.params if p.grad is not None]
-        key = tuple((p.data_ptr(), p.grad.data_ptr()) for p in live)
+    def _build(self, grads=None):
+        """grads: optional {param: gradient tensor} (the data-parallel reducer's reduced bucket slices, fp32 or bf16);
+        default: every parameter's .grad."""
+        if grads is None:
+            live = [(p, p.grad) for p in self.params if p.grad is not None]
+        else:
+            live = [(p, grads[p]) for p in self.params if grads.get(p) is not None]
+        key = tuple((p.data_ptr(), g.data_ptr(), g.dtype) for p, g in live)
         if key != self._cache_key:
-            entries = []
-            for p in live:
-                g = p.grad
-                if g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
-                    raise ValueError("FusedAdamW takes contiguous fp32 gradients on the parameter's device")
+            by_dtype = {torch.float32: [], torch.bfloat16: []}
+            for p, g in live:
+                if g.dtype not in by_dtype or not g.is_contiguous() or g.device != p.device or g.numel() != p.numel():
+                    raise ValueError("FusedAdamW takes contiguous fp32 or bf16 gradients on the parameter's device")
                 m, v = self.state[p]
                 sh = self.shadows.get(id(p))
-                entries.append((p.data, g, m, v, sh[1] if sh is not None else None))
-            self._cache_key, self._cache = key, _tables(entries)
+                by_dtype[g.dtype].append((p.data, g, m, v, sh[1] if sh is not None else None))
+            self._cache_key = key
+            self._cache = _tables(by_dtype[torch.float32]) + _tables(by_dtype[torch.bfloat16], g_bf16=True)
         return self._cache
 
     @torch.no_grad()
-    def step(self):
-        tabs = self._build()
+    def step(self, grads=None):
+        tabs = self._build(grads)
         st = nv.stream()
         self._step.add_(1.0)
         sumsq = None

@@ -18,14 +18,17 @@ class TrainStep:
     (ops.use_fused_linear).  Input shapes and non-tensor arguments must not change between calls."""
 
     def __init__(self, model, lr=5e-5, betas=(0.9, 0.999), weight_decay=0.0, max_grad_norm=1.0,
-                 bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3, own_optimizer=True):
+                 bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3, own_optimizer=True, grad_dtype=None):
         self.model = model
         self.bf16 = bf16
         self.max_grad_norm = max_grad_norm
         broadcast_parameters(model, 0, group)
         self.params = [p for p in model.parameters() if p.requires_grad]
-        self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group)
         fused = self._fused = self.params[0].is_cuda
+        own = bool(own_optimizer) and fused and all(p.dtype == torch.float32 and p.is_contiguous() for p in self.params)
+        if grad_dtype is not None and not own:
+            raise ValueError("grad_dtype (compressed gradient buckets) needs the library's optimizer (CUDA, fp32 parameters)")
+        self.reducer = BucketedGradAllReduce(self.params, bucket_mb=bucket_mb, group=group, grad_dtype=grad_dtype)
         self.graph = bool(graph) and fused
         self._graph_warmup, self._calls = int(graph_warmup), 0
         self._g = self._static = self._loss = self._seed_t = None
@@ -39,7 +42,7 @@ class TrainStep:
             self._arena = torch.zeros(1 << 20, dtype=torch.float32, device=self.params[0].device)
         # The step after backward on the library's multi-tensor kernels (optim.py: gradient norm, clip + AdamW, the bf16
         # weight shadows written by the update itself) -- or torch's optimizer (CPU tensors: the gloo tests)
-        self._own = bool(own_optimizer) and fused and all(p.dtype == torch.float32 and p.is_contiguous() for p in self.params)
+        self._own = own
         if self._own:
             self.opt = FusedAdamW(self.params, lr=lr, betas=betas, weight_decay=weight_decay, max_norm=max_grad_norm or 0.0,
                                   shadows=self._shadows)
@@ -109,7 +112,7 @@ class TrainStep:
         loss.backward()
         self.reducer.finish()
         if self._own:
-            self.opt.step()                      # gradient norm + clip + AdamW (+ shadows): optim.py
+            self.opt.step(self.reducer.grads())  # gradient norm + clip + AdamW (+ shadows): optim.py
             return loss.detach()
         if self.max_grad_norm and self._fused:
             # clip_grad_norm_ without its own pass over the gradients: fused AdamW divides every gradient by
@@ -159,6 +162,8 @@ class TrainStep:
             torch.cuda.synchronize()
             self._g.reset()
             self._g, self._calls = None, 0
+            self._static = self._loss = None
+            self.reducer._handles = []          # work handles created under capture never complete outside the graph
 
     def __call__(self, labels, *args, **kwargs):
         """One optimisation step; returns the (device) loss tensor (graph mode: a static tensor the next

@@ -141,6 +141,40 @@ def test_parameter_used_on_one_rank_only_stays_in_sync():
     assert not torch.equal(p0[2], init[2])                         # and `extra.weight` did move on both
 
 
+def _bf16_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        model = Net()
+        red = BucketedGradAllReduce(list(model.parameters()), bucket_mb=0.002, grad_dtype=torch.bfloat16)
+        x, y = _data()
+        n = x.shape[0] // world
+        red.zero_grad()
+        nn.functional.cross_entropy(model(x[rank * n:(rank + 1) * n]), y[rank * n:(rank + 1) * n]).backward()
+        local = {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
+        red.finish()
+        g = red.grads()
+        assert all(p.grad is None for p in model.parameters())          # compressed mode hands gradients out via grads()
+        assert all(t.dtype == torch.bfloat16 for t in g.values())
+        out[rank] = ({k: g[p].float().clone() for k, p in model.named_parameters()}, local)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(180)
+def test_bf16_buckets_average_within_bf16_rounding():
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_bf16_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    (g0, l0), (g1, l1) = out[0], out[1]
+    for k in l0:
+        want = 0.5 * (l0[k] + l1[k])
+        assert torch.equal(g0[k], g1[k])                                    # every rank ends with the same bits
+        assert float((g0[k] - want).abs().max()) <= 2e-2 * float(want.abs().max()) + 1e-6
+    assert float(g0["unused.weight"].abs().max()) == 0.0
+
+
 def test_single_rank_keeps_autograd_gradients():
     """With one rank nothing is packed: .grad is whatever autograd produced, None at the start of a step."""
     torch.manual_seed(0)

@@ -44,6 +44,29 @@ def test_fused_adamw_matches_torch(wd, max_norm, gscale):
     assert opt.launches >= 2
 
 
+def test_fused_adamw_takes_bf16_gradient_slices():
+    """The data-parallel reducer's compressed buckets: gradients arrive as bf16 slices of flat buffers through grads=."""
+    mine, ref = _params(2), _params(2)
+    opt = FusedAdamW(mine, lr=1e-3, weight_decay=0.0, max_norm=1.0)
+    topt = torch.optim.AdamW(ref, lr=1e-3, weight_decay=0.0)
+    g = torch.Generator().manual_seed(9)
+    flat = torch.empty(sum(p.numel() for p in mine) + 8, dtype=torch.bfloat16, device="cuda")
+    for _ in range(3):
+        grads, off = {}, 1                        # odd offset: slices are only 2-byte aligned, the scalar path must cope
+        for a, b in zip(mine, ref):
+            gr = torch.randn(*a.shape, generator=g).cuda().bfloat16()
+            view = flat[off:off + a.numel()].view_as(a)
+            view.copy_(gr)
+            grads[a] = view
+            b.grad = gr.float()
+            off += a.numel()
+        torch.nn.utils.clip_grad_norm_(ref, 1.0)
+        topt.step()
+        opt.step(grads)
+    for a, b in zip(mine, ref):
+        assert torch.allclose(a.detach(), b.detach(), rtol=2e-5, atol=2e-6), a.shape
+
+
 def test_prob_cross_entropy_matches_torch():
     torch.manual_seed(0)
     for b, c in ((64, 2), (1, 2), (300, 5)):

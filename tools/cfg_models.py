@@ -85,6 +85,7 @@ def attention_flops(sq, sk, dh, heads, seqs, causal, backward):
 CATEGORIES = (("library_gemm", ("nvjet", "cutlass", "gemm", "cublas", "sm100_xmma", "sm90_xmma")),
               ("attention", ("attn", "q1_")),
               ("norm", ("norm_fwd", "norm_bwd", "layernorm")),
+              ("optimizer", ("adamw", "sqnorm", "multi_tensor_apply", "fusedoptimizer")),
               ("nccl", ("nccl",)))
 
 
