@@ -42,7 +42,9 @@ void meant_reset_launch_count(void);
  *                 (meant/meant.py:116,120 residual adds feeding encode2[0] / the next block)
  *   pre_gelu    : s = gelu(x), exact erf form (meant/meant.py:107 GELU -> RMSNorm); not together with
  *                 res (MEANT_EARG): the backward keeps one tensor and could not split the two gradients
- *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107);
+ *   drop_p,seed : inverted dropout on y with a counter-based mask (meant/meant.py:105,107); the probability is
+ *                 realised as round(256 p) / 256 (one hashed byte per element: exact for the block's p = 0.5) and the
+ *                 survivors are scaled by the reciprocal of the realised keep probability;
  *                 seed_dev (optional, device memory) is added to seed when the kernel runs, so a
  *                 captured CUDA graph draws a fresh mask on every replay
  * rinv[rows] receives 1/(rms+eps) for the backward pass.                                  */

@@ -116,10 +116,9 @@ __global__ void __launch_bounds__(EW * 32) embed_ln_fwd_kernel(EmbArgs a) {
       float y[4] = {(f[4 * v] - mean) * rstd * lw.x + lb.x, (f[4 * v + 1] - mean) * rstd * lw.y + lb.y,
                     (f[4 * v + 2] - mean) * rstd * lw.z + lb.z, (f[4 * v + 3] - mean) * rstd * lw.w + lb.w};
       if (a.drop_thresh) {
-        float k0, k1, k2, k3;
-        drop_pair(seed, (uint64_t)(tok * a.d + c0) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
-        drop_pair(seed, (uint64_t)(tok * a.d + c0 + 2) >> 1, a.drop_thresh, a.drop_inv_keep, k2, k3);
-        y[0] *= k0; y[1] *= k1; y[2] *= k2; y[3] *= k3;
+        const uint32_t m4 = drop_mask4(seed, (uint64_t)(tok * a.d + c0) >> 2, a.drop_thresh);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y[j] = drop_sel(y[j], m4, j) * a.drop_inv_keep;
       }
       T* dst = static_cast<T*>(a.out) + tok * a.d + c0;
       if (VN == 4) {
@@ -181,10 +180,9 @@ __global__ void __launch_bounds__(EW * 32) embed_ln_bwd_kernel(EmbBwdArgs b) {
         dy[0] = lo.x; dy[1] = lo.y; dy[2] = hi.x; dy[3] = hi.y;
       }
       if (a.drop_thresh) {
-        float k0, k1, k2, k3;
-        drop_pair(seed, (uint64_t)(tok * a.d + c0) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
-        drop_pair(seed, (uint64_t)(tok * a.d + c0 + 2) >> 1, a.drop_thresh, a.drop_inv_keep, k2, k3);
-        dy[0] *= k0; dy[1] *= k1; dy[2] *= k2; dy[3] *= k3;
+        const uint32_t m4 = drop_mask4(seed, (uint64_t)(tok * a.d + c0) >> 2, a.drop_thresh);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dy[j] = drop_sel(dy[j], m4, j) * a.drop_inv_keep;
       }
       const float4 lw = __ldg(reinterpret_cast<const float4*>(a.ln_w + c0));
       const float lwv[4] = {lw.x, lw.y, lw.z, lw.w};
@@ -245,11 +243,13 @@ __global__ void __launch_bounds__(EW * 32) embed_ln_bwd_kernel(EmbBwdArgs b) {
   }
 }
 
-static uint32_t emb_thr16(float p) {
+static uint32_t emb_thr8(float p) {   // round(256 p): common.cuh drop_mask4
   if (!(p > 0.f)) return 0u;
-  const uint32_t t = (uint32_t)(p * 65536.0f + 0.5f);
-  return t < 1u ? 1u : (t > 65535u ? 65535u : t);
+  const uint32_t t = (uint32_t)(p * 256.0f + 0.5f);
+  return t < 1u ? 1u : (t > 255u ? 255u : t);
 }
+static uint32_t emb_thr4(float p) { return emb_thr8(p) * 0x01010101u; }
+static float emb_scale(float p) { return 256.0f / (256.0f - (float)emb_thr8(p)); }
 
 template <typename Kern, typename Args>
 static int launch_emb(Kern kern, const Args& args, int64_t N, size_t smem, cudaStream_t st) {
@@ -291,7 +291,7 @@ extern "C" int meant_embed_ln_fwd(const int64_t* ids, const float* word, const f
                                   int S, int d, int64_t vocab, int max_pos, int pad_idx, float drop_p, uint64_t seed,
                                   const uint64_t* seed_dev, int dtype, meant_stream_t stream) {
   EmbArgs a{ids, word, pos, type, ln_w, ln_b, out, pos_ids, mean, rstd, N, vocab, S, d, max_pos, pad_idx, eps,
-            emb_thr16(drop_p), 1.0f / (1.0f - drop_p), seed, reinterpret_cast<const unsigned long long*>(seed_dev)};
+            emb_thr4(drop_p), emb_scale(drop_p), seed, reinterpret_cast<const unsigned long long*>(seed_dev)};
   if (!emb_ok(a) || !out || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   const size_t smem = sizeof(int) * (size_t)S;
@@ -304,8 +304,8 @@ extern "C" int meant_embed_ln_bwd(const void* dy, const int64_t* ids, const int*
                                   int64_t vocab, int max_pos, float drop_p, uint64_t seed, const uint64_t* seed_dev, int dtype,
                                   meant_stream_t stream) {
   EmbBwdArgs b{{ids, word, pos, type, ln_w, ln_w /* ln_b is not needed */, nullptr, const_cast<int*>(pos_ids),
-                const_cast<float*>(mean), const_cast<float*>(rstd), N, vocab, S, d, max_pos, 0, 0.f, emb_thr16(drop_p),
-                1.0f / (1.0f - drop_p), seed, reinterpret_cast<const unsigned long long*>(seed_dev)},
+                const_cast<float*>(mean), const_cast<float*>(rstd), N, vocab, S, d, max_pos, 0, 0.f, emb_thr4(drop_p),
+                emb_scale(drop_p), seed, reinterpret_cast<const unsigned long long*>(seed_dev)},
                dy, dword, dpos, dtype_row, dln_w, dln_b};
   if (!emb_ok(b.f) || !dy || !dword || !dpos || !dtype_row || !dln_w || !dln_b || drop_p < 0.f || drop_p >= 1.f) return MEANT_EARG;
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);

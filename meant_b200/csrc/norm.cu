@@ -22,7 +22,7 @@ struct NormArgs {
   int d;
   float eps;
   int pre_gelu;
-  uint32_t drop_thresh;  // 0 = no dropout
+  uint32_t drop_thresh;  // round(256 p) in each byte (drop_mask4); 0 = no dropout
   float drop_inv_keep;
   uint64_t seed;
   const unsigned long long* seed_dev;   // optional device-resident addend (CUDA-graph replays advance it)
@@ -50,16 +50,27 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
     }
   }
   const float inv_d = 1.0f / (float)a.d;
-  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
-    const int64_t base = row * a.d;
-    float v[CHUNKS][V];
-    Vec16<T> t[CHUNKS], r[CHUNKS];
+  // The next row's loads are issued before this row is touched: a warp always has two rows of requests in flight, which
+  // is what keeps HBM busy while the GELU / dropout arithmetic of the current row runs (the kernel was latency-bound
+  // with one row in flight per warp: 20 warps x 1.5 KB per SM against the ~27 KB Little's law asks for).
+  const int64_t stride = (int64_t)gridDim.x * 4;
+  Vec16<T> t[CHUNKS], r[CHUNKS];
+  auto fetch = [&](int64_t row_, Vec16<T>* tt, Vec16<T>* rr) {
+    const int64_t b_ = row_ * a.d;
 #pragma unroll
-    for (int c = 0; c < CHUNKS; ++c) t[c].load(x + base + (lane + 32 * c) * V);
+    for (int c = 0; c < CHUNKS; ++c) tt[c].load(x + b_ + (lane + 32 * c) * V);
     if (res) {
 #pragma unroll
-      for (int c = 0; c < CHUNKS; ++c) r[c].load(res + base + (lane + 32 * c) * V);
+      for (int c = 0; c < CHUNKS; ++c) rr[c].load(res + b_ + (lane + 32 * c) * V);
     }
+  };
+  const int64_t row0 = (int64_t)blockIdx.x * 4 + warp;
+  if (row0 < a.rows) fetch(row0, t, r);
+  for (int64_t row = row0; row < a.rows; row += stride) {
+    const int64_t base = row * a.d;
+    float v[CHUNKS][V];
+    Vec16<T> tn[CHUNKS], rn[CHUNKS];
+    if (row + stride < a.rows) fetch(row + stride, tn, rn);
     float ss = 0.f, sm = 0.f;
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
@@ -110,17 +121,18 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
       for (int i = 0; i < V; ++i) o[i] = LN ? (v[c][i] - mean) * rinv * g[c][i] + bb[c][i] : g[c][i] * (v[c][i] * rinv_o);
       if (!LN && a.drop_thresh) {
 #pragma unroll
-        for (int i = 0; i < V; i += 2) {
-          bool k0, k1;
-          drop_pair_keep(seed, (uint64_t)(base + col + i) >> 1, a.drop_thresh, k0, k1);
-          o[i] = k0 ? o[i] : 0.f;
-          o[i + 1] = k1 ? o[i + 1] : 0.f;
+        for (int i = 0; i < V; i += 4) {
+          const uint32_t m4 = drop_mask4(seed, (uint64_t)(base + col + i) >> 2, a.drop_thresh);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) o[i + j] = drop_sel(o[i + j], m4, j);
         }
       }
       Vec16<T> ov;
       ov.pack(o);
       ov.store(y + base + col);
     }
+#pragma unroll
+    for (int c = 0; c < CHUNKS; ++c) { t[c] = tn[c]; r[c] = rn[c]; }
   }
 }
 
@@ -192,7 +204,7 @@ struct NormBwdArgs {
 // 3-4 CTAs of 4 warps per SM keep >= 36 KB of loads in flight.
 // COLSUM (RMSNorm only): also accumulate sum_rows dx into a.dbias -- the bias gradient of the Linear that produced x.
 template <typename T, int CHUNKS, bool LN, bool GELU, bool COLSUM = false>
-__global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_kernel(NormBwdArgs a) {
+__global__ void __launch_bounds__(128, GELU ? 2 : ((LN || COLSUM) ? 3 : 4)) norm_bwd_kernel(NormBwdArgs a) {
   static_assert(!(LN && COLSUM), "the dbias accumulators serve LayerNorm's bias OR the column sum of dx");
   uint64_t seed = a.seed;
   if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
@@ -209,20 +221,36 @@ __global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_
 #pragma unroll
     for (int i = 0; i < V; ++i) { g[c][i] = a.gain[(lane + 32 * c) * V + i]; dg[c][i] = 0.f; db[c][i] = 0.f; }
   const float inv_d = 1.0f / (float)a.d;
-  for (int64_t row = (int64_t)blockIdx.x * 4 + warp; row < a.rows; row += (int64_t)gridDim.x * 4) {
-    const int64_t base = row * a.d;
-    Vec16<T> tu[CHUNKS], tg[CHUNKS], ts[CHUNKS];
+  // GELU forms (arithmetic-heavy: erf polynomial, its derivative, the dropout hash): as in the forward kernel, the next
+  // row's loads (src, dy, the row statistics) are in flight while this row computes -- measured 195 -> 166 us per launch.
+  // The other forms are faster WITHOUT it (the extra registers cost a resident CTA): PF is off for them and the "next"
+  // fetch below degenerates to loading the current row at the top of each iteration.
+  constexpr bool PF = GELU;
+  const int64_t stride = (int64_t)gridDim.x * 4;
+  Vec16<T> tu[CHUNKS], tg[CHUNKS], ts[CHUNKS];
+  float mean_n = 0.f, rinv_n = 0.f;
+  auto fetch = [&](int64_t row_, Vec16<T>* uu, Vec16<T>* gg, float& mn, float& ri) {
+    const int64_t b_ = row_ * a.d;
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) {
-      tu[c].load(src + base + (lane + 32 * c) * V);
-      tg[c].load(dy + base + (lane + 32 * c) * V);
+      uu[c].load(src + b_ + (lane + 32 * c) * V);
+      gg[c].load(dy + b_ + (lane + 32 * c) * V);
     }
+    mn = LN ? a.stat0[row_] : 0.f;
+    ri = LN ? a.stat1[row_] : a.stat0[row_];
+  };
+  const int64_t row0 = (int64_t)blockIdx.x * 4 + warp;
+  if (PF && row0 < a.rows) fetch(row0, tu, tg, mean_n, rinv_n);
+  for (int64_t row = row0; row < a.rows; row += stride) {
+    const int64_t base = row * a.d;
+    if (!PF) fetch(row, tu, tg, mean_n, rinv_n);
+    const float mean = mean_n, rinv = rinv_n;
     if (dsi) {
 #pragma unroll
       for (int c = 0; c < CHUNKS; ++c) ts[c].load(dsi + base + (lane + 32 * c) * V);
     }
-    const float mean = LN ? a.stat0[row] : 0.f;
-    const float rinv = LN ? a.stat1[row] : a.stat0[row];
+    Vec16<T> un[PF ? CHUNKS : 1], gn[PF ? CHUNKS : 1];
+    if (PF && row + stride < a.rows) fetch(row + stride, un, gn, mean_n, rinv_n);
     float sk[GELU ? CHUNKS : 1][V], gk[GELU ? CHUNKS : 1][V];   // GELU form: activation and its derivative
     float t1 = 0.f, t2 = 0.f;
 #pragma unroll
@@ -232,11 +260,10 @@ __global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_
       tg[c].unpack(gy);
       if (a.drop_thresh) {
 #pragma unroll
-        for (int i = 0; i < V; i += 2) {
-          float k0, k1;
-          drop_pair(seed, (uint64_t)(base + (lane + 32 * c) * V + i) >> 1, a.drop_thresh, a.drop_inv_keep, k0, k1);
-          gy[i] *= k0;
-          gy[i + 1] *= k1;
+        for (int i = 0; i < V; i += 4) {
+          const uint32_t m4 = drop_mask4(seed, (uint64_t)(base + (lane + 32 * c) * V + i) >> 2, a.drop_thresh);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) gy[i + j] = drop_sel(gy[i + j], m4, j) * a.drop_inv_keep;
         }
         tg[c].pack(gy);     // the second sweep re-reads the masked gradient (exact: 0 or a power-of-two scale for p = 0.5;
                             // otherwise one extra rounding of dy * inv_keep to T, as if dropout's backward had run in T)
@@ -285,6 +312,10 @@ __global__ void __launch_bounds__(128, (GELU || LN || COLSUM) ? 3 : 4) norm_bwd_
       Vec16<T> ov;
       ov.pack(o);
       ov.store(dx + base + (lane + 32 * c) * V);
+    }
+    if (PF) {
+#pragma unroll
+      for (int c = 0; c < CHUNKS; ++c) { tu[c] = un[c]; tg[c] = gn[c]; }
     }
   }
   // block-level reduction of the per-warp column sums, then one atomic per column per block
@@ -349,15 +380,17 @@ __global__ void __launch_bounds__(128) norm_bwd_generic_kernel(NormBwdArgs a) {
   }
 }
 
-static uint32_t drop_thr16(float p) {   // 16-bit keep threshold (common.cuh: drop_pair); 0 = dropout off
+static uint32_t drop_thr8(float p) {   // 8-bit drop threshold round(256 p) (common.cuh: drop_mask4); 0 = dropout off
   if (!(p > 0.f)) return 0u;
-  const uint32_t t = (uint32_t)(p * 65536.0f + 0.5f);
-  return t < 1u ? 1u : (t > 65535u ? 65535u : t);
+  const uint32_t t = (uint32_t)(p * 256.0f + 0.5f);
+  return t < 1u ? 1u : (t > 255u ? 255u : t);
 }
+static uint32_t drop_thr4(float p) { return drop_thr8(p) * 0x01010101u; }
+static float drop_scale(float p) { return 256.0f / (256.0f - (float)drop_thr8(p)); }   // 1 / realised keep probability
 
 static int grid_for(int64_t rows) {
   int64_t blocks = (rows + 3) / 4;
-  const int64_t cap = 148 * 8;  // persistent-ish: <= 8 resident 128-thread CTAs per SM
+  const int64_t cap = 148 * 4;  // persistent: one resident wave of 128-thread CTAs (4 per SM at ~125 registers)
   return (int)(blocks < cap ? (blocks > 0 ? blocks : 1) : cap);
 }
 
@@ -383,7 +416,7 @@ template <typename T, bool LN>
 static int launch_bwd(const NormBwdArgs& a, cudaStream_t st) {
   constexpr int V = Vec16<T>::N;
   int g = grid_for(a.rows);
-  if (g > 148 * 4) g = 148 * (a.pre_gelu ? 3 : 4);  // one resident wave: fewer dgain atomics
+  if (g > 148 * 2) g = 148 * (a.pre_gelu ? 2 : ((LN || a.dbias) ? 3 : 4));  // one resident wave: fewer dgain atomics
   const bool vec_ok = (a.d % (32 * V) == 0) &&
                       ((reinterpret_cast<uintptr_t>(a.dy) | reinterpret_cast<uintptr_t>(a.src) |
                         reinterpret_cast<uintptr_t>(a.dx) | reinterpret_cast<uintptr_t>(a.dsum_in)) % 16 == 0);
@@ -422,7 +455,7 @@ extern "C" int meant_rmsnorm_fwd(const void* x, const void* res, const float* ga
   if (pre_gelu && res) return MEANT_EARG;
   if (rows == 0) return 0;
   NormArgs a{x, res, gain, nullptr, y, sum_out, rinv, nullptr, rows, d, eps, pre_gelu,
-             drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
+             drop_thr4(drop_p), drop_scale(drop_p), seed,
              reinterpret_cast<const unsigned long long*>(seed_dev)};
   if (dtype == MEANT_DT_F32) return launch_fwd<float, false>(a, stream);
   if (dtype == MEANT_DT_BF16) return launch_fwd<__nv_bfloat16, false>(a, stream);
@@ -437,7 +470,7 @@ extern "C" int meant_rmsnorm_bwd(const void* dy, const void* src, const float* g
   if (pre_gelu && dsum_in) return MEANT_EARG;   // see meant_rmsnorm_fwd
   if (rows == 0) return 0;
   NormBwdArgs a{dy, src, gain, rinv, nullptr, dsum_in, dx, dgain, dxsum, rows, d, eps, pre_gelu,
-                drop_thr16(drop_p), 1.0f / (1.0f - drop_p), seed,
+                drop_thr4(drop_p), drop_scale(drop_p), seed,
                 reinterpret_cast<const unsigned long long*>(seed_dev)};
   if (dtype != MEANT_DT_F32 && dtype != MEANT_DT_BF16) return MEANT_EUNSUPPORTED;
   int rc = dtype == MEANT_DT_F32 ? launch_bwd<float, false>(a, stream) : launch_bwd<__nv_bfloat16, false>(a, stream);

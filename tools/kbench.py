@@ -101,7 +101,10 @@ def norm(args):
     g = torch.ones(d, device="cuda", requires_grad=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     byts = rows * d * 2
-    for name, kw, tf, tb in (("plain", {}, 2, 3), ("gelu", {"pre_gelu": True}, 2, 3), ("res", {"residual": res}, 4, 4)):
+    for name, kw, tf, tb in (("plain", {}, 2, 3), ("gelu", {"pre_gelu": True}, 2, 3), ("gelu+drop", {"pre_gelu": True, "drop_p": 0.5}, 2, 3),
+                             ("plain+drop", {"drop_p": 0.5}, 2, 3), ("res", {"residual": res}, 4, 4)):
+        if args.only and name != args.only:
+            continue
         f_med, f_min = timeit(lambda: ops.rms_norm(x.detach(), g.detach(), **kw), args.iters, flush)
         y = ops.rms_norm(x, g, **kw)
         outs = y if isinstance(y, tuple) else (y,)
@@ -153,6 +156,7 @@ if __name__ == "__main__":
     ap.add_argument("--causal", type=int, default=1)
     ap.add_argument("--norot", action="store_true")
     ap.add_argument("--impl", default="auto")
+    ap.add_argument("--only", default="", help="norm: run one variant only (plain, gelu, gelu+drop, plain+drop, res)")
     ap.add_argument("--prerotate", type=int, default=1, help="multi-tile attention: rotate Q, K once into scratch (0: in the kernels)")
     a = ap.parse_args()
     a.causal = bool(a.causal)
