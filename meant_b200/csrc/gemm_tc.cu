@@ -372,7 +372,8 @@ extern "C" int meant_gemm_bf16_tn(const void* A, const void* W, const float* bia
   const int64_t tiles_n = (N + g1::BN - 1) / g1::BN;
   // CTA pairs with a multicast W box: correct but measured 2-15 % SLOWER than the single-CTA kernel on the bench shapes
   // (the pair runs in lock step; L2 -> SM traffic was not the limiter), so it is opt-in: MEANT_GEMM_MC=1
-  const bool mc = sms % 2 == 0 && ((M + 255) / 256) * tiles_n >= 2 * (int64_t)sms && getenv("MEANT_GEMM_MC") != nullptr;
+  static const bool env_mc = getenv("MEANT_GEMM_MC") != nullptr, env_t256 = getenv("MEANT_GEMM_TILE256") != nullptr;   // read once
+  const bool mc = sms % 2 == 0 && ((M + 255) / 256) * tiles_n >= 2 * (int64_t)sms && env_mc;
   if (!rc) rc = g1::make_map2(&maps.w, W, N, K, ldw, g1::BK, mc ? 128 : g1::BN);
   if (!rc) rc = g1::make_map2(&maps.c, C, M, N, ldc, 64, 128);
   if (rc) return rc;
@@ -384,7 +385,7 @@ extern "C" int meant_gemm_bf16_tn(const void* A, const void* W, const float* bia
     return 0;
   }
   // 256-row tiles measured slower on the bench shapes (exposed epilogue, coarser waves): opt-in for experiments
-  const bool big = getenv("MEANT_GEMM_TILE256") != nullptr && ((M + 255) / 256) * tiles_n >= 4 * (int64_t)sms;
+  const bool big = env_t256 && ((M + 255) / 256) * tiles_n >= 4 * (int64_t)sms;
   const int bm = big ? 256 : 128;
   const size_t smem = big ? g1::Cfg<2>::SMEM_TOTAL : g1::Cfg<1>::SMEM_TOTAL;
   auto kern = big ? g1::gemm_tn_kernel<2> : g1::gemm_tn_kernel<1>;
