@@ -9,7 +9,8 @@
  *   - every pointer is a DEVICE pointer into caller-owned memory; nothing is allocated here;
  *   - `stream` is the CUDA stream to launch on (the caller's current stream);
  *   - return value: 0 = ok, > 0 = cudaError_t of the failed launch, < 0 = argument error
- *     (MEANT_EARG -1 bad argument, MEANT_EUNSUPPORTED -2 unsupported dtype/shape);
+ *     (MEANT_EARG -1 bad argument, MEANT_EUNSUPPORTED -2 unsupported dtype/shape, MEANT_ETOOBIG -3 problem
+ *     larger than a fixed-size internal buffer: meant_attn_q1_fwd_static only);
  *     no exception crosses the boundary;
  *   - re-entrant and thread-safe (no global state besides the launch counter and the
  *     one-time cudaFuncSetAttribute calls);
@@ -137,6 +138,18 @@ int64_t meant_attn_tma_fallbacks(void);
  *      also receive gradients from the group attention of the same module).                                   */
 int meant_attn_q1_fwd(const meant_attn_args* args, float* partial, int dtype, meant_stream_t stream);
 int meant_attn_q1_bwd(const meant_attn_args* args, float* partial, int accumulate, int dtype, meant_stream_t stream);
+/* meant_attn_q1_fwd without the caller-owned scratch and without any allocation.  NO COUNTERPART IN THE REFERENCE:
+ * added for callers that cannot call cudaMalloc (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as meant_attn_q1_fwd;
+ * the partial (max, sum, sum p v) records live in a file-scope `static __device__` array of
+ * MEANT_Q1_STATIC_FLOATS fp32 (4 MiB, held by every GPU that loads the library until exit).  Problems with
+ * N * H * ceil(Sk/64) * (Dh + 2) > MEANT_Q1_STATIC_FLOATS are rejected with MEANT_ETOOBIG (-3) and a message on
+ * stderr; nothing is launched.  The call itself calls no cudaMalloc / cudaFree / allocating routine (the array's
+ * device address is looked up once per device with cudaGetSymbolAddress and cached).  Every call on a GPU shares the
+ * array: calls that overlap on that GPU (different streams, or graphs replayed concurrently) RACE -- serialise them.
+ * Nothing has to start at zero (the partial pass writes every record the merge pass reads).                  */
+#define MEANT_Q1_STATIC_FLOATS (1 << 20)
+int meant_attn_q1_fwd_static(const meant_attn_args* args, int dtype, meant_stream_t stream);
 
 /* ---- mean over the token axis: meant/meant.py:231, meant/meant_tweet.py:157 ------------- */
 int meant_meanpool_fwd(const void* x, void* y, int64_t N, int S, int D, int dtype, meant_stream_t stream);

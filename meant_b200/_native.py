@@ -66,6 +66,7 @@ SIGNATURES = {
     "meant_attn_tma_fallbacks": (i64, []),
     "meant_attn_q1_fwd": (i32, [C.POINTER(AttnArgs), vp, i32, vp]),
     "meant_attn_q1_bwd": (i32, [C.POINTER(AttnArgs), vp, i32, i32, vp]),
+    "meant_attn_q1_fwd_static": (i32, [C.POINTER(AttnArgs), i32, vp]),
     "meant_meanpool_fwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_meanpool_bwd": (i32, [vp, vp, i64, i32, i32, i32, vp]),
     "meant_geglu_fwd": (i32, [vp, vp, i64, i32, i32, vp]),

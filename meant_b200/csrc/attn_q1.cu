@@ -10,6 +10,8 @@
 // HBM-bound: K and V are read once (forward), once more plus one read-modify-write of dK, dV (backward).
 #include "attn_common.cuh"
 #include <math_constants.h>
+#include <atomic>
+#include <cstdio>
 
 namespace meant {
 namespace q1 {
@@ -276,6 +278,34 @@ static int bwd(const AttnArgs& a, float* dq32, int accumulate, cudaStream_t st) 
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------ no-allocation forward
+// Scratch for meant_attn_q1_fwd_static: a file-scope device array, so the call needs no caller buffer and no
+// allocation (CUDA-graph capture, serving loops that may not call cudaMalloc).  Every GPU that loads the library holds
+// these MEANT_Q1_STATIC_FLOATS * 4 bytes (4 MiB) until exit.  The forward's partial pass writes every entry its merge
+// pass reads, so nothing has to start at zero; calls that overlap on one GPU share the array and race.
+static __device__ __align__(256) float q1_static_scratch[MEANT_Q1_STATIC_FLOATS];
+
+constexpr int Q1_MAX_DEV = 64;
+static std::atomic<float*> q1_static_ptr[Q1_MAX_DEV];
+
+// the array's DEVICE address on the current device (in host code its name is only a host-side stand-in): looked up
+// once per device with that device current, then cached
+static int q1_static_addr(float** out) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= Q1_MAX_DEV) return MEANT_EUNSUPPORTED;
+  float* p = q1_static_ptr[dev].load(std::memory_order_acquire);
+  if (!p) {
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), q1_static_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (!p) return MEANT_EUNSUPPORTED;
+    q1_static_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return 0;
+}
+
 }  // namespace q1
 }  // namespace meant
 
@@ -295,5 +325,23 @@ extern "C" int meant_attn_q1_bwd(const meant_attn_args* args, float* partial, in
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (dtype == MEANT_DT_F32) return q1::bwd<float>(*args, partial, accumulate, st);
   if (dtype == MEANT_DT_BF16) return q1::bwd<__nv_bfloat16>(*args, partial, accumulate, st);
+  return MEANT_EUNSUPPORTED;
+}
+
+extern "C" int meant_attn_q1_fwd_static(const meant_attn_args* args, int dtype, meant_stream_t stream) {
+  if (!args || !q1::q1_ok(*args, false)) return MEANT_EARG;
+  const int64_t nchunk = (args->Sk + q1::KC - 1) / q1::KC;
+  const int64_t need = (int64_t)args->N * args->H * nchunk * (args->Dh + 2);
+  if (need > (int64_t)MEANT_Q1_STATIC_FLOATS) {
+    fprintf(stderr, "meant_attn_q1_fwd_static: N * H * ceil(Sk/64) * (Dh + 2) = %lld floats exceeds the static scratch of %d "
+            "floats; use meant_attn_q1_fwd with a caller buffer\n", (long long)need, (int)MEANT_Q1_STATIC_FLOATS);
+    return MEANT_ETOOBIG;
+  }
+  float* scratch = nullptr;
+  const int rc = q1::q1_static_addr(&scratch);
+  if (rc) return rc;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (dtype == MEANT_DT_F32) return q1::fwd<float>(*args, scratch, st);
+  if (dtype == MEANT_DT_BF16) return q1::fwd<__nv_bfloat16>(*args, scratch, st);
   return MEANT_EUNSUPPORTED;
 }

@@ -10,6 +10,7 @@
 
 // C-ABI error codes (include/meant_b200.h): 0 ok, >0 cudaError_t, <0 argument error.
 #define MEANT_EARG (-1)
+#define MEANT_ETOOBIG (-3)
 #define MEANT_EUNSUPPORTED (-2)
 
 extern "C" void meant_count_launch_(int n);
