@@ -61,6 +61,9 @@ def workload_config(args, n):
             "mode": "train (dropout on)",
             "launch": "whole step (incl. the NCCL gradient all-reduces) replayed from one CUDA graph" if args.graph else "eager launches",
             "linear_forward_gemm": getattr(args, "gemm", "library"),
+            "linear_weight_gradient": "meant_gemm_bf16_wgrad (hand-written tcgen05, bias gradient from an extra MMA column) where the bias "
+                                      "gradient would need its own pass (q|v|k and norm-less Linears); library GEMM elsewhere"
+                                      if getattr(args, "gemm", "library") == "library" else "native",
             "l2": "no flush needed: each step streams >10 GB of activations/weights, far above the 126 MB L2"}
 
 
@@ -210,6 +213,13 @@ def rooflines(args, stats, steps):
             extra.append({"kernel": name, "bound": "hbm", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
                           "frac": round(ach / hbm, 4), "traffic": None, "avg_ms": round(ms, 4),
                           "launches_per_step": count / steps, "peak_source": src})
+        elif name.startswith("gemm_wgrad/") or name.startswith("gemm_dgrad/"):
+            dims = [int(f[1:]) for f in name.split("/")[1:4]]
+            fl = 2.0 * dims[0] * dims[1] * dims[2]
+            tf = fl / (ms * 1e-3) / 1e12
+            extra.append({"kernel": name + " (hand-written tcgen05, gemm_tc2.cu)", "bound": "tensor", "achieved": round(tf, 1),
+                          "peak": tf_sus, "unit": "TFLOP/s", "frac": round(tf / tf_sus, 4), "traffic": None,
+                          "avg_ms": round(ms, 4), "launches_per_step": count / steps, "peak_source": src + ", sustained"})
         elif name.startswith("bias_grad/"):
             r_, c_ = (int(f[1:]) for f in name.split("/")[1:3])
             if r_ < tokens:

@@ -207,6 +207,20 @@ int meant_embed_ln_bwd(const void* dy, const int64_t* ids, const int* pos_ids, c
  *      lda / ldw / ldc: row pitches in elements.  N and K multiples of 8; pointers 16-byte aligned. ---------- */
 int meant_gemm_bf16_tn(const void* A, const void* W, const float* bias, void* C, int64_t M, int N, int K,
                        int64_t lda, int64_t ldw, int64_t ldc, meant_stream_t stream);
+/* The other forms of the same Linear layers (backward of meant/meant.py:101-107, meant/xPosAttention.py:24-32), same
+ * pipeline.  C[M, N] (bf16) = op(A) op(B) (+ bias[N], fp32) (+ residual[M, N], bf16; row pitch ldr):
+ *   a_mn = 0: A is [M, K] row-major (lda >= K);   a_mn = 1: A is stored [K, M] row-major (lda >= M; M % 8 == 0)
+ *   b_mn = 0: B is [N, K] row-major (C = A B^T: nn.Linear forward);  b_mn = 1: B is stored [K, N] (C = A B: dX = dY W)
+ * Nothing is transposed in memory: MN-major operands are read with 64 x 64 TMA boxes and MN-major MMA descriptors. */
+int meant_gemm_bf16(const void* A, const void* B, void* C, int64_t M, int N, int K, int64_t lda, int64_t ldb,
+                    int64_t ldc, int a_mn, int b_mn, const float* bias, const void* residual, int64_t ldr,
+                    meant_stream_t stream);
+/* Weight and bias gradient of a Linear: dW[N, K] (fp32) += dY[T, N]^T X[T, K] and, when db != NULL, db[N] (fp32) +=
+ * column sums of dY (from an extra MMA column against a tile of ones: no pass over dY).  ACCUMULATES: zero dW / db
+ * first for a plain gradient.  Split over the T tokens with TMA reduce-add of fp32 partial tiles: the summation
+ * order is not fixed (results can differ in the last bits between runs).                                        */
+int meant_gemm_bf16_wgrad(const void* dY, const void* X, float* dW, float* db, int64_t T, int N, int K, int64_t lddy,
+                          int64_t ldx, int64_t lddw, meant_stream_t stream);
 
 /* ---- the step after backward: src/in_loop_train.py:237-244 (CrossEntropyLoss on the sigmoid outputs, clip_grad_norm_(1.0),
  *      AdamW: :568), as multi-tensor kernels.  A launch takes a BY-VALUE table of up to MEANT_OPT_MAX_TENSORS fp32 tensors

@@ -51,6 +51,8 @@ SIGNATURES = {
     "meant_rmsnorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, f32, u64, vp, vp, i32, vp]),
     "meant_bias_grad": (i32, [vp, vp, i64, i32, i64, i32, vp]),
     "meant_gemm_bf16_tn": (i32, [vp, vp, vp, vp, i64, i32, i32, i64, i64, i64, vp]),
+    "meant_gemm_bf16": (i32, [vp, vp, vp, i64, i32, i32, i64, i64, i64, i32, i32, vp, vp, i64, vp]),
+    "meant_gemm_bf16_wgrad": (i32, [vp, vp, vp, vp, i64, i32, i32, i64, i64, i64, vp]),
     "meant_embedding_fwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
     "meant_embedding_bwd": (i32, [vp, vp, vp, i64, i32, i64, i32, vp]),
     "meant_patchify": (i32, [vp, vp, i64, i32, i32, i32, i32, i32, i32, i32, vp]),

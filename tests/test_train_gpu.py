@@ -222,8 +222,10 @@ def test_clip_folded_into_adamw_matches_clip_grad_norm(own):
 
 
 def test_native_gemm_in_the_linear_wrapper():
-    """ops.use_native_gemm routes the Linear forward through meant_gemm_bf16_tn: same outputs and gradients (the
-    native kernel adds the fp32 bias before rounding, the library path adds a bf16 bias: <= 1 bf16 ulp apart)."""
+    """The Linear wrapper's three GEMM routes: library everywhere (+ meant_bias_grad), the default (library forward and
+    dgrad, meant_gemm_bf16_wgrad for dW and db in one kernel), and use_native_gemm (forward, dgrad and wgrad through
+    the hand-written tcgen05 kernels): same outputs and gradients (the native forward adds the fp32 bias before
+    rounding, the library path adds a bf16 bias: <= 1 bf16 ulp apart)."""
     from meant_b200 import ops
     torch.manual_seed(0)
     lin = nn.Linear(768, 2304).cuda()
@@ -232,8 +234,9 @@ def test_native_gemm_in_the_linear_wrapper():
     res = {}
     try:
         ops.use_fused_linear(True)
-        for native in (False, True):
-            ops.use_native_gemm(native)
+        for mode in ("library", "default", "native"):
+            ops.use_native_gemm(mode == "native")
+            ops.use_native_wgrad(mode != "library")
             for t in (x, lin.weight, lin.bias):
                 t.grad = None
             nv = _lib()
@@ -241,10 +244,12 @@ def test_native_gemm_in_the_linear_wrapper():
             with torch.autocast("cuda", dtype=torch.bfloat16):
                 y = ops.linear(x, lin.weight, lin.bias)
             y.backward(dy)
-            res[native] = (y.detach().float(), x.grad.clone(), lin.weight.grad.clone(), nv.launch_count())
+            res[mode] = (y.detach().float(), x.grad.clone(), lin.weight.grad.clone(), lin.bias.grad.clone(), nv.launch_count())
     finally:
         ops.use_native_gemm(False)
+        ops.use_native_wgrad(True)
         ops.use_fused_linear(False)
-    assert res[True][3] == res[False][3] + 1                 # one more native launch: the GEMM
-    for a, b in zip(res[True][:3], res[False][:3]):
-        assert float((a - b).abs().max()) <= 2e-2 * max(1.0, float(b.abs().max()))
+    assert res["library"][4] == 1 and res["default"][4] == 1 and res["native"][4] == 3     # bias_grad | wgrad | fwd, dgrad, wgrad
+    for mode in ("default", "native"):
+        for a, b in zip(res[mode][:4], res["library"][:4]):
+            assert float((a - b).abs().max()) <= 2e-2 * max(1.0, float(b.abs().max())), mode

@@ -103,7 +103,7 @@ def step_split_ms(run_step):
             continue
         launches += 1
         name = ev.name.lower()
-        if name.startswith("meant::gemm") or "gemm_tc" in name:
+        if "meant::g1::gemm" in name or "meant::g2::gemm" in name:
             split.setdefault("own_gemm", 0.0)
             split["own_gemm"] += ev.device_time / 1e3
             continue
