@@ -1200,6 +1200,25 @@ __global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
         const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)sr * a.rot_dim + ch * 8);
         ca = __ldg(c4), cb = __ldg(c4 + 1), sa = __ldg(s4), sb = __ldg(s4 + 1);
       }
+      if (a.H == 8) {          // the models' head count: all eight 16-byte loads in flight before the first store
+        uint4 raw[8];
+#pragma unroll
+        for (int h = 0; h < 8; ++h) raw[h] = tc::ldg_stream16(sp + (int64_t)h * src.sh);
+#pragma unroll
+        for (int h = 0; h < 8; ++h) {
+          if (rot) {
+            __nv_bfloat162* h2 = reinterpret_cast<__nv_bfloat162*>(&raw[h]);
+            const float2 p0 = __bfloat1622float2(h2[0]), p1 = __bfloat1622float2(h2[1]);
+            const float2 p2 = __bfloat1622float2(h2[2]), p3 = __bfloat1622float2(h2[3]);
+            h2[0] = __floats2bfloat162_rn(p0.x * ca.x - p0.y * sa.x, p0.y * ca.y + p0.x * sa.y);
+            h2[1] = __floats2bfloat162_rn(p1.x * ca.z - p1.y * sa.z, p1.y * ca.w + p1.x * sa.w);
+            h2[2] = __floats2bfloat162_rn(p2.x * cb.x - p2.y * sb.x, p2.y * cb.y + p2.x * sb.y);
+            h2[3] = __floats2bfloat162_rn(p3.x * cb.z - p3.y * sb.z, p3.y * cb.w + p3.x * sb.w);
+          }
+          *reinterpret_cast<uint4*>(dp + (int64_t)h * dst.sh) = raw[h];
+        }
+        continue;
+      }
 #pragma unroll 4
       for (int h = 0; h < a.H; ++h) {
         uint4 raw = *reinterpret_cast<const uint4*>(sp + (int64_t)h * src.sh);
@@ -1247,6 +1266,8 @@ __global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
 int attn_tc2_supported(const AttnArgs& a, int backward);
 int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_bwd(const AttnArgs& a, cudaStream_t st);
+int attn_tc2_ms_supported(const AttnArgs& a);
+int attn_tc2_fwd_ms(const AttnArgs& a, cudaStream_t st);
 
 static bool view_ok(const HeadView& v) {
   return v.p != nullptr && (reinterpret_cast<uintptr_t>(v.p) % 16 == 0) && v.sn1 % 8 == 0 && v.sn2 % 8 == 0 &&
@@ -1332,6 +1353,11 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     const int r2 = attn_tc2_fwd(a, st);
     if (r2 != MEANT_EUNSUPPORTED) return r2;     // views TMA cannot describe fall through to the multi-tile kernel
     ++g_tma_fallbacks;
+  }
+  static const bool old_mt = getenv("MEANT_ATTN_OLD_MT") != nullptr;   // read once: A/B against the per-tile-pair kernel below
+  if (!old_mt && attn_tc2_ms_supported(a)) {
+    const int r2 = attn_tc2_fwd_ms(a, st);
+    if (r2 != MEANT_EUNSUPPORTED) return r2;
   }
   dim3 grid((a.Sq + TQ - 1) / TQ, a.H, a.N);
   FwdMtMaps maps;

@@ -117,6 +117,23 @@ __device__ __forceinline__ void load_tab(RotTab<RC>& T, const float* cs, const f
   }
 }
 
+// the same with 16-byte loads (tables 16-byte aligned, rot_dim % 4 == 0): a quarter of the load instructions -- the
+// multi-step kernel reloads the key-side table at every step
+template <int RC>
+__device__ __forceinline__ void load_tab4(RotTab<RC>& T, const float* cs, const float* sn, int pos, int rot_dim) {
+  const float4* c4 = reinterpret_cast<const float4*>(cs + (int64_t)pos * rot_dim);
+  const float4* s4 = reinterpret_cast<const float4*>(sn + (int64_t)pos * rot_dim);
+#pragma unroll
+  for (int i = 0; i < RC * 2; ++i) {
+    float4 a = make_float4(1.f, 1.f, 1.f, 1.f), b = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (4 * i < rot_dim) { a = __ldg(c4 + i); b = __ldg(s4 + i); }
+    T.c[2 * i] = __floats2half2_rn(a.x, a.y);
+    T.c[2 * i + 1] = __floats2half2_rn(a.z, a.w);
+    T.s[2 * i] = __floats2half2_rn(b.x, b.y);
+    T.s[2 * i + 1] = __floats2half2_rn(b.z, b.w);
+  }
+}
+
 // Rotate (INV = false) or un-rotate (transpose rotation, INV = true) the first rc chunks of one
 // row r of an operand tile in place (RC <= 8: the rotated chunks all live in the SWIZZLE_128B sub-tile).
 template <int RC, bool INV>
@@ -579,6 +596,387 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
       tc::fence_before_sync();
       tc::mbar_arrive(&o_staged[st]);
       pf.tick(7);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// ============================================================================== forward, several key tiles per query tile
+// The same three-role pipeline for Sq or Sk > 128 (the 196-patch vision path, S = 512 text): a work item is one
+// (sequence, head, 128-query tile) and runs one STEP per 128-key tile, each step being exactly a single-tile pass --
+// Q | K | V boxes into a stage (Q is simply fetched again: it comes from L2), rotation in place, S = Q K^T into the
+// stage's TMEM buffer, softmax out of TMEM, P over the consumed Q | K, O_j = P V over the consumed S -- except that
+// the softmax is the online one: the running row max / row sum and the output accumulator (this thread's half of the
+// head dimension) live in registers across the steps, O_j is folded in with the usual exp2(m_old - m_new) correction,
+// and only the item's last step normalises, stages and stores.  Steps of consecutive items are pipelined exactly
+// like single-tile items (NST stages in flight), so the tensor core, the TMA loads and the softmax of neighbouring
+// steps overlap and nobody who computes waits for an instruction issue.  Rotation happens in the kernel: no
+// pre-rotated copies of Q and K exist.  Causal problems (Sq == Sk) skip the key tiles above the diagonal; the query
+// tiles are dealt so that every CTA sees a mix of short and long items (ms_item).
+struct MsDims { int nq, nk; };                    // query tiles / key tiles per (sequence, head)
+
+template <int DH>
+struct FwdMsL {
+  using G = Geo<DH>;
+  static constexpr int NST = 3;
+  static constexpr uint32_t STAGE = 3 * G::OPER;
+  static constexpr uint32_t AUX = NST * STAGE;                 // [NST][128] fp32 additive key bias (exp2 domain)
+  static constexpr uint32_t RED = AUX + NST * 512;             // [2][2][128] row max (double buffered) | [2][128] row sum
+  static constexpr uint32_t BARS = RED + 3072;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;
+  static_assert(G::PBUF <= 2 * G::OPER, "P must fit in Q | K");
+};
+
+// item id -> sequence, head, query tile.  The query tiles of one (sequence, head) are permuted by a rotation that
+// depends on that pair only (a bijection per pair), pseudo-randomly, so that a CTA whose ids are congruent mod nq
+// (gridDim.x a multiple of nq) still sees every query tile -- causal items differ in length.
+__device__ __forceinline__ void ms_item(int id, int j, int H, int nq, int& n, int& h, int& qt) {
+  (void)j;
+  const int nh = id / nq;
+  qt = (id - nh * nq + __popc(nh)) % nq;
+  n = nh / H;
+  h = nh - n * H;
+}
+// number of key tiles item (.., qt) visits
+__device__ __forceinline__ int ms_steps(const AttnArgs& a, int qt, int nk) {
+  if (!a.causal) return nk;
+  const int last_q = min(qt * 128 + 128, a.Sq) - 1;
+  return min(nk, last_q / 128 + 1);
+}
+
+template <int DH, int RC>
+__global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n_items, const __grid_constant__ FwdMaps maps,
+                                                               const MsDims dm) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  using L = FwdMsL<DH>;
+  using G = Geo<DH>;
+  constexpr int NST = L::NST;
+  constexpr int HALF = DH / 2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *landed = bars, *s_full = bars + NST, *o_full = bars + 2 * NST, *o_staged = bars + 3 * NST,
+           *aux_ready = bars + 4 * NST, *rot_done = bars + 5 * NST, *p_ready = bars + 6 * NST;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < NST; ++i) {
+      tc::mbar_init(&landed[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);
+      tc::mbar_init(&s_full[i], 1);
+      tc::mbar_init(&o_full[i], 1);
+      tc::mbar_init(&o_staged[i], NC);
+      tc::mbar_init(&rot_done[i], NC);
+      tc::mbar_init(&p_ready[i], NC);
+    }
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int rc = (a.qcos && !a.q_rot.p) ? a.rot_dim / 8 : 0;      // q_rot / k_rot given: the maps read those, nothing to rotate
+  const uint32_t s0 = tc::smem_u32(smem);
+
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    // what stage st holds when it is about to be refilled: the staged output of a finished item, or nothing
+    int held_n[NST], held_h[NST], held_q[NST];
+#pragma unroll
+    for (int i = 0; i < NST; ++i) { held_q[i] = -1; held_n[i] = 0; held_h[i] = 0; }
+    auto store_out = [&](int st) {                                // lane 0
+      const uint32_t sb = s0 + st * L::STAGE;
+      const int n1 = held_n[st] / a.n2_count, n2 = held_n[st] - n1 * a.n2_count;
+      tma::store_box(&maps.m[6], sb, 0, held_h[st], held_q[st] * 128, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[7], sb + SUB_A, 64, held_h[st], held_q[st] * 128, n2, n1);
+      tma::store_commit();
+    };
+    int s = 0;
+    for (int j = 0; j < n_my; ++j) {
+      int n, h, qt;
+      ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, n, h, qt);
+      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      const int steps = ms_steps(a, qt, dm.nk);
+      for (int kt = 0; kt < steps; ++kt, ++s) {
+        const int st = s % NST;
+        if (s >= NST) {
+          tc::mbar_wait(&o_staged[st], ((s - NST) / NST) & 1);
+          if (lane == 0 && held_q[st] >= 0) {
+            store_out(st);
+            tma::store_wait_read<0>();                            // the stage may be overwritten now
+          }
+        }
+        // static indexing of the held_* arrays (they stay in registers)
+#pragma unroll
+        for (int i = 0; i < NST; ++i)
+          if (i == st) {
+            held_q[i] = kt == steps - 1 ? qt : -1;
+            held_n[i] = n;
+            held_h[i] = h;
+          }
+        if (lane == 0) {
+          const uint32_t sb = s0 + st * L::STAGE;
+          tma::mbar_expect_tx(&landed[st], 3 * G::OPER);
+#pragma unroll
+          for (int v = 0; v < 3; ++v) {
+            const int r0 = v == 0 ? qt * 128 : kt * 128;
+            tma::load_box(sb + v * G::OPER, &maps.m[2 * v], &landed[st], 0, h, r0, n2, n1);
+            if (G::TAIL) tma::load_box(sb + v * G::OPER + SUB_A, &maps.m[2 * v + 1], &landed[st], 64, h, r0, n2, n1);
+          }
+        }
+        float4 mv = make_float4(1.f, 1.f, 1.f, 1.f);
+        const int k0 = kt * 128 + lane * 4;
+        if (a.key_mask) {
+          const float* mrow = a.key_mask + (int64_t)n * a.Sk;
+          if (k0 + 3 < a.Sk && (a.Sk & 3) == 0) mv = __ldg(reinterpret_cast<const float4*>(mrow + k0));
+          else {
+            if (k0 < a.Sk) mv.x = __ldg(mrow + k0);
+            if (k0 + 1 < a.Sk) mv.y = __ldg(mrow + k0 + 1);
+            if (k0 + 2 < a.Sk) mv.z = __ldg(mrow + k0 + 2);
+            if (k0 + 3 < a.Sk) mv.w = __ldg(mrow + k0 + 3);
+          }
+        }
+        reinterpret_cast<float4*>(smem + L::AUX + st * 512)[lane] =
+            make_float4(key_bias2(mv.x, k0, a.Sk), key_bias2(mv.y, k0 + 1, a.Sk), key_bias2(mv.z, k0 + 2, a.Sk),
+                        key_bias2(mv.w, k0 + 3, a.Sk));
+        tc::mbar_arrive(&aux_ready[st]);
+      }
+    }
+    // drain: the last min(s, NST) steps' stages, oldest first
+    for (int u = max(0, s - NST); u < s; ++u) {
+      const int st = u % NST;
+      tc::mbar_wait(&o_staged[st], (u / NST) & 1);
+#pragma unroll
+      for (int i = 0; i < NST; ++i)
+        if (i == st && lane == 0 && held_q[i] >= 0) store_out(i);
+    }
+    if (lane == 0) tma::store_wait_all();
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      int total = 0;
+      for (int j = 0; j < n_my; ++j) {
+        int n, h, qt;
+        ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, n, h, qt);
+        total += ms_steps(a, qt, dm.nk);
+      }
+      auto issue_s = [&](int s) {
+        const int st = s % NST;
+        tc::mbar_wait(&rot_done[st], (s / NST) & 1);
+        tc::fence_after_sync();
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+        const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + st * 128, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
+        tc::mma_commit(&s_full[st]);
+      };
+      // S runs two steps ahead of P V: S(s + 1) is complete by the time the softmax of step s is, so the compute
+      // warps go from one step's softmax straight into the next one's
+      if (total > 0) issue_s(0);
+      if (total > 1) issue_s(1);
+      for (int s = 0; s < total; ++s) {
+        const int st = s % NST;
+        tc::mbar_wait(&p_ready[st], (s / NST) & 1);
+        tc::fence_after_sync();
+        const uint32_t sp = s0 + st * L::STAGE, sv = sp + 2 * G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) mma_oper_mn<DH>(tmem + st * 128, desc_p_k(sp, ks), sv, ks, 0, ks > 0);
+        tc::mma_commit(&o_full[st]);
+        if (s + 2 < total) issue_s(s + 2);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;
+    const int t = rg * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    float* red_max = reinterpret_cast<float*>(smem + L::RED);     // [2 (step parity)][2 (half)][128]
+    float* red_sum = red_max + 512;                               // [2][128]
+    RotTab<RC> tab;
+    const float* tcs = half ? a.kcos : a.qcos;
+    const float* tsn = half ? a.ksin : a.qsin;
+    int cur_pos = -1;
+    const bool vec_tab = ((reinterpret_cast<uintptr_t>(tcs) | reinterpret_cast<uintptr_t>(tsn)) & 15) == 0 && (a.rot_dim & 3) == 0;
+    // the step sequence of this CTA, walked twice: one step ahead (prepare) and in place (softmax)
+    struct Walk {
+      int j, kt, steps, n, h, qt;
+    };
+    auto start = [&](Walk& w, int j) {
+      w.j = j;
+      w.kt = 0;
+      if (j < n_my) {
+        ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, w.n, w.h, w.qt);
+        w.steps = ms_steps(a, w.qt, dm.nk);
+      }
+    };
+    auto advance = [&](Walk& w) {
+      if (++w.kt == w.steps) start(w, w.j + 1);
+    };
+    // rotate the step's Q (half 0) / K (half 1) rows in place and hand the stage to the MMA warp
+    auto prepare = [&](const Walk& w, int s) {
+      const int st = s % NST;
+      if (rc) {
+        const int pos = a.pos_is_head ? w.h : (half ? min(w.kt * 128 + t, a.Sk - 1) : min(w.qt * 128 + t, a.Sq - 1));
+        if (pos != cur_pos) {
+          if (vec_tab) load_tab4<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          else load_tab<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          cur_pos = pos;
+        }
+      }
+      tc::mbar_wait(&landed[st], (s / NST) & 1);
+      if (rc) rot_row<RC, false>(smem + st * L::STAGE + half * G::OPER, t, rc, tab);
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&rot_done[st]);
+    };
+    Walk wp, wc;
+    start(wp, 0);
+    start(wc, 0);
+    for (int u = 0; u < 2; ++u)                                   // two steps ahead of the softmax
+      if (wp.j < n_my) {
+        prepare(wp, u);
+        advance(wp);
+      }
+    float m_run = -CUDART_INF_F, l_run = 0.f;
+    float o_acc[HALF];
+    for (int s = 0; wc.j < n_my; ++s) {
+      const int st = s % NST;
+      const uint32_t par = (s / NST) & 1;
+      const bool first = wc.kt == 0, last = wc.kt == wc.steps - 1;
+      if (first) {
+        m_run = -CUDART_INF_F;
+        l_run = 0.f;
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) o_acc[i] = 0.f;
+      }
+      const int k0 = wc.kt * 128, q0 = wc.qt * 128;
+      const bool dtile = a.causal && k0 == q0;                      // the diagonal tile: keys after the query are masked
+      int nblk = (min(a.Sk - k0, 128) + 31) >> 5;
+      if (dtile) nblk = min(nblk, rg + 1);
+      tc::mbar_wait(&aux_ready[st], par);
+      tc::mbar_wait(&s_full[st], par);
+      tc::fence_after_sync();
+      const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + st * 512);
+      const uint32_t ts = lane_base + st * 128;
+      float m = -CUDART_INF_F;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {                                           // warp-uniform
+          float sv[32];
+          tc::tmem_ld32(ts + blk * 32, sv);
+          tc::tmem_ld_wait();
+          const bool diag = dtile && blk == rg;
+#pragma unroll
+          for (int e = 0; e < 32; e += 4) {
+            const float4 b = b4[(blk * 32 + e) >> 2];
+            const float bb[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) sv[e + u] = fmaf(sv[e + u], scale2, bb[u]);
+          }
+          if (diag) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) m = fmaxf(m, e > lane ? -CUDART_INF_F : sv[e]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) m = fmaxf(m, sv[e]);
+          }
+        }
+      }
+      float* rmx = red_max + (s & 1) * 256;
+      rmx[half * 128 + t] = m;
+      tc::bar_sync(BAR_PAIR + rg, 64);
+      m = fmaxf(m, rmx[(half ^ 1) * 128 + t]);
+      const float m_new = fmaxf(m_run, m);
+      const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
+      const float corr = tc::ex2(m_run - m_use);                    // m_run = -inf -> 0
+      m_run = m_new;
+      float l0 = 0.f, l1 = 0.f;
+      uint8_t* pbuf = smem + st * L::STAGE;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {
+          float sv[32];
+          tc::tmem_ld32(ts + blk * 32, sv);
+          tc::tmem_ld_wait();
+          const bool diag = dtile && blk == rg;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 ba = b4[(blk * 32 + q * 8) >> 2], bc = b4[((blk * 32 + q * 8) >> 2) + 1];
+            const float bb[8] = {ba.x, ba.y, ba.z, ba.w, bc.x, bc.y, bc.z, bc.w};
+            uint4 pk;
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = q * 8 + 2 * u;
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - m_use)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - m_use));
+              if (diag) {
+                if (e > lane) p0 = 0.f;
+                if (e + 1 > lane) p1 = 0.f;
+              }
+              l0 += p0;
+              l1 += p1;
+              ph[u] = __floats2bfloat162_rn(p0, p1);
+            }
+            *reinterpret_cast<uint4*>(pbuf + pbuf_off(t, blk * 4 + q)) = pk;
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(pbuf + pbuf_off(t, blk * 4 + q)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      l_run = fmaf(l_run, corr, l0 + l1);
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&p_ready[st]);                                // the MMA warp starts O_j = P V
+      if (wp.j < n_my) {                                            // rotation of step s + 2 hides the P V latency of step s
+        prepare(wp, s + 2);
+        advance(wp);
+      }
+      float l = l_run;
+      if (last) {
+        red_sum[half * 128 + t] = l_run;
+        tc::bar_sync(BAR_PAIR + rg, 64);
+        l += red_sum[(half ^ 1) * 128 + t];
+      }
+      tc::mbar_wait(&o_full[st], par);
+      tc::fence_after_sync();
+      {
+        float pv[HALF];
+        tc::tmem_ld32(ts + half * HALF, pv);
+        if constexpr (HALF > 32) tc::tmem_ld16(ts + half * HALF + 32, pv + 32);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) o_acc[i] = fmaf(o_acc[i], corr, pv[i]);
+      }
+      if (last) {
+        const float inv = l > 0.f ? 1.0f / l : 0.f;
+        uint8_t* tile = smem + st * L::STAGE;
+#pragma unroll
+        for (int q = 0; q < HALF / 8; ++q) {
+          uint4 pk;
+          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(o_acc[q * 8 + 2 * i] * inv, o_acc[q * 8 + 2 * i + 1] * inv);
+          *reinterpret_cast<uint4*>(tile + oper_off(t, half * (HALF / 8) + q)) = pk;
+        }
+        if (half == 0 && a.lse && q0 + t < a.Sq)
+          a.lse[((int64_t)wc.n * a.H + wc.h) * a.Sq + q0 + t] = m_use * LN2 + logf(l);
+        tc::fence_async_smem();
+      }
+      tc::fence_before_sync();
+      tc::mbar_arrive(&o_staged[st]);
+      advance(wc);
     }
   }
   tc::fence_before_sync();
@@ -1171,6 +1569,51 @@ static int launch_bwd(const AttnArgs& a, cudaStream_t st) {
   if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7, g)) return rc;
   if (g.G) return launch2(t2::attn2_bwd_kernel<DH, RC, true>, t2::BwdL<DH>::TOTAL, a, maps, g, st);
   return launch2(t2::attn2_bwd_kernel<DH, RC, false>, t2::BwdL<DH>::TOTAL, a, maps, g, st);
+}
+
+// multi-tile problems the multi-step forward takes (the caller has already checked dtype, views, Dh)
+int attn_tc2_ms_supported(const AttnArgs& a) {
+  if (a.Sq <= 128 && a.Sk <= 128) return 0;
+  if (a.kx.p != nullptr) return 0;
+  if (a.causal && a.Sq != a.Sk) return 0;
+  if (a.qcos && !a.q_rot.p) {
+    const int rc_max = a.Dh == 96 ? 6 : 8;
+    if (a.rot_dim / 8 > rc_max) return 0;
+    const uintptr_t al = reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) |
+                         reinterpret_cast<uintptr_t>(a.kcos) | reinterpret_cast<uintptr_t>(a.ksin);
+    if (al % 8 != 0) return 0;
+  }
+  const bool pre = a.q_rot.p != nullptr;
+  const HeadView* vs[4] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o};
+  for (int i = 0; i < 4; ++i)
+    if (vs[i]->ss <= 0 || vs[i]->ss >= (1 << 23)) return 0;
+  return 1;
+}
+
+template <int DH, int RC>
+static int launch_fwd_ms(const AttnArgs& a, cudaStream_t st) {
+  t2::FwdMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const t2::Grp g = {0, 0, 0, 0, 0};
+  const bool pre = a.q_rot.p != nullptr;
+  const HeadView* vs[4] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o};
+  const int seq[4] = {a.Sq, a.Sk, a.Sk, a.Sq};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 4, g)) return rc;
+  const t2::MsDims dm = {(a.Sq + 127) / 128, (a.Sk + 127) / 128};
+  const int64_t items = (int64_t)a.N * a.H * dm.nq;
+  if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
+  auto kern = t2::attn2_fwd_ms_kernel<DH, RC>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t2::FwdMsL<DH>::TOTAL);
+  if (e != cudaSuccess) return (int)e;
+  const int grid = (int)(items < num_sms() ? items : num_sms());
+  kern<<<grid, t2::F_NT, t2::FwdMsL<DH>::TOTAL, st>>>(a, (int)items, maps, dm);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+int attn_tc2_fwd_ms(const AttnArgs& a, cudaStream_t st) {
+  if (a.Dh == 96) return launch_fwd_ms<96, 6>(a, st);
+  return launch_fwd_ms<64, 8>(a, st);
 }
 
 // MEANT_EUNSUPPORTED: a view the tensor maps cannot describe (the caller falls back to the multi-tile kernels)

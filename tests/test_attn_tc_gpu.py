@@ -152,7 +152,9 @@ def test_prerotated_and_in_flight_rotation_agree(s, causal):
     finally:
         ops.PREROTATE = True
     torch.cuda.synchronize()
-    # same bf16 rotation arithmetic either way: outputs agree to rounding of the accumulation order
-    assert float((got[0][0] - got[1][0]).abs().max()) < 1e-2
+    # outputs agree to one bf16 ulp of the value (rounding of the accumulation order; the in-flight path of the
+    # multi-step forward keeps its rotation tables in fp16): 2^-7 relative, 1e-2 absolute below 1
+    diff, mag = (got[0][0] - got[1][0]).abs(), got[0][0].abs().clamp(min=1.0)
+    assert bool((diff <= 1e-2 * mag).all()), float((diff / mag).max())
     c = torch.nn.functional.cosine_similarity(got[0][1].flatten(), got[1][1].flatten(), dim=0)
     assert float(c) > 0.9999, float(c)

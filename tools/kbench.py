@@ -86,6 +86,23 @@ def attn(args):
 
     b_med, b_min = timeit(bwd, args.iters, flush)
     prof("bwd", n * heads, 3 + args.iters)
+    if args.kernels:                       # per-kernel device times of one forward + backward (torch.profiler)
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CUDA]) as pr:
+            for _ in range(5):
+                flush.zero_()
+                out2 = fwd()
+                out2.backward(dout)
+            torch.cuda.synchronize()
+        agg = {}
+        for ev in pr.events():
+            if ev.device_type == torch.autograd.DeviceType.CUDA:
+                k = ev.name[:90]
+                a_ = agg.setdefault(k, [0, 0.0])
+                a_[0] += 1
+                a_[1] += ev.device_time
+        for k, (c, tot) in sorted(agg.items(), key=lambda kv: -kv[1][1])[:12]:
+            print(f"    {tot / c:9.1f} us x{c // 5}/iter  {k}")
     # algorithmic work: fwd reads q,k,v + writes o; bwd reads q,k,v,dO (+lse) + writes dq,dk,dv
     tile = n * s * dim * 2
     fl = (2.0 if args.causal else 4.0) * s * s * dh * heads * n
@@ -157,6 +174,7 @@ if __name__ == "__main__":
     ap.add_argument("--norot", action="store_true")
     ap.add_argument("--impl", default="auto")
     ap.add_argument("--only", default="", help="norm: run one variant only (plain, gelu, gelu+drop, plain+drop, res)")
+    ap.add_argument("--kernels", action="store_true", help="attn: print per-kernel device times (torch.profiler)")
     ap.add_argument("--prerotate", type=int, default=1, help="multi-tile attention: rotate Q, K once into scratch (0: in the kernels)")
     a = ap.parse_args()
     a.causal = bool(a.causal)
