@@ -3,7 +3,10 @@
 torch is the plumbing here (device memory, streams, autograd graph); every op below runs a
 hand-written sm_100a kernel from libmeant_b200.so and raises if that is impossible.
 """
+import contextlib
 import math
+import threading
+import weakref
 
 import torch
 
@@ -43,42 +46,118 @@ def _f32(t):
     return t.detach().float().contiguous()
 
 
-# ---- per-step state installed by train.TrainStep (inactive otherwise) ------------------------------------------
-# _shadow: {id(param): (param, bf16 copy)} refreshed once per step with ONE multi-tensor cast instead of one cast
-# kernel per Linear per step; ("packed", id(wq), id(wv), id(wk)) -> (packed weight, packed bias) for the fused q|v|k
-# projection.  _arena: a zeroed fp32 buffer handed out in slices for the small per-column accumulators of the norm
-# backward kernels (one fill per step instead of ~100).
-_shadow = None
-_arena = None
-_arena_off = 0
+# ---- operator context ------------------------------------------------------------------------------------------
+class OpsContext:
+    """State the operator wrappers consult, owned by whoever drives a step (train.TrainStep builds one per instance and
+    activates it around its forward + backward with `use`).  Two models or two TrainSteps therefore never share it, and
+    a backward pass running on an autograd worker thread sees the context of ITS forward: every autograd Function
+    stores `current()` at forward time and reads only that object in backward.
+
+      shadow        {id(param): (param, bf16 copy)} kept current by the optimizer update (or one multi-tensor cast per
+                    step); ("packed", id(wq), id(wv), id(wk)) -> (packed weight, packed bias, weights) for the fused
+                    q | v | k projection
+      arena         zeroed fp32 buffer handed out in slices for the small per-column accumulators of the norm backward
+                    kernels (one fill per step instead of ~100); arena_off is the bump pointer, reset by begin_step()
+      graph_seed    device int64 added to every dropout seed by the kernels (advanced inside a captured step)
+      fused_linear  route ops.linear / ops.linear3 through _LinearFn / _Linear3Fn
+      native_gemm   forward + dgrad + wgrad of those through the hand-written tcgen05 GEMMs
+      native_wgrad  wgrad + bias gradient in one tcgen05 kernel wherever the bias gradient would need its own pass
+      attn_impl, prerotate   None = the module-level defaults DEFAULT_ATTN_IMPL / PREROTATE
+    """
+
+    def __init__(self, shadow=None, arena=None, fused_linear=False, native_gemm=None, native_wgrad=None, attn_impl=None,
+                 prerotate=None):
+        self.shadow = shadow
+        self.arena = arena
+        self.arena_off = 0
+        self.graph_seed = None
+        self.fused_linear = bool(fused_linear)
+        self._native_gemm = native_gemm
+        self._native_wgrad = native_wgrad
+        self.attn_impl = attn_impl
+        self.prerotate = prerotate
+        self._colsum = {}
+
+    # a context without its own choice follows the process-wide default context (use_native_gemm / use_native_wgrad)
+    @property
+    def native_gemm(self):
+        return _default.native_gemm if (self._native_gemm is None and self is not _default) else bool(self._native_gemm)
+
+    @native_gemm.setter
+    def native_gemm(self, v):
+        self._native_gemm = v
+
+    @property
+    def native_wgrad(self):
+        if self._native_wgrad is None:
+            return True if self is _default else _default.native_wgrad
+        return bool(self._native_wgrad)
+
+    @native_wgrad.setter
+    def native_wgrad(self, v):
+        self._native_wgrad = v
+
+    def begin_step(self):
+        self.arena_off = 0
+        self._colsum.clear()
+
+    def shadow_of(self, p, dtype):
+        if self.shadow is None or p is None:
+            return None
+        e = self.shadow.get(id(p))
+        return e[1] if e is not None and e[0] is p and e[1].dtype == dtype else None
+
+    def zeros(self, n, device):
+        if self.arena is not None and self.arena.device == device:
+            start = (self.arena_off + 63) // 64 * 64
+            if start + n <= self.arena.numel():
+                self.arena_off = start + n
+                return self.arena[start:start + n]
+        return torch.zeros(n, dtype=torch.float32, device=device)
+
+    # The norm backward also sums dx over rows; when that dx is the dy of a Linear, the sum IS the layer's bias gradient.
+    # The hand-off is keyed by the tensor object autograd passes on (identity + version), and lives here, not on the tensor.
+    def put_colsum(self, dx, colsum):
+        self._colsum[id(dx)] = (weakref.ref(dx), dx._version, colsum)
+
+    def take_colsum(self, dy, n_out, dtype):
+        e = self._colsum.pop(id(dy), None)
+        if e is None or e[0]() is not dy or e[1] != dy._version or e[2].numel() != n_out or dy.dtype != dtype:
+            return None
+        return e[2]
 
 
+_default = OpsContext()
+_tls = threading.local()
+
+
+def current():
+    """The active context of this thread (the process-wide default one outside any `use`)."""
+    return getattr(_tls, "ctx", None) or _default
+
+
+@contextlib.contextmanager
+def use(ctx):
+    prev = getattr(_tls, "ctx", None)
+    _tls.ctx = ctx
+    try:
+        yield ctx
+    finally:
+        _tls.ctx = prev
+
+
+# process-wide defaults (benchmarks, tests, eager use without a TrainStep) act on the default context
 def set_weight_shadows(d):
-    global _shadow
-    _shadow = d
-
-
-def _shadow_of(p, dtype):
-    if _shadow is None or p is None:
-        return None
-    e = _shadow.get(id(p))
-    return e[1] if e is not None and e[0] is p and e[1].dtype == dtype else None
+    _default.shadow = d
 
 
 def set_zero_arena(buf):
     """buf: fp32 tensor that the caller zeroes at the start of every step (None switches the arena off)."""
-    global _arena, _arena_off
-    _arena, _arena_off = buf, 0
+    _default.arena, _default.arena_off = buf, 0
 
 
-def _zeros(n, device):
-    global _arena_off
-    if _arena is not None and _arena.device == device:
-        start = (_arena_off + 63) // 64 * 64
-        if start + n <= _arena.numel():
-            _arena_off = start + n
-            return _arena[start:start + n]
-    return torch.zeros(n, dtype=torch.float32, device=device)
+def set_graph_seed(t):
+    _default.graph_seed = t
 
 
 # ------------------------------------------------------------------------------ RMSNorm
@@ -95,7 +174,8 @@ class _RMSNormFn(torch.autograd.Function):
         s = torch.empty_like(x2) if r2 is not None else None
         rinv = torch.empty(rows, dtype=torch.float32, device=x2.device)
         tag = f"rmsnorm_fwd/d{d}/res{int(r2 is not None)}/gelu{int(pre_gelu)}"
-        sdev = _graph_seed if drop_p > 0.0 else None
+        octx = ctx.octx = current()
+        sdev = octx.graph_seed if drop_p > 0.0 else None
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_fwd, nv.ptr(x2), nv.ptr(r2), nv.ptr(g32), nv.ptr(y), nv.ptr(s),
                           nv.ptr(rinv), rows, d, eps, int(pre_gelu), drop_p, seed, nv.ptr(sdev), nv.dt(x2),
                           nv.stream()), "meant_rmsnorm_fwd")
@@ -116,27 +196,19 @@ class _RMSNormFn(torch.autograd.Function):
         dy = torch.zeros_like(src) if dy is None else dy.to(src.dtype).contiguous()
         ds = dsum.to(src.dtype).contiguous() if dsum is not None else None
         dx = torch.empty_like(src)
-        dgain = _zeros(d, src.device)
+        octx = ctx.octx
+        dgain = octx.zeros(d, src.device)
         # with the Linear wrapper active the kernel also sums dx over rows: if x came out of a Linear, that is the
-        # layer's bias gradient (picked up by _LinearFn.backward through the tag below)
-        dxsum = _zeros(d, src.device) if _fused_linear and xdt == src.dtype else None
+        # layer's bias gradient (picked up by _LinearFn.backward through the context's colsum hand-off)
+        dxsum = octx.zeros(d, src.device) if octx.fused_linear and xdt == src.dtype else None
         tag = f"rmsnorm_bwd/d{d}/res{int(ds is not None)}/gelu{pre_gelu}" + ("/colsum" if dxsum is not None else "")
         nv.check(nv.timed(tag, nv.lib().meant_rmsnorm_bwd, nv.ptr(dy), nv.ptr(src), nv.ptr(g32), nv.ptr(rinv),
                           nv.ptr(ds), nv.ptr(dx), nv.ptr(dgain), rows, d, eps, pre_gelu, drop_p, seed,
                           nv.ptr(ctx.sdev), nv.ptr(dxsum), nv.dt(src), nv.stream()), "meant_rmsnorm_bwd")
+        dxo = dx.to(xdt)
         if dxsum is not None:
-            dx._meant_colsum = (dxsum, dx._version)     # valid only while dx is not modified (version check)
-        return dx.to(xdt), (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
-
-
-# Device-resident int64 added to every dropout seed by the kernels.  train.TrainStep sets it while a step is
-# captured into a CUDA graph (and advances it inside the graph), so replays draw fresh masks.
-_graph_seed = None
-
-
-def set_graph_seed(t):
-    global _graph_seed
-    _graph_seed = t
+            octx.put_colsum(dxo, dxsum)                 # valid only while dx is not modified (version check)
+        return dxo, (dx.to(rdt) if has_res else None), dgain.to(gdt), None, None, None, None
 
 
 def _seed():
@@ -166,25 +238,18 @@ def _mm_f32(a, b):
         return torch.mm(a, b).float()
 
 
-_native_gemm = False
-
-
 def use_native_gemm(on=True):
-    """Forward GEMM of the Linear wrappers through the hand-written tcgen05 kernel (meant_gemm_bf16_tn) instead of
-    cuBLASLt.  Off by default: the library GEMM is still 7-10 % faster on the bench shapes."""
-    global _native_gemm
-    _native_gemm = bool(on)
-
-
-_native_wgrad = True
+    """Forward, dgrad and wgrad GEMMs of the Linear wrappers through the hand-written tcgen05 kernels (meant_gemm_bf16_tn,
+    meant_gemm_bf16, meant_gemm_bf16_wgrad) instead of cuBLASLt, for every context that has no choice of its own.
+    Off by default: the library GEMM is still 7-10 % faster on the forward / dgrad shapes."""
+    _default.native_gemm = bool(on)
 
 
 def use_native_wgrad(on=True):
     """Weight + bias gradient of the Linear wrappers through meant_gemm_bf16_wgrad whenever the bias gradient would
     otherwise need its own pass over dY (on by default: 112 vs 103 + 41 us at 98304 x 768 x 768, 328 vs 290 + 97 us at
     N = 2304).  With use_native_gemm(True) every weight gradient takes it."""
-    global _native_wgrad
-    _native_wgrad = bool(on)
+    _default.native_wgrad = bool(on)
 
 
 def _gemm_ok(t2):
@@ -213,21 +278,21 @@ def _dgrad_native(dy2, wc):
     return dx
 
 
-def _linear_bwd(ctx_needs, dy2, x2, wc, colsum, want_db):
+def _linear_bwd(octx, ctx_needs, dy2, x2, wc, colsum, want_db):
     """The three gradients of a Linear from 2-D bf16/fp32 operands: (dx | None, dw fp32 | None, db fp32 | None)."""
     n_out, n_in = wc.shape
     native_ok = _gemm_ok(dy2) and _gemm_ok(x2) and _gemm_ok(wc) and n_out % 8 == 0 and n_in % 8 == 0 and dy2.shape[0] >= 1024
     dx = dw = db = None
     if ctx_needs[0]:
-        dx = _dgrad_native(dy2, wc) if (_native_gemm and native_ok) else torch.mm(dy2, wc)
+        dx = _dgrad_native(dy2, wc) if (octx.native_gemm and native_ok) else torch.mm(dy2, wc)
     need_db = want_db and colsum is None
-    if ctx_needs[1] and native_ok and (_native_gemm or (_native_wgrad and need_db)):
+    if ctx_needs[1] and native_ok and (octx.native_gemm or (octx.native_wgrad and need_db)):
         dw, db = _wgrad_native(dy2, x2, need_db)
         need_db = False
     elif ctx_needs[1]:
         dw = _mm_f32(dy2.t(), x2)
     if want_db and colsum is not None:
-        db = colsum[0]
+        db = colsum
     elif need_db:
         db = torch.empty(n_out, dtype=torch.float32, device=dy2.device)
         nv.check(nv.timed(f"bias_grad/r{dy2.shape[0]}/c{n_out}", nv.lib().meant_bias_grad, nv.ptr(dy2), nv.ptr(db),
@@ -235,10 +300,10 @@ def _linear_bwd(ctx_needs, dy2, x2, wc, colsum, want_db):
     return dx, dw, db
 
 
-def _gemm_fwd(xc, wc, bc, bias_f32):
+def _gemm_fwd(octx, xc, wc, bc, bias_f32):
     """y = xc @ wc^T + bias for bf16 operands: the tcgen05 kernel when selected and applicable, else F.linear."""
     n_out, n_in = wc.shape
-    if _native_gemm and xc.dtype == torch.bfloat16 and n_out % 8 == 0 and n_in % 8 == 0 and xc.is_contiguous() \
+    if octx.native_gemm and xc.dtype == torch.bfloat16 and n_out % 8 == 0 and n_in % 8 == 0 and xc.is_contiguous() \
             and wc.stride(1) == 1 and wc.stride(0) % 8 == 0 and (bias_f32 is None or bias_f32.dtype == torch.float32):
         x2 = xc.reshape(-1, n_in)
         y = torch.empty(x2.shape[0], n_out, dtype=xc.dtype, device=xc.device)
@@ -261,11 +326,12 @@ class _LinearFn(torch.autograd.Function):
         nv.require_cuda(x, weight, bias)
         with torch.autocast("cuda", enabled=False):
             xc = x.to(dtype)
-            wc = _shadow_of(weight, dtype)
+            octx = ctx.octx = current()
+            wc = octx.shadow_of(weight, dtype)
             wc = weight.to(dtype) if wc is None else wc
-            bc = _shadow_of(bias, dtype)
+            bc = octx.shadow_of(bias, dtype)
             bc = (bias.to(dtype) if bias is not None else None) if bc is None else bc
-            y = _gemm_fwd(xc, wc, bc, bias.detach() if bias is not None else None)
+            y = _gemm_fwd(octx, xc, wc, bc, bias.detach() if bias is not None else None)
         ctx.save_for_backward(xc, wc)
         ctx.cfg = (x.dtype, weight.dtype, bias.dtype if bias is not None else None)
         return y
@@ -275,16 +341,15 @@ class _LinearFn(torch.autograd.Function):
         xc, wc = ctx.saved_tensors
         xdt, wdt, bdt = ctx.cfg
         n_out, n_in = wc.shape
-        colsum = getattr(dy, "_meant_colsum", None)       # left by _RMSNormFn.backward: sum_rows of this very tensor
-        if colsum is not None and (colsum[1] != dy._version or colsum[0].numel() != n_out or dy.dtype != wc.dtype):
-            colsum = None
+        octx = ctx.octx
+        colsum = octx.take_colsum(dy, n_out, wc.dtype)    # left by _RMSNormFn.backward: sum over rows of this very tensor
         with torch.autocast("cuda", enabled=False):
             dy2 = dy.to(wc.dtype).reshape(-1, n_out)
             if dy2.stride(-1) != 1 or dy2.stride(0) % 8 or dy2.data_ptr() % 16:
                 dy2 = dy2.contiguous()
             x2 = xc.reshape(-1, n_in)
             want_db = bdt is not None and ctx.needs_input_grad[2]
-            dx, dw, db = _linear_bwd(ctx.needs_input_grad, dy2, x2, wc, colsum, want_db)
+            dx, dw, db = _linear_bwd(octx, ctx.needs_input_grad, dy2, x2, wc, colsum, want_db)
             dx = dx.view(xc.shape).to(xdt) if dx is not None else None
             dw = dw.to(wdt) if dw is not None else None
             db = db.to(bdt) if db is not None else None
@@ -300,7 +365,8 @@ class _Linear3Fn(torch.autograd.Function):
     def forward(ctx, x, w0, w1, w2, b0, b1, b2):
         dtype = compute_dtype(x)
         nv.require_cuda(x, w0)
-        packed = _shadow.get(("packed", id(w0), id(w1), id(w2))) if _shadow is not None else None
+        octx = ctx.octx = current()
+        packed = octx.shadow.get(("packed", id(w0), id(w1), id(w2))) if octx.shadow is not None else None
         with torch.autocast("cuda", enabled=False):
             if packed is not None and packed[0].dtype == dtype and packed[2][0] is w0:
                 wc, bc = packed[0], packed[1]
@@ -321,7 +387,7 @@ class _Linear3Fn(torch.autograd.Function):
             dy2 = dy.to(wc.dtype).reshape(-1, n_out)
             if dy2.stride(-1) != 1 or dy2.stride(0) % 8 or dy2.data_ptr() % 16:
                 dy2 = dy2.contiguous()
-            dx, dw, db = _linear_bwd((ctx.needs_input_grad[0], True), dy2, xc.reshape(-1, n_in), wc, None, True)
+            dx, dw, db = _linear_bwd(ctx.octx, (ctx.needs_input_grad[0], True), dy2, xc.reshape(-1, n_in), wc, None, True)
             dx = dx.view(xc.shape).to(xdt) if dx is not None else None
             dw = dw.to(wdt).split(sizes, 0)
             db = db.to(bdt).split(sizes)
@@ -330,7 +396,7 @@ class _Linear3Fn(torch.autograd.Function):
 
 def linear3(x, m0, m1, m2):
     """cat(m0(x), m1(x), m2(x)) along the feature axis for three nn.Linear modules, as one GEMM."""
-    if _fused_linear and x.is_cuda and torch.is_grad_enabled() and m0.bias is not None and m1.bias is not None \
+    if current().fused_linear and x.is_cuda and torch.is_grad_enabled() and m0.bias is not None and m1.bias is not None \
             and m2.bias is not None and x.numel() // x.shape[-1] >= 1024 and m0.weight.shape[0] % 8 == 0 \
             and m1.weight.shape[0] % 8 == 0:
         return _Linear3Fn.apply(x, m0.weight, m1.weight, m2.weight, m0.bias, m1.bias, m2.bias)
@@ -339,18 +405,14 @@ def linear3(x, m0, m1, m2):
     return linear(x, w, b)
 
 
-_fused_linear = False
-
-
 def use_fused_linear(on=True):
-    """Route ops.linear through _LinearFn (set by TrainStep(graph=True); see _LinearFn)."""
-    global _fused_linear
-    _fused_linear = bool(on)
+    """Route ops.linear through _LinearFn in the default context (TrainStep(graph=True) sets it in its own context)."""
+    _default.fused_linear = bool(on)
 
 
 def linear(x, weight, bias=None):
     """nn.Linear forward (meant/meant.py:102,106,107)."""
-    if _fused_linear and bias is not None and x.is_cuda and torch.is_grad_enabled() and \
+    if current().fused_linear and bias is not None and x.is_cuda and torch.is_grad_enabled() and \
             (weight.shape[0] % 8 == 0) and x.numel() // x.shape[-1] >= 1024:
         return _LinearFn.apply(x, weight, bias)
     return torch.nn.functional.linear(x, weight, bias)
@@ -394,7 +456,7 @@ class _EmbedBlockFn(torch.autograd.Function):
         pos_ids = torch.empty(n, s, dtype=torch.int32, device=dev)
         mean = torch.empty(n, s, dtype=torch.float32, device=dev)
         rstd = torch.empty_like(mean)
-        sdev = _graph_seed if drop_p > 0.0 else None
+        sdev = current().graph_seed if drop_p > 0.0 else None
         nv.check(nv.timed(f"embed_ln_fwd/S{s}/d{d}", nv.lib().meant_embed_ln_fwd, nv.ptr(ids2), nv.ptr(word), nv.ptr(pos), nv.ptr(typ),
                           nv.ptr(lw), nv.ptr(lb), float(eps), nv.ptr(out), nv.ptr(pos_ids), nv.ptr(mean), nv.ptr(rstd), n, s, d,
                           word.shape[0], pos.shape[0], int(pad), float(drop_p), seed, nv.ptr(sdev), nv.dt(out), nv.stream()),
@@ -602,7 +664,8 @@ class _AttnFn(torch.autograd.Function):
         # Multi-tile problems on the tensor-core path: rotate Q and K ONCE into scratch (every query tile needs every
         # key tile; the kernels then stage plain tiles), kept for the backward pass.
         qrot = krot = None
-        if (PREROTATE and tabs is not None and (sq > 128 or sk > 128) and impl != nv.IMPL_EXACT
+        octx = current()
+        if ((PREROTATE if octx.prerotate is None else octx.prerotate) and tabs is not None and (sq > 128 or sk > 128) and impl != nv.IMPL_EXACT
                 and nv.lib().meant_attn_tcgen05_supported(a, nv.dt(t0), 0)):
             qrot = torch.empty(n, sq, dim, dtype=dtype, device=t0.device)
             krot = torch.empty(n, sk, dim, dtype=dtype, device=t0.device)
@@ -666,7 +729,8 @@ def attention(qkv=None, q=None, kv=None, k=None, v=None, *, heads, scale, causal
               pos_is_head=False, key_mask=None, impl=None):
     """softmax((Rq q)(Rk k)^T * scale + masks) v on packed `b s (h d)` projections.
     Returns [N, Sq, dim] in `b s (h d)` layout (no rearrange is materialised)."""
-    impl = DEFAULT_ATTN_IMPL if impl is None else impl
+    if impl is None:
+        impl = DEFAULT_ATTN_IMPL if current().attn_impl is None else current().attn_impl
     if qkv is not None:
         return _AttnFn.apply(qkv, None, None, "qkv", heads, scale, causal, rot, pos_is_head, key_mask, impl)
     if kv is not None:
@@ -685,6 +749,7 @@ class _DividedAttnFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, qkv, heads, scale, f, n, time_mode, rot, impl):
+        ctx.octx = current()
         dtype = compute_dtype(qkv)
         nv.require_cuda(qkv)
         qkv = qkv.to(dtype)
@@ -770,7 +835,7 @@ class _DividedAttnFn(torch.autograd.Function):
         dh = inner // heads
         dout = dout.to(out.dtype).contiguous()
         dqkv = torch.empty_like(qkv)
-        acc = _zeros(3 * b * inner, qkv.device).view(3, b, inner)          # dkx | dvx | dq of the cls row, fp32
+        acc = ctx.octx.zeros(3 * b * inner, qkv.device).view(3, b, inner)          # dkx | dvx | dq of the cls row, fp32
         # groups: dq, dk, dv of the body rows (written), gradient of the shared cls key / value (accumulated)
         g, _ = _DividedAttnFn._group_args(qkv, out, lse_g, heads, scale, f, n, time_mode, tabs)
         es = qkv.element_size()
@@ -806,7 +871,8 @@ def divided_attention(qkv, *, heads, scale, frames, patches, time_mode, rot=None
     q | k | v projection [b, 1 + frames*patches, 3*heads*dim_head]; returns [b, 1 + frames*patches, heads*dim_head].
     rot = (qcos, qsin, kcos, ksin): query tables with one row per group position, key tables with one more row (the
     cls key, not rotated)."""
-    impl = DEFAULT_ATTN_IMPL if impl is None else impl
+    if impl is None:
+        impl = DEFAULT_ATTN_IMPL if current().attn_impl is None else current().attn_impl
     return _DividedAttnFn.apply(qkv, heads, scale, frames, patches, time_mode, rot, impl)
 
 

@@ -14,8 +14,9 @@ class TrainStep:
     backward, the bucketed NCCL gradient all-reduces (captured on NCCL's stream, still overlapping backward),
     clip, AdamW -- is captured once into a CUDA graph and replayed, so the ~2000 launches of a step cost no
     host time; inputs are copied into static buffers, dropout masks advance through
-    a device-resident seed (ops.set_graph_seed), and the bias-gradient kernel replaces autograd's reduction
-    (ops.use_fused_linear).  Input shapes and non-tensor arguments must not change between calls."""
+    a device-resident seed, and the bias-gradient kernels replace autograd's reduction.  All of that state (weight
+    shadows, the zero arena, the seed, the Linear routing) lives in this instance's own ops.OpsContext (`self.ctx`),
+    active only around its forward + backward: two TrainSteps / models never see each other's.  Input shapes and non-tensor arguments must not change between calls."""
 
     def __init__(self, model, lr=5e-5, betas=(0.9, 0.999), weight_decay=0.0, max_grad_norm=1.0,
                  bucket_mb=25.0, bf16=True, group=None, graph=False, graph_warmup=3, own_optimizer=True, grad_dtype=None):
@@ -34,12 +35,12 @@ class TrainStep:
         self._g = self._static = self._loss = self._seed_t = None
         self.launches_per_replay = 0            # native-library launches captured in one step
         self._shadow_src = self._shadow_dst = self._shadows = self._arena = None
+        from . import ops
         if self.graph:
-            from . import ops
-            ops.use_fused_linear(True)
             if bf16:
                 self._build_shadows()
             self._arena = torch.zeros(1 << 20, dtype=torch.float32, device=self.params[0].device)
+        self.ctx = ops.OpsContext(shadow=self._shadows, arena=self._arena, fused_linear=self.graph)
         # The step after backward on the library's multi-tensor kernels (optim.py: gradient norm, clip + AdamW, the bf16
         # weight shadows written by the update itself) -- or torch's optimizer (CPU tensors: the gloo tests)
         self._own = own
@@ -95,13 +96,9 @@ class TrainStep:
             torch._foreach_copy_(self._shadow_dst, self._shadow_src)
         if self._arena is not None:
             self._arena.zero_()
-        ops.set_weight_shadows(self._shadows)
-        ops.set_zero_arena(self._arena)
-        try:
+        self.ctx.begin_step()
+        with ops.use(self.ctx):
             return self._step_body(labels, args, kwargs)
-        finally:
-            ops.set_weight_shadows(None)
-            ops.set_zero_arena(None)
 
     def _step_body(self, labels, args, kwargs):
         self.reducer.zero_grad()
@@ -132,14 +129,14 @@ class TrainStep:
         self._seed_t = torch.zeros(1, dtype=torch.int64, device=labels.device)
         torch.cuda.synchronize()
         self._g = torch.cuda.CUDAGraph()
-        ops.set_graph_seed(self._seed_t)
+        self.ctx.graph_seed = self._seed_t
         n0 = nv.launch_count()
         try:
             with torch.cuda.graph(self._g):
                 self._seed_t.add_(0x1E3779B97F4A7C15)     # every replay shifts all dropout seeds
                 self._loss = self._step(self._static[0], self._static[1], self._static[2])
         finally:
-            ops.set_graph_seed(None)
+            self.ctx.graph_seed = None
         self.launches_per_replay = nv.launch_count() - n0
 
     def _load(self, labels, args, kwargs):

@@ -157,6 +157,25 @@ def gemm(args):
     fl = 2.0 * m * n * k
     print(f"gemm M={m} N={n} K={k} bf16: tcgen05 {t_nat*1e3:.1f} us {fl/t_nat/1e9:.0f} TFLOP/s | library {t_lib*1e3:.1f} us "
           f"{fl/t_lib/1e9:.0f} TFLOP/s | max|diff| {err:.3g}")
+    # the backward forms (gemm_tc2.cu): launch order after the forward pair is [dgrad x (3 + iters)], [wgrad x (3 + iters)]
+    dy = (torch.randn(m, n, device="cuda") * 0.1).bfloat16()
+    dx = torch.empty(m, k, device="cuda", dtype=torch.bfloat16)
+    dw, db = torch.zeros(n, k, device="cuda"), torch.zeros(n, device="cuda")
+
+    def dgrad():
+        rc = nv.lib().meant_gemm_bf16(nv.ptr(dy), nv.ptr(w), nv.ptr(dx), m, k, n, n, k, k, 0, 1, None, None, 0, nv.stream())
+        assert rc == 0, rc
+
+    def wgrad():
+        rc = nv.lib().meant_gemm_bf16_wgrad(nv.ptr(dy), nv.ptr(x), nv.ptr(dw), nv.ptr(db), m, n, k, n, k, k, nv.stream())
+        assert rc == 0, rc
+
+    t_dg, _ = timeit(dgrad, args.iters, flush)
+    t_wg, _ = timeit(wgrad, args.iters, flush)
+    t_ldg, _ = timeit(lambda: torch.mm(dy, w), args.iters, flush)
+    t_lwg, _ = timeit(lambda: torch.mm(dy.t(), x, out_dtype=torch.float32), args.iters, flush)
+    print(f"  dgrad: tcgen05 {t_dg*1e3:.1f} us {fl/t_dg/1e9:.0f} TFLOP/s | library {t_ldg*1e3:.1f} us;  wgrad + bias grad: tcgen05 "
+          f"{t_wg*1e3:.1f} us {fl/t_wg/1e9:.0f} TFLOP/s | library wgrad alone {t_lwg*1e3:.1f} us")
 
 
 if __name__ == "__main__":
