@@ -1268,6 +1268,8 @@ int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_bwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_ms_supported(const AttnArgs& a);
 int attn_tc2_fwd_ms(const AttnArgs& a, cudaStream_t st);
+int attn_tc2_ms_bwd_supported(const AttnArgs& a);
+int attn_tc2_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st);
 
 static bool view_ok(const HeadView& v) {
   return v.p != nullptr && (reinterpret_cast<uintptr_t>(v.p) % 16 == 0) && v.sn1 % 8 == 0 && v.sn2 % 8 == 0 &&
@@ -1312,7 +1314,7 @@ static bool mt_no_tma() {
 }
 
 template <int DH>
-static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
+static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st, int parts = 3) {
   // persistent kernels: one CTA per SM, work items (tile, head, sequence) strided inside the kernel
   const int64_t ik = (int64_t)((a.Sk + TK - 1) / TK) * a.H * a.N, iq = (int64_t)((a.Sq + TQ - 1) / TQ) * a.H * a.N;
   const dim3 gk((unsigned)(ik < 148 ? ik : 148)), gq((unsigned)(iq < 148 ? iq : 148));
@@ -1341,9 +1343,22 @@ static int launch_bwd_mt(const AttnArgs& a, cudaStream_t st) {
     MEANT_LAUNCH_CHECK();
     return 0;
   };
-  const int r = launch(attn_tc_bwd_mt_kernel<DH, 1>, gq);
-  if (r != 0) return r;
-  return launch(attn_tc_bwd_mt_kernel<DH, 0>, gk);
+  if (parts & 2) {
+    const int r = launch(attn_tc_bwd_mt_kernel<DH, 1>, gq);
+    if (r != 0) return r;
+  }
+  return (parts & 1) ? launch(attn_tc_bwd_mt_kernel<DH, 0>, gk) : 0;
+}
+
+// which parts of the multi-tile backward the multi-step kernels (attn_tc2.cu) take: bit 1 the dQ pass, bit 0 the
+// dK | dV pass.  MEANT_ATTN_BWD_MS (0..3, read once) overrides for A/B runs; MEANT_ATTN_OLD_MT forces 0.
+static int bwd_ms_parts() {
+  static const int v = [] {
+    if (getenv("MEANT_ATTN_OLD_MT")) return 0;
+    const char* e = getenv("MEANT_ATTN_BWD_MS");
+    return e ? atoi(e) & 3 : 3;
+  }();
+  return v;
 }
 
 static std::atomic<long long> g_tma_fallbacks{0};   // single-tile problems that had to leave the TMA kernels
@@ -1390,7 +1405,16 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
     if (r2 != MEANT_EUNSUPPORTED) return r2;
     ++g_tma_fallbacks;
   }
-  if (a.Sq > TQ || a.Sk > TK || a.kx.p != nullptr) return a.Dh == 96 ? launch_bwd_mt<96>(a, st) : launch_bwd_mt<64>(a, st);
+  if (a.Sq > TQ || a.Sk > TK || a.kx.p != nullptr) {
+    int ms = attn_tc2_ms_bwd_supported(a) ? bwd_ms_parts() : 0;
+    if (ms) {
+      const int r2 = attn_tc2_bwd_ms(a, ms, st);           // delta + the selected passes
+      if (r2 == MEANT_EUNSUPPORTED) ms = 0;
+      else if (r2 != 0) return r2;
+    }
+    if (ms == 3) return 0;
+    return a.Dh == 96 ? launch_bwd_mt<96>(a, st, 3 & ~ms) : launch_bwd_mt<64>(a, st, 3 & ~ms);
+  }
   dim3 grid(1, a.H, a.N);
   if (a.Dh == 96) return launch_tc(attn_tc_bwd_kernel<96>, BwdSmem<96>::TOTAL, grid, a, st);
   return launch_tc(attn_tc_bwd_kernel<64>, BwdSmem<64>::TOTAL, grid, a, st);

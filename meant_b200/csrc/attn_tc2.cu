@@ -984,6 +984,833 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
+// ============================================================================== backward, several tiles: dQ pass
+// The multi-step pipeline again, for the gradient of the queries when Sq or Sk > 128.  An item is a (sequence, head,
+// 128-query tile), a step one 128-key tile: Q | dO | K | V boxes into one of two stages, S = Q K^T and dP = dO V^T into
+// the stage's two TMEM buffers (issued one step ahead, under the previous step's arithmetic), P = exp2(S * scale - LSE)
+// and dS = P (dP - delta) * scale out of TMEM in ONE pass (the row statistics are known: no max, no exchange between
+// the two threads of a row), dS (bf16) into its own buffer, dQ_j = dS K over the consumed S, folded into this thread's
+// half of the dQ row in registers.  Q, dO and V of a stage are dead as soon as S | dP have run, so their next boxes are
+// issued then -- a whole step before K's, which has to wait for dQ_j.  The item's last step un-rotates (transpose
+// rotation, table fetched under the last MMA), stages over the consumed K and TMA-stores.
+// delta = rowsum(dO * O) comes from attn_delta_kernel (below), which runs first.
+template <int DH>
+struct BwdDqL {
+  using G = Geo<DH>;
+  // Buffers are recycled as early as their last reader allows: Q | dO (two pairs) and V (one) are dead once S | dP of
+  // their step have run -- a whole step before that step's arithmetic -- while K lives until dQ_j = dS K at the end of
+  // the step, so K gets three buffers: the boxes of step s + 2 are in flight while step s computes.
+  static constexpr uint32_t QDO = 0;                           // [2][Q | dO]
+  static constexpr uint32_t V = 4 * G::OPER;                   // [1]
+  static constexpr uint32_t K = 5 * G::OPER;                   // [3]   (the dQ staging of an item's last step aliases its K)
+  static constexpr uint32_t DS = 8 * G::OPER;                  // one dS tile: dQ_j has consumed it before the next one is written
+  static constexpr uint32_t AUX = DS + G::PBUF;                // [2][128] fp32 additive key bias (exp2 domain)
+  static constexpr uint32_t BARS = AUX + 2 * 512;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;
+  static_assert(TOTAL <= 232448, "exceeds the 227 KB of shared memory a CTA can opt in to");
+};
+
+struct BwdMsMaps { CUtensorMap m[14]; };   // q, k, v, dO (loads), dq, dk, dv (stores)  x  (SWIZZLE_128B part, SWIZZLE_64B part)
+
+// un-rotate (transpose rotation) 8 fp32 gradient values of chunk ch in place
+template <int RC>
+__device__ __forceinline__ void unrot8(float* g, int ch, const RotTab<RC>& T) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 c = __half22float2(T.c[ch * 4 + i]), s = __half22float2(T.s[ch * 4 + i]);
+    const float y0 = g[2 * i] * c.x + g[2 * i + 1] * s.y, y1 = g[2 * i + 1] * c.y - g[2 * i] * s.x;
+    g[2 * i] = y0;
+    g[2 * i + 1] = y1;
+  }
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];\n" ::"l"(p)); }
+
+// ROT_IN: rotate Q / K on the way in (no pre-rotated copies were passed); the table registers exist only then
+template <int DH, int RC, bool ROT_IN>
+__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMsMaps maps,
+                                                                  const MsDims dm) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  using L = BwdDqL<DH>;
+  using G = Geo<DH>;
+  constexpr int HALF = DH / 2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *landed_qdo = bars, *landed_k = bars + 2, *landed_v = bars + 5, *sdp_full = bars + 6, *dq_full = bars + 8,
+           *freed = bars + 10, *aux_ready = bars + 13, *rot_done = bars + 15, *ds_ready = bars + 17;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&landed_qdo[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);
+      tc::mbar_init(&sdp_full[i], 1);
+      tc::mbar_init(&dq_full[i], 1);
+      tc::mbar_init(&rot_done[i], NC);
+      tc::mbar_init(&ds_ready[i], NC);
+    }
+    for (int i = 0; i < 3; ++i) {
+      tc::mbar_init(&landed_k[i], 1);
+      tc::mbar_init(&freed[i], NC);
+    }
+    tc::mbar_init(landed_v, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int rc = a.qcos ? a.rot_dim / 8 : 0;                    // chunks to un-rotate in dQ
+  const int rc_in = ROT_IN ? rc : 0;                            // chunks to rotate on the way in
+  const uint32_t s0 = tc::smem_u32(smem);
+
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 10; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    int held_n[3], held_h[3], held_q[3];                          // what K buffer kb stages: a finished item's dQ, or nothing
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { held_q[i] = -1; held_n[i] = 0; held_h[i] = 0; }
+    auto store_out = [&](int kb) {                                // lane 0
+      const uint32_t sb = s0 + L::K + kb * G::OPER;
+      const int n1 = held_n[kb] / a.n2_count, n2 = held_n[kb] - n1 * a.n2_count;
+      tma::store_box(&maps.m[8], sb, 0, held_h[kb], held_q[kb] * 128, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[9], sb + SUB_A, 64, held_h[kb], held_q[kb] * 128, n2, n1);
+      tma::store_commit();
+    };
+    int s = 0;
+    for (int j = 0; j < n_my; ++j) {
+      int n, h, qt;
+      ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, n, h, qt);
+      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      const int steps = ms_steps(a, qt, dm.nk);
+      for (int kt = 0; kt < steps; ++kt, ++s) {
+        const int b2 = s & 1, kb = s % 3;
+        auto load_tile = [&](uint32_t dst, int view, int r0, uint64_t* bar) {
+          tma::load_box(dst, &maps.m[2 * view], bar, 0, h, r0, n2, n1);
+          if (G::TAIL) tma::load_box(dst + SUB_A, &maps.m[2 * view + 1], bar, 64, h, r0, n2, n1);
+        };
+        // Q | dO pair b2: free once S | dP of step s - 2 have run
+        if (s >= 2) tc::mbar_wait(&sdp_full[b2], ((s - 2) >> 1) & 1);
+        if (lane == 0) {
+          tma::mbar_expect_tx(&landed_qdo[b2], 2 * G::OPER);
+          load_tile(s0 + L::QDO + b2 * 2 * G::OPER, 0, qt * 128, &landed_qdo[b2]);
+          load_tile(s0 + L::QDO + b2 * 2 * G::OPER + G::OPER, 3, qt * 128, &landed_qdo[b2]);
+        }
+        // V: free once dP of step s - 1 has run
+        if (s >= 1) tc::mbar_wait(&sdp_full[b2 ^ 1], ((s - 1) >> 1) & 1);
+        if (lane == 0) {
+          tma::mbar_expect_tx(landed_v, G::OPER);
+          load_tile(s0 + L::V, 2, kt * 128, landed_v);
+        }
+        // K buffer kb: free once step s - 3 is over (dQ_j read it; a last step staged its dQ there: store it first)
+        if (s >= 3) {
+          tc::mbar_wait(&freed[kb], ((s - 3) / 3) & 1);
+          if (lane == 0 && held_q[kb] >= 0) {
+            store_out(kb);
+            tma::store_wait_read<0>();
+          }
+        }
+        held_q[kb] = kt == steps - 1 ? qt : -1;
+        held_n[kb] = n;
+        held_h[kb] = h;
+        if (lane == 0) {
+          tma::mbar_expect_tx(&landed_k[kb], G::OPER);
+          load_tile(s0 + L::K + kb * G::OPER, 1, kt * 128, &landed_k[kb]);
+        }
+        // key bias slot b2: the arithmetic of step s - 2 has read it
+        if (s >= 2) tc::mbar_wait(&freed[(s - 2) % 3], ((s - 2) / 3) & 1);
+        float4 mv = make_float4(1.f, 1.f, 1.f, 1.f);
+        const int k0 = kt * 128 + lane * 4;
+        if (a.key_mask) {
+          const float* mrow = a.key_mask + (int64_t)n * a.Sk;
+          if (k0 + 3 < a.Sk && (a.Sk & 3) == 0) mv = __ldg(reinterpret_cast<const float4*>(mrow + k0));
+          else {
+            if (k0 < a.Sk) mv.x = __ldg(mrow + k0);
+            if (k0 + 1 < a.Sk) mv.y = __ldg(mrow + k0 + 1);
+            if (k0 + 2 < a.Sk) mv.z = __ldg(mrow + k0 + 2);
+            if (k0 + 3 < a.Sk) mv.w = __ldg(mrow + k0 + 3);
+          }
+        }
+        reinterpret_cast<float4*>(smem + L::AUX + b2 * 512)[lane] =
+            make_float4(key_bias2(mv.x, k0, a.Sk), key_bias2(mv.y, k0 + 1, a.Sk), key_bias2(mv.z, k0 + 2, a.Sk),
+                        key_bias2(mv.w, k0 + 3, a.Sk));
+        tc::mbar_arrive(&aux_ready[b2]);
+      }
+    }
+    for (int u = max(0, s - 3); u < s; ++u) {
+      const int kb = u % 3;
+      tc::mbar_wait(&freed[kb], (u / 3) & 1);
+      if (lane == 0 && held_q[kb] >= 0) store_out(kb);
+    }
+    if (lane == 0) tma::store_wait_all();
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      int total = 0;
+      for (int j = 0; j < n_my; ++j) {
+        int n, h, qt;
+        ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, n, h, qt);
+        total += ms_steps(a, qt, dm.nk);
+      }
+      auto issue_sdp = [&](int s) {
+        const int b2 = s & 1;
+        tc::mbar_wait(&rot_done[b2], (s >> 1) & 1);
+        tc::fence_after_sync();
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+        const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER, sdo = sq + G::OPER, sk = s0 + L::K + (s % 3) * G::OPER, sv = s0 + L::V;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + b2 * 256, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + b2 * 256 + 128, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
+        tc::mma_commit(&sdp_full[b2]);
+      };
+      if (total > 0) issue_sdp(0);
+      for (int s = 0; s < total; ++s) {
+        const int b2 = s & 1;
+        if (s + 1 < total) issue_sdp(s + 1);                      // one step ahead: runs under this step's dS arithmetic
+        tc::mbar_wait(&ds_ready[b2], (s >> 1) & 1);
+        tc::fence_after_sync();
+        const uint32_t sds = s0 + L::DS, sk = s0 + L::K + (s % 3) * G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) mma_oper_mn<DH>(tmem + b2 * 256, desc_p_k(sds, ks), sk, ks, 0, ks > 0);
+        tc::mma_commit(&dq_full[b2]);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;
+    const int t = rg * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    RotTab<RC> tab;                                               // rotation on the way in: half 0 q tables, half 1 k tables
+    const float* tcs = half ? a.kcos : a.qcos;
+    const float* tsn = half ? a.ksin : a.qsin;
+    int cur_pos = -1;
+    const bool vec_tab = ((reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) | reinterpret_cast<uintptr_t>(a.kcos) |
+                           reinterpret_cast<uintptr_t>(a.ksin)) & 15) == 0 && (a.rot_dim & 3) == 0;
+    const bool unrot_mine = rc && half * (HALF / 8) < rc;         // this thread's chunks include rotated ones
+    struct Walk {
+      int j, kt, steps, n, h, qt;
+    };
+    auto start = [&](Walk& w, int j) {
+      w.j = j;
+      w.kt = 0;
+      if (j < n_my) {
+        ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nq, w.n, w.h, w.qt);
+        w.steps = ms_steps(a, w.qt, dm.nk);
+      }
+    };
+    auto advance = [&](Walk& w) {
+      if (++w.kt == w.steps) start(w, w.j + 1);
+    };
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
+    float lse2_n = 0.f, dlt_n = 0.f;                              // row statistics of the walker's item, fetched one step ahead
+    auto prepare = [&](const Walk& w, int s) {
+      const int b2 = s & 1, kb = s % 3;
+      if (w.kt == 0) {
+        const int row = min(w.qt * 128 + t, a.Sq - 1);
+        const int64_t si = ((int64_t)w.n * a.H + w.h) * a.Sq + row;
+        lse2_n = __ldg(a.lse + si);
+        dlt_n = __ldg(a.delta + si);
+        if (unrot_mine) {                                           // the un-rotation table of this row: towards L1 now, used at the item's end
+          const int pos = a.pos_is_head ? w.h : row;
+          const char* c = reinterpret_cast<const char*>(a.qcos + (int64_t)pos * a.rot_dim);
+          const char* sn = reinterpret_cast<const char*>(a.qsin + (int64_t)pos * a.rot_dim);
+          for (int o = 0; o < a.rot_dim * 4; o += 128) { prefetch_l1(c + o); prefetch_l1(sn + o); }
+        }
+      }
+      if (ROT_IN && rc_in) {
+        const int pos = a.pos_is_head ? w.h : (half ? min(w.kt * 128 + t, a.Sk - 1) : min(w.qt * 128 + t, a.Sq - 1));
+        if (pos != cur_pos) {
+          if (vec_tab) load_tab4<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          else load_tab<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          cur_pos = pos;
+        }
+      }
+      pf.tick(6);
+      tc::mbar_wait(&landed_qdo[b2], (s >> 1) & 1);
+      pf.tick(7);
+      tc::mbar_wait(&landed_k[kb], (s / 3) & 1);
+      pf.tick(8);
+      tc::mbar_wait(landed_v, s & 1);
+      pf.tick(9);
+      if (ROT_IN && rc_in) rot_row<RC, false>(smem + (half ? L::K + kb * G::OPER : L::QDO + b2 * 2 * G::OPER), t, rc_in, tab);
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&rot_done[b2]);
+    };
+    Walk wp, wc;
+    start(wp, 0);
+    start(wc, 0);
+    if (wp.j < n_my) {
+      prepare(wp, 0);
+      advance(wp);
+    }
+    float lse2 = 0.f, dlt = 0.f;
+    float dq_acc[HALF];
+    for (int s = 0; wc.j < n_my; ++s) {
+      const int b2 = s & 1, kb = s % 3;
+      const uint32_t par = (s >> 1) & 1;
+      const bool first = wc.kt == 0, last = wc.kt == wc.steps - 1;
+      const int k0 = wc.kt * 128, q0 = wc.qt * 128;
+      if (first) {
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) dq_acc[i] = 0.f;
+        lse2 = lse2_n * LOG2E;                                      // fetched when the walker entered this item
+        dlt = dlt_n;
+      }
+      if (wp.j < n_my) {                                            // next step's operands: S | dP (s + 1) run under this step
+        prepare(wp, s + 1);
+        advance(wp);
+      }
+      const bool dtile = a.causal && k0 == q0;
+      int nblk = (min(a.Sk - k0, 128) + 31) >> 5;
+      if (dtile) nblk = min(nblk, rg + 1);
+      pf.tick(0);
+      tc::mbar_wait(&aux_ready[b2], par);
+      tc::mbar_wait(&sdp_full[b2], par);
+      tc::fence_after_sync();
+      pf.tick(1);
+      const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + b2 * 512);
+      const uint32_t ts = lane_base + b2 * 256;
+      uint8_t* dsbuf = smem + L::DS;
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {                                           // warp-uniform
+          float sv[32], dp[32];
+          tc::tmem_ld32(ts + blk * 32, sv);
+          tc::tmem_ld32(ts + 128 + blk * 32, dp);
+          tc::tmem_ld_wait();
+          const bool diag = dtile && blk == rg;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 ba = b4[(blk * 32 + q * 8) >> 2], bc = b4[((blk * 32 + q * 8) >> 2) + 1];
+            const float bb[8] = {ba.x, ba.y, ba.z, ba.w, bc.x, bc.y, bc.z, bc.w};
+            uint4 pk;
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = q * 8 + 2 * u;
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - lse2)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - lse2));
+              if (diag) {
+                if (e > lane) p0 = 0.f;
+                if (e + 1 > lane) p1 = 0.f;
+              }
+              ph[u] = __floats2bfloat162_rn(p0 * (dp[e] - dlt) * a.scale, p1 * (dp[e + 1] - dlt) * a.scale);
+            }
+            *reinterpret_cast<uint4*>(dsbuf + pbuf_off(t, blk * 4 + q)) = pk;
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) *reinterpret_cast<uint4*>(dsbuf + pbuf_off(t, blk * 4 + q)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&ds_ready[b2]);                               // the MMA warp starts dQ_j = dS K
+      pf.tick(2);
+      tc::mbar_wait(&dq_full[b2], par);
+      tc::fence_after_sync();
+      pf.tick(3);
+      {
+        float g[HALF];
+        tc::tmem_ld32(ts + half * HALF, g);
+        if constexpr (HALF > 32) tc::tmem_ld16(ts + half * HALF + 32, g + 32);
+        tc::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < HALF; ++i) dq_acc[i] += g[i];
+      }
+      pf.tick(4);
+      if (last) {
+        // un-rotate with the query-side table of this row (transpose rotation), bf16, staged over the consumed K
+        if (unrot_mine) {
+          // three chunks at a time: 12 independent 16-byte loads in flight (the whole table at once did not fit in
+          // registers beside the accumulator and the compiler serialised the loads)
+          const int pos = a.pos_is_head ? wc.h : min(q0 + t, a.Sq - 1);
+          const float* cb = a.qcos + (int64_t)pos * a.rot_dim + half * HALF;
+          const float* sb = a.qsin + (int64_t)pos * a.rot_dim + half * HALF;
+#pragma unroll
+          for (int r = 0; r < HALF / 8; r += 3) {
+            float cv[24], sv2[24];
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const int ch = half * (HALF / 8) + r + q;                    // global chunk index (runtime through `half`)
+              const bool on = r + q < HALF / 8 && ch < rc;
+#pragma unroll
+              for (int e = 0; e < 8; e += 4) {                           // 16-byte loads (alignment checked on the host)
+                const float4 c4 = on ? __ldg(reinterpret_cast<const float4*>(cb + (r + q) * 8 + e)) : make_float4(1.f, 1.f, 1.f, 1.f);
+                const float4 s4 = on ? __ldg(reinterpret_cast<const float4*>(sb + (r + q) * 8 + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                cv[q * 8 + e] = c4.x; cv[q * 8 + e + 1] = c4.y; cv[q * 8 + e + 2] = c4.z; cv[q * 8 + e + 3] = c4.w;
+                sv2[q * 8 + e] = s4.x; sv2[q * 8 + e + 1] = s4.y; sv2[q * 8 + e + 2] = s4.z; sv2[q * 8 + e + 3] = s4.w;
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              if (r + q < HALF / 8) {
+                float* g = dq_acc + (r + q) * 8;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float c0 = cv[q * 8 + 2 * i], c1 = cv[q * 8 + 2 * i + 1], s0_ = sv2[q * 8 + 2 * i], s1_ = sv2[q * 8 + 2 * i + 1];
+                  const float y0 = g[2 * i] * c0 + g[2 * i + 1] * s1_, y1 = g[2 * i + 1] * c1 - g[2 * i] * s0_;
+                  g[2 * i] = y0;
+                  g[2 * i + 1] = y1;
+                }
+              }
+            }
+          }
+        }
+        uint8_t* tile = smem + L::K + kb * G::OPER;
+#pragma unroll
+        for (int q = 0; q < HALF / 8; ++q) {
+          uint4 pk;
+          __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(dq_acc[q * 8 + 2 * i], dq_acc[q * 8 + 2 * i + 1]);
+          *reinterpret_cast<uint4*>(tile + oper_off(t, half * (HALF / 8) + q)) = pk;
+        }
+        tc::fence_async_smem();
+      }
+      tc::fence_before_sync();
+      tc::mbar_arrive(&freed[kb]);
+      pf.tick(5);
+      advance(wc);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// ============================================================================== backward, several tiles: dK | dV pass
+// An item is a (sequence, head, 128-key tile) whose K | V stay in shared memory; a step is one 128-query tile (causal:
+// the tiles on and below the diagonal): Q | dO boxes into one of two pairs, S = Q K^T and dP = dO V^T into TMEM, P and
+// dS recomputed in one pass as in the dQ kernel and written as bf16 tiles, dV += P^T dO and dK += dS^T Q accumulated
+// in TMEM across the item's steps (both operands MN-major: nothing is transposed).  The MMA thread issues S | dP of
+// step s + 1 BEFORE dV | dK of step s, so the next step's arithmetic (kept in registers until the P / dS tiles are
+// free) runs under them.  K | V of the next item are fetched as soon as the last S | dP of this one have run.  The
+// item's last step drains the accumulators, un-rotates dK (transpose rotation), stages over P / dS and TMA-stores.
+template <int DH>
+struct BwdDkvL {
+  using G = Geo<DH>;
+  static constexpr uint32_t KV = 0;                            // K | V of the item
+  static constexpr uint32_t QDO = 2 * G::OPER;                 // [2][Q | dO]
+  static constexpr uint32_t P = 6 * G::OPER, DS = P + G::PBUF; // one tile each (dV / dK staging at the item's end)
+  static constexpr uint32_t AUX = DS + G::PBUF;                // [2][128] fp32 additive key bias (exp2 domain), by item parity
+  static constexpr uint32_t BARS = AUX + 2 * 512;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;
+  static_assert(G::OPER <= G::PBUF, "gradient staging must fit in the P / dS tiles");
+  static_assert(TOTAL <= 232448, "exceeds the 227 KB of shared memory a CTA can opt in to");
+};
+
+// first query tile of key tile kt's item, and its number of steps
+__device__ __forceinline__ int dkv_q0(const AttnArgs& a, int kt) { return a.causal ? kt : 0; }
+
+template <int DH, int RC, bool ROT_IN>
+__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMsMaps maps,
+                                                                   const MsDims dm) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  using L = BwdDkvL<DH>;
+  using G = Geo<DH>;
+  constexpr int HALF = DH / 2;
+  constexpr uint32_t T_S = 0, T_DP = 128, T_DV = 256, T_DK = 352;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *landed_kv = bars, *landed_qdo = bars + 1, *aux_ready = bars + 3, *rot_done = bars + 5, *sdp_full = bars + 7,
+           *pds_ready = bars + 8, *mma_done = bars + 9, *drained = bars + 11, *staged = bars + 12, *stg_free = bars + 13;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    tc::mbar_init(landed_kv, 1);
+    tc::mbar_init(sdp_full, 1);
+    tc::mbar_init(pds_ready, NC);
+    tc::mbar_init(drained, NC);
+    tc::mbar_init(staged, NC);
+    tc::mbar_init(stg_free, 1);
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&landed_qdo[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);          // by item parity: the producer can never be two phases ahead of a reader
+      tc::mbar_init(&rot_done[i], NC);
+      tc::mbar_init(&mma_done[i], 1);
+    }
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int rc = a.qcos ? a.rot_dim / 8 : 0;                    // chunks to un-rotate in dK
+  const int rc_in = ROT_IN ? rc : 0;
+  const uint32_t s0 = tc::smem_u32(smem);
+  // item j of this CTA -> (sequence, head, key tile); steps = query tiles q0 .. nq - 1
+  auto item_of = [&](int j, int& n, int& h, int& kt, int& q0, int& steps) {
+    ms_item(blockIdx.x + j * gridDim.x, j, a.H, dm.nk, n, h, kt);
+    q0 = dkv_q0(a, kt);
+    steps = dm.nq - q0;
+  };
+
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 14; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    auto load_tile = [&](uint32_t dst, int view, int r0, uint64_t* bar, int h, int n2, int n1) {
+      tma::load_box(dst, &maps.m[2 * view], bar, 0, h, r0, n2, n1);
+      if (G::TAIL) tma::load_box(dst + SUB_A, &maps.m[2 * view + 1], bar, 64, h, r0, n2, n1);
+    };
+    auto store_tile = [&](int view, uint32_t src, int r0, int h, int n2, int n1) {
+      tma::store_box(&maps.m[2 * view], src, 0, h, r0, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[2 * view + 1], src + SUB_A, 64, h, r0, n2, n1);
+    };
+    int s = 0, pn = 0, ph = 0, pkt = 0;                           // previous item's coordinates (its staged gradients)
+    for (int j = 0; j < n_my; ++j) {
+      int n, h, kt, q0, steps;
+      item_of(j, n, h, kt, q0, steps);
+      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      for (int u = 0; u < steps; ++u, ++s) {
+        const int b2 = s & 1;
+        // every phase of sdp_full is waited for, in order (a wait that skipped phases could be satisfied by an older
+        // phase of the same parity); it completes long before mma_done(s - 2) below, so nothing is delayed by it
+        if (s >= 1) tc::mbar_wait(sdp_full, (s - 1) & 1);
+        if (u == 0) {                                             // K | V of the previous item are dead
+          if (lane == 0) {
+            tma::mbar_expect_tx(landed_kv, 2 * G::OPER);
+            load_tile(s0 + L::KV, 1, kt * 128, landed_kv, h, n2, n1);
+            load_tile(s0 + L::KV + G::OPER, 2, kt * 128, landed_kv, h, n2, n1);
+          }
+          float4 mv = make_float4(1.f, 1.f, 1.f, 1.f);
+          const int k0 = kt * 128 + lane * 4;
+          if (a.key_mask) {
+            const float* mrow = a.key_mask + (int64_t)n * a.Sk;
+            if (k0 + 3 < a.Sk && (a.Sk & 3) == 0) mv = __ldg(reinterpret_cast<const float4*>(mrow + k0));
+            else {
+              if (k0 < a.Sk) mv.x = __ldg(mrow + k0);
+              if (k0 + 1 < a.Sk) mv.y = __ldg(mrow + k0 + 1);
+              if (k0 + 2 < a.Sk) mv.z = __ldg(mrow + k0 + 2);
+              if (k0 + 3 < a.Sk) mv.w = __ldg(mrow + k0 + 3);
+            }
+          }
+          reinterpret_cast<float4*>(smem + L::AUX + (j & 1) * 512)[lane] =
+              make_float4(key_bias2(mv.x, k0, a.Sk), key_bias2(mv.y, k0 + 1, a.Sk), key_bias2(mv.z, k0 + 2, a.Sk),
+                          key_bias2(mv.w, k0 + 3, a.Sk));
+          tc::mbar_arrive(&aux_ready[j & 1]);
+        }
+        if (s >= 2) tc::mbar_wait(&mma_done[b2], ((s - 2) >> 1) & 1);   // dV | dK of step s - 2 have read this Q | dO pair
+        if (lane == 0) {
+          tma::mbar_expect_tx(&landed_qdo[b2], 2 * G::OPER);
+          load_tile(s0 + L::QDO + b2 * 2 * G::OPER, 0, (q0 + u) * 128, &landed_qdo[b2], h, n2, n1);
+          load_tile(s0 + L::QDO + b2 * 2 * G::OPER + G::OPER, 3, (q0 + u) * 128, &landed_qdo[b2], h, n2, n1);
+        }
+        if (u == 0 && j > 0) {                                    // the previous item's staged dV (over P) and dK (over dS)
+          tc::mbar_wait(staged, (j - 1) & 1);
+          if (lane == 0) {
+            const int p1 = pn / a.n2_count, p2 = pn - p1 * a.n2_count;
+            store_tile(6, s0 + L::P, pkt * 128, ph, p2, p1);
+            store_tile(5, s0 + L::DS, pkt * 128, ph, p2, p1);
+            tma::store_commit();
+            tma::store_wait_read<0>();
+            tc::mbar_arrive(stg_free);
+          }
+        }
+      }
+      pn = n; ph = h; pkt = kt;
+    }
+    if (n_my > 0) {
+      tc::mbar_wait(staged, (n_my - 1) & 1);
+      if (lane == 0) {
+        const int p1 = pn / a.n2_count, p2 = pn - p1 * a.n2_count;
+        store_tile(6, s0 + L::P, pkt * 128, ph, p2, p1);
+        store_tile(5, s0 + L::DS, pkt * 128, ph, p2, p1);
+        tma::store_commit();
+        tma::store_wait_all();
+      }
+    }
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      const uint32_t sk = s0 + L::KV, sv = sk + G::OPER, sp = s0 + L::P, sds = s0 + L::DS;
+      auto issue_sdp = [&](int s) {
+        const int b2 = s & 1;
+        tc::mbar_wait(&rot_done[b2], (s >> 1) & 1);
+        tc::fence_after_sync();
+        constexpr uint32_t idesc = tc::make_idesc(128, 128, 0, 0);
+        const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER, sdo = sq + G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), desc_oper_k(sk, ks), idesc, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), desc_oper_k(sv, ks), idesc, ks > 0);
+        tc::mma_commit(sdp_full);
+      };
+      int total = 0;
+      for (int j = 0; j < n_my; ++j) {
+        int n, h, kt, q0, steps;
+        item_of(j, n, h, kt, q0, steps);
+        total += steps;
+      }
+      if (total > 0) issue_sdp(0);
+      int s = 0;
+      for (int j = 0; j < n_my; ++j) {
+        int n, h, kt, q0, steps;
+        item_of(j, n, h, kt, q0, steps);
+        for (int u = 0; u < steps; ++u, ++s) {
+          const int b2 = s & 1;
+          tc::mbar_wait(pds_ready, s & 1);                        // P, dS written; S | dP read
+          tc::fence_after_sync();
+          if (s + 1 < total) issue_sdp(s + 1);                    // first: the next step's arithmetic runs under dV | dK
+          if (u == 0 && j > 0) {
+            tc::mbar_wait(drained, (j - 1) & 1);                  // the previous item's accumulators have been read
+            tc::fence_after_sync();
+          }
+          const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER, sdo = sq + G::OPER;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks) {                        // two independent accumulation chains, interleaved
+            mma_oper_mn<DH>(tmem + T_DV, desc_p_mn(sp, ks), sdo, ks, 1, u > 0 || ks > 0);    // dV += P^T dO
+            mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, u > 0 || ks > 0);    // dK += dS^T Q
+          }
+          tc::mma_commit(&mma_done[b2]);
+        }
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;
+    const int t = rg * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    RotTab<RC> tab;                                               // rotation on the way in: half 0 q tables, half 1 k tables
+    const float* tcs = half ? a.kcos : a.qcos;
+    const float* tsn = half ? a.ksin : a.qsin;
+    int cur_pos = -1;
+    const bool vec_tab = ((reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) | reinterpret_cast<uintptr_t>(a.kcos) |
+                           reinterpret_cast<uintptr_t>(a.ksin)) & 15) == 0 && (a.rot_dim & 3) == 0;
+    const bool unrot_mine = rc && half * (HALF / 8) < rc;
+    struct Walk {
+      int j, u, steps, n, h, kt, q0;
+    };
+    auto start = [&](Walk& w, int j) {
+      w.j = j;
+      w.u = 0;
+      if (j < n_my) item_of(j, w.n, w.h, w.kt, w.q0, w.steps);
+    };
+    auto advance = [&](Walk& w) {
+      if (++w.u == w.steps) start(w, w.j + 1);
+    };
+    float lse_n = 0.f, dlt_n = 0.f;                               // row statistics of the walker's query tile
+    auto prepare = [&](const Walk& w, int s) {
+      const int b2 = s & 1;
+      {
+        const int row = min((w.q0 + w.u) * 128 + t, a.Sq - 1);
+        const int64_t si = ((int64_t)w.n * a.H + w.h) * a.Sq + row;
+        lse_n = __ldg(a.lse + si);
+        dlt_n = __ldg(a.delta + si);
+      }
+      if (ROT_IN && rc_in) {
+        const int pos = a.pos_is_head ? w.h : (half ? min(w.kt * 128 + t, a.Sk - 1) : min((w.q0 + w.u) * 128 + t, a.Sq - 1));
+        if (pos != cur_pos) {
+          if (vec_tab) load_tab4<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          else load_tab<RC>(tab, tcs, tsn, pos, a.rot_dim);
+          cur_pos = pos;
+        }
+      }
+      tc::mbar_wait(&landed_qdo[b2], (s >> 1) & 1);
+      if (w.u == 0) tc::mbar_wait(landed_kv, w.j & 1);
+      if (ROT_IN && rc_in) {
+        if (half == 0) rot_row<RC, false>(smem + L::QDO + b2 * 2 * G::OPER, t, rc_in, tab);
+        else if (w.u == 0) rot_row<RC, false>(smem + L::KV, t, rc_in, tab);
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&rot_done[b2]);
+    };
+    Walk wp, wc;
+    start(wp, 0);
+    start(wc, 0);
+    if (wp.j < n_my) {
+      prepare(wp, 0);
+      advance(wp);
+    }
+    for (int s = 0; wc.j < n_my; ++s) {
+      const bool first = wc.u == 0, last = wc.u == wc.steps - 1;
+      const int qt = wc.q0 + wc.u, k0 = wc.kt * 128;
+      const float lse2 = lse_n * LOG2E, dlt = dlt_n;                // fetched by the walker one step ahead
+      const bool dtile = a.causal && qt == wc.kt;
+      int nblk = (min(a.Sk - k0, 128) + 31) >> 5;
+      if (dtile) nblk = min(nblk, rg + 1);
+      if (first) tc::mbar_wait(&aux_ready[wc.j & 1], (wc.j >> 1) & 1);
+      tc::mbar_wait(sdp_full, s & 1);
+      tc::fence_after_sync();
+      const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + (wc.j & 1) * 512);
+      // arithmetic first, into registers: the P / dS tiles may still be read by dV | dK of the previous step
+      uint4 pp[2][4], dd[2][4];
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {                                           // warp-uniform
+          float sv[32], dp[32];
+          tc::tmem_ld32(lane_base + T_S + blk * 32, sv);
+          tc::tmem_ld32(lane_base + T_DP + blk * 32, dp);
+          tc::tmem_ld_wait();
+          const bool diag = dtile && blk == rg;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float4 ba = b4[(blk * 32 + q * 8) >> 2], bc = b4[((blk * 32 + q * 8) >> 2) + 1];
+            const float bb[8] = {ba.x, ba.y, ba.z, ba.w, bc.x, bc.y, bc.z, bc.w};
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pp[i][q]);
+            __nv_bfloat162* dh = reinterpret_cast<__nv_bfloat162*>(&dd[i][q]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = q * 8 + 2 * u;
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - lse2)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - lse2));
+              if (diag) {
+                if (e > lane) p0 = 0.f;
+                if (e + 1 > lane) p1 = 0.f;
+              }
+              ph[u] = __floats2bfloat162_rn(p0, p1);
+              dh[u] = __floats2bfloat162_rn(p0 * (dp[e] - dlt) * a.scale, p1 * (dp[e + 1] - dlt) * a.scale);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) pp[i][q] = dd[i][q] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
+      tc::fence_before_sync();                                      // the TMEM reads above are complete (tcgen05.wait::ld)
+      if (s >= 1) tc::mbar_wait(&mma_done[(s - 1) & 1], ((s - 1) >> 1) & 1);   // P / dS tiles are free
+      if (first && wc.j > 0) tc::mbar_wait(stg_free, (wc.j - 1) & 1);          // ... and the staged gradients have left them
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const int blk = 2 * i + half;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          *reinterpret_cast<uint4*>(smem + L::P + pbuf_off(t, blk * 4 + q)) = pp[i][q];
+          *reinterpret_cast<uint4*>(smem + L::DS + pbuf_off(t, blk * 4 + q)) = dd[i][q];
+        }
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(pds_ready);
+      if (wp.j < n_my) {
+        prepare(wp, s + 1);
+        advance(wp);
+      }
+      if (last) {
+        tc::mbar_wait(&mma_done[s & 1], (s >> 1) & 1);              // the item's accumulators are complete
+        tc::fence_after_sync();
+        float gv[HALF], gk[HALF];
+        tc::tmem_ld32(lane_base + T_DV + half * HALF, gv);
+        if constexpr (HALF > 32) tc::tmem_ld16(lane_base + T_DV + half * HALF + 32, gv + 32);
+        tc::tmem_ld32(lane_base + T_DK + half * HALF, gk);
+        if constexpr (HALF > 32) tc::tmem_ld16(lane_base + T_DK + half * HALF + 32, gk + 32);
+        tc::tmem_ld_wait();
+        tc::fence_before_sync();
+        tc::mbar_arrive(drained);                                   // the next item's dV | dK may overwrite them
+        if (unrot_mine) {
+          const int pos = a.pos_is_head ? wc.h : min(k0 + t, a.Sk - 1);
+          const float* cb = a.kcos + (int64_t)pos * a.rot_dim + half * HALF;
+          const float* sb = a.ksin + (int64_t)pos * a.rot_dim + half * HALF;
+#pragma unroll
+          for (int r = 0; r < HALF / 8; r += 3) {
+            float cv[24], sv2[24];
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              const int ch = half * (HALF / 8) + r + q;
+              const bool on = r + q < HALF / 8 && ch < rc;
+#pragma unroll
+              for (int e = 0; e < 8; e += 4) {
+                const float4 c4 = on ? __ldg(reinterpret_cast<const float4*>(cb + (r + q) * 8 + e)) : make_float4(1.f, 1.f, 1.f, 1.f);
+                const float4 s4 = on ? __ldg(reinterpret_cast<const float4*>(sb + (r + q) * 8 + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                cv[q * 8 + e] = c4.x; cv[q * 8 + e + 1] = c4.y; cv[q * 8 + e + 2] = c4.z; cv[q * 8 + e + 3] = c4.w;
+                sv2[q * 8 + e] = s4.x; sv2[q * 8 + e + 1] = s4.y; sv2[q * 8 + e + 2] = s4.z; sv2[q * 8 + e + 3] = s4.w;
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 3; ++q) {
+              if (r + q < HALF / 8) {
+                float* g = gk + (r + q) * 8;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                  const float c0 = cv[q * 8 + 2 * i], c1 = cv[q * 8 + 2 * i + 1], s0_ = sv2[q * 8 + 2 * i], s1_ = sv2[q * 8 + 2 * i + 1];
+                  const float y0 = g[2 * i] * c0 + g[2 * i + 1] * s1_, y1 = g[2 * i + 1] * c1 - g[2 * i] * s0_;
+                  g[2 * i] = y0;
+                  g[2 * i + 1] = y1;
+                }
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < HALF / 8; ++q) {
+          uint4 pv, pk;
+          __nv_bfloat162* hv = reinterpret_cast<__nv_bfloat162*>(&pv);
+          __nv_bfloat162* hk = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            hv[i] = __floats2bfloat162_rn(gv[q * 8 + 2 * i], gv[q * 8 + 2 * i + 1]);
+            hk[i] = __floats2bfloat162_rn(gk[q * 8 + 2 * i], gk[q * 8 + 2 * i + 1]);
+          }
+          *reinterpret_cast<uint4*>(smem + L::P + oper_off(t, half * (HALF / 8) + q)) = pv;
+          *reinterpret_cast<uint4*>(smem + L::DS + oper_off(t, half * (HALF / 8) + q)) = pk;
+        }
+        tc::fence_async_smem();
+        tc::mbar_arrive(staged);
+      }
+      advance(wc);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// delta[n, h, s] = sum_d dO[n, s, h, d] * O[n, s, h, d]  (args: o = dO, out_saved = O).  A CTA takes DROWS token rows:
+// thread i multiplies 16-byte chunks i, i + 256, ... of the rows' H * Dh / 8 chunks (consecutive threads read
+// consecutive chunks: coalesced when the heads of a row are contiguous), the partial dot products go to shared memory
+// and one thread per (row, head) adds its Dh / 8 partials.  HBM-bound: reads dO and O once.
+constexpr int DROWS = 8;
+__global__ void __launch_bounds__(256) attn_delta_kernel(AttnArgs a) {
+  extern __shared__ float part[];                                  // [DROWS][H * cpr]
+  const int cpr = a.Dh >> 3, per_row = a.H * cpr;
+  const int64_t rows = (int64_t)a.N * a.Sq;
+  for (int64_t r0 = (int64_t)blockIdx.x * DROWS; r0 < rows; r0 += (int64_t)gridDim.x * DROWS) {
+    const int nr = (int)(rows - r0 < DROWS ? rows - r0 : DROWS);
+    for (int i = threadIdx.x; i < nr * per_row; i += 256) {
+      const int rr = i / per_row, c = i - rr * per_row, h = c / cpr, cc = c - h * cpr;
+      const int64_t row = r0 + rr;
+      const int s = (int)(row % a.Sq), n = (int)(row / a.Sq);
+      const uint4 x = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, s, h) + cc * 8);
+      const uint4 y = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, s, h) + cc * 8);
+      const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x);
+      const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&y);
+      float acc = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 u = __bfloat1622float2(xh[k]), v = __bfloat1622float2(yh[k]);
+        acc = fmaf(u.x, v.x, fmaf(u.y, v.y, acc));
+      }
+      part[i] = acc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < nr * a.H; i += 256) {
+      const int rr = i / a.H, h = i - rr * a.H;
+      float acc = 0.f;
+      for (int c = 0; c < cpr; ++c) acc += part[rr * per_row + h * cpr + c];
+      const int64_t row = r0 + rr;
+      a.delta[((int64_t)(row / a.Sq) * a.H + h) * a.Sq + (row % a.Sq)] = acc;
+    }
+    __syncthreads();
+  }
+}
+
 // ============================================================================== backward
 // Shared memory: the Q | K pair is double buffered (item j+1's pair lands while item j computes).  V and dO swap two
 // slots: V(j)'s slot is free as soon as dP = dO V^T has run and takes dO(j+1); dO(j)'s slot is free as soon as
@@ -1589,6 +2416,21 @@ int attn_tc2_ms_supported(const AttnArgs& a) {
     if (vs[i]->ss <= 0 || vs[i]->ss >= (1 << 23)) return 0;
   return 1;
 }
+// ... and the multi-step backward (q_rot / k_rot, when given, are what forward saved)
+int attn_tc2_ms_bwd_supported(const AttnArgs& a) {
+  if (!attn_tc2_ms_supported(a) || !a.lse || !a.delta || !a.out_saved.p) return 0;
+  if (a.qcos) {                                     // the un-rotation of dQ / dK always runs in the kernel (16-byte table loads)
+    const int rc_max = a.Dh == 96 ? 6 : 8;
+    if (a.rot_dim / 8 > rc_max || a.rot_dim % 8) return 0;
+    const uintptr_t al = reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) |
+                         reinterpret_cast<uintptr_t>(a.kcos) | reinterpret_cast<uintptr_t>(a.ksin);
+    if (al % 16 != 0) return 0;
+  }
+  const HeadView* gs[3] = {&a.dq, &a.dk, &a.dv};
+  for (int i = 0; i < 3; ++i)
+    if (!gs[i]->p || gs[i]->ss <= 0 || gs[i]->ss >= (1 << 23)) return 0;
+  return 1;
+}
 
 template <int DH, int RC>
 static int launch_fwd_ms(const AttnArgs& a, cudaStream_t st) {
@@ -1609,6 +2451,55 @@ static int launch_fwd_ms(const AttnArgs& a, cudaStream_t st) {
   kern<<<grid, t2::F_NT, t2::FwdMsL<DH>::TOTAL, st>>>(a, (int)items, maps, dm);
   MEANT_LAUNCH_CHECK();
   return 0;
+}
+
+// multi-step backward: delta, then the dQ pass (bit 1 of `parts`) and / or the dK | dV pass (bit 0)
+template <int DH, int RC>
+static int launch_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
+  if (!a.lse || !a.delta || !a.out_saved.p) return MEANT_EARG;
+  t2::BwdMsMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const t2::Grp g = {0, 0, 0, 0, 0};
+  const bool pre = a.q_rot.p != nullptr;
+  const HeadView* vs[7] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o, &a.dq, &a.dk, &a.dv};
+  const int seq[7] = {a.Sq, a.Sk, a.Sk, a.Sq, a.Sq, a.Sk, a.Sk};
+  if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7, g)) return rc;
+  const t2::MsDims dm = {(a.Sq + 127) / 128, (a.Sk + 127) / 128};
+  {
+    const int64_t rows = (int64_t)a.N * a.Sq;
+    int64_t blocks = (rows + t2::DROWS - 1) / t2::DROWS;
+    if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+    const size_t sm = sizeof(float) * t2::DROWS * a.H * (a.Dh / 8);
+    if (sm > 48 * 1024) return MEANT_EUNSUPPORTED;
+    t2::attn_delta_kernel<<<(unsigned)blocks, 256, sm, st>>>(a);
+    MEANT_LAUNCH_CHECK();
+  }
+  if (parts & 2) {
+    const int64_t items = (int64_t)a.N * a.H * dm.nq;
+    if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
+    auto kern = pre ? t2::attn2_bwd_dq_ms_kernel<DH, RC, false> : t2::attn2_bwd_dq_ms_kernel<DH, RC, true>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t2::BwdDqL<DH>::TOTAL);
+    if (e != cudaSuccess) return (int)e;
+    const int grid = (int)(items < num_sms() ? items : num_sms());
+    kern<<<grid, t2::F_NT, t2::BwdDqL<DH>::TOTAL, st>>>(a, (int)items, maps, dm);
+    MEANT_LAUNCH_CHECK();
+  }
+  if (parts & 1) {
+    const int64_t items = (int64_t)a.N * a.H * dm.nk;
+    if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
+    auto kern = pre ? t2::attn2_bwd_dkv_ms_kernel<DH, RC, false> : t2::attn2_bwd_dkv_ms_kernel<DH, RC, true>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t2::BwdDkvL<DH>::TOTAL);
+    if (e != cudaSuccess) return (int)e;
+    const int grid = (int)(items < num_sms() ? items : num_sms());
+    kern<<<grid, t2::F_NT, t2::BwdDkvL<DH>::TOTAL, st>>>(a, (int)items, maps, dm);
+    MEANT_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+int attn_tc2_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
+  if (a.Dh == 96) return launch_bwd_ms<96, 6>(a, parts, st);
+  return launch_bwd_ms<64, 8>(a, parts, st);
 }
 
 int attn_tc2_fwd_ms(const AttnArgs& a, cudaStream_t st) {
