@@ -1776,36 +1776,57 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
 // thread i multiplies 16-byte chunks i, i + 256, ... of the rows' H * Dh / 8 chunks (consecutive threads read
 // consecutive chunks: coalesced when the heads of a row are contiguous), the partial dot products go to shared memory
 // and one thread per (row, head) adds its Dh / 8 partials.  HBM-bound: reads dO and O once.
-constexpr int DROWS = 8;
+constexpr int DROWS = 10;     // 10 rows x 96 chunks = 960 chunk pairs: just under four per thread
 __global__ void __launch_bounds__(256) attn_delta_kernel(AttnArgs a) {
   extern __shared__ float part[];                                  // [DROWS][H * cpr]
   const int cpr = a.Dh >> 3, per_row = a.H * cpr;
   const int64_t rows = (int64_t)a.N * a.Sq;
   for (int64_t r0 = (int64_t)blockIdx.x * DROWS; r0 < rows; r0 += (int64_t)gridDim.x * DROWS) {
     const int nr = (int)(rows - r0 < DROWS ? rows - r0 : DROWS);
-    for (int i = threadIdx.x; i < nr * per_row; i += 256) {
-      const int rr = i / per_row, c = i - rr * per_row, h = c / cpr, cc = c - h * cpr;
-      const int64_t row = r0 + rr;
-      const int s = (int)(row % a.Sq), n = (int)(row / a.Sq);
-      const uint4 x = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, s, h) + cc * 8);
-      const uint4 y = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, s, h) + cc * 8);
-      const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x);
-      const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&y);
-      float acc = 0.f;
+    const int n0 = (int)(r0 / a.Sq), s0 = (int)(r0 - (int64_t)n0 * a.Sq);   // the only 64-bit division of the round
+    auto locate = [&](int rr, int& n, int& s) {                    // row r0 + rr -> (sequence, position), 32-bit
+      n = n0;
+      s = s0 + rr;
+      while (s >= a.Sq) { s -= a.Sq; ++n; }
+    };
+    // up to four chunk pairs per thread per round, all eight 16-byte loads in flight before the first multiply
+    for (int i0 = threadIdx.x; i0 < nr * per_row; i0 += 4 * 256) {
+      uint4 x[4], y[4];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const float2 u = __bfloat1622float2(xh[k]), v = __bfloat1622float2(yh[k]);
-        acc = fmaf(u.x, v.x, fmaf(u.y, v.y, acc));
+        const int i = i0 + k * 256;
+        if (i < nr * per_row) {
+          const int rr = i / per_row, c = i - rr * per_row, h = c / cpr, cc = c - h * cpr;
+          int n, s;
+          locate(rr, n, s);
+          x[k] = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, s, h) + cc * 8);
+          y[k] = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, s, h) + cc * 8);
+        }
       }
-      part[i] = acc;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = i0 + k * 256;
+        if (i < nr * per_row) {
+          const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x[k]);
+          const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&y[k]);
+          float acc = 0.f;
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 u = __bfloat1622float2(xh[e]), v = __bfloat1622float2(yh[e]);
+            acc = fmaf(u.x, v.x, fmaf(u.y, v.y, acc));
+          }
+          part[i] = acc;
+        }
+      }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < nr * a.H; i += 256) {
       const int rr = i / a.H, h = i - rr * a.H;
       float acc = 0.f;
       for (int c = 0; c < cpr; ++c) acc += part[rr * per_row + h * cpr + c];
-      const int64_t row = r0 + rr;
-      a.delta[((int64_t)(row / a.Sq) * a.H + h) * a.Sq + (row % a.Sq)] = acc;
+      int n, s;
+      locate(rr, n, s);
+      a.delta[((int64_t)n * a.H + h) * a.Sq + s] = acc;
     }
     __syncthreads();
   }
