@@ -51,6 +51,10 @@ CASES = [  # n, s, heads, dh, causal, xpos, masked, backward
     # more work items than CTAs: the persistent multi-tile backward walks 4-5 items per CTA
     (40, 196, 8, 96, False, True, False, True),   # 640 items per pass
     (26, 300, 8, 96, True, True, True, True),     # 624 items, causal tiles of unequal length
+    # multi-step kernels (attn_tc2.cu): Dh = 64 with a 48-wide rotation, five key tiles, three full causal tiles
+    (3, 260, 8, 64, True, True, True, True),
+    (2, 640, 8, 96, False, True, True, True),
+    (21, 384, 8, 96, True, True, False, True),    # 504 items in the dQ pass: several per CTA, steps 1..3
 ]
 
 
@@ -99,6 +103,9 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
                     continue
                 c = torch.nn.functional.cosine_similarity(g[..., sl].flatten(), want, dim=0)
                 assert float(c) > 0.998, (name, part, float(c))
+                # magnitude too: a uniform scale error (softmax scale / log2e folded wrongly) keeps the cosine at 1
+                ratio = float(g[..., sl].norm() / want.norm())
+                assert abs(ratio - 1.0) <= 3e-2, (name, part, ratio)
 
 
 def test_multitile_backward_is_reproducible_and_cross_shaped():
