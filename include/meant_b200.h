@@ -118,7 +118,9 @@ typedef struct {
 
 /* Rotates q -> q_rot and k -> k_rot (caller-owned buffers, any head-view strides) with the qcos.. tables of `args`:
  * the per-position pair rotation of meant/rotary_embedding_torch.py:37-44,96-110 applied once per element.
- * bf16 only.  Optional: without it (q_rot.p == NULL) the attention kernels rotate in flight.              */
+ * bf16 only.  Optional: without it (q_rot.p == NULL) the attention kernels rotate in flight.  IN PLACE when q_rot and
+ * k_rot are the very views q and k (same pointer and strides): only the rotated columns are read and written, and the
+ * caller then passes q_rot = q, k_rot = k to meant_attn_fwd / meant_attn_bwd (which un-rotate dq / dk as always).   */
 int meant_attn_prerotate(const meant_attn_args* args, int dtype, meant_stream_t stream);
 
 int meant_attn_fwd(const meant_attn_args* args, int dtype, int impl, meant_stream_t stream);

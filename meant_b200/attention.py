@@ -28,7 +28,7 @@ class attention(nn.Module):
             raise NotImplementedError("attention(mask=True) is unusable in the reference; only mask=False exists")
         n = input.shape[1]
         qkv = _packed_qkv(self, input)
-        o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
+        o = ops.attention(qkv, consume=True, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
                           rot=self.pos_emb.tables(n, input.device))
         return self.dropout(ops.linear(o, self.multi_mad.weight, self.multi_mad.bias))
 
@@ -50,6 +50,6 @@ class flash_attention(nn.Module):
 
     def forward(self, input):
         qkv = _packed_qkv(self, input)
-        o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / self.dim, causal=bool(self.mask),
+        o = ops.attention(qkv, consume=True, heads=self.num_heads, scale=1.0 / self.dim, causal=bool(self.mask),
                           rot=self.pos_emb.tables(self.num_heads, input.device), pos_is_head=True)
         return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)

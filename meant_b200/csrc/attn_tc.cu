@@ -1182,7 +1182,10 @@ __global__ void __launch_bounds__(256) attn_prerotate_kernel(AttnArgs a) {
   const HeadView& dst = isk ? a.k_rot : a.q_rot;
   const float* __restrict__ cs = isk ? a.kcos : a.qcos;
   const float* __restrict__ sn = isk ? a.ksin : a.qsin;
-  const int S = isk ? a.Sk : a.Sq, cpr = a.Dh >> 3;
+  const int S = isk ? a.Sk : a.Sq;
+  // in place (q_rot aliases q): only the rotated chunks of a head row are touched -- half the traffic at rot_dim = Dh / 2
+  const bool inplace = src.p == dst.p;
+  const int cpr = inplace ? (a.rot_dim >> 3) : (a.Dh >> 3);
   if (!a.pos_is_head) {
     // Token-position tables do not depend on the head: a thread owns (row, chunk), fetches its 64 bytes of table
     // values ONCE and walks the heads (table traffic through L1 was 4x the payload with a thread per head chunk).
@@ -1423,7 +1426,8 @@ int attn_tc_bwd(const AttnArgs& a, cudaStream_t st) {
 long long attn_tma_fallbacks() { return g_tma_fallbacks.load(); }
 
 int attn_prerotate(const AttnArgs& a, int dtype, cudaStream_t st) {
-  if (dtype != MEANT_DT_BF16 || !a.qcos || !a.qsin || !a.kcos || !a.ksin) return MEANT_EARG;
+  if (dtype != MEANT_DT_BF16 || !a.qcos || !a.qsin || !a.kcos || !a.ksin || a.rot_dim <= 0) return MEANT_EARG;
+  if ((a.q_rot.p == a.q.p) != (a.k_rot.p == a.k.p)) return MEANT_EARG;      // in place for both or for neither
   if (!view_ok(a.q) || !view_ok(a.k) || !view_ok(a.q_rot) || !view_ok(a.k_rot)) return MEANT_EUNSUPPORTED;
   if (a.N <= 0 || a.H <= 0 || a.Sq <= 0 || a.Sk <= 0 || a.n2_count <= 0 || a.Dh % 8 != 0 || a.rot_dim % 8 != 0 ||
       a.rot_dim > a.Dh)

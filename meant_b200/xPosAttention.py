@@ -37,7 +37,7 @@ class xPosAttention(nn.Module):
             raise NotImplementedError("dropout on attention scores is not on the MEANT hot path (droput=0 everywhere)")
         s = input.shape[1]
         qkv = _packed_qkv(self, input)
-        o = ops.attention(qkv, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
+        o = ops.attention(qkv, consume=True, heads=self.num_heads, scale=1.0 / math.sqrt(self.Dh * self.num_heads),
                           causal=bool(self.mask), rot=self.xPos.tables(s, input.device), key_mask=attention_mask)
         return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)
 
@@ -61,6 +61,6 @@ class xPosAttention_flash(nn.Module):
 
     def forward(self, input):
         qkv = _packed_qkv(self, input)
-        o = ops.attention(qkv, heads=self.num_heads, scale=self.Dh ** -0.5, causal=bool(self.mask),
+        o = ops.attention(qkv, consume=True, heads=self.num_heads, scale=self.Dh ** -0.5, causal=bool(self.mask),
                           rot=self.xPos.tables(self.num_heads, input.device), pos_is_head=True)
         return ops.linear(o, self.multi_mad.weight, self.multi_mad.bias)

@@ -165,3 +165,30 @@ def test_prerotated_and_in_flight_rotation_agree(s, causal):
     assert bool((diff <= 1e-2 * mag).all()), float((diff / mag).max())
     c = torch.nn.functional.cosine_similarity(got[0][1].flatten(), got[1][1].flatten(), dim=0)
     assert float(c) > 0.9999, float(c)
+
+
+@pytest.mark.parametrize("s,causal", [(196, False), (512, True)])
+def test_in_place_rotation_matches_rotated_copies(s, causal):
+    """consume=True: Q and K of the projection buffer are rotated in place (no q_rot / k_rot copies).  Same outputs and
+    gradients as the copying path, V untouched, Q / K overwritten with exactly what meant_attn_prerotate writes."""
+    torch.manual_seed(s + 1)
+    heads, dh, n = 8, 96, 3
+    dim = heads * dh
+    base = torch.randn(n, s, 3 * dim, device="cuda").bfloat16()
+    rot = RotaryEmbedding(dim=48, use_xpos=True).tables(s, "cuda")
+    probe = torch.randn(n, s, dim, device="cuda")
+    got = []
+    for consume in (False, True):
+        x = base.clone().requires_grad_(True)
+        o = ops.attention(x, heads=heads, scale=dim ** -0.5, causal=causal, rot=rot, impl=nv.IMPL_TCGEN05, consume=consume)
+        (o.float() * probe).sum().backward()
+        got.append((o.float(), x.grad.float(), x.detach().clone()))
+    torch.cuda.synchronize()
+    assert torch.equal(got[0][0], got[1][0])                      # the kernels read bit-identical rotated operands
+    assert torch.equal(got[0][1], got[1][1])
+    assert torch.equal(got[0][2], base)                           # copying path: input untouched
+    after = got[1][2]
+    assert torch.equal(after[..., 2 * dim:], base[..., 2 * dim:])                      # V
+    qk = after[..., :2 * dim].view(n, s, 2 * heads, dh)
+    assert torch.equal(qk[..., 48:], base[..., :2 * dim].view(n, s, 2 * heads, dh)[..., 48:])   # un-rotated tail of every head
+    assert not torch.equal(qk[..., :48], base[..., :2 * dim].view(n, s, 2 * heads, dh)[..., :48])
