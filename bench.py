@@ -168,8 +168,8 @@ def kernel_stats(timers):
 # ncu `dram__bytes_read.sum + dram__bytes_write.sum` per launch of the dominant kernels at THIS workload, read from a
 # committed `ncu --set full` capture (N=768, H=8, S=128, Dh=96): equal to the algorithmic bytes, nothing is re-read.
 # It is a profile-derived constant, NOT a measurement of the run that prints it: `traffic_source` says so in the line.
-NCU_TRAFFIC = {"attn_fwd": 581.6e6, "attn_bwd": 1017.6e6}
-NCU_TRAFFIC_SOURCE = "profiles/r1n_ncu/r1n_attn128_summary.txt (ncu --set full capture of this kernel at this shape, scaled by " \
+NCU_TRAFFIC = {"attn_fwd": 584.9e6, "attn_bwd": 1019.7e6}    # dram__bytes_read.sum + dram__bytes_write.sum per launch at 768 sequences
+NCU_TRAFFIC_SOURCE = "profiles/r2s_ncu/r2s_attn128_summary.txt (ncu --set full capture of this kernel at this shape, scaled by " \
                      "sequences/768; not re-measured by this run)"
 
 
