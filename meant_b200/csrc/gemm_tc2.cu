@@ -20,6 +20,8 @@
 #include "tc_utils.cuh"
 #include "tma_utils.cuh"
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 namespace meant {
 namespace g2 {
@@ -282,6 +284,197 @@ __global__ void __launch_bounds__(NT, 1) gemm_gen_kernel(const __grid_constant__
   if (warp == 1) tc::tmem_dealloc(tmem, 512);
 }
 
+// ------------------------------------------------------------------------------------------ CTA pairs (cta_group::2)
+// The same GEMM with two CTAs (one cluster, neighbouring SMs) on one 256 x 256 tile: each CTA loads ITS 128 rows of A
+// and HALF of the B tile (128 of the 256 output columns) per K step, the leader CTA issues one
+// tcgen05.mma.cta_group::2 (M = 256) that feeds both tensor cores -- each reads its own A rows and both halves of B --
+// and each CTA's TMEM receives its 128 x 256 half of the accumulator.  Per CTA and K step the TMA writes 32 KB instead
+// of 48 KB and the MMA reads a third less shared memory.  Correct, but measured SLOWER than the single-CTA kernel on
+// the block's shapes (180 vs 102 us at 98304 x 768 x 768; 103 us with the loads switched off, i.e. MMA + epilogue alone
+// already sit at the single-CTA kernel's time: with K = 768 a tile is 12 K steps against a 64 KB epilogue), so it is
+// opt-in: MEANT_GEMM_PAIR=1.
+//   full[s]      lives in the LEADER: both producers arrive on it (the peer remotely) with their own byte counts, and
+//                both CTAs' boxes complete on it (cp.async.bulk.tensor ... cta_group::2 may signal the peer's barrier)
+//   empty[s]     in each CTA, signalled by the leader's tcgen05.commit multicast: the stage may be refilled
+//   acc_full[a]  in each CTA, same multicast: each epilogue drains its own TMEM half
+//   acc_empty[a] in the leader, two arrivals: one elected epilogue thread per CTA (the peer's remotely)
+// A is K-major; B K-major (forward) or MN-major (dgrad).  Bias epilogue only.
+constexpr int NSTAGE2 = 6;
+constexpr uint32_t HALF_B = 128 * BK * 2, STAGE2 = A_BYTES + HALF_B;
+constexpr uint32_t OFF_OUT2 = NSTAGE2 * STAGE2, OFF_BARS2 = OFF_OUT2 + 2 * OUT_BOX, SMEM_TOTAL2 = OFF_BARS2 + 256 + 1024;
+static_assert(SMEM_TOTAL2 <= 232448, "exceeds the shared memory a CTA can opt in to");
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// shared::cluster address of `local` (a shared::cta address) in CTA `rank` of this cluster
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void remote_arrive_expect_tx(uint32_t bar_cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;\n" ::"r"(bar_cluster_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void remote_arrive(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(bar_cluster_addr) : "memory");
+}
+// TMA box into this CTA's shared memory, completion counted on a barrier that may live in the peer CTA
+__device__ __forceinline__ void load_box2_pair(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n"
+               ::"r"(dst), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void mma_ss_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) {           // arrives on `bar` in BOTH CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+               ::"r"(tc::smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+
+template <bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NT, 1) gemm_pair_kernel(const __grid_constant__ Maps maps, const Params p) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BARS2);
+  uint64_t *full = bars, *empty = bars + NSTAGE2, *acc_full = bars + 2 * NSTAGE2, *acc_empty = acc_full + 2;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
+  if (tid == 0) {
+    for (int i = 0; i < NSTAGE2; ++i) { tc::mbar_init(&full[i], 2); tc::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(&acc_full[i], 1); tc::mbar_init(&acc_empty[i], 2); }
+    tc::fence_mbar_init();
+  }
+  if (warp == 1) {                                         // one warp of EACH CTA of the pair
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(tc::smem_u32(&tmem_slot)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();                                      // both CTAs' barriers and TMEM exist before anything remote happens
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot, s0 = tc::smem_u32(smem);
+  const int tiles_n = (p.N + BN - 1) / BN, tiles_m = (p.M + 255) / 256, tiles = tiles_m * tiles_n, kt = (p.K + BK - 1) / BK;
+  const int cluster = blockIdx.x >> 1, n_clusters = gridDim.x >> 1;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      tma::prefetch_map(&maps.a);
+      tma::prefetch_map(&maps.b);
+      int it = 0;
+      for (int t = cluster; t < tiles; t += n_clusters) {
+        const int m0 = (t / tiles_n) * 256 + (int)rank * 128, n0 = (t % tiles_n) * BN + (int)rank * 128;
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE2;
+          if (it >= NSTAGE2) tc::mbar_wait(&empty[s], ((it / NSTAGE2) - 1) & 1);
+          const uint32_t fb = map_to_cta(tc::smem_u32(&full[s]), 0);       // the leader's barrier
+          remote_arrive_expect_tx(fb, STAGE2);
+          const uint32_t sa = s0 + s * STAGE2, sb = sa + A_BYTES;
+          load_box2_pair(sa, &maps.a, fb, k * BK, m0);
+          if (!B_MN) load_box2_pair(sb, &maps.b, fb, k * BK, n0);
+          else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) load_box2_pair(sb + j * SUB, &maps.b, fb, n0 + 64 * j, k * BK);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {
+      constexpr uint32_t idesc = tc::make_idesc(256, BN, 0, B_MN);
+      int it = 0, ti = 0;
+      for (int t = cluster; t < tiles; t += n_clusters, ++ti) {
+        const int acc = ti & 1, use = ti >> 1;
+        if (use >= 1) tc::mbar_wait(&acc_empty[acc], (use - 1) & 1);
+        tc::fence_after_sync();
+        for (int k = 0; k < kt; ++k, ++it) {
+          const int s = it % NSTAGE2;
+          tc::mbar_wait(&full[s], (it / NSTAGE2) & 1);
+          tc::fence_after_sync();
+          const uint32_t sa = s0 + s * STAGE2, sb = sa + A_BYTES;
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk) {
+            const uint64_t ad = tc::make_desc_sw(sa + kk * 32, 16, 1024, 2);
+            const uint64_t bd = B_MN ? tc::make_desc_sw(sb + kk * 2048, SUB, 1024, 2) : tc::make_desc_sw(sb + kk * 32, 16, 1024, 2);
+            mma_ss_pair(tmem + acc * BN, ad, bd, idesc, (k > 0 || kk > 0) ? 1u : 0u);
+          }
+          mma_commit_pair(&empty[s]);                      // both CTAs may refill the stage
+        }
+        mma_commit_pair(&acc_full[acc]);
+      }
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+    const bool elected = warp == 2 && lane == 0;
+    int ti = 0;
+    for (int t = cluster; t < tiles; t += n_clusters, ++ti) {
+      const int m0 = (t / tiles_n) * 256 + (int)rank * 128, n0 = (t % tiles_n) * BN, acc = ti & 1, use = ti >> 1;
+      tc::mbar_wait(&acc_full[acc], use & 1);
+      tc::fence_after_sync();
+#pragma unroll 1
+      for (int r = 0; r < 2; ++r) {
+        if (elected) tma::store_wait_read<0>();
+        tc::bar_sync(BAR_EPI, 128);
+#pragma unroll
+        for (int bi = 0; bi < 2; ++bi) {
+          const int g = r * 2 + bi;
+          uint8_t* box = smem + OFF_OUT2 + bi * OUT_BOX;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            float v[32];
+            tc::tmem_ld32(lane_base + acc * BN + g * 64 + c * 32, v);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int gq = 0; gq < 4; ++gq) {
+              float b[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+              const int col = n0 + g * 64 + c * 32 + gq * 8;
+              if (p.bias && col < p.N) {
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + 1);
+                b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+              }
+              uint4 pk;
+              __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+              for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(v[gq * 8 + 2 * i] + b[2 * i], v[gq * 8 + 2 * i + 1] + b[2 * i + 1]);
+              *reinterpret_cast<uint4*>(box + tc::sw128_off(row, c * 4 + gq)) = pk;
+            }
+          }
+        }
+        tc::fence_async_smem();
+        tc::fence_before_sync();
+        tc::bar_sync(BAR_EPI, 128);
+        if (elected) {
+          if (r == 1) remote_arrive(map_to_cta(tc::smem_u32(&acc_empty[acc]), 0));   // this CTA's half of the accumulator is drained
+#pragma unroll
+          for (int bi = 0; bi < 2; ++bi) {
+            const int c0 = n0 + (r * 2 + bi) * 64;
+            if (c0 < p.N && m0 < p.M) store_box2(&maps.c, s0 + OFF_OUT2 + bi * OUT_BOX, c0, m0);
+          }
+          tma::store_commit();
+        }
+      }
+    }
+    if (elected) tma::store_wait_all();
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  cluster_sync_all();                                      // nobody leaves (or frees TMEM) while the peer may still signal it
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(512u) : "memory");
+}
+
 // 2-D tensor map over a row-major tensor: `cols` contiguous elements per row, row pitch ld elements, SWIZZLE_128B
 static int make_map2(CUtensorMap* m, const void* p, int64_t rows, int64_t cols, int64_t ld, int box_cols, int box_rows, bool f32) {
   tma::EncodeTiledFn enc = tma::encode_fn();
@@ -344,6 +537,42 @@ extern "C" int meant_gemm_bf16(const void* A, const void* B, void* C, int64_t M,
   const int64_t tiles = ((M + g2::BM - 1) / g2::BM) * ((N + g2::BN - 1) / g2::BN);
   const int grid = (int)(tiles < sms ? tiles : sms);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // CTA pairs (cta_group::2) for the large forward / dgrad problems: MEANT_GEMM_PAIR=1 (read once; experiments)
+  static const bool env_pair = getenv("MEANT_GEMM_PAIR") != nullptr;
+  if (env_pair && !a_mn && !residual && sms % 2 == 0 && ((M + 255) / 256) * ((N + g2::BN - 1) / g2::BN) >= sms / 2) {
+    g2::Maps m2 = maps;
+    int rc2 = b_mn ? 0 : g2::make_map2(&m2.b, B, N, K, ldb, g2::BK, 128, false);     // half a B tile per CTA
+    if (rc2) return rc2;
+    auto kern = b_mn ? g2::gemm_pair_kernel<true> : g2::gemm_pair_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g2::SMEM_TOTAL2);
+    if (e != cudaSuccess) return (int)e;
+    // A pair needs both SMs of one TPC; not every TPC of a B200 has two SMs enabled, so fewer than sms / 2 pairs can
+    // be resident.  The persistent grid must not exceed that number: a pair that starts late starts after the early
+    // ones have taken its tiles' time (a grid of sms CTAs measured exactly 2x slower).
+    static int pairs_cached[2] = {0, 0};
+    int& pairs = pairs_cached[b_mn ? 1 : 0];
+    if (pairs == 0) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)sms);
+      cfg.blockDim = dim3(g2::NT);
+      cfg.dynamicSmemBytes = g2::SMEM_TOTAL2;
+      cudaLaunchAttribute at;
+      at.id = cudaLaunchAttributeClusterDimension;
+      at.val.clusterDim.x = 2;
+      at.val.clusterDim.y = 1;
+      at.val.clusterDim.z = 1;
+      cfg.attrs = &at;
+      cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) n = sms / 2;
+      if (n > sms / 2) n = sms / 2;
+      pairs = n;
+      if (getenv("MEANT_DEBUG")) fprintf(stderr, "meant_gemm_bf16: %d resident CTA pairs of %d SMs\n", n, sms);
+    }
+    kern<<<2 * pairs, g2::NT, g2::SMEM_TOTAL2, st>>>(m2, p);
+    MEANT_LAUNCH_CHECK();
+    return 0;
+  }
   if (!a_mn && !b_mn) return g2::launch(g2::gemm_gen_kernel<false, false, 0>, grid, maps, p, st);
   if (!a_mn && b_mn) return g2::launch(g2::gemm_gen_kernel<false, true, 0>, grid, maps, p, st);
   if (a_mn && !b_mn) return g2::launch(g2::gemm_gen_kernel<true, false, 0>, grid, maps, p, st);

@@ -109,3 +109,18 @@ def test_gemm_general_argument_errors():
     assert lib.meant_gemm_bf16(nv.ptr(x), nv.ptr(x), nv.ptr(x), 16, 12, 16, 16, 16, 16, 0, 1, None, None, 0, None) == -2
     assert lib.meant_gemm_bf16_wgrad(nv.ptr(x), nv.ptr(x), None, None, 16, 16, 16, 16, 16, 16, None) == -1
     assert lib.meant_gemm_bf16_wgrad(nv.ptr(x), nv.ptr(x), nv.ptr(f), None, 16, 16, 16, 8, 16, 16, None) == -1   # lddy < N
+
+
+def test_gemm_cta_pair_kernel_in_a_subprocess():
+    """The cta_group::2 kernel (two CTAs per 256 x 256 tile, opt-in through MEANT_GEMM_PAIR, which is read once per
+    process): forward and dgrad forms, full and ragged shapes, against torch (tools/gemm_pair_check.py)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, MEANT_GEMM_PAIR="1", MEANT_DEBUG="1")
+    r = subprocess.run([sys.executable, os.path.join(root, "tools", "gemm_pair_check.py")], env=env, capture_output=True, text=True,
+                       timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert r.stdout.count(" OK") == 6 and "MISMATCH" not in r.stdout, r.stdout
+    assert "resident CTA pairs" in r.stderr, r.stderr[-500:]          # the pair kernel really ran
