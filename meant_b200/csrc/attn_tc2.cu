@@ -1772,63 +1772,44 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
-// delta[n, h, s] = sum_d dO[n, s, h, d] * O[n, s, h, d]  (args: o = dO, out_saved = O).  A CTA takes DROWS token rows:
-// thread i multiplies 16-byte chunks i, i + 256, ... of the rows' H * Dh / 8 chunks (consecutive threads read
-// consecutive chunks: coalesced when the heads of a row are contiguous), the partial dot products go to shared memory
-// and one thread per (row, head) adds its Dh / 8 partials.  HBM-bound: reads dO and O once.
-constexpr int DROWS = 10;     // 10 rows x 96 chunks = 960 chunk pairs: just under four per thread
+// delta[n, h, s] = sum_d dO[n, s, h, d] * O[n, s, h, d]  (args: o = dO, out_saved = O).  Four lanes per (token, head):
+// a lane multiplies Dh / 32 consecutive 16-byte chunks of both rows (all loads issued before the first multiply), two
+// shuffles add the four partial sums.  A warp covers eight consecutive (token, head) pairs per iteration -- with eight
+// heads exactly one token row of dO and one of O, read as contiguous 16-byte chunks.  HBM-bound: reads dO and O once.
+constexpr int DROWS = 8;      // (kept for the host-side grid computation: token rows per CTA iteration)
+template <int CPL>            // chunks per lane: Dh / 32
 __global__ void __launch_bounds__(256) attn_delta_kernel(AttnArgs a) {
-  extern __shared__ float part[];                                  // [DROWS][H * cpr]
-  const int cpr = a.Dh >> 3, per_row = a.H * cpr;
-  const int64_t rows = (int64_t)a.N * a.Sq;
-  for (int64_t r0 = (int64_t)blockIdx.x * DROWS; r0 < rows; r0 += (int64_t)gridDim.x * DROWS) {
-    const int nr = (int)(rows - r0 < DROWS ? rows - r0 : DROWS);
-    const int n0 = (int)(r0 / a.Sq), s0 = (int)(r0 - (int64_t)n0 * a.Sq);   // the only 64-bit division of the round
-    auto locate = [&](int rr, int& n, int& s) {                    // row r0 + rr -> (sequence, position), 32-bit
-      n = n0;
-      s = s0 + rr;
-      while (s >= a.Sq) { s -= a.Sq; ++n; }
-    };
-    // up to four chunk pairs per thread per round, all eight 16-byte loads in flight before the first multiply
-    for (int i0 = threadIdx.x; i0 < nr * per_row; i0 += 4 * 256) {
-      uint4 x[4], y[4];
+  const int lane = threadIdx.x & 31, part = lane & 3;
+  const int64_t units = (int64_t)a.N * a.Sq * a.H;                 // (token, head) pairs, heads fastest
+  const int64_t wstride = (int64_t)gridDim.x * 8 * 8;
+  for (int64_t u0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 8; u0 < units; u0 += wstride) {
+    const int64_t u = u0 + (lane >> 2);
+    float acc = 0.f;
+    int64_t out_idx = -1;
+    if (u < units) {
+      const int h = (int)(u % a.H);
+      const int64_t row = u / a.H;
+      const int s = (int)(row % a.Sq), n = (int)(row / a.Sq);
+      const uint4* xp = reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, s, h)) + part * CPL;
+      const uint4* yp = reinterpret_cast<const uint4*>(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, s, h)) + part * CPL;
+      uint4 x[CPL], y[CPL];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = i0 + k * 256;
-        if (i < nr * per_row) {
-          const int rr = i / per_row, c = i - rr * per_row, h = c / cpr, cc = c - h * cpr;
-          int n, s;
-          locate(rr, n, s);
-          x[k] = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.o, n, a.n2_count, s, h) + cc * 8);
-          y[k] = tc::ldg_stream16(view_ptr<__nv_bfloat16>(a.out_saved, n, a.n2_count, s, h) + cc * 8);
+      for (int c = 0; c < CPL; ++c) { x[c] = tc::ldg_stream16(xp + c); y[c] = tc::ldg_stream16(yp + c); }
+#pragma unroll
+      for (int c = 0; c < CPL; ++c) {
+        const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x[c]);
+        const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&y[c]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 p = __bfloat1622float2(xh[e]), q = __bfloat1622float2(yh[e]);
+          acc = fmaf(p.x, q.x, fmaf(p.y, q.y, acc));
         }
       }
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int i = i0 + k * 256;
-        if (i < nr * per_row) {
-          const __nv_bfloat162* xh = reinterpret_cast<const __nv_bfloat162*>(&x[k]);
-          const __nv_bfloat162* yh = reinterpret_cast<const __nv_bfloat162*>(&y[k]);
-          float acc = 0.f;
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const float2 u = __bfloat1622float2(xh[e]), v = __bfloat1622float2(yh[e]);
-            acc = fmaf(u.x, v.x, fmaf(u.y, v.y, acc));
-          }
-          part[i] = acc;
-        }
-      }
+      out_idx = ((int64_t)n * a.H + h) * a.Sq + s;
     }
-    __syncthreads();
-    for (int i = threadIdx.x; i < nr * a.H; i += 256) {
-      const int rr = i / a.H, h = i - rr * a.H;
-      float acc = 0.f;
-      for (int c = 0; c < cpr; ++c) acc += part[rr * per_row + h * cpr + c];
-      int n, s;
-      locate(rr, n, s);
-      a.delta[((int64_t)n * a.H + h) * a.Sq + s] = acc;
-    }
-    __syncthreads();
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    if (part == 0 && out_idx >= 0) a.delta[out_idx] = acc;
   }
 }
 
@@ -2487,12 +2468,11 @@ static int launch_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
   if (int rc = build_maps<DH>(maps.m, a, vs, seq, 7, g)) return rc;
   const t2::MsDims dm = {(a.Sq + 127) / 128, (a.Sk + 127) / 128};
   {
-    const int64_t rows = (int64_t)a.N * a.Sq;
-    int64_t blocks = (rows + t2::DROWS - 1) / t2::DROWS;
+    const int64_t units = (int64_t)a.N * a.Sq * a.H;
+    int64_t blocks = (units + 63) / 64;                      // 8 warps x 8 (token, head) pairs per CTA iteration
     if (blocks > num_sms() * 8) blocks = num_sms() * 8;
-    const size_t sm = sizeof(float) * t2::DROWS * a.H * (a.Dh / 8);
-    if (sm > 48 * 1024) return MEANT_EUNSUPPORTED;
-    t2::attn_delta_kernel<<<(unsigned)blocks, 256, sm, st>>>(a);
+    if (DH == 96) t2::attn_delta_kernel<3><<<(unsigned)blocks, 256, 0, st>>>(a);
+    else t2::attn_delta_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(a);
     MEANT_LAUNCH_CHECK();
   }
   if (parts & 2) {
