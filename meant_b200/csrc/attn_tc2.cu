@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_kernel(AttnArgs a, int n_it
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
               const int e = q * 8 + 2 * u;
-              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - m_use)), p1 = tc::ex2_poly(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - m_use));
+              float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - m_use)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - m_use));
               if (GRP) {
                 const int c = blk * 32 + e;
                 if (!((c >= glo && c < ghi) || c == gx)) p0 = 0.f;

@@ -157,22 +157,6 @@ __device__ __forceinline__ float ex2(float x) {
   return y;
 }
 
-// 2^x for x <= 0 on the FMA / ALU pipes instead of the SFU (MUFU.EX2 issues for 8 cycles per warp, a quarter-rate
-// pipe the two softmax warps of a scheduler share: the exponentials bound pass 2 of the single-tile kernels).
-// Cody-Waite: n = round(x) taken from the mantissa of x + 1.5 * 2^23, r = x - n in [-0.5, 0.5], degree-3 minimax
-// polynomial for 2^r (max relative error 7.5e-5: a twentieth of the bf16 rounding of P), n added to the exponent
-// field.  x is clamped at -125 (masked scores, -inf: the result, 2^-125, is ~0 in every sum here; one step lower and
-// the exponent of p in [0.707, 1.414) would wrap into the NaN range).  Used for every other element of a row.
-__device__ __forceinline__ float ex2_poly(float x) {
-  x = fmaxf(x, -125.0f);
-  const float t = x + 12582912.0f;
-  const float r = x - (t - 12582912.0f);
-  float p = fmaf(r, 0.05517167f, 0.24261113f);
-  p = fmaf(p, r, 0.69326097f);
-  p = fmaf(p, r, 0.99992806f);
-  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
-}
-
 // ---- mbarrier -------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(count) : "memory");
