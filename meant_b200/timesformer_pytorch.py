@@ -83,7 +83,11 @@ class FeedForward(nn.Module):
                                  nn.Linear(dim * mult, dim))
 
     def forward(self, x):
-        return self.net(x)
+        # the two Linears through the fused wrapper (bias gradient from the weight-gradient kernel instead of autograd's
+        # generic reduction); the parameters stay in `net` (state_dict contract)
+        x = ops.linear(x, self.net[0].weight, self.net[0].bias)
+        x = self.net[2](self.net[1](x))
+        return ops.linear(x, self.net[3].weight, self.net[3].bias)
 
 
 class Attention(nn.Module):
@@ -119,7 +123,7 @@ class Attention(nn.Module):
         # cls query over every key (:119) + the grouped attention (:122-139), read and written in place
         out = ops.divided_attention(qkv, heads=self.heads, scale=self.scale, frames=f, patches=n, time_mode=time_mode,
                                     rot=rot)
-        return self.to_out(out)
+        return self.to_out[1](ops.linear(out, self.to_out[0].weight, self.to_out[0].bias))
 
 
 class TimeSformer(nn.Module):
@@ -158,7 +162,7 @@ class TimeSformer(nn.Module):
         hp, wp = hh // p, ww // p
         n = hp * wp
         v = ops.patchify(video.reshape(b * f, c, hh, ww), p).view(b, f * n, p * p * c)
-        tokens = self.to_patch_embedding(v)
+        tokens = ops.linear(v, self.to_patch_embedding.weight, self.to_patch_embedding.bias)
         x = torch.cat((self.cls_token.to(tokens.dtype)[None].expand(b, -1, -1), tokens), dim=1)
         x = x.to(ops.compute_dtype(x))
         frot = arot = None
