@@ -108,12 +108,13 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
                 assert abs(ratio - 1.0) <= 3e-2, (name, part, ratio)
 
 
-def test_multitile_backward_is_reproducible_and_cross_shaped():
-    """Multi-tile backward: bit-identical gradients run to run (no atomics), and Sq != Sk (q | kv inputs)."""
+@pytest.mark.parametrize("n,sq,sk", [(2, 200, 333), (3, 100, 300), (3, 300, 100), (20, 129, 257)])
+def test_multitile_backward_is_reproducible_and_cross_shaped(n, sq, sk):
+    """Multi-tile backward: bit-identical gradients run to run (no atomics), and Sq != Sk (q | kv inputs): one query tile
+    against several key tiles, several against one, and more work items than CTAs with one-row tail tiles."""
     torch.manual_seed(5)
     heads, dh = 8, 96
     dim = heads * dh
-    n, sq, sk = 2, 200, 333
     q0 = torch.randn(n, sq, dim, device="cuda").bfloat16()
     kv0 = torch.randn(n, sk, 2 * dim, device="cuda").bfloat16()
     probe = torch.randn(n, sq, dim, device="cuda")
