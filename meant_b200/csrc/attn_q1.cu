@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(NW * 32) q1_partial_kernel(AttnArgs a, float* 
 #pragma unroll
     for (int i = 0; i < MAXP; ++i) o[i] = make_float2(0.f, 0.f);
     const int kend = min(KC, a.Sk - k0);
+#pragma unroll 8                                      // eight rows' loads in flight: the loop was one L2 latency per key
     for (int j = 0; j < kend; ++j) {
       const float pj = __shfl_sync(0xffffffffu, j < 32 ? p0 : p1, j & 31);
       const T* vrow = view_ptr<T>(a.v, n, a.n2_count, k0 + j, h);
@@ -184,6 +185,7 @@ __global__ void __launch_bounds__(NW * 32) q1_bwd_kernel(AttnArgs a, float* __re
         dsv[u] = dsc;
         T* gk = view_ptr<T>(a.dk, n, a.n2_count, kj, h);
         T* gv = view_ptr<T>(a.dv, n, a.n2_count, kj, h);
+#pragma unroll 4
         for (int d0 = 0; d0 < Dh; d0 += N) {          // dK = dS (q * scale), dV = p dO: this lane's own rows
           float fk[N], fv[N];
           if (ACC) {
@@ -214,6 +216,7 @@ __global__ void __launch_bounds__(NW * 32) q1_bwd_kernel(AttnArgs a, float* __re
 #pragma unroll
     for (int i = 0; i < MAXP; ++i) acc[i] = make_float2(0.f, 0.f);
     const int kend = min(KC, a.Sk - k0);
+#pragma unroll 8
     for (int j = 0; j < kend; ++j) {
       const float dj = __shfl_sync(0xffffffffu, j < 32 ? dsv[0] : dsv[1], j & 31);
       const T* krow = view_ptr<T>(a.k, n, a.n2_count, k0 + j, h);
