@@ -62,9 +62,8 @@ def build(what, batch, dev, encoders=12, depth=1, seed=1234):
 
             def forward(self, ids, mask):
                 from meant_b200 import ops
-                x = ops.embed(self.embedding, ids)
-                for enc in self.languageEncoders:
-                    x = enc(x, attention_mask=mask)
+                from meant_b200.meant import _run_stack      # how meant_vqa / meant_language_pretrainer run this stack
+                x = _run_stack(self.languageEncoders, ops.embed(self.embedding, ids), mask)
                 return torch.sigmoid(self.head(x.mean(dim=1).float()))
 
         ids = torch.randint(0, VOCAB, (b, s), generator=g).to(dev)
