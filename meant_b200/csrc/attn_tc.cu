@@ -1271,6 +1271,8 @@ int attn_tc2_fwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_bwd(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_ms_supported(const AttnArgs& a);
 int attn_tc2_fwd_ms(const AttnArgs& a, cudaStream_t st);
+int attn_tc2_wk_supported(const AttnArgs& a);
+int attn_tc2_fwd_wk(const AttnArgs& a, cudaStream_t st);
 int attn_tc2_ms_bwd_supported(const AttnArgs& a);
 int attn_tc2_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st);
 
@@ -1373,6 +1375,11 @@ int attn_tc_fwd(const AttnArgs& a, cudaStream_t st) {
     ++g_tma_fallbacks;
   }
   static const bool old_mt = getenv("MEANT_ATTN_OLD_MT") != nullptr;   // read once: A/B against the per-tile-pair kernel below
+  static const bool no_wk = getenv("MEANT_ATTN_NO_WK") != nullptr;      // read once: A/B against the multi-step kernel
+  if (!old_mt && !no_wk && attn_tc2_wk_supported(a)) {
+    const int r2 = attn_tc2_fwd_wk(a, st);
+    if (r2 != MEANT_EUNSUPPORTED) return r2;
+  }
   if (!old_mt && attn_tc2_ms_supported(a)) {
     const int r2 = attn_tc2_fwd_ms(a, st);
     if (r2 != MEANT_EUNSUPPORTED) return r2;

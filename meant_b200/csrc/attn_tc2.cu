@@ -984,6 +984,324 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
   if (warp == 0) tc::tmem_dealloc(tmem, 512);
 }
 
+// ============================================================================== forward, one wide key tile
+// 128 < Sk <= 208 (the 196-patch vision path): every key of a (sequence, head) fits ONE tile of 208 rows, so a work
+// item -- one (sequence, head, 128-query tile) -- is a single-tile pass again: Q | K | V boxes into one of two stages,
+// ONE S = Q K^T of N = ceil16(Sk) columns into the stage's 256 TMEM columns, a plain two-pass softmax out of TMEM
+// (no running max, no correction of the output accumulator, no fold through registers), P [128 x 224] over the
+// consumed Q | K, O = P V over the consumed S, normalise, stage, TMA-store.  Against the multi-step kernel on the
+// same problem this halves the steps, never touches the padded second key tile's 60 empty columns and drops the
+// online-softmax arithmetic.  K | V boxes of the item after next are issued as soon as P V has run (their stage half
+// is dead then); the MMA thread polls "next item's boxes landed" and "this item's P ready" together, so neither
+// S(j + 1) nor P V(j) ever waits behind the other's barrier.
+// Rotation is not done here: q_rot / k_rot (meant_attn_prerotate, or in place) or no tables at all.
+template <int DH>
+struct FwdWkL {
+  using G = Geo<DH>;
+  static constexpr int KW = 208;                                // key rows of a K / V tile: 13 MMA K steps
+  static constexpr int NST = 2;
+  static constexpr uint32_t KA = KW * 128u;                     // columns [0, 64): SWIZZLE_128B rows
+  static constexpr uint32_t KB = G::TAIL ? KW * 64u : 0u;       // columns [64, 96): SWIZZLE_64B rows
+  static constexpr uint32_t OPERK = KA + KB;
+  static constexpr uint32_t PW = 3 * SUB_A + SUB_B;             // P: key columns [0, 192) in three sub-tiles, [192, 224) in a fourth
+  static constexpr bool P_ALIAS = PW <= G::OPER + OPERK;        // P over the consumed Q | K; else one separate P tile
+  static constexpr uint32_t STAGE = G::OPER + 2 * OPERK;        // Q | K | V
+  static constexpr uint32_t PSEP = NST * STAGE;
+  static constexpr uint32_t AUX = PSEP + (P_ALIAS ? 0u : PW);   // [NST][256] fp32 additive key bias (exp2 domain)
+  static constexpr uint32_t RED = AUX + NST * 1024;             // [2 (item parity)][2 (half)][128] row max | the same for the row sum
+  static constexpr uint32_t BARS = RED + 4096;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;
+  static_assert(TOTAL <= 227 * 1024, "shared memory");
+  static_assert(KA % 1024 == 0 && KB % 1024 == 0 && STAGE % 1024 == 0, "swizzle atoms are 1024-byte aligned");
+};
+
+// chunk c (8 key columns) of row r of the wide P tile
+__device__ __forceinline__ uint32_t pw_off(int r, int c) {
+  return c < 24 ? (c >> 3) * SUB_A + tc::sw128_off(r, c & 7) : 3 * SUB_A + tc::sw64_off(r, c - 24);
+}
+// K-major view of the wide P tile, K step ks (16 key columns)
+__device__ __forceinline__ uint64_t desc_pw_k(uint32_t base, int ks) {
+  return ks < 12 ? tc::make_desc_sw(base + (ks >> 2) * SUB_A + (ks & 3) * 32, 16, 1024, 2) : tc::make_desc_sw(base + 3 * SUB_A, 16, 512, 4);
+}
+
+template <int DH>
+__global__ void __launch_bounds__(F_NT, 1) attn2_fwd_wk_kernel(AttnArgs a, int n_items, const __grid_constant__ FwdMaps maps,
+                                                               const MsDims dm) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  using L = FwdWkL<DH>;
+  using G = Geo<DH>;
+  constexpr int NST = L::NST;
+  constexpr int HALF = DH / 2;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *landed = bars, *s_full = bars + NST, *o_full = bars + 2 * NST, *o_staged = bars + 3 * NST,
+           *aux_ready = bars + 4 * NST, *p_ready = bars + 5 * NST;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // V rows in [Sk, ceil16(Sk)) are read by the last P V step and never written by a box: everything starts as zero
+  for (uint32_t i = tid * 16; i < L::AUX; i += F_NT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0u, 0u, 0u, 0u);
+  tc::fence_async_smem();
+  if (tid == 0) {
+    for (int i = 0; i < NST; ++i) {
+      tc::mbar_init(&landed[i], 1);
+      tc::mbar_init(&aux_ready[i], 32);
+      tc::mbar_init(&s_full[i], 1);
+      tc::mbar_init(&o_full[i], 1);
+      tc::mbar_init(&o_staged[i], NC);
+      tc::mbar_init(&p_ready[i], NC);
+    }
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const uint32_t s0 = tc::smem_u32(smem);
+  const int n_s = (a.Sk + 15) & ~15;                               // S columns / P V K extent
+  // item -> (sequence, head, query tile): the query tiles of one (sequence, head) are neighbours (K, V come from L2)
+  auto coords = [&](int item, int& n1, int& n2, int& h, int& qt) {
+    qt = item % dm.nq;
+    const int nh = item / dm.nq;
+    const int n = nh / a.H;
+    h = nh - n * a.H;
+    n1 = n / a.n2_count;
+    n2 = n - n1 * a.n2_count;
+  };
+
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    auto store_out = [&](int item, int st) {                       // lane 0
+      int n1, n2, h, qt;
+      coords(item, n1, n2, h, qt);
+      const uint32_t sb = s0 + st * L::STAGE;
+      tma::store_box(&maps.m[6], sb, 0, h, qt * 128, n2, n1);
+      if (G::TAIL) tma::store_box(&maps.m[7], sb + SUB_A, 64, h, qt * 128, n2, n1);
+      tma::store_commit();
+    };
+    const uint32_t kv_bytes = (uint32_t)a.Sk * DH * 2u;
+    Prof pf;
+    pf.init(blockIdx.x == 0 && lane == 0, 16);
+    for (int j = 0; j < n_my; ++j) {
+      pf.tick(0);
+      const int item = blockIdx.x + j * gridDim.x, st = j % NST;
+      int n1, n2, h, qt;
+      coords(item, n1, n2, h, qt);
+      const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER, sv = sk + L::OPERK;
+      if (j >= NST) {                                              // the stage still holds item j - NST's staged output
+        tc::mbar_wait(&o_staged[st], ((j - NST) / NST) & 1);
+        pf.tick(1);
+        if (lane == 0) {
+          store_out(item - NST * (int)gridDim.x, st);
+          tma::store_wait_read<0>();
+        }
+      }
+      pf.tick(2);
+      // (issuing the K | V boxes earlier -- their half of the stage is dead once P V has run -- measured slower: the
+      // output store then queues behind them)
+      if (lane == 0) {
+        tma::mbar_expect_tx(&landed[st], G::OPER + 2 * kv_bytes);
+        tma::load_box(sq, &maps.m[0], &landed[st], 0, h, qt * 128, n2, n1);
+        if (G::TAIL) tma::load_box(sq + SUB_A, &maps.m[1], &landed[st], 64, h, qt * 128, n2, n1);
+        tma::load_box(sk, &maps.m[2], &landed[st], 0, h, 0, n2, n1);
+        if (G::TAIL) tma::load_box(sk + L::KA, &maps.m[3], &landed[st], 64, h, 0, n2, n1);
+        tma::load_box(sv, &maps.m[4], &landed[st], 0, h, 0, n2, n1);
+        if (G::TAIL) tma::load_box(sv + L::KA, &maps.m[5], &landed[st], 64, h, 0, n2, n1);
+      }
+      float* bias = reinterpret_cast<float*>(smem + L::AUX + st * 1024);
+      const float* mrow = a.key_mask ? a.key_mask + (int64_t)(n1 * a.n2_count + n2) * a.Sk : nullptr;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int k = u * 32 + lane;
+        bias[k] = key_bias2(mrow && k < a.Sk ? __ldg(mrow + k) : 1.f, k, a.Sk);
+      }
+      tc::mbar_arrive(&aux_ready[st]);
+      pf.tick(3);
+    }
+    for (int j = max(0, n_my - NST); j < n_my; ++j) {
+      const int st = j % NST;
+      tc::mbar_wait(&o_staged[st], (j / NST) & 1);
+      if (lane == 0) store_out(blockIdx.x + j * gridDim.x, st);
+    }
+    if (lane == 0) tma::store_wait_all();
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      const uint32_t idesc_s = tc::make_idesc(128, n_s, 0, 0);
+      auto issue_s = [&](int j) {
+        const int st = j % NST;
+        tc::mbar_wait(&landed[st], (j / NST) & 1);
+        tc::fence_after_sync();
+        const uint32_t sq = s0 + st * L::STAGE, sk = sq + G::OPER;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) {
+          const uint64_t bd = ks < 4 ? tc::make_desc_sw(sk + ks * 32, 16, 1024, 2) : tc::make_desc_sw(sk + L::KA + (ks - 4) * 32, 16, 512, 4);
+          tc::mma_ss(tmem + st * 256, desc_oper_k(sq, ks), bd, idesc_s, ks > 0);
+        }
+        tc::mma_commit(&s_full[st]);
+      };
+      Prof pf;
+      pf.init(blockIdx.x == 0, 32);
+      if (n_my > 0) issue_s(0);
+      for (int j = 0; j < n_my; ++j) {
+        const int st = j % NST;
+        pf.tick(0);
+        // S of the next item as soon as its boxes have landed -- but never in front of a P V that is ready to go
+        // (item j's P is usually complete before item j + 1's loads are: they could only start once item j - 1 left)
+        bool s_next = j + 1 >= n_my;
+        const long long t0 = clock64();
+        while (!tc::mbar_test(&p_ready[st], (j / NST) & 1)) {
+          if (!s_next && tc::mbar_test(&landed[(j + 1) % NST], ((j + 1) / NST) & 1)) {
+            issue_s(j + 1);
+            s_next = true;
+          }
+          if (clock64() - t0 > 4000000000LL) __trap();            // bounded, like tc::mbar_wait
+        }
+        tc::mbar_wait(&p_ready[st], (j / NST) & 1);
+        pf.tick(s_next ? 1 : 2);
+        tc::fence_after_sync();
+        const uint32_t sp = L::P_ALIAS ? s0 + st * L::STAGE : s0 + L::PSEP;
+        const uint32_t sv = s0 + st * L::STAGE + G::OPER + L::OPERK;
+        for (int ks = 0; ks * 16 < n_s; ++ks) {
+          const uint64_t ad = desc_pw_k(sp, ks);
+          tc::mma_ss(tmem + st * 256, ad, tc::make_desc_sw(sv + ks * 2048, SUB_A, 1024, 2), tc::make_idesc(128, 64, 0, 1), ks > 0);
+          if (G::TAIL)
+            tc::mma_ss(tmem + st * 256 + 64, ad, tc::make_desc_sw(sv + L::KA + ks * 1024, SUB_B, 512, 4), tc::make_idesc(128, 32, 0, 1), ks > 0);
+        }
+        tc::mma_commit(&o_full[st]);
+        pf.tick(3);
+        if (!s_next) issue_s(j + 1);
+        pf.tick(4);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;                     // TMEM lane quarter / which 32-column blocks
+    const int t = rg * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    float* red_max = reinterpret_cast<float*>(smem + L::RED);      // [2][2][128]
+    float* red_sum = red_max + 512;                                // [2][2][128]
+    const int nblk = (a.Sk + 31) >> 5;                             // <= 7; block 6 holds 16 columns
+    // scores of block blk (32 key columns; block 6: 16 + 16 masked), scaled, biased
+    auto load_blk = [&](uint32_t ts, const float* bias, int blk, float* sv) {
+      if (blk < 6) tc::tmem_ld32(ts + blk * 32, sv);
+      else {
+        tc::tmem_ld16(ts + 192, sv);
+#pragma unroll
+        for (int e = 16; e < 32; ++e) sv[e] = 0.f;
+      }
+      tc::tmem_ld_wait();
+      const float4* b4 = reinterpret_cast<const float4*>(bias + blk * 32);
+#pragma unroll
+      for (int e = 0; e < 32; e += 4) {
+        const float4 b = b4[e >> 2];
+        sv[e] = fmaf(sv[e], scale2, b.x);
+        sv[e + 1] = fmaf(sv[e + 1], scale2, b.y);
+        sv[e + 2] = fmaf(sv[e + 2], scale2, b.z);
+        sv[e + 3] = fmaf(sv[e + 3], scale2, b.w);
+      }
+    };
+    // row max of item j (both halves)
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
+    auto row_max = [&](int j) -> float {
+      const int st = j % NST;
+      const uint32_t par = (j / NST) & 1;
+      pf.tick(0);
+      tc::mbar_wait(&aux_ready[st], par);
+      tc::mbar_wait(&s_full[st], par);
+      pf.tick(1);
+      tc::fence_after_sync();
+      const float* bias = reinterpret_cast<const float*>(smem + L::AUX + st * 1024);
+      const uint32_t ts = lane_base + st * 256;
+      float m = -CUDART_INF_F;
+      // (letting the warps whose 32 query rows all lie past Sq -- one of four in the last tile at Sq = 196 -- skip the
+      // arithmetic measured slower, not faster)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {                                           // warp-uniform
+          float sv[32];
+          load_blk(ts, bias, blk, sv);
+#pragma unroll
+          for (int e = 0; e < 32; ++e) m = fmaxf(m, sv[e]);
+        }
+      }
+      float* rmx = red_max + (j & 1) * 256;
+      rmx[half * 128 + t] = m;
+      pf.tick(2);
+      tc::bar_sync(BAR_PAIR + rg, 64);
+      pf.tick(3);
+      return fmaxf(m, rmx[(half ^ 1) * 128 + t]);
+    };
+    for (int j = 0; j < n_my; ++j) {
+      const int item = blockIdx.x + j * gridDim.x, st = j % NST;
+      const float m_cur = row_max(j);
+      const uint32_t par = (j / NST) & 1;
+      const float* bias = reinterpret_cast<const float*>(smem + L::AUX + st * 1024);
+      const uint32_t ts = lane_base + st * 256;
+      const float m_use = m_cur == -CUDART_INF_F ? 0.f : m_cur;
+      float l0 = 0.f, l1 = 0.f;
+      uint8_t* pbuf = L::P_ALIAS ? smem + st * L::STAGE : smem + L::PSEP;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {
+          float sv[32];
+          load_blk(ts, bias, blk, sv);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (blk == 6 && q >= 2) break;                          // columns [208, 224) do not exist
+            uint4 pk;
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = q * 8 + 2 * u;
+              const float p0 = tc::ex2(sv[e] - m_use), p1 = tc::ex2(sv[e + 1] - m_use);
+              l0 += p0;
+              l1 += p1;
+              ph[u] = __floats2bfloat162_rn(p0, p1);
+            }
+            *reinterpret_cast<uint4*>(pbuf + pw_off(t, blk * 4 + q)) = pk;
+          }
+        }
+      }
+      float l = l0 + l1;
+      float* rsm = red_sum + (j & 1) * 256;
+      rsm[half * 128 + t] = l;
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&p_ready[st]);                                // the MMA warp starts O = P V
+      pf.tick(4);
+      tc::bar_sync(BAR_PAIR + rg, 64);
+      l += rsm[(half ^ 1) * 128 + t];
+      pf.tick(5);
+      tc::mbar_wait(&o_full[st], par);
+      pf.tick(6);
+      tc::fence_after_sync();
+      stage_acc_sw<G::CPR / 2>(ts + half * HALF, smem + st * L::STAGE, t, half * (G::CPR / 2), l > 0.f ? 1.0f / l : 0.f);
+      if (half == 0 && a.lse) {
+        const int qt = item % dm.nq, nh = item / dm.nq;
+        if (qt * 128 + t < a.Sq) a.lse[(int64_t)nh * a.Sq + qt * 128 + t] = m_use * LN2 + logf(l);
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&o_staged[st]);
+      pf.tick(7);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
 // ============================================================================== backward, several tiles: dQ pass
 // The multi-step pipeline again, for the gradient of the queries when Sq or Sk > 128.  An item is a (sequence, head,
 // 128-query tile), a step one 128-key tile: Q | dO | K | V boxes into one of two stages, S = Q K^T and dP = dO V^T into
@@ -2496,6 +2814,47 @@ static int launch_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
     MEANT_LAUNCH_CHECK();
   }
   return 0;
+}
+
+// one-wide-key-tile forward: 128 < Sk <= 208, not causal, rotation already applied (or none)
+int attn_tc2_wk_supported(const AttnArgs& a) {
+  if (a.Sk <= 128 || a.Sk > t2::FwdWkL<96>::KW || a.causal || a.kx.p != nullptr) return 0;
+  if (a.qcos && !a.q_rot.p) return 0;
+  const bool pre = a.q_rot.p != nullptr;
+  const HeadView* vs[4] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o};
+  for (int i = 0; i < 4; ++i)
+    if (vs[i]->ss <= 0 || vs[i]->ss >= (1 << 23)) return 0;
+  return 1;
+}
+
+template <int DH>
+static int launch_fwd_wk(const AttnArgs& a, cudaStream_t st) {
+  t2::FwdMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  const bool pre = a.q_rot.p != nullptr;
+  const HeadView* vs[4] = {pre ? &a.q_rot : &a.q, pre ? &a.k_rot : &a.k, &a.v, &a.o};
+  const int seq[4] = {a.Sq, a.Sk, a.Sk, a.Sq};
+  const int rows[4] = {128, a.Sk, a.Sk, 128};                 // K and V: one box holds every key
+  for (int i = 0; i < 4; ++i) {
+    int rc = tma::make_head_map(&maps.m[2 * i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 64, rows[i], 1);
+    if (rc == 0 && DH > 64) rc = tma::make_head_map(&maps.m[2 * i + 1], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 32, rows[i], 1);
+    if (rc) return rc;
+  }
+  const t2::MsDims dm = {(a.Sq + 127) / 128, 1};
+  const int64_t items = (int64_t)a.N * a.H * dm.nq;
+  if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
+  auto kern = t2::attn2_fwd_wk_kernel<DH>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t2::FwdWkL<DH>::TOTAL);
+  if (e != cudaSuccess) return (int)e;
+  const int grid = (int)(items < num_sms() ? items : num_sms());
+  kern<<<grid, t2::F_NT, t2::FwdWkL<DH>::TOTAL, st>>>(a, (int)items, maps, dm);
+  MEANT_LAUNCH_CHECK();
+  return 0;
+}
+
+int attn_tc2_fwd_wk(const AttnArgs& a, cudaStream_t st) {
+  if (a.Dh == 96) return launch_fwd_wk<96>(a, st);
+  return launch_fwd_wk<64>(a, st);
 }
 
 int attn_tc2_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {

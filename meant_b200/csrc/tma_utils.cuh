@@ -33,7 +33,8 @@ inline EncodeTiledFn encode_fn() {
 // SWIZZLE_64B) -- the operand sub-tile layout of attn_tc2.cu.  Rows >= S are out of bounds: zero-filled on load,
 // dropped on store.  Returns 0, or MEANT_EUNSUPPORTED when the view cannot be described.
 // box_rows x box_n2: rows of one sequence x consecutive n2 sequences per box (default: one 128-row tile of one sequence;
-// the packed-group kernels of attn_tc2.cu take gl rows of G groups, which land as tile rows g * gl + s).
+// the packed-group kernels of attn_tc2.cu take gl rows of G groups, which land as tile rows g * gl + s; the wide-key
+// forward takes every key of a sequence, up to 208 rows, in one box).
 inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count, int H, int S, int Dh, int box_cols,
                          int box_rows = 128, int box_n2 = 1) {
   EncodeTiledFn enc = encode_fn();
@@ -47,7 +48,7 @@ inline int make_head_map(CUtensorMap* m, const HeadView& v, int N, int n2_count,
     if (st[i] <= 0 || st[i] % 16 || st[i] >= ((int64_t)1 << 40)) return MEANT_EUNSUPPORTED;
     strides[i] = (cuuint64_t)st[i];
   }
-  if (box_rows <= 0 || box_rows > 256 || box_n2 <= 0 || box_n2 > 256 || box_rows * box_n2 > 128) return MEANT_EUNSUPPORTED;
+  if (box_rows <= 0 || box_rows > 256 || box_n2 <= 0 || box_n2 > 256 || box_rows * box_n2 > 256) return MEANT_EUNSUPPORTED;
   const cuuint32_t box[5] = {(cuuint32_t)box_cols, 1u, (cuuint32_t)box_rows, (cuuint32_t)box_n2, 1u};
   const cuuint32_t estr[5] = {1u, 1u, 1u, 1u, 1u};
   const CUtensorMapSwizzle sw = box_cols * 2 == 128 ? CU_TENSOR_MAP_SWIZZLE_128B

@@ -55,6 +55,13 @@ CASES = [  # n, s, heads, dh, causal, xpos, masked, backward
     (3, 260, 8, 64, True, True, True, True),
     (2, 640, 8, 96, False, True, True, True),
     (21, 384, 8, 96, True, True, False, True),    # 504 items in the dQ pass: several per CTA, steps 1..3
+    # wide-key forward (attn2_fwd_wk_kernel: 128 < Sk <= 208, not causal): padding masks, the 208-key limit, S a
+    # multiple of 16 / of 32, more items than CTAs
+    (3, 160, 8, 96, False, True, True, True),
+    (2, 208, 8, 64, False, False, True, True),
+    (2, 192, 8, 96, False, False, False, True),
+    (2, 209, 8, 96, False, True, True, True),     # one key too many: the multi-step kernel
+    (30, 201, 8, 64, False, True, True, True),    # 480 items
 ]
 
 
@@ -108,7 +115,8 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
                 assert abs(ratio - 1.0) <= 3e-2, (name, part, ratio)
 
 
-@pytest.mark.parametrize("n,sq,sk", [(2, 200, 333), (3, 100, 300), (3, 300, 100), (20, 129, 257)])
+@pytest.mark.parametrize("n,sq,sk", [(2, 200, 333), (3, 100, 300), (3, 300, 100), (20, 129, 257),
+                                     (3, 300, 150), (20, 129, 208), (2, 64, 193)])   # the last three: wide-key forward
 def test_multitile_backward_is_reproducible_and_cross_shaped(n, sq, sk):
     """Multi-tile backward: bit-identical gradients run to run (no atomics), and Sq != Sk (q | kv inputs): one query tile
     against several key tiles, several against one, and more work items than CTAs with one-row tail tiles."""

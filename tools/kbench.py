@@ -47,7 +47,8 @@ def prof(tag, items, launches):
     if fn(buf, 1) != 1:
         return
     per = launches * ((items + 147) // 148)
-    print(f"  prof {tag}: compute", [round(buf[i] / per) for i in range(16)], "loader", [round(buf[16 + i] / per) for i in range(16)])
+    print(f"  prof {tag}: compute", [round(buf[i] / per) for i in range(16)], "loader", [round(buf[16 + i] / per) for i in range(16)],
+          "mma", [round(buf[32 + i] / per) for i in range(8)])
     fn2 = getattr(nv.lib(), "meant_debug_prof_mt", None)   # multi-tile forward: cycles per phase, CTA (0,0,0), per launch
     if fn2 is not None:
         b2 = (ctypes.c_ulonglong * 32)()

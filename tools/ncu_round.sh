@@ -25,7 +25,7 @@ run attn128 'attn2_' 6 2 python tools/kbench.py attn --iters 3
 # multi-tile: [prerotate, multi-step fwd] x 7, then [bwd dQ pass, bwd dK|dV pass] x 6
 # multi-step kernels: [prerotate, fwd_ms] x 7, then [delta, dQ pass, dK|dV pass] x 6: skip 12 -> the 7th forward pair + one backward
 run attn512 'attn2_fwd_ms|attn2_bwd_|attn_delta|attn_tc_|attn_prerotate' 12 5 python tools/kbench.py attn --n 128 --s 512 --iters 3
-run attn196 'attn2_fwd_ms|attn2_bwd_|attn_delta|attn_tc_|attn_prerotate' 12 5 python tools/kbench.py attn --n 192 --s 196 --causal 0 --iters 3
+run attn196 'attn2_fwd_wk|attn2_fwd_ms|attn2_bwd_|attn_delta|attn_tc_|attn_prerotate' 12 5 python tools/kbench.py attn --n 192 --s 196 --causal 0 --iters 3
 run norm 'norm_' 5 3 python tools/kbench.py norm --iters 3
 run gemm 'gemm_tn|nvjet' 5 2 python tools/kbench.py gemm --iters 3
 # general forms: after the 6 + 6 forward launches come 6 dgrad launches, then 6 wgrad launches (gemm_gen_kernel)
