@@ -991,9 +991,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
 // (no running max, no correction of the output accumulator, no fold through registers), P [128 x 224] over the
 // consumed Q | K, O = P V over the consumed S, normalise, stage, TMA-store.  Against the multi-step kernel on the
 // same problem this halves the steps, never touches the padded second key tile's 60 empty columns and drops the
-// online-softmax arithmetic.  K | V boxes of the item after next are issued as soon as P V has run (their stage half
-// is dead then); the MMA thread polls "next item's boxes landed" and "this item's P ready" together, so neither
-// S(j + 1) nor P V(j) ever waits behind the other's barrier.
+// online-softmax arithmetic.
 // Rotation is not done here: q_rot / k_rot (meant_attn_prerotate, or in place) or no tables at all.
 template <int DH>
 struct FwdWkL {
@@ -1152,19 +1150,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_wk_kernel(AttnArgs a, int n
       for (int j = 0; j < n_my; ++j) {
         const int st = j % NST;
         pf.tick(0);
-        // S of the next item as soon as its boxes have landed -- but never in front of a P V that is ready to go
-        // (item j's P is usually complete before item j + 1's loads are: they could only start once item j - 1 left)
-        bool s_next = j + 1 >= n_my;
-        const long long t0 = clock64();
-        while (!tc::mbar_test(&p_ready[st], (j / NST) & 1)) {
-          if (!s_next && tc::mbar_test(&landed[(j + 1) % NST], ((j + 1) / NST) & 1)) {
-            issue_s(j + 1);
-            s_next = true;
-          }
-          if (clock64() - t0 > 4000000000LL) __trap();            // bounded, like tc::mbar_wait
-        }
         tc::mbar_wait(&p_ready[st], (j / NST) & 1);
-        pf.tick(s_next ? 1 : 2);
+        pf.tick(1);
         tc::fence_after_sync();
         const uint32_t sp = L::P_ALIAS ? s0 + st * L::STAGE : s0 + L::PSEP;
         const uint32_t sv = s0 + st * L::STAGE + G::OPER + L::OPERK;
@@ -1176,7 +1163,10 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_wk_kernel(AttnArgs a, int n
         }
         tc::mma_commit(&o_full[st]);
         pf.tick(3);
-        if (!s_next) issue_s(j + 1);
+        // S of the next item behind P V: it is complete by the time the compute warps have staged this item's output.
+        // (Issued in front of P V -- blocking, or polled together with p_ready -- it measured 111 / 92 us against 89:
+        // P is usually ready before the next boxes are, and a polling MMA thread takes issue slots from two softmax warps)
+        if (j + 1 < n_my) issue_s(j + 1);
         pf.tick(4);
       }
     }
