@@ -1057,7 +1057,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_wk_kernel(AttnArgs a, int n
   const uint32_t tmem = tmem_slot;
   const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
   const uint32_t s0 = tc::smem_u32(smem);
-  const int n_s = (a.Sk + 15) & ~15;                               // S columns / P V K extent
+  const int n_s = min((a.Sk + 31) & ~31, L::KW);                   // S columns / P V K extent: whole 32-column blocks (the softmax reads them)
   // item -> (sequence, head, query tile): the query tiles of one (sequence, head) are neighbours (K, V come from L2)
   auto coords = [&](int item, int& n1, int& n2, int& h, int& qt) {
     qt = item % dm.nq;
@@ -1501,7 +1501,8 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
     int cur_pos = -1;
     const bool vec_tab = ((reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) | reinterpret_cast<uintptr_t>(a.kcos) |
                            reinterpret_cast<uintptr_t>(a.ksin)) & 15) == 0 && (a.rot_dim & 3) == 0;
-    const bool unrot_mine = rc && half * (HALF / 8) < rc;         // this thread's chunks include rotated ones
+    // the two threads of a row take the 8-column chunks of dQ alternately (c = 2 i + half): both share the rotated ones
+    constexpr int NCH = G::CPR / 2, RCT = (RC + 1) / 2;           // chunks per thread / of them at most rotated
     struct Walk {
       int j, kt, steps, n, h, qt;
     };
@@ -1526,12 +1527,6 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
         const int64_t si = ((int64_t)w.n * a.H + w.h) * a.Sq + row;
         lse2_n = __ldg(a.lse + si);
         dlt_n = __ldg(a.delta + si);
-        if (unrot_mine) {                                           // the un-rotation table of this row: towards L1 now, used at the item's end
-          const int pos = a.pos_is_head ? w.h : row;
-          const char* c = reinterpret_cast<const char*>(a.qcos + (int64_t)pos * a.rot_dim);
-          const char* sn = reinterpret_cast<const char*>(a.qsin + (int64_t)pos * a.rot_dim);
-          for (int o = 0; o < a.rot_dim * 4; o += 128) { prefetch_l1(c + o); prefetch_l1(sn + o); }
-        }
       }
       if (ROT_IN && rc_in) {
         const int pos = a.pos_is_head ? w.h : (half ? min(w.kt * 128 + t, a.Sk - 1) : min(w.qt * 128 + t, a.Sq - 1));
@@ -1561,7 +1556,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
       advance(wp);
     }
     float lse2 = 0.f, dlt = 0.f;
-    float dq_acc[HALF];
+    float dq_acc[NCH][8];
     for (int s = 0; wc.j < n_my; ++s) {
       const int b2 = s & 1, kb = s % 3;
       const uint32_t par = (s >> 1) & 1;
@@ -1569,7 +1564,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
       const int k0 = wc.kt * 128, q0 = wc.qt * 128;
       if (first) {
 #pragma unroll
-        for (int i = 0; i < HALF; ++i) dq_acc[i] = 0.f;
+        for (int i = 0; i < NCH; ++i)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dq_acc[i][e] = 0.f;
         lse2 = lse2_n * LOG2E;                                      // fetched when the walker entered this item
         dlt = dlt_n;
       }
@@ -1624,64 +1621,65 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
       tc::fence_before_sync();
       tc::mbar_arrive(&ds_ready[b2]);                               // the MMA warp starts dQ_j = dS K
       pf.tick(2);
+      // the un-rotation tables of this thread's chunks: fetched under the item's last dQ_j MMAs (fetched after them, by
+      // the thread that held every rotated column, they cost as much as a step)
+      float cv[RCT][8], sn[RCT][8];
+      if (last) {
+        const int pos = a.pos_is_head ? wc.h : min(q0 + t, a.Sq - 1);
+        const float* cb = a.qcos + (int64_t)pos * a.rot_dim;
+        const float* sb = a.qsin + (int64_t)pos * a.rot_dim;
+#pragma unroll
+        for (int i = 0; i < RCT; ++i) {
+          const int c = 2 * i + half;
+          if (c < rc) {
+            const float4 c0 = __ldg(reinterpret_cast<const float4*>(cb + c * 8)), c1 = __ldg(reinterpret_cast<const float4*>(cb + c * 8 + 4));
+            const float4 z0 = __ldg(reinterpret_cast<const float4*>(sb + c * 8)), z1 = __ldg(reinterpret_cast<const float4*>(sb + c * 8 + 4));
+            cv[i][0] = c0.x; cv[i][1] = c0.y; cv[i][2] = c0.z; cv[i][3] = c0.w; cv[i][4] = c1.x; cv[i][5] = c1.y; cv[i][6] = c1.z; cv[i][7] = c1.w;
+            sn[i][0] = z0.x; sn[i][1] = z0.y; sn[i][2] = z0.z; sn[i][3] = z0.w; sn[i][4] = z1.x; sn[i][5] = z1.y; sn[i][6] = z1.z; sn[i][7] = z1.w;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { cv[i][e] = 1.f; sn[i][e] = 0.f; }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < RCT; ++i)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { cv[i][e] = 1.f; sn[i][e] = 0.f; }
+      }
       tc::mbar_wait(&dq_full[b2], par);
       tc::fence_after_sync();
       pf.tick(3);
       {
-        float g[HALF];
-        tc::tmem_ld32(ts + half * HALF, g);
-        if constexpr (HALF > 32) tc::tmem_ld16(ts + half * HALF + 32, g + 32);
+        float g[NCH][8];
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) tc::tmem_ld8(ts + (2 * i + half) * 8, g[i]);
         tc::tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < HALF; ++i) dq_acc[i] += g[i];
+        for (int i = 0; i < NCH; ++i)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dq_acc[i][e] += g[i][e];
       }
       pf.tick(4);
       if (last) {
-        // un-rotate with the query-side table of this row (transpose rotation), bf16, staged over the consumed K
-        if (unrot_mine) {
-          // three chunks at a time: 12 independent 16-byte loads in flight (the whole table at once did not fit in
-          // registers beside the accumulator and the compiler serialised the loads)
-          const int pos = a.pos_is_head ? wc.h : min(q0 + t, a.Sq - 1);
-          const float* cb = a.qcos + (int64_t)pos * a.rot_dim + half * HALF;
-          const float* sb = a.qsin + (int64_t)pos * a.rot_dim + half * HALF;
+        // un-rotate (transpose rotation; identity tables past rc), bf16, staged over the consumed K
 #pragma unroll
-          for (int r = 0; r < HALF / 8; r += 3) {
-            float cv[24], sv2[24];
+        for (int i = 0; i < RCT; ++i) {
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              const int ch = half * (HALF / 8) + r + q;                    // global chunk index (runtime through `half`)
-              const bool on = r + q < HALF / 8 && ch < rc;
-#pragma unroll
-              for (int e = 0; e < 8; e += 4) {                           // 16-byte loads (alignment checked on the host)
-                const float4 c4 = on ? __ldg(reinterpret_cast<const float4*>(cb + (r + q) * 8 + e)) : make_float4(1.f, 1.f, 1.f, 1.f);
-                const float4 s4 = on ? __ldg(reinterpret_cast<const float4*>(sb + (r + q) * 8 + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                cv[q * 8 + e] = c4.x; cv[q * 8 + e + 1] = c4.y; cv[q * 8 + e + 2] = c4.z; cv[q * 8 + e + 3] = c4.w;
-                sv2[q * 8 + e] = s4.x; sv2[q * 8 + e + 1] = s4.y; sv2[q * 8 + e + 2] = s4.z; sv2[q * 8 + e + 3] = s4.w;
-              }
-            }
-#pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              if (r + q < HALF / 8) {
-                float* g = dq_acc + (r + q) * 8;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  const float c0 = cv[q * 8 + 2 * i], c1 = cv[q * 8 + 2 * i + 1], s0_ = sv2[q * 8 + 2 * i], s1_ = sv2[q * 8 + 2 * i + 1];
-                  const float y0 = g[2 * i] * c0 + g[2 * i + 1] * s1_, y1 = g[2 * i + 1] * c1 - g[2 * i] * s0_;
-                  g[2 * i] = y0;
-                  g[2 * i + 1] = y1;
-                }
-              }
-            }
+          for (int e = 0; e < 8; e += 2) {
+            const float y0 = dq_acc[i][e] * cv[i][e] + dq_acc[i][e + 1] * sn[i][e + 1], y1 = dq_acc[i][e + 1] * cv[i][e + 1] - dq_acc[i][e] * sn[i][e];
+            dq_acc[i][e] = y0;
+            dq_acc[i][e + 1] = y1;
           }
         }
         uint8_t* tile = smem + L::K + kb * G::OPER;
 #pragma unroll
-        for (int q = 0; q < HALF / 8; ++q) {
+        for (int i = 0; i < NCH; ++i) {
           uint4 pk;
           __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) ph[i] = __floats2bfloat162_rn(dq_acc[q * 8 + 2 * i], dq_acc[q * 8 + 2 * i + 1]);
-          *reinterpret_cast<uint4*>(tile + oper_off(t, half * (HALF / 8) + q)) = pk;
+          for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(dq_acc[i][2 * e], dq_acc[i][2 * e + 1]);
+          *reinterpret_cast<uint4*>(tile + oper_off(t, 2 * i + half)) = pk;
         }
         tc::fence_async_smem();
       }
@@ -1689,6 +1687,329 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_ms_kernel(AttnArgs a, in
       tc::mbar_arrive(&freed[kb]);
       pf.tick(5);
       advance(wc);
+    }
+  }
+  tc::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+
+// ============================================================================== backward, one wide key tile: dQ pass
+// The dQ pass of the multi-step backward for the shapes of the wide-key forward (128 < Sk <= 208, not causal,
+// rotation already applied): an item is one (sequence, head, 128-query tile) and sees every key at once -- Q | dO
+// boxes into one of two pairs, the WHOLE K into one of two 208-row tiles, the whole V into a single one (it is dead as
+// soon as dP has run), S = Q K^T and dP = dO V^T with N = Sk rounded up into 2 x 208 TMEM columns, P = exp2(S * scale -
+// LSE) and dS = P (dP - delta) * scale in one pass out of TMEM, dS [128 x 224] over the consumed Q | dO (its last 32
+// columns in a sub-tile of their own), dQ = dS K into the remaining 96 TMEM columns, un-rotate, stage over the Q tile,
+// TMA-store.  One step per item: no fold of dQ_j through registers, half the S | dP launches, no padded key tile.
+template <int DH>
+struct BwdDqWkL {
+  using G = Geo<DH>;
+  using W = FwdWkL<DH>;
+  static constexpr bool DS_ALIAS = 3 * SUB_A <= 2 * G::OPER;   // dS columns [0, 192) over the consumed Q | dO (Dh = 96)
+  static constexpr uint32_t QDO = 0;                           // [2][Q | dO]
+  static constexpr uint32_t K = 4 * G::OPER;                   // [2] wide K tiles
+  static constexpr uint32_t V = K + 2 * W::OPERK;              // one wide V tile
+  static constexpr uint32_t DST = V + W::OPERK;                // dS columns [192, 224): SWIZZLE_64B sub-tile
+  static constexpr uint32_t DSM = DST + SUB_B;                 // dS columns [0, 192) when they have their own buffer
+  static constexpr uint32_t AUX = DSM + (DS_ALIAS ? 0u : 3 * SUB_A);   // [2][256] fp32 additive key bias
+  static constexpr uint32_t BARS = AUX + 2048;
+  static constexpr uint32_t TOTAL = BARS + 256 + 1024;
+  static_assert(TOTAL <= 227 * 1024, "shared memory");
+};
+
+template <int DH, int RC>
+__global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dq_wk_kernel(AttnArgs a, int n_items, const __grid_constant__ BwdMsMaps maps,
+                                                                  const MsDims dm) {
+  extern __shared__ __align__(128) uint8_t smem_raw[];
+  __shared__ uint32_t tmem_slot;
+  uint8_t* smem = smem_raw + ((1024u - (tc::smem_u32(smem_raw) & 1023u)) & 1023u);
+  using L = BwdDqWkL<DH>;
+  using W = FwdWkL<DH>;
+  using G = Geo<DH>;
+  constexpr int HALF = DH / 2;
+  constexpr uint32_t T_S = 0, T_DP = W::KW, T_DQ = 2 * W::KW;   // TMEM columns
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::BARS);
+  uint64_t *landed_qdo = bars, *landed_k = bars + 2, *landed_v = bars + 4, *sdp_full = bars + 5, *dq_full = bars + 6,
+           *ds_ready = bars + 7, *staged = bars + 8, *aux_ready = bars + 10;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // K / V rows in [Sk, n_s) are read by the MMAs and never written by a box: everything starts as zero
+  for (uint32_t i = tid * 16; i < L::AUX; i += F_NT * 16) *reinterpret_cast<uint4*>(smem + i) = make_uint4(0u, 0u, 0u, 0u);
+  tc::fence_async_smem();
+  if (tid == 0) {
+    for (int i = 0; i < 2; ++i) {
+      tc::mbar_init(&landed_qdo[i], 1);
+      tc::mbar_init(&landed_k[i], 1);
+      tc::mbar_init(&staged[i], NC);
+      tc::mbar_init(&aux_ready[i], 32);
+    }
+    tc::mbar_init(landed_v, 1);
+    tc::mbar_init(sdp_full, 1);
+    tc::mbar_init(dq_full, 1);
+    tc::mbar_init(ds_ready, NC);
+    tc::fence_mbar_init();
+  }
+  if (warp == 0) tc::tmem_alloc(&tmem_slot, 512);
+  tc::fence_before_sync();
+  __syncthreads();
+  tc::fence_after_sync();
+  const uint32_t tmem = tmem_slot;
+  const int n_my = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int rc = a.qcos ? a.rot_dim / 8 : 0;                    // chunks to un-rotate in dQ
+  const uint32_t s0 = tc::smem_u32(smem);
+  const int n_s = min((a.Sk + 31) & ~31, W::KW);                // S | dP columns, dQ K extent (whole 32-column blocks)
+  auto coords = [&](int item, int& n, int& h, int& qt) {
+    qt = item % dm.nq;
+    const int nh = item / dm.nq;
+    n = nh / a.H;
+    h = nh - n * a.H;
+  };
+  // dS: key columns [0, 192) in three SWIZZLE_128B sub-tiles at `dsm`, [192, 224) in a SWIZZLE_64B sub-tile at DST
+  auto ds_main = [&](int b2) -> uint32_t { return L::DS_ALIAS ? L::QDO + b2 * 2 * G::OPER : L::DSM; };
+
+  if (warp == F_PROD) {
+    // ------------------------------------------------------------------ producer warp
+    if (lane == 0) {
+#pragma unroll
+      for (int i = 0; i < 10; ++i)
+        if (G::TAIL || !(i & 1)) tma::prefetch_map(&maps.m[i]);
+    }
+    const uint32_t kv_bytes = (uint32_t)a.Sk * DH * 2u;
+    Prof pf;
+    pf.init(blockIdx.x == 0 && lane == 0, 16);
+    for (int j = 0; j < n_my; ++j) {
+      pf.tick(0);
+      const int item = blockIdx.x + j * gridDim.x, b2 = j & 1;
+      int n, h, qt;
+      coords(item, n, h, qt);
+      const int n1 = n / a.n2_count, n2 = n - n1 * a.n2_count;
+      const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER, sk = s0 + L::K + b2 * W::OPERK, sv = s0 + L::V;
+      if (j >= 2) {                   // pair / K tile b2 belong to item j - 2: its dQ, staged over the Q tile, goes out first
+        tc::mbar_wait(&staged[b2], ((j - 2) >> 1) & 1);
+        pf.tick(1);
+        if (lane == 0) {
+          int pn, ph, pq;
+          coords(item - 2 * (int)gridDim.x, pn, ph, pq);
+          const int p1 = pn / a.n2_count, p2 = pn - p1 * a.n2_count;
+          tma::store_box(&maps.m[8], sq, 0, ph, pq * 128, p2, p1);
+          if (G::TAIL) tma::store_box(&maps.m[9], sq + SUB_A, 64, ph, pq * 128, p2, p1);
+          tma::store_commit();
+          tma::store_wait_read<0>();
+        }
+      }
+      if (lane == 0) {
+        tma::mbar_expect_tx(&landed_qdo[b2], 2 * G::OPER);
+        tma::load_box(sq, &maps.m[0], &landed_qdo[b2], 0, h, qt * 128, n2, n1);
+        if (G::TAIL) tma::load_box(sq + SUB_A, &maps.m[1], &landed_qdo[b2], 64, h, qt * 128, n2, n1);
+        tma::load_box(sq + G::OPER, &maps.m[6], &landed_qdo[b2], 0, h, qt * 128, n2, n1);
+        if (G::TAIL) tma::load_box(sq + G::OPER + SUB_A, &maps.m[7], &landed_qdo[b2], 64, h, qt * 128, n2, n1);
+        tma::mbar_expect_tx(&landed_k[b2], kv_bytes);
+        tma::load_box(sk, &maps.m[2], &landed_k[b2], 0, h, 0, n2, n1);
+        if (G::TAIL) tma::load_box(sk + W::KA, &maps.m[3], &landed_k[b2], 64, h, 0, n2, n1);
+      }
+      pf.tick(2);
+      // V: free once dP of item j - 1 has run (every phase of sdp_full is waited for, in order)
+      if (j >= 1) tc::mbar_wait(sdp_full, (j - 1) & 1);
+      pf.tick(3);
+      if (lane == 0) {
+        tma::mbar_expect_tx(landed_v, kv_bytes);
+        tma::load_box(sv, &maps.m[4], landed_v, 0, h, 0, n2, n1);
+        if (G::TAIL) tma::load_box(sv + W::KA, &maps.m[5], landed_v, 64, h, 0, n2, n1);
+      }
+      float* bias = reinterpret_cast<float*>(smem + L::AUX + b2 * 1024);   // item j - 2 has read it (staged above)
+      const float* mrow = a.key_mask ? a.key_mask + (int64_t)n * a.Sk : nullptr;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int k = u * 32 + lane;
+        bias[k] = key_bias2(mrow && k < a.Sk ? __ldg(mrow + k) : 1.f, k, a.Sk);
+      }
+      tc::mbar_arrive(&aux_ready[b2]);
+      pf.tick(4);
+    }
+    for (int j = max(0, n_my - 2); j < n_my; ++j) {
+      const int b2 = j & 1;
+      tc::mbar_wait(&staged[b2], (j >> 1) & 1);
+      if (lane == 0) {
+        int pn, ph, pq;
+        coords(blockIdx.x + j * gridDim.x, pn, ph, pq);
+        const int p1 = pn / a.n2_count, p2 = pn - p1 * a.n2_count;
+        const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER;
+        tma::store_box(&maps.m[8], sq, 0, ph, pq * 128, p2, p1);
+        if (G::TAIL) tma::store_box(&maps.m[9], sq + SUB_A, 64, ph, pq * 128, p2, p1);
+        tma::store_commit();
+      }
+    }
+    if (lane == 0) tma::store_wait_all();
+  } else if (warp == F_MMA) {
+    // ------------------------------------------------------------------ MMA-issue warp (one thread)
+    if (lane == 0) {
+      const uint32_t idesc_s = tc::make_idesc(128, n_s, 0, 0);
+      auto wide_k = [&](uint32_t base, int ks) -> uint64_t {      // K-major view of a wide K / V tile, K step ks of the head dimension
+        return ks < 4 ? tc::make_desc_sw(base + ks * 32, 16, 1024, 2) : tc::make_desc_sw(base + W::KA + (ks - 4) * 32, 16, 512, 4);
+      };
+      auto issue_sdp = [&](int j) {
+        const int b2 = j & 1;
+        tc::mbar_wait(&landed_qdo[b2], (j >> 1) & 1);
+        tc::mbar_wait(&landed_k[b2], (j >> 1) & 1);
+        tc::mbar_wait(landed_v, j & 1);
+        tc::fence_after_sync();
+        const uint32_t sq = s0 + L::QDO + b2 * 2 * G::OPER, sdo = sq + G::OPER, sk = s0 + L::K + b2 * W::OPERK, sv = s0 + L::V;
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_S, desc_oper_k(sq, ks), wide_k(sk, ks), idesc_s, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < DH / 16; ++ks) tc::mma_ss(tmem + T_DP, desc_oper_k(sdo, ks), wide_k(sv, ks), idesc_s, ks > 0);
+        tc::mma_commit(sdp_full);
+      };
+      Prof pf;
+      pf.init(blockIdx.x == 0, 32);
+      if (n_my > 0) issue_sdp(0);
+      for (int j = 0; j < n_my; ++j) {
+        const int b2 = j & 1;
+        pf.tick(0);
+        tc::mbar_wait(ds_ready, j & 1);                           // dS written; S | dP (and the previous dQ) read
+        pf.tick(1);
+        tc::fence_after_sync();
+        const uint32_t dsm = s0 + ds_main(b2), dst = s0 + L::DST, sk = s0 + L::K + b2 * W::OPERK;
+        for (int ks = 0; ks * 16 < n_s; ++ks) {
+          const uint64_t ad = ks < 12 ? tc::make_desc_sw(dsm + (ks >> 2) * SUB_A + (ks & 3) * 32, 16, 1024, 2)
+                                      : tc::make_desc_sw(dst + (ks - 12) * 32, 16, 512, 4);
+          tc::mma_ss(tmem + T_DQ, ad, tc::make_desc_sw(sk + ks * 2048, SUB_A, 1024, 2), tc::make_idesc(128, 64, 0, 1), ks > 0);
+          if (G::TAIL)
+            tc::mma_ss(tmem + T_DQ + 64, ad, tc::make_desc_sw(sk + W::KA + ks * 1024, SUB_B, 512, 4), tc::make_idesc(128, 32, 0, 1), ks > 0);
+        }
+        tc::mma_commit(dq_full);
+        pf.tick(2);
+        if (j + 1 < n_my) issue_sdp(j + 1);                       // behind dQ: runs while the compute warps drain and stage it
+        pf.tick(3);
+      }
+    }
+  } else {
+    // ------------------------------------------------------------------ compute group
+    const int rg = warp & 3, half = warp >> 2;
+    const int t = rg * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(rg * 32) << 16);
+    const float scale2 = a.scale * LOG2E;
+    const int nblk = (a.Sk + 31) >> 5;                            // <= 7; block 6 holds 16 columns
+    constexpr int NCH = G::CPR / 2, RCT = (RC + 1) / 2;           // chunks of the dQ row per thread / of them at most rotated
+    auto row_stats = [&](int j, float& lse2, float& dlt) {
+      int n, h, qt;
+      coords(blockIdx.x + j * gridDim.x, n, h, qt);
+      const int row = min(qt * 128 + t, a.Sq - 1);
+      const int64_t si = ((int64_t)n * a.H + h) * a.Sq + row;
+      lse2 = __ldg(a.lse + si) * LOG2E;
+      dlt = __ldg(a.delta + si);
+    };
+    float lse2 = 0.f, dlt = 0.f;
+    if (n_my > 0) row_stats(0, lse2, dlt);
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
+    for (int j = 0; j < n_my; ++j) {
+      const int item = blockIdx.x + j * gridDim.x, b2 = j & 1;
+      int n, h, qt;
+      coords(item, n, h, qt);
+      pf.tick(0);
+      tc::mbar_wait(&aux_ready[b2], (j >> 1) & 1);
+      tc::mbar_wait(sdp_full, j & 1);
+      pf.tick(1);
+      tc::fence_after_sync();
+      const float* bias = reinterpret_cast<const float*>(smem + L::AUX + b2 * 1024);
+      uint8_t* dsm = smem + ds_main(b2);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int blk = 2 * i + half;
+        if (blk < nblk) {                                           // warp-uniform
+          float sv[32], dp[32];
+          if (blk < 6) {
+            tc::tmem_ld32(lane_base + T_S + blk * 32, sv);
+            tc::tmem_ld32(lane_base + T_DP + blk * 32, dp);
+          } else {
+            tc::tmem_ld16(lane_base + T_S + 192, sv);
+            tc::tmem_ld16(lane_base + T_DP + 192, dp);
+#pragma unroll
+            for (int e = 16; e < 32; ++e) sv[e] = dp[e] = 0.f;
+          }
+          tc::tmem_ld_wait();
+          const float4* b4 = reinterpret_cast<const float4*>(bias + blk * 32);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (blk == 6 && q >= 2) break;                          // columns [208, 224) do not exist
+            const float4 ba = b4[2 * q], bc = b4[2 * q + 1];
+            const float bb[8] = {ba.x, ba.y, ba.z, ba.w, bc.x, bc.y, bc.z, bc.w};
+            uint4 pk;
+            __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int e = q * 8 + 2 * u;
+              const float p0 = tc::ex2(fmaf(sv[e], scale2, bb[2 * u] - lse2)), p1 = tc::ex2(fmaf(sv[e + 1], scale2, bb[2 * u + 1] - lse2));
+              ph[u] = __floats2bfloat162_rn(p0 * (dp[e] - dlt) * a.scale, p1 * (dp[e + 1] - dlt) * a.scale);
+            }
+            const int c = blk * 4 + q;
+            uint8_t* dstp = c < 24 ? dsm + (c >> 3) * SUB_A + tc::sw128_off(t, c & 7) : smem + L::DST + tc::sw64_off(t, c - 24);
+            *reinterpret_cast<uint4*>(dstp) = pk;
+          }
+        }
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(ds_ready);                                    // the MMA warp starts dQ = dS K
+      pf.tick(2);
+      float lse2_n = 0.f, dlt_n = 0.f;
+      if (j + 1 < n_my) row_stats(j + 1, lse2_n, dlt_n);           // in flight under dQ
+      // The two threads of a row take the 8-column chunks of dQ alternately (c = 2 i + half), so both share the rotated
+      // ones; the un-rotation tables of this thread's chunks are fetched NOW, under the dQ MMAs (fetched after them,
+      // by the thread that held all the rotated columns, they were a third of the item's time)
+      float cv[RCT][8], sn[RCT][8];
+      {
+        const int pos = a.pos_is_head ? h : min(qt * 128 + t, a.Sq - 1);
+        const float* cb = a.qcos + (int64_t)pos * a.rot_dim;
+        const float* sb = a.qsin + (int64_t)pos * a.rot_dim;
+#pragma unroll
+        for (int i = 0; i < RCT; ++i) {
+          const int c = 2 * i + half;
+          if (c < rc) {
+            const float4 c0 = __ldg(reinterpret_cast<const float4*>(cb + c * 8)), c1 = __ldg(reinterpret_cast<const float4*>(cb + c * 8 + 4));
+            const float4 z0 = __ldg(reinterpret_cast<const float4*>(sb + c * 8)), z1 = __ldg(reinterpret_cast<const float4*>(sb + c * 8 + 4));
+            cv[i][0] = c0.x; cv[i][1] = c0.y; cv[i][2] = c0.z; cv[i][3] = c0.w; cv[i][4] = c1.x; cv[i][5] = c1.y; cv[i][6] = c1.z; cv[i][7] = c1.w;
+            sn[i][0] = z0.x; sn[i][1] = z0.y; sn[i][2] = z0.z; sn[i][3] = z0.w; sn[i][4] = z1.x; sn[i][5] = z1.y; sn[i][6] = z1.z; sn[i][7] = z1.w;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { cv[i][e] = 1.f; sn[i][e] = 0.f; }
+          }
+        }
+      }
+      pf.tick(3);
+      tc::mbar_wait(dq_full, j & 1);
+      pf.tick(4);
+      tc::fence_after_sync();
+      float g[NCH][8];
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) tc::tmem_ld8(lane_base + T_DQ + (2 * i + half) * 8, g[i]);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < RCT; ++i) {                               // transpose rotation (identity tables past rc)
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) {
+          const float y0 = g[i][e] * cv[i][e] + g[i][e + 1] * sn[i][e + 1], y1 = g[i][e + 1] * cv[i][e + 1] - g[i][e] * sn[i][e];
+          g[i][e] = y0;
+          g[i][e + 1] = y1;
+        }
+      }
+      pf.tick(5);
+      uint8_t* tile = smem + L::QDO + b2 * 2 * G::OPER;             // over the consumed Q (and the dS that followed it)
+#pragma unroll
+      for (int i = 0; i < NCH; ++i) {
+        uint4 pk;
+        __nv_bfloat162* ph = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) ph[e] = __floats2bfloat162_rn(g[i][2 * e], g[i][2 * e + 1]);
+        *reinterpret_cast<uint4*>(tile + oper_off(t, 2 * i + half)) = pk;
+      }
+      tc::fence_async_smem();
+      tc::fence_before_sync();
+      tc::mbar_arrive(&staged[b2]);
+      pf.tick(6);
+      lse2 = lse2_n;
+      dlt = dlt_n;
     }
   }
   tc::fence_before_sync();
@@ -1901,7 +2222,6 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
     int cur_pos = -1;
     const bool vec_tab = ((reinterpret_cast<uintptr_t>(a.qcos) | reinterpret_cast<uintptr_t>(a.qsin) | reinterpret_cast<uintptr_t>(a.kcos) |
                            reinterpret_cast<uintptr_t>(a.ksin)) & 15) == 0 && (a.rot_dim & 3) == 0;
-    const bool unrot_mine = rc && half * (HALF / 8) < rc;
     struct Walk {
       int j, u, steps, n, h, kt, q0;
     };
@@ -2012,62 +2332,61 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
         advance(wp);
       }
       if (last) {
-        tc::mbar_wait(&mma_done[s & 1], (s >> 1) & 1);              // the item's accumulators are complete
-        tc::fence_after_sync();
-        float gv[HALF], gk[HALF];
-        tc::tmem_ld32(lane_base + T_DV + half * HALF, gv);
-        if constexpr (HALF > 32) tc::tmem_ld16(lane_base + T_DV + half * HALF + 32, gv + 32);
-        tc::tmem_ld32(lane_base + T_DK + half * HALF, gk);
-        if constexpr (HALF > 32) tc::tmem_ld16(lane_base + T_DK + half * HALF + 32, gk + 32);
-        tc::tmem_ld_wait();
-        tc::fence_before_sync();
-        tc::mbar_arrive(drained);                                   // the next item's dV | dK may overwrite them
-        if (unrot_mine) {
+        // The two threads of a row take the 8-column chunks of dV and dK alternately (c = 2 i + half), so both share dK's
+        // rotated chunks; their un-rotation tables are fetched first, under the item's last dV | dK MMAs (fetched after
+        // them, by the thread that held every rotated column, they cost as much as a step)
+        constexpr int NCH = G::CPR / 2, RCT = (RC + 1) / 2;
+        float cv[RCT][8], sn[RCT][8];
+        {
           const int pos = a.pos_is_head ? wc.h : min(k0 + t, a.Sk - 1);
-          const float* cb = a.kcos + (int64_t)pos * a.rot_dim + half * HALF;
-          const float* sb = a.ksin + (int64_t)pos * a.rot_dim + half * HALF;
+          const float* cb = a.kcos + (int64_t)pos * a.rot_dim;
+          const float* sb = a.ksin + (int64_t)pos * a.rot_dim;
 #pragma unroll
-          for (int r = 0; r < HALF / 8; r += 3) {
-            float cv[24], sv2[24];
+          for (int i = 0; i < RCT; ++i) {
+            const int c = 2 * i + half;
+            if (c < rc) {
+              const float4 c0 = __ldg(reinterpret_cast<const float4*>(cb + c * 8)), c1 = __ldg(reinterpret_cast<const float4*>(cb + c * 8 + 4));
+              const float4 z0 = __ldg(reinterpret_cast<const float4*>(sb + c * 8)), z1 = __ldg(reinterpret_cast<const float4*>(sb + c * 8 + 4));
+              cv[i][0] = c0.x; cv[i][1] = c0.y; cv[i][2] = c0.z; cv[i][3] = c0.w; cv[i][4] = c1.x; cv[i][5] = c1.y; cv[i][6] = c1.z; cv[i][7] = c1.w;
+              sn[i][0] = z0.x; sn[i][1] = z0.y; sn[i][2] = z0.z; sn[i][3] = z0.w; sn[i][4] = z1.x; sn[i][5] = z1.y; sn[i][6] = z1.z; sn[i][7] = z1.w;
+            } else {
 #pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              const int ch = half * (HALF / 8) + r + q;
-              const bool on = r + q < HALF / 8 && ch < rc;
-#pragma unroll
-              for (int e = 0; e < 8; e += 4) {
-                const float4 c4 = on ? __ldg(reinterpret_cast<const float4*>(cb + (r + q) * 8 + e)) : make_float4(1.f, 1.f, 1.f, 1.f);
-                const float4 s4 = on ? __ldg(reinterpret_cast<const float4*>(sb + (r + q) * 8 + e)) : make_float4(0.f, 0.f, 0.f, 0.f);
-                cv[q * 8 + e] = c4.x; cv[q * 8 + e + 1] = c4.y; cv[q * 8 + e + 2] = c4.z; cv[q * 8 + e + 3] = c4.w;
-                sv2[q * 8 + e] = s4.x; sv2[q * 8 + e + 1] = s4.y; sv2[q * 8 + e + 2] = s4.z; sv2[q * 8 + e + 3] = s4.w;
-              }
-            }
-#pragma unroll
-            for (int q = 0; q < 3; ++q) {
-              if (r + q < HALF / 8) {
-                float* g = gk + (r + q) * 8;
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                  const float c0 = cv[q * 8 + 2 * i], c1 = cv[q * 8 + 2 * i + 1], s0_ = sv2[q * 8 + 2 * i], s1_ = sv2[q * 8 + 2 * i + 1];
-                  const float y0 = g[2 * i] * c0 + g[2 * i + 1] * s1_, y1 = g[2 * i + 1] * c1 - g[2 * i] * s0_;
-                  g[2 * i] = y0;
-                  g[2 * i + 1] = y1;
-                }
-              }
+              for (int e = 0; e < 8; ++e) { cv[i][e] = 1.f; sn[i][e] = 0.f; }
             }
           }
         }
+        tc::mbar_wait(&mma_done[s & 1], (s >> 1) & 1);              // the item's accumulators are complete
+        tc::fence_after_sync();
+        float gv[NCH][8], gk[NCH][8];
 #pragma unroll
-        for (int q = 0; q < HALF / 8; ++q) {
+        for (int i = 0; i < NCH; ++i) {
+          tc::tmem_ld8(lane_base + T_DV + (2 * i + half) * 8, gv[i]);
+          tc::tmem_ld8(lane_base + T_DK + (2 * i + half) * 8, gk[i]);
+        }
+        tc::tmem_ld_wait();
+        tc::fence_before_sync();
+        tc::mbar_arrive(drained);                                   // the next item's dV | dK may overwrite them
+#pragma unroll
+        for (int i = 0; i < RCT; ++i) {                             // transpose rotation (identity tables past rc)
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            const float y0 = gk[i][e] * cv[i][e] + gk[i][e + 1] * sn[i][e + 1], y1 = gk[i][e + 1] * cv[i][e + 1] - gk[i][e] * sn[i][e];
+            gk[i][e] = y0;
+            gk[i][e + 1] = y1;
+          }
+        }
+#pragma unroll
+        for (int i = 0; i < NCH; ++i) {
           uint4 pv, pk;
           __nv_bfloat162* hv = reinterpret_cast<__nv_bfloat162*>(&pv);
           __nv_bfloat162* hk = reinterpret_cast<__nv_bfloat162*>(&pk);
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            hv[i] = __floats2bfloat162_rn(gv[q * 8 + 2 * i], gv[q * 8 + 2 * i + 1]);
-            hk[i] = __floats2bfloat162_rn(gk[q * 8 + 2 * i], gk[q * 8 + 2 * i + 1]);
+          for (int e = 0; e < 4; ++e) {
+            hv[e] = __floats2bfloat162_rn(gv[i][2 * e], gv[i][2 * e + 1]);
+            hk[e] = __floats2bfloat162_rn(gk[i][2 * e], gk[i][2 * e + 1]);
           }
-          *reinterpret_cast<uint4*>(smem + L::P + oper_off(t, half * (HALF / 8) + q)) = pv;
-          *reinterpret_cast<uint4*>(smem + L::DS + oper_off(t, half * (HALF / 8) + q)) = pk;
+          *reinterpret_cast<uint4*>(smem + L::P + oper_off(t, 2 * i + half)) = pv;
+          *reinterpret_cast<uint4*>(smem + L::DS + oper_off(t, 2 * i + half)) = pk;
         }
         tc::fence_async_smem();
         tc::mbar_arrive(staged);
@@ -2763,6 +3082,8 @@ static int launch_fwd_ms(const AttnArgs& a, cudaStream_t st) {
   return 0;
 }
 
+int attn_tc2_wk_supported(const AttnArgs& a);
+
 // multi-step backward: delta, then the dQ pass (bit 1 of `parts`) and / or the dK | dV pass (bit 0)
 template <int DH, int RC>
 static int launch_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
@@ -2782,6 +3103,29 @@ static int launch_bwd_ms(const AttnArgs& a, int parts, cudaStream_t st) {
     if (DH == 96) t2::attn_delta_kernel<3><<<(unsigned)blocks, 256, 0, st>>>(a);
     else t2::attn_delta_kernel<2><<<(unsigned)blocks, 256, 0, st>>>(a);
     MEANT_LAUNCH_CHECK();
+  }
+  static const bool no_wk = getenv("MEANT_ATTN_NO_WK") != nullptr;    // read once: A/B against the multi-step dQ pass
+  if ((parts & 2) && !no_wk && attn_tc2_wk_supported(a)) {
+    // every key in one tile: the wide-key dQ pass (K and V boxes hold all Sk rows)
+    t2::BwdMsMaps wm;
+    memset(&wm, 0, sizeof(wm));
+    const int rows[5] = {128, a.Sk, a.Sk, 128, 128};
+    int rcw = 0;
+    for (int i = 0; i < 5 && rcw == 0; ++i) {
+      rcw = tma::make_head_map(&wm.m[2 * i], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 64, rows[i], 1);
+      if (rcw == 0 && DH > 64) rcw = tma::make_head_map(&wm.m[2 * i + 1], *vs[i], a.N, a.n2_count, a.H, seq[i], DH, 32, rows[i], 1);
+    }
+    if (rcw == 0) {
+      const int64_t items = (int64_t)a.N * a.H * dm.nq;
+      if (items > 0x7fffffff) return MEANT_EUNSUPPORTED;
+      auto kern = t2::attn2_bwd_dq_wk_kernel<DH, RC>;
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)t2::BwdDqWkL<DH>::TOTAL);
+      if (e != cudaSuccess) return (int)e;
+      const int grid = (int)(items < num_sms() ? items : num_sms());
+      kern<<<grid, t2::F_NT, t2::BwdDqWkL<DH>::TOTAL, st>>>(a, (int)items, wm, dm);
+      MEANT_LAUNCH_CHECK();
+      parts &= ~2;
+    }
   }
   if (parts & 2) {
     const int64_t items = (int64_t)a.N * a.H * dm.nq;
