@@ -2195,7 +2195,11 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
           const int b2 = s & 1;
           tc::mbar_wait(pds_ready, s & 1);                        // P, dS written; S | dP read
           tc::fence_after_sync();
-          if (s + 1 < total) issue_sdp(s + 1);                    // first: the next step's arithmetic runs under dV | dK
+          // the next step's S | dP first (its arithmetic then runs under dV | dK) -- except at the item's last step,
+          // where the compute warps wait for the accumulators: there dV | dK go first and the next item's S | dP run
+          // while the gradients are drained, un-rotated and staged
+          const bool last_u = u == steps - 1;
+          if (s + 1 < total && !last_u) issue_sdp(s + 1);
           if (u == 0 && j > 0) {
             tc::mbar_wait(drained, (j - 1) & 1);                  // the previous item's accumulators have been read
             tc::fence_after_sync();
@@ -2207,6 +2211,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
             mma_oper_mn<DH>(tmem + T_DK, desc_p_mn(sds, ks), sq, ks, 1, u > 0 || ks > 0);    // dK += dS^T Q
           }
           tc::mma_commit(&mma_done[b2]);
+          if (s + 1 < total && last_u) issue_sdp(s + 1);
         }
       }
     }
@@ -2267,9 +2272,12 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
       prepare(wp, 0);
       advance(wp);
     }
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
     for (int s = 0; wc.j < n_my; ++s) {
       const bool first = wc.u == 0, last = wc.u == wc.steps - 1;
       const int qt = wc.q0 + wc.u, k0 = wc.kt * 128;
+      pf.tick(0);
       const float lse2 = lse_n * LOG2E, dlt = dlt_n;                // fetched by the walker one step ahead
       const bool dtile = a.causal && qt == wc.kt;
       int nblk = (min(a.Sk - k0, 128) + 31) >> 5;
@@ -2277,6 +2285,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
       if (first) tc::mbar_wait(&aux_ready[wc.j & 1], (wc.j >> 1) & 1);
       tc::mbar_wait(sdp_full, s & 1);
       tc::fence_after_sync();
+      pf.tick(1);
       const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + (wc.j & 1) * 512);
       // arithmetic first, into registers: the P / dS tiles may still be read by dV | dK of the previous step
       uint4 pp[2][4], dd[2][4];
@@ -2313,8 +2322,10 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
         }
       }
       tc::fence_before_sync();                                      // the TMEM reads above are complete (tcgen05.wait::ld)
+      pf.tick(2);
       if (s >= 1) tc::mbar_wait(&mma_done[(s - 1) & 1], ((s - 1) >> 1) & 1);   // P / dS tiles are free
       if (first && wc.j > 0) tc::mbar_wait(stg_free, (wc.j - 1) & 1);          // ... and the staged gradients have left them
+      pf.tick(3);
 #pragma unroll
       for (int i = 0; i < 2; ++i) {
         const int blk = 2 * i + half;
@@ -2327,10 +2338,12 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
       tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(pds_ready);
+      pf.tick(4);
       if (wp.j < n_my) {
         prepare(wp, s + 1);
         advance(wp);
       }
+      pf.tick(5);
       if (last) {
         // The two threads of a row take the 8-column chunks of dV and dK alternately (c = 2 i + half), so both share dK's
         // rotated chunks; their un-rotation tables are fetched first, under the item's last dV | dK MMAs (fetched after
@@ -2357,6 +2370,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
         }
         tc::mbar_wait(&mma_done[s & 1], (s >> 1) & 1);              // the item's accumulators are complete
         tc::fence_after_sync();
+        pf.tick(6);
         float gv[NCH][8], gk[NCH][8];
 #pragma unroll
         for (int i = 0; i < NCH; ++i) {
@@ -2390,6 +2404,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_bwd_dkv_ms_kernel(AttnArgs a, i
         }
         tc::fence_async_smem();
         tc::mbar_arrive(staged);
+        pf.tick(7);
       }
       advance(wc);
     }
