@@ -116,7 +116,8 @@ def test_tcgen05_matches_exact_and_torch(n, s, heads, dh, causal, xpos, masked, 
 
 
 @pytest.mark.parametrize("n,sq,sk", [(2, 200, 333), (3, 100, 300), (3, 300, 100), (20, 129, 257),
-                                     (3, 300, 150), (20, 129, 208), (2, 64, 193)])   # the last three: wide-key forward
+                                     (3, 300, 150), (20, 129, 208), (2, 64, 193),     # these three: wide-key forward
+                                     (3, 150, 300), (2, 208, 100)])   # wide-query dK | dV pass beside multi-step / single-key-tile kernels
 def test_multitile_backward_is_reproducible_and_cross_shaped(n, sq, sk):
     """Multi-tile backward: bit-identical gradients run to run (no atomics), and Sq != Sk (q | kv inputs): one query tile
     against several key tiles, several against one, and more work items than CTAs with one-row tail tiles."""
