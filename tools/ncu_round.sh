@@ -22,8 +22,8 @@ run() { # name, kernel regex, skip, count, command...
 }
 # kbench attn --iters 3 launches: 7 forwards (1 + 3 warm-up + 3 timed), then 6 backwards
 run attn128 'attn2_' 6 2 python tools/kbench.py attn --iters 3
-# multi-tile: [prerotate, multi-step fwd] x 7, then [bwd dQ pass, bwd dK|dV pass] x 6
-# multi-step kernels: [prerotate, fwd_ms] x 7, then [delta, dQ pass, dK|dV pass] x 6: skip 12 -> the 7th forward pair + one backward
+# multi-tile: [prerotate, forward] x 7, then [delta, dQ pass, dK|dV pass] x 6: skip 12 -> the 7th forward pair + one backward
+# (S = 512: the multi-step kernels; 192 x 196: the wide-key forward and dQ pass, the multi-step dK|dV pass)
 run attn512 'attn2_fwd_ms|attn2_bwd_|attn_delta|attn_tc_|attn_prerotate' 12 5 python tools/kbench.py attn --n 128 --s 512 --iters 3
 run attn196 'attn2_fwd_wk|attn2_fwd_ms|attn2_bwd_|attn_delta|attn_tc_|attn_prerotate' 12 5 python tools/kbench.py attn --n 192 --s 196 --causal 0 --iters 3
 run norm 'norm_' 5 3 python tools/kbench.py norm --iters 3
