@@ -6,6 +6,7 @@
 // One warp per row, 128-bit coalesced loads, the row kept in registers (single HBM read),
 // warp-shuffle reductions, fp32 math.  HBM-bound: algorithmic bytes are listed in DESIGN.md.
 #include "common.cuh"
+#include <algorithm>
 
 namespace meant {
 
@@ -29,8 +30,9 @@ struct NormArgs {
 };
 
 // ------------------------------------------------------------------ forward, row in registers
-template <typename T, int CHUNKS, bool LN>
-__global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
+// RES: a residual is added (its two rows of prefetched vectors cost 24 registers: without them a fifth CTA fits an SM)
+template <typename T, int CHUNKS, bool LN, bool RES>
+__global__ void __launch_bounds__(128, (RES || CHUNKS > 3) ? 4 : 5) norm_fwd_kernel(NormArgs a) {
   uint64_t seed = a.seed;
   if (a.drop_thresh && a.seed_dev) seed += __ldg(a.seed_dev);
   constexpr int V = Vec16<T>::N;
@@ -59,7 +61,7 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
     const int64_t b_ = row_ * a.d;
 #pragma unroll
     for (int c = 0; c < CHUNKS; ++c) tt[c].load(x + b_ + (lane + 32 * c) * V);
-    if (res) {
+    if (RES) {
 #pragma unroll
       for (int c = 0; c < CHUNKS; ++c) rr[c].load(res + b_ + (lane + 32 * c) * V);
     }
@@ -79,7 +81,7 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
 #pragma unroll
         for (int i = 0; i < V; ++i) v[c][i] = gelu_f(v[c][i]);
       }
-      if (res) {
+      if (RES) {
         float rv[V];
         r[c].unpack(rv);
 #pragma unroll
@@ -132,7 +134,10 @@ __global__ void __launch_bounds__(128) norm_fwd_kernel(NormArgs a) {
       ov.store(y + base + col);
     }
 #pragma unroll
-    for (int c = 0; c < CHUNKS; ++c) { t[c] = tn[c]; r[c] = rn[c]; }
+    for (int c = 0; c < CHUNKS; ++c) {
+      t[c] = tn[c];
+      if (RES) r[c] = rn[c];
+    }
   }
 }
 
@@ -402,10 +407,21 @@ static int launch_fwd(const NormArgs& a, cudaStream_t st) {
                       ((reinterpret_cast<uintptr_t>(a.x) | reinterpret_cast<uintptr_t>(a.y) |
                         reinterpret_cast<uintptr_t>(a.res) | reinterpret_cast<uintptr_t>(a.sum_out)) % 16 == 0);
   const int chunks = vec_ok ? a.d / (32 * V) : 0;
+  const bool res = a.res != nullptr;
+  const int g5 = (chunks == 3 && !res) ? (int)std::min<int64_t>((a.rows + 3) / 4 > 0 ? (a.rows + 3) / 4 : 1, 148 * 5) : g;   // five CTAs per SM
   switch (chunks) {
-    case 3: norm_fwd_kernel<T, 3, LN><<<g, 128, 0, st>>>(a); break;
-    case 6: norm_fwd_kernel<T, 6, LN><<<g, 128, 0, st>>>(a); break;
-    case 12: norm_fwd_kernel<T, 12, LN><<<g, 128, 0, st>>>(a); break;
+    case 3:
+      if (res) norm_fwd_kernel<T, 3, LN, true><<<g, 128, 0, st>>>(a);
+      else norm_fwd_kernel<T, 3, LN, false><<<g5, 128, 0, st>>>(a);
+      break;
+    case 6:
+      if (res) norm_fwd_kernel<T, 6, LN, true><<<g, 128, 0, st>>>(a);
+      else norm_fwd_kernel<T, 6, LN, false><<<g, 128, 0, st>>>(a);
+      break;
+    case 12:
+      if (res) norm_fwd_kernel<T, 12, LN, true><<<g, 128, 0, st>>>(a);
+      else norm_fwd_kernel<T, 12, LN, false><<<g, 128, 0, st>>>(a);
+      break;
     default: norm_fwd_generic_kernel<T, LN><<<g, 128, 0, st>>>(a); break;
   }
   MEANT_LAUNCH_CHECK();
