@@ -114,6 +114,8 @@ def attn(args):
 
 def norm(args):
     rows, d = args.rows, args.d
+    if args.colsum:      # the backward also sums dx over rows (the form a TrainStep(graph=True) step runs)
+        ops.current().fused_linear = True
     x = torch.randn(rows, d, device="cuda").bfloat16().requires_grad_(True)
     res = torch.randn(rows, d, device="cuda").bfloat16()
     g = torch.ones(d, device="cuda", requires_grad=True)
@@ -192,6 +194,7 @@ if __name__ == "__main__":
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--causal", type=int, default=1)
     ap.add_argument("--norot", action="store_true")
+    ap.add_argument("--colsum", action="store_true", help="norm: backward with the fused column sum of dx")
     ap.add_argument("--impl", default="auto")
     ap.add_argument("--only", default="", help="norm: run one variant only (plain, gelu, gelu+drop, plain+drop, res)")
     ap.add_argument("--kernels", action="store_true", help="attn: print per-kernel device times (torch.profiler)")
