@@ -848,9 +848,12 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       }
     float m_run = -CUDART_INF_F, l_run = 0.f;
     float o_acc[HALF];
+    Prof pf;
+    pf.init(blockIdx.x == 0 && tid == 96, 0);
     for (int s = 0; wc.j < n_my; ++s) {
       const int st = s % NST;
       const uint32_t par = (s / NST) & 1;
+      pf.tick(0);
       const bool first = wc.kt == 0, last = wc.kt == wc.steps - 1;
       if (first) {
         m_run = -CUDART_INF_F;
@@ -865,6 +868,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       tc::mbar_wait(&aux_ready[st], par);
       tc::mbar_wait(&s_full[st], par);
       tc::fence_after_sync();
+      pf.tick(1);
       const float4* b4 = reinterpret_cast<const float4*>(smem + L::AUX + st * 512);
       const uint32_t ts = lane_base + st * 128;
       float m = -CUDART_INF_F;
@@ -894,7 +898,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       }
       float* rmx = red_max + (s & 1) * 256;
       rmx[half * 128 + t] = m;
+      pf.tick(2);
       tc::bar_sync(BAR_PAIR + rg, 64);
+      pf.tick(3);
       m = fmaxf(m, rmx[(half ^ 1) * 128 + t]);
       const float m_new = fmaxf(m_run, m);
       const float m_use = m_new == -CUDART_INF_F ? 0.f : m_new;
@@ -939,10 +945,12 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       tc::fence_async_smem();
       tc::fence_before_sync();
       tc::mbar_arrive(&p_ready[st]);                                // the MMA warp starts O_j = P V
+      pf.tick(4);
       if (wp.j < n_my) {                                            // rotation of step s + 2 hides the P V latency of step s
         prepare(wp, s + 2);
         advance(wp);
       }
+      pf.tick(5);
       float l = l_run;
       if (last) {
         red_sum[half * 128 + t] = l_run;
@@ -951,6 +959,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       }
       tc::mbar_wait(&o_full[st], par);
       tc::fence_after_sync();
+      pf.tick(6);
       {
         float pv[HALF];
         tc::tmem_ld32(ts + half * HALF, pv);
@@ -976,6 +985,7 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
       }
       tc::fence_before_sync();
       tc::mbar_arrive(&o_staged[st]);
+      pf.tick(7);
       advance(wc);
     }
   }
