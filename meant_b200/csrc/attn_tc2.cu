@@ -997,8 +997,9 @@ __global__ void __launch_bounds__(F_NT, 1) attn2_fwd_ms_kernel(AttnArgs a, int n
 // ============================================================================== forward, one wide key tile
 // 128 < Sk <= 208 (the 196-patch vision path): every key of a (sequence, head) fits ONE tile of 208 rows, so a work
 // item -- one (sequence, head, 128-query tile) -- is a single-tile pass again: Q | K | V boxes into one of two stages,
-// ONE S = Q K^T of N = Sk rounded up to whole 32-column blocks (at most 208) into the stage's 256 TMEM columns, a plain two-pass softmax out of TMEM
-// (no running max, no correction of the output accumulator, no fold through registers), P [128 x 224] over the
+// ONE S = Q K^T of N = Sk rounded up to whole 32-column blocks (at most 208) into the stage's 256 TMEM columns, a
+// plain two-pass softmax out of TMEM (no running max, no correction of the output accumulator, no fold through
+// registers), P [128 x 224] over the
 // consumed Q | K, O = P V over the consumed S, normalise, stage, TMA-store.  Against the multi-step kernel on the
 // same problem this halves the steps, never touches the padded second key tile's 60 empty columns and drops the
 // online-softmax arithmetic.
